@@ -1,0 +1,141 @@
+/*
+ * vitsb200 — C ABI of the B200-native flow-reverse + Generator engine.
+ *
+ * Drop-in boundary for emotional-vits' latent->waveform stage.  The reference
+ * has no FFI/plugin registry; its boundary is Python method signatures on
+ * nn.Modules.  Each entry point below names the reference
+ * interface it replaces; paths are relative to emotional-vits/.
+ *
+ * Conventions
+ *   - every function returns a vitsb_status (0 = ok); nothing throws across
+ *     the ABI; vitsb_last_error(h) gives the message of the last failure.
+ *   - the caller owns every input, output and workspace buffer.  The handle
+ *     owns only packed weights.  Calls are asynchronous on `stream`.
+ *   - tensors at the seam use the reference's layout: channel-major
+ *     [B, C, T] fp32, contiguous.  `len` is a HOST array of B valid frame
+ *     counts (the reference has them on the host too: infer.py:171,
+ *     models.py:547); rows are zero beyond len[b].
+ *   - there is no CPU fallback: without a CUDA device every compute call
+ *     fails with VITSB_ERR_CUDA.
+ */
+#ifndef VITSB200_H
+#define VITSB200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct vitsb_handle vitsb_handle;
+typedef void* vitsb_stream;            /* cudaStream_t */
+
+typedef enum {
+  VITSB_OK = 0,
+  VITSB_ERR_BAD_ARG = 1,      /* null pointer, bad shape, B/T out of range */
+  VITSB_ERR_UNSUPPORTED = 2,  /* config the kernels do not cover (e.g. resblock "1", modules.py:185-220) */
+  VITSB_ERR_WEIGHTS = 3,      /* missing / mis-shaped state_dict entry */
+  VITSB_ERR_CUDA = 4,         /* CUDA runtime / driver failure, or no device */
+  VITSB_ERR_WORKSPACE = 5     /* workspace too small */
+} vitsb_status;
+
+typedef enum {
+  VITSB_PREC_FP16 = 0,   /* fp16 operands on tcgen05 (kind::f16), fp32 accumulate + fp32 residual streams.
+                            Default 16-bit path: the reference's production dtype (infer.py:66 model.half()) */
+  VITSB_PREC_BF16 = 1,   /* bf16 operands, same kernels */
+  VITSB_PREC_FP32 = 2    /* fp32-verification build: CUDA-core FFMA implicit GEMM, accurate tanh/exp */
+} vitsb_precision;
+
+#define VITSB_MAX_LIST 8
+
+/* Mirrors the hot-path subset of configs/base.json "model" (models.py:416-448). */
+typedef struct {
+  int32_t inter_channels;                 /* 192 */
+  int32_t hidden_channels;                /* 256 */
+  int32_t gin_channels;                   /* 1024 */
+  int32_t n_flows;                        /* 4   (models.py:441) */
+  int32_t flow_kernel_size;               /* 5   (models.py:462) */
+  int32_t flow_n_layers;                  /* 4   (models.py:462) */
+  int32_t flow_dilation_rate[VITSB_MAX_LIST];
+  int32_t n_resblock_kernels;             /* 3 */
+  int32_t resblock_kernel_sizes[VITSB_MAX_LIST];                    /* 3,7,11 */
+  int32_t n_resblock_dilations;           /* 3 */
+  int32_t resblock_dilation_sizes[VITSB_MAX_LIST][VITSB_MAX_LIST];  /* [kernel][iter] 1,3,5 */
+  int32_t n_upsamples;                    /* 4 */
+  int32_t upsample_rates[VITSB_MAX_LIST];        /* 8,6,2,2 */
+  int32_t upsample_kernel_sizes[VITSB_MAX_LIST]; /* 16,12,4,4 */
+  int32_t upsample_initial_channel;       /* 512 */
+  int32_t precision;                      /* vitsb_precision */
+} vitsb_config;
+
+typedef enum { VITSB_F32 = 0, VITSB_F16 = 1, VITSB_BF16 = 2 } vitsb_dtype;
+
+/* One state_dict entry, HOST memory, contiguous, named by its reference key
+ * (e.g. "dec.ups.0.weight_v"). */
+typedef struct {
+  const char* name;
+  const void* data;
+  int32_t dtype;        /* vitsb_dtype */
+  int32_t ndim;
+  int64_t shape[4];
+} vitsb_tensor_desc;
+
+/* Replaces: constructing models.Generator (models.py:282-304) and
+ * models.ResidualCouplingBlock (models.py:192-217) for inference. */
+int vitsb_create(const vitsb_config* cfg, int device, vitsb_handle** out);
+void vitsb_destroy(vitsb_handle* h);
+const char* vitsb_last_error(const vitsb_handle* h);   /* h may be NULL: last create() error */
+
+/* Replaces: load_state_dict (export.py:59) + SynthesizerTrn.remove_weight_norm
+ * (models.py:467-474) for the dec.* / flow.* keys.  Accepts folded `weight` or
+ * `weight_g`/`weight_v` pairs; other keys are ignored.  Folds, repacks
+ * (tap-major, Flip folded into pre/post, gate halves tiled, polyphase ups) and
+ * uploads.  May be called again to swap checkpoints. */
+int vitsb_load_weights(vitsb_handle* h, const vitsb_tensor_desc* tensors, int n);
+
+/* Bytes of device workspace needed for a call with B rows of at most T_max frames. */
+size_t vitsb_workspace_bytes(const vitsb_handle* h, int B, int T_max);
+
+/* Replaces: ResidualCouplingBlock.infer(x, g, reverse=True) (models.py:228-235)
+ * and the masked .forward(x, x_mask, g, reverse=True) (models.py:219-226):
+ * rows beyond len[b] are treated as masked (zero).
+ *   z_p, z : device fp32 [B, inter, T_max];  g : device fp32 [B, gin]. */
+int vitsb_flow_reverse(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len,
+                       int B, int T_max, float* z, void* ws, size_t ws_bytes, vitsb_stream stream);
+
+/* Replaces: Generator.forward(x, g) (models.py:306-318).
+ *   ragged = 1: row b equals the B=1 call on its own len[b] frames, zero beyond
+ *               (SynthesizerTrn.infer_p2 semantics, models.py:573-574)
+ *   ragged = 0: every row is decoded over all T_max frames, unmasked
+ *               (SynthesizerTrn.inference semantics, models.py:534)
+ *   z : device fp32 [B, inter, T_max];  wav : device fp32 [B, 1, T_max*prod(upsample_rates)]. */
+int vitsb_decode(vitsb_handle* h, const float* z, const float* g, const int32_t* len,
+                 int B, int T_max, int ragged, float* wav, void* ws, size_t ws_bytes, vitsb_stream stream);
+
+/* Replaces: the tail of SynthesizerTrn.infer_p2 (models.py:573-574) /
+ * inference (models.py:533-534): flow-reverse then decode without leaving the
+ * time-major layout.  z_out may be NULL. */
+int vitsb_synthesize(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len,
+                     int B, int T_max, int ragged, float* z_out, float* wav,
+                     void* ws, size_t ws_bytes, vitsb_stream stream);
+
+/* Introspection for tests and bench.py. */
+int vitsb_total_upsample(const vitsb_handle* h);
+/* Number of kernels one vitsb_synthesize call launches for (B, T_max). */
+int vitsb_launches_per_call(const vitsb_handle* h, int B, int T_max);
+/* Algorithmic FLOP per latent frame (2*Cin*Cout*k per output position). */
+double vitsb_flop_per_frame(const vitsb_handle* h);
+/* Library build info: "sm_100a;tcgen05;..." */
+const char* vitsb_build_info(void);
+
+/* Bring-up self-test of one implicit-GEMM conv tile configuration on the
+ * tcgen05 path against the CUDA-core fp32 path (tests/test_conv_unit.py).
+ * Returns max-abs difference in *max_err. */
+int vitsb_selftest_conv(int device, int precision, int Cin, int N, int k, int dil, int L, int B,
+                        int gate, uint32_t seed, double* max_err, double* ref_scale);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* VITSB200_H */

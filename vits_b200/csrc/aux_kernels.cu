@@ -1,0 +1,158 @@
+// Memory-bound kernels around the implicit-GEMM convs: layout pack/unpack at
+// the seam, the per-call conditioning GEMV, and conv_post+tanh (N=1, CUDA cores).
+#include "common.h"
+#include "kernels.h"
+
+namespace vitsb {
+
+// ---------------------------------------------------------------------------
+// [B][C][T] -> [B][T][C] (fp32 + operand copy), masked beyond len[b]
+// ---------------------------------------------------------------------------
+template <typename OpT>
+__global__ void pack_time_major_kernel(const float* __restrict__ src, int C, int T, const int* __restrict__ len,
+                                       float* __restrict__ dst_f32, OpT* __restrict__ dst_op) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int valid = len ? len[b] : T;
+  const float* s = src + (long long)b * C * T;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    int c = c0 + i, t = t0 + threadIdx.x;
+    tile[i][threadIdx.x] = (c < C && t < T && t < valid) ? s[(long long)c * T + t] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    int t = t0 + i, c = c0 + threadIdx.x;
+    if (t < T && c < C) {
+      float v = tile[threadIdx.x][i];
+      long long o = ((long long)b * T + t) * C + c;
+      if (dst_f32) dst_f32[o] = v;
+      if (dst_op) dst_op[o] = to_op<OpT>(v);
+    }
+  }
+}
+
+cudaError_t launch_pack_time_major(const float* src, int B, int C, int T, const int* len,
+                                   float* dst_f32, void* dst_op, int op, cudaStream_t stream) {
+  dim3 grid(ceil_div(T, 32), ceil_div(C, 32), B), block(32, 8);
+  if (op == OP_F16) pack_time_major_kernel<__half><<<grid, block, 0, stream>>>(src, C, T, len, dst_f32, (__half*)dst_op);
+  else if (op == OP_BF16) pack_time_major_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(src, C, T, len, dst_f32, (__nv_bfloat16*)dst_op);
+  else pack_time_major_kernel<float><<<grid, block, 0, stream>>>(src, C, T, len, dst_f32, (float*)dst_op);
+  return cudaGetLastError();
+}
+
+__global__ void unpack_channel_major_kernel(const float* __restrict__ src, int C, int T, float* __restrict__ dst) {
+  __shared__ float tile[32][33];
+  const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    int t = t0 + i, c = c0 + threadIdx.x;
+    tile[i][threadIdx.x] = (t < T && c < C) ? src[((long long)b * T + t) * C + c] : 0.f;
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    int c = c0 + i, t = t0 + threadIdx.x;
+    if (c < C && t < T) dst[((long long)b * C + c) * T + t] = tile[threadIdx.x][i];
+  }
+}
+
+cudaError_t launch_unpack_channel_major(const float* src, int B, int C, int T, float* dst, cudaStream_t stream) {
+  dim3 grid(ceil_div(T, 32), ceil_div(C, 32), B), block(32, 8);
+  unpack_channel_major_kernel<<<grid, block, 0, stream>>>(src, C, T, dst);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// conditioning GEMV: one warp per output row n, all batch rows per pass of W
+// (W is read once per call: 12.5k x 1024 fp32 at base config)
+// ---------------------------------------------------------------------------
+constexpr int kCondBChunk = 8;
+__global__ void __launch_bounds__(256)
+cond_gemv_kernel(const float* __restrict__ W, const float* __restrict__ bias, const float* __restrict__ g,
+                 int B, int Ncond, int gin, float* __restrict__ out) {
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  if (warp >= Ncond) return;
+  const float* wr = W + (long long)warp * gin;
+  for (int b0 = 0; b0 < B; b0 += kCondBChunk) {
+    float acc[kCondBChunk];
+#pragma unroll
+    for (int i = 0; i < kCondBChunk; ++i) acc[i] = 0.f;
+    for (int k = lane * 4; k < gin; k += 128) {
+      float4 wv = *reinterpret_cast<const float4*>(wr + k);
+#pragma unroll
+      for (int i = 0; i < kCondBChunk; ++i) {
+        if (b0 + i < B) {
+          float4 gv = *reinterpret_cast<const float4*>(g + (long long)(b0 + i) * gin + k);
+          acc[i] = fmaf(wv.x, gv.x, acc[i]); acc[i] = fmaf(wv.y, gv.y, acc[i]);
+          acc[i] = fmaf(wv.z, gv.z, acc[i]); acc[i] = fmaf(wv.w, gv.w, acc[i]);
+        }
+      }
+    }
+#pragma unroll
+    for (int i = 0; i < kCondBChunk; ++i) {
+      float v = acc[i];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0 && b0 + i < B) out[(long long)(b0 + i) * Ncond + warp] = v + bias[warp];
+    }
+  }
+}
+
+cudaError_t launch_cond_gemv(const float* W, const float* bias, const float* g, int B, int Ncond, int gin,
+                             float* out, cudaStream_t stream) {
+  const int warps_per_block = 8;
+  cond_gemv_kernel<<<ceil_div(Ncond, warps_per_block), warps_per_block * 32, 0, stream>>>(W, bias, g, B, Ncond, gin, out);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
+// conv_post (Conv1d C->1, k taps, no bias) + tanh.  HBM-bound: reads C op
+// values and writes one fp32 sample per output position.  The input already
+// carries the preceding leaky-relu (slope 0.01), fused by the last MRF epilogue.
+// ---------------------------------------------------------------------------
+constexpr int kPostTile = 256;
+template <typename OpT>
+__global__ void __launch_bounds__(kPostTile)
+conv_post_kernel(const OpT* __restrict__ in, int L, int C, int k, const float* __restrict__ w,
+                 const int* __restrict__ len, int len_mul, float* __restrict__ wav) {
+  extern __shared__ float sm[];
+  const int pad = (k - 1) / 2;
+  const int rows = kPostTile + k - 1;
+  const int ldc = C + 1;                       // +1: conflict-free row-per-thread reads
+  float* tile = sm;                            // [rows][C+1]
+  float* ws = sm + rows * ldc;                 // [k][C]
+  const int b = blockIdx.y, t0 = blockIdx.x * kPostTile;
+  const int valid = len ? len[b] * len_mul : L;
+  if (t0 >= valid) {                           // fully masked tile: write zeros
+    int t = t0 + threadIdx.x;
+    if (t < L) wav[(long long)b * L + t] = 0.f;
+    return;
+  }
+  const OpT* src = in + (long long)b * L * C;
+  for (int i = threadIdx.x; i < rows * C; i += kPostTile) {
+    int r = i / C, c = i - r * C, t = t0 + r - pad;
+    tile[r * ldc + c] = (t >= 0 && t < L) ? from_op<OpT>(src[(long long)t * C + c]) : 0.f;
+  }
+  for (int i = threadIdx.x; i < k * C; i += kPostTile) ws[i] = w[i];
+  __syncthreads();
+  const int t = t0 + threadIdx.x;
+  if (t >= L) return;
+  float acc = 0.f;
+  for (int j = 0; j < k; ++j) {
+    const float* row = tile + (threadIdx.x + j) * ldc;
+    const float* wj = ws + j * C;
+#pragma unroll 8
+    for (int c = 0; c < C; ++c) acc = fmaf(row[c], wj[c], acc);
+  }
+  wav[(long long)b * L + t] = t < valid ? tanhf(acc) : 0.f;
+}
+
+cudaError_t launch_conv_post(const void* in, int op, int B, int L, int C, int k, const float* w,
+                             const int* len, int len_mul, float* wav, cudaStream_t stream) {
+  dim3 grid(ceil_div(L, kPostTile), B);
+  size_t smem = (size_t)((kPostTile + k - 1) * (C + 1) + k * C) * sizeof(float);
+  if (op == OP_F16) conv_post_kernel<__half><<<grid, kPostTile, smem, stream>>>((const __half*)in, L, C, k, w, len, len_mul, wav);
+  else if (op == OP_BF16) conv_post_kernel<__nv_bfloat16><<<grid, kPostTile, smem, stream>>>((const __nv_bfloat16*)in, L, C, k, w, len, len_mul, wav);
+  else conv_post_kernel<float><<<grid, kPostTile, smem, stream>>>((const float*)in, L, C, k, w, len, len_mul, wav);
+  return cudaGetLastError();
+}
+
+}  // namespace vitsb

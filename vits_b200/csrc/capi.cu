@@ -1,0 +1,171 @@
+// extern "C" surface declared in include/vitsb200.h.
+#include <cstdio>
+#include <cstring>
+#include <random>
+
+#include "engine.h"
+
+using namespace vitsb;
+
+struct vitsb_handle { Engine eng; };
+
+static thread_local std::string g_create_err;
+
+extern "C" {
+
+int vitsb_create(const vitsb_config* cfg, int device, vitsb_handle** out) {
+  if (!cfg || !out) { g_create_err = "null argument"; return VITSB_ERR_BAD_ARG; }
+  *out = nullptr;
+  vitsb_handle* h = new (std::nothrow) vitsb_handle();
+  if (!h) { g_create_err = "out of memory"; return VITSB_ERR_BAD_ARG; }
+  h->eng.cfg = *cfg;
+  h->eng.device = device;
+  int rc = h->eng.validate_config();
+  if (rc != VITSB_OK) { g_create_err = h->eng.err; delete h; return rc; }
+  int ndev = 0;
+  cudaError_t e = cudaGetDeviceCount(&ndev);
+  if (e != cudaSuccess || device < 0 || device >= ndev) {
+    g_create_err = e != cudaSuccess ? std::string("no CUDA device: ") + cudaGetErrorString(e) : "device index out of range";
+    delete h;
+    return VITSB_ERR_CUDA;      // no CPU fallback, by design
+  }
+  *out = h;
+  return VITSB_OK;
+}
+
+void vitsb_destroy(vitsb_handle* h) { delete h; }
+
+const char* vitsb_last_error(const vitsb_handle* h) { return h ? h->eng.err.c_str() : g_create_err.c_str(); }
+
+int vitsb_load_weights(vitsb_handle* h, const vitsb_tensor_desc* tensors, int n) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  return h->eng.load(tensors, n);
+}
+
+size_t vitsb_workspace_bytes(const vitsb_handle* h, int B, int T_max) {
+  if (!h || B < 1 || T_max < 1) return 0;
+  return h->eng.layout(B, T_max).total;
+}
+
+int vitsb_flow_reverse(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len, int B, int T_max,
+                       float* z, void* ws, size_t ws_bytes, vitsb_stream stream) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  if (!z) return h->eng.fail(VITSB_ERR_BAD_ARG, "null z");
+  return h->eng.run(Engine::RUN_FLOW, z_p, g, len, B, T_max, 1, z, nullptr, ws, ws_bytes, (cudaStream_t)stream, false, nullptr);
+}
+
+int vitsb_decode(vitsb_handle* h, const float* z, const float* g, const int32_t* len, int B, int T_max, int ragged,
+                 float* wav, void* ws, size_t ws_bytes, vitsb_stream stream) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  return h->eng.run(Engine::RUN_DEC, z, g, len, B, T_max, ragged, nullptr, wav, ws, ws_bytes, (cudaStream_t)stream, false, nullptr);
+}
+
+int vitsb_synthesize(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len, int B, int T_max, int ragged,
+                     float* z_out, float* wav, void* ws, size_t ws_bytes, vitsb_stream stream) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  return h->eng.run(Engine::RUN_FLOW | Engine::RUN_DEC, z_p, g, len, B, T_max, ragged, z_out, wav, ws, ws_bytes,
+                    (cudaStream_t)stream, false, nullptr);
+}
+
+int vitsb_total_upsample(const vitsb_handle* h) { return h ? h->eng.up_total : 0; }
+
+int vitsb_launches_per_call(const vitsb_handle* h, int B, int T_max) {
+  if (!h) return 0;
+  int n = 0;
+  Engine* e = const_cast<Engine*>(&h->eng);
+  if (e->run(Engine::RUN_FLOW | Engine::RUN_DEC, nullptr, nullptr, nullptr, B, T_max, 1, nullptr, nullptr, nullptr, 0, 0, true, &n) != VITSB_OK)
+    return 0;
+  return n;
+}
+
+double vitsb_flop_per_frame(const vitsb_handle* h) { return h ? h->eng.flop_per_frame : 0.0; }
+
+const char* vitsb_build_info(void) {
+  return "vitsb200;arch=sm_100a;tensor=tcgen05.mma.kind::f16+TMEM;copy=TMA(cp.async.bulk.tensor);verify=fp32-ffma;cpu_fallback=none";
+}
+
+// ---------------------------------------------------------------------------
+// Bring-up self-test: one conv configuration on the tcgen05 path against the
+// CUDA-core fp32 kernel on identical (operand-rounded) data.
+// ---------------------------------------------------------------------------
+int vitsb_selftest_conv(int device, int precision, int Cin, int N, int k, int dil, int L, int B, int gate, uint32_t seed,
+                        double* max_err, double* ref_scale) {
+  if (!max_err || !ref_scale) return VITSB_ERR_BAD_ARG;
+  if (precision != VITSB_PREC_FP16 && precision != VITSB_PREC_BF16) return VITSB_ERR_BAD_ARG;
+  const int op = precision == VITSB_PREC_BF16 ? OP_BF16 : OP_F16;
+  const int NT = N <= kMaxTileN ? N : kMaxTileN;
+  if (!conv_tc_supported(Cin, Cin, N, NT, k) || (gate && NT % 32)) return VITSB_ERR_UNSUPPORTED;
+  if (cudaSetDevice(device) != cudaSuccess) return VITSB_ERR_CUDA;
+  std::mt19937 rng(seed);
+  std::uniform_real_distribution<float> U(-1.f, 1.f);
+  const size_t n_in = (size_t)B * L * Cin, n_w = (size_t)N * k * Cin, Nout = gate ? N / 2 : N, n_out = (size_t)B * L * Nout;
+  std::vector<float> in(n_in), w(n_w), bias((size_t)B * N), res(n_out);
+  const float ws = 1.0f / std::sqrt((float)(k * Cin));
+  auto rnd = [&](float v) { return op == OP_BF16 ? __bfloat162float(__float2bfloat16_rn(v)) : __half2float(__float2half_rn(v)); };
+  for (auto& x : in) x = rnd(U(rng));
+  for (auto& x : w) x = rnd(U(rng) * ws * 1.7f);
+  for (auto& x : bias) x = U(rng) * 0.3f;
+  for (auto& x : res) x = U(rng);
+  std::vector<uint16_t> in16(n_in), w16(n_w);
+  for (size_t i = 0; i < n_in; ++i) {
+    if (op == OP_BF16) { __nv_bfloat16 h = __float2bfloat16_rn(in[i]); std::memcpy(&in16[i], &h, 2); }
+    else { __half h = __float2half_rn(in[i]); std::memcpy(&in16[i], &h, 2); }
+  }
+  for (size_t i = 0; i < n_w; ++i) {
+    if (op == OP_BF16) { __nv_bfloat16 h = __float2bfloat16_rn(w[i]); std::memcpy(&w16[i], &h, 2); }
+    else { __half h = __float2half_rn(w[i]); std::memcpy(&w16[i], &h, 2); }
+  }
+  std::vector<int> len(B);
+  for (int b = 0; b < B; ++b) len[b] = b == 0 ? L : (int)(L * (0.35 + 0.6 * (b % 3) / 2.0));
+  float *d_in32, *d_w32, *d_bias, *d_res, *d_o1, *d_o2; void *d_in16, *d_w16, *d_op1, *d_op2; int* d_len;
+  cudaMalloc(&d_in32, n_in * 4); cudaMalloc(&d_w32, n_w * 4); cudaMalloc(&d_bias, bias.size() * 4); cudaMalloc(&d_res, n_out * 4);
+  cudaMalloc(&d_o1, n_out * 4); cudaMalloc(&d_o2, n_out * 4); cudaMalloc(&d_in16, n_in * 2); cudaMalloc(&d_w16, n_w * 2);
+  cudaMalloc(&d_op1, n_out * 4); cudaMalloc(&d_op2, n_out * 2); cudaMalloc(&d_len, B * 4);
+  cudaMemcpy(d_in32, in.data(), n_in * 4, cudaMemcpyHostToDevice); cudaMemcpy(d_w32, w.data(), n_w * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(d_bias, bias.data(), bias.size() * 4, cudaMemcpyHostToDevice); cudaMemcpy(d_res, res.data(), n_out * 4, cudaMemcpyHostToDevice);
+  cudaMemcpy(d_in16, in16.data(), n_in * 2, cudaMemcpyHostToDevice); cudaMemcpy(d_w16, w16.data(), n_w * 2, cudaMemcpyHostToDevice);
+  cudaMemcpy(d_len, len.data(), B * 4, cudaMemcpyHostToDevice);
+  cudaMemset(d_o1, 0xff, n_out * 4); cudaMemset(d_o2, 0xff, n_out * 4);
+  ConvArgs a{};
+  a.in_ld = Cin; a.in_bstride = (long long)L * Cin; a.Cin = Cin; a.N = N; a.NT = NT; a.k = k; a.dil = dil; a.pad = (k - 1) / 2 * dil;
+  a.L = L; a.B = B; a.len = d_len; a.len_mul = 1;
+  a.epi.bias = d_bias; a.epi.bias_bstride = N; a.epi.alpha = gate ? 1.f : 0.5f; a.epi.beta = 0.75f; a.epi.out_slope = 0.1f;
+  a.epi.gate = gate;
+  if (!gate) { a.epi.res = d_res; a.epi.res_ld = (int)Nout; a.epi.res_bstride = (long long)L * Nout; }
+  a.epi.out_f32_ld = (int)Nout; a.epi.out_f32_bstride = (long long)L * Nout;
+  a.epi.out_op_ld = (int)Nout; a.epi.out_op_bstride = (long long)L * Nout;
+  ConvArgs r = a;
+  r.in = d_in32; r.w = d_w32; r.epi.out_f32 = d_o1; r.epi.out_op = d_op1;
+  a.in = d_in16; a.w = d_w16; a.epi.out_f32 = d_o2; a.epi.out_op = d_op2;
+  cudaError_t e1 = launch_conv_f32(r, 0);
+  cudaError_t e2 = launch_conv_tc(a, op, 0);
+  cudaError_t e3 = cudaDeviceSynchronize();
+  int rc = VITSB_OK;
+  if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) {
+    std::fprintf(stderr, "selftest: f32=%s tc=%s sync=%s\n", cudaGetErrorString(e1), cudaGetErrorString(e2), cudaGetErrorString(e3));
+    rc = VITSB_ERR_CUDA;
+  } else {
+    std::vector<float> o1(n_out), o2(n_out);
+    cudaMemcpy(o1.data(), d_o1, n_out * 4, cudaMemcpyDeviceToHost); cudaMemcpy(o2.data(), d_o2, n_out * 4, cudaMemcpyDeviceToHost);
+    double me = 0, sc = 0;
+    for (int b = 0; b < B; ++b) {
+      // rows that were computed: t < ceil128(len + halo); others are never written by either path
+      for (int t = 0; t < L; ++t) {
+        bool written64 = (t / 64) * 64 < len[b] + kHaloRows, written128 = (t / 128) * 128 < len[b] + kHaloRows;
+        if (!(written64 && written128)) continue;
+        for (size_t n = 0; n < Nout; ++n) {
+          size_t i = ((size_t)b * L + t) * Nout + n;
+          double d = std::fabs((double)o1[i] - (double)o2[i]);
+          if (!(d <= me)) me = d;          // NaN-propagating max
+          if (std::fabs(o1[i]) > sc) sc = std::fabs(o1[i]);
+        }
+      }
+    }
+    *max_err = me; *ref_scale = sc;
+  }
+  cudaFree(d_in32); cudaFree(d_w32); cudaFree(d_bias); cudaFree(d_res); cudaFree(d_o1); cudaFree(d_o2);
+  cudaFree(d_in16); cudaFree(d_w16); cudaFree(d_op1); cudaFree(d_op2); cudaFree(d_len);
+  return rc;
+}
+
+}  // extern "C"

@@ -1,0 +1,329 @@
+// tcgen05 implicit-GEMM conv1d over time-major 16-bit activations (sm_100a).
+//
+//   out[b, t, n] = sum_{j<k} sum_{c<Cin} W[n][j*Cin + c] * in[b, t + j*dil - pad, c]
+//
+// One CTA computes a 128 (time) x NT (channels) accumulator tile in TMEM.
+//   warp 0      : TMA producer.  For every (tap j, 64-channel block) it loads the
+//                 A box [128 rows x BK ch] at row coordinate t0 + j*dil - pad of the
+//                 3-D activation map (C, L, B) — negative / past-the-end rows are
+//                 zero-filled by TMA, which IS the conv's zero padding — and the
+//                 B box [NT x BK] of the K-major packed weights.
+//   warp 1      : allocates TMEM, issues tcgen05.mma (M=128, N=NT, K=16) from smem
+//                 descriptors, commits stage release / accumulator-ready mbarriers.
+//   warps 2..5  : epilogue.  tcgen05.ld 16 columns at a time (thread = time row),
+//                 fused bias + conditioning + residual + accumulate + gate + leaky-relu,
+//                 fp32 and operand-typed stores, masked beyond len[b].
+// Roofline: tensor (2*128*NT*K flop per tile); HBM traffic is one pass over the
+// input rows and the output rows, weights stay in L2.
+#include "common.h"
+#include "kernels.h"
+#include "ptx.h"
+
+#include <mutex>
+
+namespace vitsb {
+
+struct TcGeom {
+  int BK;            // channels per K block (16 / 32 / 64) = swizzle span / 2
+  int kchunks;       // Cin / BK
+  int iters;         // k * kchunks
+  int stages;
+  uint32_t a_bytes;  // 128 * BK * 2
+  uint32_t b_bytes;  // NT * BK * 2 (rounded to 1024 in smem)
+  uint32_t b_stride; // smem bytes per B stage
+  uint32_t tmem_cols;
+  uint32_t idesc;
+};
+
+constexpr int kTcThreads = 192;
+
+template <typename OpT> struct Pack16;   // 16 floats -> 16 OpT (32 bytes) as two uint4
+template <> struct Pack16<__half> {
+  __device__ static __forceinline__ uint32_t pack2(float a, float b) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+};
+template <> struct Pack16<__nv_bfloat16> {
+  __device__ static __forceinline__ uint32_t pack2(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+};
+
+template <typename OpT>
+__device__ __forceinline__ void store_op16(OpT* dst, const float (&v)[16], float slope) {
+  uint32_t p[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    float x = v[2 * i], y = v[2 * i + 1];
+    x = x >= 0.f ? x : slope * x;
+    y = y >= 0.f ? y : slope * y;
+    p[i] = Pack16<OpT>::pack2(x, y);
+  }
+  uint4* d = reinterpret_cast<uint4*>(dst);
+  d[0] = make_uint4(p[0], p[1], p[2], p[3]);
+  d[1] = make_uint4(p[4], p[5], p[6], p[7]);
+}
+
+__device__ __forceinline__ void load16(const float* src, float (&v)[16]) {
+  const float4* s = reinterpret_cast<const float4*>(src);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    float4 x = s[i];
+    v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
+  }
+}
+__device__ __forceinline__ void store16(float* dst, const float (&v)[16]) {
+  float4* d = reinterpret_cast<float4*>(dst);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) d[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+}
+
+template <typename OpT>
+__global__ void __launch_bounds__(kTcThreads, 1)
+conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const ConvArgs a, const TcGeom g) {
+  const int b = blockIdx.z;
+  const int t0 = blockIdx.x * kTileM;
+  const int ntile = blockIdx.y;
+  const int valid = a.len ? a.len[b] * a.len_mul : a.L;
+  if (t0 >= valid + kHaloRows) return;            // CTA-uniform: rows nobody reads
+
+  extern __shared__ uint8_t smem_raw[];
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sA = smem_base;
+  const uint32_t sB = sA + g.stages * g.a_bytes;
+  const uint32_t bars = sB + g.stages * g.b_stride;          // 8-byte aligned (multiples of 1024 above)
+  auto full_bar = [&](int s) { return bars + 8u * s; };
+  auto empty_bar = [&](int s) { return bars + 8u * (g.stages + s); };
+  const uint32_t accum_bar = bars + 8u * (2 * g.stages);
+  const uint32_t tmem_slot = accum_bar + 8u;
+  // generic pointer to the TMEM-address slot
+  uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - ptx::smem_u32(smem_raw)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmA);
+    ptx::prefetch_tmap(&tmB);
+    for (int s = 0; s < g.stages; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
+    ptx::mbar_init(accum_bar, 1);
+    ptx::mbar_fence_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(tmem_slot, g.tmem_cols);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===== TMA producer =====
+      const uint32_t tx_bytes = g.a_bytes + g.b_bytes;
+      for (int it = 0; it < g.iters; ++it) {
+        const int s = it % g.stages;
+        const uint32_t ph = (it / g.stages) & 1;
+        ptx::mbar_wait(empty_bar(s), ph ^ 1u);
+        ptx::mbar_expect_tx(full_bar(s), tx_bytes);
+        const int j = it / g.kchunks, kc = it - j * g.kchunks;
+        ptx::tma_load_3d(sA + s * g.a_bytes, &tmA, full_bar(s), kc * g.BK, t0 + j * a.dil - a.pad, b);
+        ptx::tma_load_2d(sB + s * g.b_stride, &tmB, full_bar(s), j * a.Cin + kc * g.BK, ntile * a.NT);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===== MMA issuer =====
+      const uint32_t swz = g.BK * 2;
+      for (int it = 0; it < g.iters; ++it) {
+        const int s = it % g.stages;
+        const uint32_t ph = (it / g.stages) & 1;
+        ptx::mbar_wait(full_bar(s), ph);
+        ptx::tc_fence_after();
+        const uint32_t abase = sA + s * g.a_bytes, bbase = sB + s * g.b_stride;
+        for (int kk = 0; kk < g.BK / 16; ++kk) {
+          const uint64_t ad = ptx::umma_smem_desc(abase + kk * 32, swz, 0);
+          const uint64_t bd = ptx::umma_smem_desc(bbase + kk * 32, swz, 0);
+          ptx::umma_f16(tmem_base, ad, bd, g.idesc, (it | kk) != 0 ? 1u : 0u);
+        }
+        ptx::umma_commit(empty_bar(s));           // frees the smem stage when these MMAs retire
+      }
+      ptx::umma_commit(accum_bar);                // accumulator complete
+    }
+    __syncwarp();
+  } else {
+    // ===== epilogue: TMEM -> registers -> fused math -> global =====
+    const Epilogue& ep = a.epi;
+    const int q = warp & 3;                       // TMEM lane quarter this warp may access
+    const int row = q * 32 + lane;
+    const int t = t0 + row;
+    const bool in_range = t < a.L;
+    const bool live = t < valid;
+    ptx::mbar_wait(accum_bar, 0);
+    ptx::tc_fence_after();
+    const uint32_t trow = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
+    const float* bias = ep.bias + (long long)b * ep.bias_bstride + (long long)ntile * a.NT;
+    if (ep.gate) {
+      const int half = a.NT >> 1;
+      const long long orow_op = (long long)b * ep.out_op_bstride + (long long)t * ep.out_op_ld + (long long)ntile * half;
+      for (int c0 = 0; c0 < half; c0 += 16) {
+        uint32_t ra[16], rb[16];
+        ptx::tmem_ld16(trow + c0, ra);
+        ptx::tmem_ld16(trow + half + c0, rb);
+        ptx::tmem_ld_wait();
+        float ba[16], bb[16], v[16];
+        load16(bias + c0, ba);
+        load16(bias + half + c0, bb);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) {
+          float xa = ep.alpha * (__uint_as_float(ra[i]) + ba[i]);
+          float xb = ep.alpha * (__uint_as_float(rb[i]) + bb[i]);
+          v[i] = live ? gate_fn<false>(xa, xb) : 0.f;
+        }
+        if (in_range) {
+          if (ep.out_f32)
+            store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + (long long)ntile * half + c0, v);
+          if (ep.out_op) store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + orow_op + c0, v, ep.out_slope);
+        }
+      }
+    } else {
+      const long long n0 = (long long)ntile * a.NT;
+      for (int c0 = 0; c0 < a.NT; c0 += 16) {
+        uint32_t r[16];
+        ptx::tmem_ld16(trow + c0, r);
+        ptx::tmem_ld_wait();
+        float bv[16], v[16];
+        load16(bias + c0, bv);
+#pragma unroll
+        for (int i = 0; i < 16; ++i) v[i] = ep.alpha * (__uint_as_float(r[i]) + bv[i]);
+        if (in_range) {
+          if (ep.res) {
+            float x[16];
+            load16(ep.res + (long long)b * ep.res_bstride + (long long)t * ep.res_ld + n0 + c0, x);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = fmaf(ep.beta, x[i], v[i]);
+          }
+          if (ep.accum) {
+            float x[16];
+            load16(ep.accum + (long long)b * ep.accum_bstride + (long long)t * ep.accum_ld + n0 + c0, x);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] += x[i];
+          }
+          if (!live) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = 0.f;
+          }
+          if (ep.out_f32)
+            store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + n0 + c0, v);
+          if (ep.out_op)
+            store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + (long long)b * ep.out_op_bstride +
+                                (long long)t * ep.out_op_ld + n0 + c0, v, ep.out_slope);
+        }
+      }
+    }
+  }
+
+  // ---- teardown: all TMEM reads done before dealloc ----
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, g.tmem_cols);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) == cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+bool conv_tc_supported(int Cin, int in_ld, int N, int NT, int k) {
+  if (!(Cin == 16 || Cin == 32 || (Cin % 64 == 0 && Cin > 0))) return false;
+  if (in_ld % 8 != 0) return false;                       // 16-byte row pitch for TMA
+  if (NT < 16 || NT > kMaxTileN || NT % 16 != 0 || N % NT != 0) return false;
+  if (k < 1) return false;
+  return true;
+}
+
+static bool make_geom(const ConvArgs& a, int op, TcGeom* g) {
+  if (!conv_tc_supported(a.Cin, a.in_ld, a.N, a.NT, a.k)) return false;
+  if (a.epi.gate && (a.NT % 32 != 0)) return false;
+  g->BK = a.Cin >= 64 ? 64 : a.Cin;
+  g->kchunks = a.Cin / g->BK;
+  g->iters = a.k * g->kchunks;
+  g->a_bytes = kTileM * g->BK * 2;
+  g->b_bytes = a.NT * g->BK * 2;
+  g->b_stride = (g->b_bytes + 1023u) & ~1023u;
+  const uint32_t budget = 192 * 1024;
+  int st = budget / (g->a_bytes + g->b_stride);
+  if (st > 8) st = 8;
+  if (st > g->iters) st = g->iters;
+  if (st < 1) st = 1;
+  g->stages = st;
+  uint32_t cols = 32;
+  while (cols < (uint32_t)a.NT) cols <<= 1;
+  g->tmem_cols = cols;
+  g->idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM, a.NT);
+  return true;
+}
+
+cudaError_t launch_conv_tc(const ConvArgs& a, int op, cudaStream_t stream) {
+  TcGeom g;
+  if (op == OP_F32 || !make_geom(a, op, &g)) return cudaErrorNotSupported;
+  EncodeTiledFn enc = get_encode_fn();
+  if (!enc) return cudaErrorNotSupported;
+
+  const CUtensorMapDataType dt = op == OP_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  const CUtensorMapSwizzle sw = g.BK == 64 ? CU_TENSOR_MAP_SWIZZLE_128B
+                               : (g.BK == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
+  CUtensorMap tmA, tmB;
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)a.Cin, (cuuint64_t)a.L, (cuuint64_t)a.B};
+    cuuint64_t strides[2] = {(cuuint64_t)a.in_ld * 2, (cuuint64_t)a.in_bstride * 2};
+    cuuint32_t box[3] = {(cuuint32_t)g.BK, (cuuint32_t)kTileM, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(&tmA, dt, 3, const_cast<void*>(a.in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)a.k * a.Cin, (cuuint64_t)a.N};
+    cuuint64_t strides[1] = {(cuuint64_t)a.k * a.Cin * 2};
+    cuuint32_t box[2] = {(cuuint32_t)g.BK, (cuuint32_t)a.NT};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = enc(&tmB, dt, 2, const_cast<void*>(a.w), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+  }
+  const size_t smem = 1024 + (size_t)g.stages * (g.a_bytes + g.b_stride) + 8 * (2 * g.stages + 1) + 16;
+  dim3 grid(ceil_div(a.L, kTileM), a.N / a.NT, a.B);
+  cudaError_t e;
+  if (op == OP_BF16) {
+    e = cudaFuncSetAttribute(conv_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+    conv_tc_kernel<__nv_bfloat16><<<grid, kTcThreads, smem, stream>>>(tmA, tmB, a, g);
+  } else {
+    e = cudaFuncSetAttribute(conv_tc_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    if (e != cudaSuccess) return e;
+    conv_tc_kernel<__half><<<grid, kTcThreads, smem, stream>>>(tmA, tmB, a, g);
+  }
+  return cudaGetLastError();
+}
+
+}  // namespace vitsb

@@ -1,0 +1,82 @@
+// Host-side engine: packed weights + the per-call launch plan.
+#pragma once
+#include <map>
+#include <string>
+#include <vector>
+
+#include "../../include/vitsb200.h"
+#include "kernels.h"
+
+namespace vitsb {
+
+// One implicit-GEMM conv after packing.
+struct PackedConv {
+  int Cin = 0, N = 0, NT = 0, k = 1, dil = 1, pad = 0;
+  bool gate = false;
+  size_t w_off = 0;        // element offset into the operand-typed weight pool, [N][k*Cin] K-major
+  size_t bias_off = 0;     // offset into the static fp32 bias pool (packed column order)
+  int cond_off = -1;       // >=0: bias = per-call conditioning vector at this column (conv bias folded in)
+  double flop_per_pos = 0; // algorithmic 2*Cin*Cout*k (true taps/channels only)
+};
+
+struct Coupling {          // modules.ResidualCouplingLayer (reverse, mean_only) with Flip folded in
+  PackedConv pre, post;
+  std::vector<PackedConv> in_layers, res, skip;
+  int coff = 0;            // physical channel offset of the half updated by `post`
+};
+
+struct ResIter { PackedConv c1, c2; };
+
+struct Stage {             // ups[i] + its MRF (num_kernels ResBlock2 x iterations)
+  PackedConv ups;
+  int u = 1, C = 0;
+  std::vector<std::vector<ResIter>> rb;   // [kernel][iter]
+};
+
+struct WsLayout {
+  size_t len = 0, cond = 0;
+  size_t zf = 0, zop = 0, hf = 0, hop = 0, acts = 0, skipf = 0, skipop = 0;   // flow
+  size_t xin_f = 0, xb_f = 0, acc_f = 0, xin_op = 0, xb_op = 0, g_op = 0, nxt_op = 0;  // decoder
+  size_t total = 0;
+};
+
+struct Engine {
+  vitsb_config cfg{};
+  int device = 0;
+  int op = OP_F16;
+  std::string err;
+
+  // packed model
+  bool loaded = false;
+  std::vector<Coupling> couplings;       // in execution order (flows.6, .4, .2, .0)
+  PackedConv conv_pre;
+  std::vector<Stage> stages;
+  int post_k = 7, post_C = 0;
+  int Ncond = 0;
+  int up_total = 1;
+  double flop_per_frame = 0;
+
+  // host staging (freed after upload)
+  std::vector<float> h_w, h_bias, h_condW, h_condB, h_post;
+
+  // device pools
+  void* d_w = nullptr;          // op-typed
+  float* d_bias = nullptr;
+  float* d_condW = nullptr;
+  float* d_condB = nullptr;
+  float* d_post = nullptr;
+
+  ~Engine();
+  int fail(int code, const std::string& msg) { err = msg; return code; }
+
+  int validate_config();
+  int load(const vitsb_tensor_desc* t, int n);
+  WsLayout layout(int B, int T) const;
+
+  // mode bits for run()
+  enum { RUN_FLOW = 1, RUN_DEC = 2 };
+  int run(int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
+          float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches);
+};
+
+}  // namespace vitsb

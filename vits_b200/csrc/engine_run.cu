@@ -1,0 +1,216 @@
+// Per-call launch plan: workspace carving and the layer sequence.
+//
+// Reference control flow being replaced (paths relative to emotional-vits/):
+//   flow  : models.py:228-235 -> modules.py:362-375 -> modules.py:157-182
+//   dec   : models.py:306-318 -> modules.py:250-260
+// Buffer roles (all time-major [B][L][C]):
+//   zf/zop      flow state, fp32 master + operand copy        [T][inter]
+//   hf/hop      WN residual stream                             [T][H]
+//   acts        gated activations (operand)                    [T][H]
+//   skipf/skipop WN skip accumulator                            [T][H]
+//   xin_f/xin_op  stage input x (after ups) and leaky_relu(x)   [L_s][C_s]
+//   xb_f/xb_op    per-branch ResBlock residual stream
+//   g_op          gated activations                             [L_s][C_s/2]
+//   acc_f         MRF accumulator (sum of branches / num_kernels)
+//   nxt_op        leaky_relu(acc) = next stage's ups / conv_post input
+#include "engine.h"
+
+namespace vitsb {
+
+static size_t align_up(size_t x, size_t a = 1024) { return (x + a - 1) / a * a; }
+
+WsLayout Engine::layout(int B, int T) const {
+  WsLayout w;
+  const size_t ob = op_bytes(op);
+  size_t off = 0;
+  auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes); return o; };
+  const size_t BT = (size_t)B * T;
+  const size_t H = cfg.hidden_channels, IC = cfg.inter_channels;
+  w.len = take(sizeof(int) * (size_t)B);
+  w.cond = take(sizeof(float) * (size_t)B * (Ncond > 0 ? Ncond : 1));
+  w.zf = take(4 * BT * IC);  w.zop = take(ob * BT * IC);
+  w.hf = take(4 * BT * H);   w.hop = take(ob * BT * H);
+  w.acts = take(ob * BT * H);
+  w.skipf = take(4 * BT * H); w.skipop = take(ob * BT * H);
+  // decoder: elements per frame of the widest stage tensor
+  size_t E = cfg.upsample_initial_channel;     // conv_pre output lives in nxt_op
+  size_t pos = 1; int C = cfg.upsample_initial_channel;
+  for (int i = 0; i < cfg.n_upsamples; ++i) {
+    pos *= cfg.upsample_rates[i]; C /= 2;
+    if (pos * C > E) E = pos * C;
+  }
+  w.xin_f = take(4 * BT * E); w.xb_f = take(4 * BT * E); w.acc_f = take(4 * BT * E);
+  w.xin_op = take(ob * BT * E); w.xb_op = take(ob * BT * E); w.g_op = take(ob * BT * E / 2 + 16); w.nxt_op = take(ob * BT * E);
+  w.total = off;
+  return w;
+}
+
+namespace {
+
+struct Ctx {
+  Engine* e;
+  cudaStream_t stream;
+  bool dry;
+  int launches = 0;
+  cudaError_t err = cudaSuccess;
+  int B, T;
+  const int* len_flow;   // device lens used for masking (nullptr = all rows live)
+  const int* len_dec;
+  const float* cond;     // device [B][Ncond]
+
+  bool ok() const { return err == cudaSuccess; }
+
+  void conv(const PackedConv& p, const void* in, int L, int len_mul, const int* len, const Epilogue& ep_in) {
+    ++launches;
+    if (dry || !ok()) return;
+    ConvArgs a{};
+    a.in = in; a.in_ld = p.Cin; a.in_bstride = (long long)L * p.Cin; a.Cin = p.Cin;
+    a.w = reinterpret_cast<const char*>(e->d_w) + p.w_off * op_bytes(e->op);
+    a.N = p.N; a.NT = p.NT; a.k = p.k; a.dil = p.dil; a.pad = p.pad; a.L = L; a.B = B;
+    a.len = len; a.len_mul = len_mul;
+    a.epi = ep_in;
+    a.epi.gate = p.gate ? 1 : 0;
+    if (p.cond_off >= 0) { a.epi.bias = cond + p.cond_off; a.epi.bias_bstride = e->Ncond; }
+    else { a.epi.bias = e->d_bias + p.bias_off; a.epi.bias_bstride = 0; }
+    err = e->op == OP_F32 ? launch_conv_f32(a, stream) : launch_conv_tc(a, e->op, stream);
+  }
+};
+
+// dense [B][L][C] epilogue target helpers
+Epilogue epi_base() {
+  Epilogue ep{};
+  ep.alpha = 1.f; ep.beta = 1.f; ep.out_slope = 1.f;
+  return ep;
+}
+void set_res(Epilogue& ep, const float* p, int ld, long long L) { ep.res = p; ep.res_ld = ld; ep.res_bstride = L * ld; }
+void set_accum(Epilogue& ep, const float* p, int ld, long long L) { ep.accum = p; ep.accum_ld = ld; ep.accum_bstride = L * ld; }
+void set_out_f32(Epilogue& ep, float* p, int ld, long long L) { ep.out_f32 = p; ep.out_f32_ld = ld; ep.out_f32_bstride = L * ld; }
+void set_out_op(Epilogue& ep, void* p, int ld, long long L, float slope) {
+  ep.out_op = p; ep.out_op_ld = ld; ep.out_op_bstride = L * ld; ep.out_slope = slope;
+}
+
+}  // namespace
+
+int Engine::run(int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
+                float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches) {
+  if (!dry) {
+    if (!loaded) return fail(VITSB_ERR_WEIGHTS, "weights not loaded");
+    if (!z_in || !g || !ws) return fail(VITSB_ERR_BAD_ARG, "null pointer");
+    if ((what & RUN_DEC) && !wav) return fail(VITSB_ERR_BAD_ARG, "null wav");
+  }
+  if (B < 1 || T < 1) return fail(VITSB_ERR_BAD_ARG, "B and T_max must be >= 1");
+  if ((long long)T * up_total > 0x7fffffffLL / 64) return fail(VITSB_ERR_BAD_ARG, "T_max too large");
+  const WsLayout W = layout(B, T);
+  if (!dry && ws_bytes < W.total) return fail(VITSB_ERR_WORKSPACE, "workspace too small");
+  if (!dry && len) for (int b = 0; b < B; ++b)
+    if (len[b] < 0 || len[b] > T) return fail(VITSB_ERR_BAD_ARG, "len[b] out of [0, T_max]");
+
+  char* base = reinterpret_cast<char*>(ws);
+  auto F = [&](size_t off) { return reinterpret_cast<float*>(base + off); };
+  auto P = [&](size_t off) { return reinterpret_cast<void*>(base + off); };
+  const size_t ob = op_bytes(op);
+  const int IC = cfg.inter_channels, H = cfg.hidden_channels;
+
+  Ctx cx{this, stream, dry};
+  cx.B = B; cx.T = T;
+  cx.cond = F(W.cond);
+  int* d_len = reinterpret_cast<int*>(base + W.len);
+  cx.len_flow = len ? d_len : nullptr;
+  cx.len_dec = (len && ragged) ? d_len : nullptr;
+
+#define AUX_LAUNCH(expr) do { ++cx.launches; if (!dry && cx.ok()) cx.err = (expr); } while (0)
+
+  if (!dry) {
+    cudaError_t e0 = cudaSetDevice(device);
+    if (e0 != cudaSuccess) return fail(VITSB_ERR_CUDA, cudaGetErrorString(e0));
+    if (len) cx.err = cudaMemcpyAsync(d_len, len, sizeof(int) * B, cudaMemcpyHostToDevice, stream);
+  }
+  // seam: channel-major fp32 -> time-major (masked beyond len)
+  AUX_LAUNCH(launch_pack_time_major(z_in, B, IC, T, cx.len_flow, (what & RUN_FLOW) ? F(W.zf) : nullptr, P(W.zop), op, stream));
+  // all conditioning Linears of the call: flow cond_layers (modules.py:161) + ResBlock conds (modules.py:254)
+  AUX_LAUNCH(launch_cond_gemv(d_condW, d_condB, g, B, Ncond, cfg.gin_channels, F(W.cond), stream));
+
+  if (what & RUN_FLOW) {
+    for (const Coupling& cp : couplings) {
+      // h = pre(x0)                                                   modules.py:364
+      { Epilogue ep = epi_base(); set_out_f32(ep, F(W.hf), H, T); set_out_op(ep, P(W.hop), H, T, 1.f);
+        cx.conv(cp.pre, P(W.zop), T, 1, cx.len_flow, ep); }
+      const int nl = (int)cp.in_layers.size();
+      for (int l = 0; l < nl; ++l) {
+        // acts = tanh(a)*sigmoid(b), a,b = in_layer(h) + cond slice     modules.py:163-172
+        { Epilogue ep = epi_base(); set_out_op(ep, P(W.acts), H, T, 1.f);
+          cx.conv(cp.in_layers[l], P(W.hop), T, 1, cx.len_flow, ep); }
+        if (l < nl - 1) {
+          // h += res_skip[:H]                                           modules.py:176-178
+          Epilogue ep = epi_base(); set_res(ep, F(W.hf), H, T); set_out_f32(ep, F(W.hf), H, T); set_out_op(ep, P(W.hop), H, T, 1.f);
+          cx.conv(cp.res[l], P(W.acts), T, 1, cx.len_flow, ep);
+        }
+        // output += res_skip[H:] (all of it on the last layer)          modules.py:179-181
+        { Epilogue ep = epi_base();
+          if (l > 0) set_accum(ep, F(W.skipf), H, T);
+          if (l < nl - 1) set_out_f32(ep, F(W.skipf), H, T); else set_out_op(ep, P(W.skipop), H, T, 1.f);
+          cx.conv(cp.skip[l], P(W.acts), T, 1, cx.len_flow, ep); }
+      }
+      // x1 = x1 - post(out)   (mean-only, logs == 0)                    modules.py:366-372
+      { Epilogue ep = epi_base(); ep.alpha = -1.f; ep.beta = 1.f;
+        ep.res = F(W.zf) + cp.coff; ep.res_ld = IC; ep.res_bstride = (long long)T * IC;
+        ep.out_f32 = F(W.zf) + cp.coff; ep.out_f32_ld = IC; ep.out_f32_bstride = (long long)T * IC;
+        ep.out_op = reinterpret_cast<char*>(P(W.zop)) + (size_t)cp.coff * ob; ep.out_op_ld = IC; ep.out_op_bstride = (long long)T * IC;
+        cx.conv(cp.post, P(W.skipop), T, 1, cx.len_flow, ep); }
+    }
+    if (z_out) AUX_LAUNCH(launch_unpack_channel_major(F(W.zf), B, IC, T, z_out, stream));
+  }
+
+  if (what & RUN_DEC) {
+    // x = conv_pre(z); the next op's leaky_relu(0.1) is folded into the operand copy   models.py:307-309
+    { Epilogue ep = epi_base(); set_out_op(ep, P(W.nxt_op), conv_pre.N, T, 0.1f);
+      cx.conv(conv_pre, P(W.zop), T, 1, cx.len_dec, ep); }
+    int L = T;              // rows per batch item at the current rate
+    int mul = 1;            // valid rows = len * mul
+    const int ns = (int)stages.size();
+    for (int s = 0; s < ns; ++s) {
+      const Stage& st = stages[s];
+      const int C = st.C, Lo = L * st.u;
+      // x = ups[i](leaky_relu(x)): phase-stacked conv, output row t holds out[u*t .. u*t+u-1]   models.py:310
+      { Epilogue ep = epi_base();
+        set_out_f32(ep, F(W.xin_f), st.ups.N, L); set_out_op(ep, P(W.xin_op), st.ups.N, L, 0.1f);
+        cx.conv(st.ups, P(W.nxt_op), L, mul, cx.len_dec, ep); }
+      L = Lo; mul *= st.u;
+      const int nk = (int)st.rb.size();
+      const float inv = 1.0f / nk;
+      const float next_slope = s + 1 < ns ? 0.1f : 0.01f;      // models.py:309 vs models.py:315
+      for (int j = 0; j < nk; ++j) {
+        const int ni = (int)st.rb[j].size();
+        for (int d = 0; d < ni; ++d) {
+          const ResIter& it = st.rb[j][d];
+          const void* xin_op = d == 0 ? P(W.xin_op) : P(W.xb_op);
+          const float* xin_f = d == 0 ? F(W.xin_f) : F(W.xb_f);
+          // xt = tanh(.)*sigmoid(.) of c1(leaky_relu(x)) + cond           modules.py:252-257
+          { Epilogue ep = epi_base(); set_out_op(ep, P(W.g_op), C / 2, L, 1.f);
+            cx.conv(it.c1, xin_op, L, mul, cx.len_dec, ep); }
+          // x = c2(xt) + x                                                modules.py:258-259
+          Epilogue ep = epi_base();
+          set_res(ep, xin_f, C, L);
+          if (d < ni - 1) {
+            set_out_f32(ep, F(W.xb_f), C, L); set_out_op(ep, P(W.xb_op), C, L, 0.1f);
+          } else {
+            // MRF: xs += branch; x = xs / num_kernels                      models.py:311-314
+            ep.alpha = inv; ep.beta = inv;
+            if (j > 0) set_accum(ep, F(W.acc_f), C, L);
+            if (j < nk - 1) set_out_f32(ep, F(W.acc_f), C, L);
+            else set_out_op(ep, P(W.nxt_op), C, L, next_slope);
+          }
+          cx.conv(it.c2, P(W.g_op), L, mul, cx.len_dec, ep);
+        }
+      }
+    }
+    // tanh(conv_post(leaky_relu(x, 0.01)))                                 models.py:315-317
+    AUX_LAUNCH(launch_conv_post(P(W.nxt_op), op, B, L, post_C, post_k, d_post, cx.len_dec, mul, wav, stream));
+  }
+#undef AUX_LAUNCH
+  if (launches) *launches = cx.launches;
+  if (!cx.ok()) return fail(VITSB_ERR_CUDA, std::string("launch failed: ") + cudaGetErrorString(cx.err));
+  return VITSB_OK;
+}
+
+}  // namespace vitsb

@@ -1,0 +1,360 @@
+// state_dict -> packed device weights.
+//
+// Reference layouts (paths relative to emotional-vits/):
+//   Conv1d.weight           [Cout][Cin][k]                 (models.py:288,301; modules.py:115,126,229-241,335-337)
+//   ConvTranspose1d.weight  [Cin][Cout][k], stride u, padding (k-u)//2   (models.py:289-293)
+//   Linear.weight           [out][in]                      (modules.py:109,243-245)
+//   weight_norm             w = g * v / ||v|| over all dims but 0       (models.py:467-474)
+// Packed layout: one K-major matrix [N][k*Cin] per implicit-GEMM conv, tap-major /
+// channel-minor, with
+//   - Flip (modules.py:278-289) folded into the channel order of flow pre/post,
+//   - gated convs' rows tiled so that the tanh half and the sigmoid half of the
+//     same channels share one N tile,
+//   - ConvTranspose1d rewritten as a stride-1 conv over the input with N = u*Cout
+//     phase-stacked outputs (time-major output [L][u*Cout] == [L*u][Cout]),
+//   - every conditioning Linear stacked into one [Ncond][gin] matrix in packed
+//     column order, conv bias folded into its bias.
+#include <cmath>
+#include <cstring>
+
+#include "engine.h"
+
+namespace vitsb {
+
+Engine::~Engine() {
+  if (d_w) cudaFree(d_w);
+  if (d_bias) cudaFree(d_bias);
+  if (d_condW) cudaFree(d_condW);
+  if (d_condB) cudaFree(d_condB);
+  if (d_post) cudaFree(d_post);
+}
+
+int Engine::validate_config() {
+  const vitsb_config& c = cfg;
+  auto bad = [&](const char* m) { return fail(VITSB_ERR_UNSUPPORTED, std::string("unsupported config: ") + m); };
+  if (c.precision < 0 || c.precision > 2) return bad("precision");
+  if (c.inter_channels <= 0 || c.inter_channels % 32 != 0) return bad("inter_channels must be a multiple of 32");
+  if (c.hidden_channels % 64 != 0) return bad("hidden_channels must be a multiple of 64");
+  if (c.gin_channels <= 0 || c.gin_channels % 4 != 0) return bad("gin_channels must be a positive multiple of 4 "
+                                                                 "(the reference hot path is always speaker-conditioned)");
+  if (c.n_flows < 1 || c.n_flows > VITSB_MAX_LIST) return bad("n_flows");
+  if (c.flow_kernel_size % 2 != 1) return bad("flow kernel size must be odd (modules.py:96)");
+  if (c.flow_n_layers < 1 || c.flow_n_layers > VITSB_MAX_LIST) return bad("flow_n_layers");
+  if (c.n_upsamples < 1 || c.n_upsamples > VITSB_MAX_LIST) return bad("n_upsamples");
+  if (c.n_resblock_kernels < 1 || c.n_resblock_kernels > VITSB_MAX_LIST) return bad("n_resblock_kernels");
+  if (c.n_resblock_dilations < 1 || c.n_resblock_dilations > VITSB_MAX_LIST) return bad("n_resblock_dilations");
+  int C = c.upsample_initial_channel;
+  if (C % 64 != 0) return bad("upsample_initial_channel must be a multiple of 64");
+  for (int i = 0; i < c.n_upsamples; ++i) {
+    if (C % 2) return bad("channel ladder");
+    C /= 2;
+    if (C % 32 != 0) return bad("every stage needs C % 32 == 0 (gate halves of 16 channels)");
+    int u = c.upsample_rates[i], k = c.upsample_kernel_sizes[i];
+    if (u < 1 || k < u || (k - u) % 2 != 0) return bad("upsample kernel/rate: need k >= u and (k-u) even");
+  }
+  for (int j = 0; j < c.n_resblock_kernels; ++j) {
+    if (c.resblock_kernel_sizes[j] % 2 != 1) return bad("resblock kernel sizes must be odd");
+    for (int d = 0; d < c.n_resblock_dilations; ++d) {
+      int pad = (c.resblock_kernel_sizes[j] - 1) / 2 * c.resblock_dilation_sizes[j][d];
+      if (pad > kHaloRows) return bad("conv receptive field exceeds the masking halo");
+    }
+  }
+  for (int i = 0; i < c.n_flows; ++i) {
+    int dr = c.flow_dilation_rate[i];
+    int pad = (c.flow_kernel_size - 1) / 2;
+    for (int l = 1; l < c.flow_n_layers; ++l) pad *= dr > 1 ? dr : 1;
+    if (dr < 1 || pad > kHaloRows) return bad("flow dilation");
+  }
+  op = c.precision == VITSB_PREC_FP32 ? OP_F32 : (c.precision == VITSB_PREC_BF16 ? OP_BF16 : OP_F16);
+  up_total = 1;
+  for (int i = 0; i < c.n_upsamples; ++i) up_total *= c.upsample_rates[i];
+  return VITSB_OK;
+}
+
+namespace {
+
+struct HostTensor { std::vector<float> v; std::vector<int64_t> shape; };
+
+float load_elem(const void* p, int dtype, size_t i) {
+  if (dtype == VITSB_F32) return reinterpret_cast<const float*>(p)[i];
+  if (dtype == VITSB_F16) return __half2float(reinterpret_cast<const __half*>(p)[i]);
+  return __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(p)[i]);
+}
+
+struct Loader {
+  std::map<std::string, HostTensor> t;
+  std::string err;
+
+  // folded weight `name`.weight (or name.weight_g/_v), checked against `shape`
+  const HostTensor* weight(const std::string& base, std::vector<int64_t> shape) {
+    auto it = t.find(base + ".weight");
+    if (it == t.end()) {
+      auto ig = t.find(base + ".weight_g"), iv = t.find(base + ".weight_v");
+      if (ig == t.end() || iv == t.end()) { err = "missing tensor " + base + ".weight"; return nullptr; }
+      const HostTensor& g = ig->second; const HostTensor& v = iv->second;
+      if (v.shape.empty() || (int64_t)g.v.size() != v.shape[0]) { err = "bad weight_g shape for " + base; return nullptr; }
+      HostTensor w; w.shape = v.shape; w.v.resize(v.v.size());
+      size_t inner = v.v.size() / (size_t)v.shape[0];
+      for (int64_t r = 0; r < v.shape[0]; ++r) {
+        double ss = 0;
+        for (size_t i = 0; i < inner; ++i) { double x = v.v[r * inner + i]; ss += x * x; }
+        float scale = (float)((double)g.v[r] / std::sqrt(ss));
+        for (size_t i = 0; i < inner; ++i) w.v[r * inner + i] = v.v[r * inner + i] * scale;
+      }
+      it = t.emplace(base + ".weight", std::move(w)).first;
+    }
+    if (it->second.shape != shape) {
+      err = "shape mismatch for " + base + ".weight";
+      return nullptr;
+    }
+    return &it->second;
+  }
+  const HostTensor* bias(const std::string& base, int64_t n) {
+    auto it = t.find(base + ".bias");
+    if (it == t.end()) { err = "missing tensor " + base + ".bias"; return nullptr; }
+    if (it->second.v.size() != (size_t)n) { err = "shape mismatch for " + base + ".bias"; return nullptr; }
+    return &it->second;
+  }
+};
+
+int pick_nt(int N) {
+  if (N <= kMaxTileN) return N;
+  for (int nt = kMaxTileN; nt >= 16; nt -= 16)
+    if (N % nt == 0) return nt;
+  return 16;
+}
+
+// packed row -> source out-channel for a gated conv with N_total = 2*Hout
+std::vector<int> gate_rows(int N_total, int NT) {
+  std::vector<int> r(N_total);
+  int Hout = N_total / 2, half = NT / 2;
+  for (int n = 0; n < N_total; ++n) {
+    int tile = n / NT, q = n % NT;
+    r[n] = q < half ? tile * half + q : Hout + tile * half + (q - half);
+  }
+  return r;
+}
+std::vector<int> iota_rows(int n0, int n) { std::vector<int> r(n); for (int i = 0; i < n; ++i) r[i] = n0 + i; return r; }
+
+}  // namespace
+
+int Engine::load(const vitsb_tensor_desc* tens, int n) {
+  if (!tens || n <= 0) return fail(VITSB_ERR_BAD_ARG, "no tensors");
+  Loader L;
+  for (int i = 0; i < n; ++i) {
+    const vitsb_tensor_desc& d = tens[i];
+    if (!d.name || !d.data) return fail(VITSB_ERR_BAD_ARG, "null tensor name/data");
+    if (std::strncmp(d.name, "dec.", 4) != 0 && std::strncmp(d.name, "flow.", 5) != 0) continue;
+    if (d.ndim < 1 || d.ndim > 4 || d.dtype < 0 || d.dtype > 2) return fail(VITSB_ERR_BAD_ARG, std::string("bad desc for ") + d.name);
+    HostTensor h; size_t cnt = 1;
+    for (int k = 0; k < d.ndim; ++k) { h.shape.push_back(d.shape[k]); cnt *= (size_t)d.shape[k]; }
+    h.v.resize(cnt);
+    for (size_t k = 0; k < cnt; ++k) h.v[k] = load_elem(d.data, d.dtype, k);
+    L.t[d.name] = std::move(h);
+  }
+
+  const vitsb_config& c = cfg;
+  h_w.clear(); h_bias.clear(); h_condW.clear(); h_condB.clear(); h_post.clear();
+  couplings.clear(); stages.clear();
+  Ncond = 0; flop_per_frame = 0;
+  const int gin = c.gin_channels;
+  bool ok = true;
+
+  // generic Conv1d packer.  rows[n] = source out-channel; cols[cp] = source in-channel or -1 (zero)
+  auto pack_conv = [&](const HostTensor* w, const HostTensor* b, const std::vector<int>& rows, const std::vector<int>& cols,
+                       int k, int dil, bool gate, int NT, const HostTensor* condW, const HostTensor* condB, int cond_row0,
+                       int true_cin) -> PackedConv {
+    PackedConv p;
+    p.Cin = (int)cols.size(); p.N = (int)rows.size(); p.NT = NT; p.k = k; p.dil = dil; p.pad = (k - 1) / 2 * dil; p.gate = gate;
+    p.flop_per_pos = 2.0 * true_cin * p.N * k;
+    if (!w || !b) { ok = false; return p; }
+    const int Cin_src = (int)w->shape[1];
+    p.w_off = h_w.size();
+    h_w.resize(h_w.size() + (size_t)p.N * k * p.Cin, 0.f);
+    float* dst = h_w.data() + p.w_off;
+    for (int nn = 0; nn < p.N; ++nn)
+      for (int j = 0; j < k; ++j)
+        for (int cp = 0; cp < p.Cin; ++cp)
+          if (cols[cp] >= 0) dst[((size_t)nn * k + j) * p.Cin + cp] = w->v[((size_t)rows[nn] * Cin_src + cols[cp]) * k + j];
+    if (condW) {
+      p.cond_off = Ncond;
+      h_condW.resize((size_t)(Ncond + p.N) * gin);
+      h_condB.resize(Ncond + p.N);
+      for (int nn = 0; nn < p.N; ++nn) {
+        std::memcpy(h_condW.data() + (size_t)(Ncond + nn) * gin, condW->v.data() + (size_t)(cond_row0 + rows[nn]) * gin, sizeof(float) * gin);
+        h_condB[Ncond + nn] = condB->v[cond_row0 + rows[nn]] + b->v[rows[nn]];
+      }
+      Ncond += p.N;
+    } else {
+      p.bias_off = h_bias.size();
+      for (int nn = 0; nn < p.N; ++nn) h_bias.push_back(b->v[rows[nn]]);
+      while (h_bias.size() % 4) h_bias.push_back(0.f);
+    }
+    return p;
+  };
+
+  // ---------------- flow (execution order: flows[2*(n_flows-1)] ... flows[0]) ----------------
+  const int H = c.hidden_channels, IC = c.inter_channels, half = IC / 2, fk = c.flow_kernel_size, nl = c.flow_n_layers;
+  for (int step = 0; step < c.n_flows && ok; ++step) {
+    const int fi = c.n_flows - 1 - step;
+    const bool flipped = ((step + 1) % 2) == 1;          // number of Flips applied before this coupling is step+1
+    const std::string p = "flow.flows." + std::to_string(2 * fi) + ".";
+    Coupling cp;
+    // pre: 1x1 conv over the logical first half; K is the full physical row (zeros on the other half)
+    {
+      std::vector<int> cols(IC, -1);
+      for (int cl = 0; cl < half; ++cl) cols[flipped ? IC - 1 - cl : cl] = cl;
+      cp.pre = pack_conv(L.weight(p + "pre", {H, half, 1}), L.bias(p + "pre", H), iota_rows(0, H), cols, 1, 1, false, pick_nt(H),
+                         nullptr, nullptr, 0, half);
+    }
+    const HostTensor* cw = L.weight(p + "enc.cond_layer", {2 * H * nl, gin});
+    const HostTensor* cb = L.bias(p + "enc.cond_layer", 2 * H * nl);
+    if (!cw || !cb) { ok = false; break; }
+    int dil = 1;
+    for (int l = 0; l < nl && ok; ++l) {
+      const std::string li = std::to_string(l);
+      const int NT = pick_nt(2 * H);
+      std::vector<int> cols = iota_rows(0, H);
+      cp.in_layers.push_back(pack_conv(L.weight(p + "enc.in_layers." + li, {2 * H, H, fk}), L.bias(p + "enc.in_layers." + li, 2 * H),
+                                       gate_rows(2 * H, NT), cols, fk, dil, true, NT, cw, cb, l * 2 * H, H));
+      const int rs = l < nl - 1 ? 2 * H : H;
+      const HostTensor* rw = L.weight(p + "enc.res_skip_layers." + li, {rs, H, 1});
+      const HostTensor* rb = L.bias(p + "enc.res_skip_layers." + li, rs);
+      if (l < nl - 1) {
+        cp.res.push_back(pack_conv(rw, rb, iota_rows(0, H), cols, 1, 1, false, pick_nt(H), nullptr, nullptr, 0, H));
+        cp.skip.push_back(pack_conv(rw, rb, iota_rows(H, H), cols, 1, 1, false, pick_nt(H), nullptr, nullptr, 0, H));
+      } else {
+        cp.skip.push_back(pack_conv(rw, rb, iota_rows(0, H), cols, 1, 1, false, pick_nt(H), nullptr, nullptr, 0, H));
+      }
+      dil *= c.flow_dilation_rate[fi];
+    }
+    // post: logical x1 channel cl lives at physical IC-1-(half+cl) when flipped, else half+cl
+    {
+      std::vector<int> rows(half);
+      for (int r = 0; r < half; ++r) rows[r] = flipped ? half - 1 - r : r;
+      cp.coff = flipped ? 0 : half;
+      cp.post = pack_conv(L.weight(p + "post", {half, H, 1}), L.bias(p + "post", half), rows, iota_rows(0, H), 1, 1, false,
+                          pick_nt(half), nullptr, nullptr, 0, H);
+    }
+    if (!ok) break;
+    flop_per_frame += cp.pre.flop_per_pos + cp.post.flop_per_pos;
+    for (auto& x : cp.in_layers) flop_per_frame += x.flop_per_pos;
+    for (auto& x : cp.res) flop_per_frame += x.flop_per_pos;
+    for (auto& x : cp.skip) flop_per_frame += x.flop_per_pos;
+    couplings.push_back(std::move(cp));
+  }
+
+  // ---------------- decoder ----------------
+  int C = c.upsample_initial_channel;
+  if (ok) {
+    conv_pre = pack_conv(L.weight("dec.conv_pre", {C, IC, 7}), L.bias("dec.conv_pre", C), iota_rows(0, C), iota_rows(0, IC), 7, 1,
+                         false, pick_nt(C), nullptr, nullptr, 0, IC);
+    flop_per_frame += conv_pre.flop_per_pos;
+  }
+  int pos_per_frame = 1;
+  for (int i = 0; i < c.n_upsamples && ok; ++i) {
+    const int Cin = C, Cout = C / 2, u = c.upsample_rates[i], k = c.upsample_kernel_sizes[i], pd = (k - u) / 2;
+    Stage st; st.u = u; st.C = Cout;
+    const std::string up = "dec.ups." + std::to_string(i);
+    const HostTensor* w = L.weight(up, {Cin, Cout, k});
+    const HostTensor* b = L.bias(up, Cout);
+    if (!w || !b) { ok = false; break; }
+    // out[u*t + ph] += W[:, :, j] x[t + dlt]  with  j = ph + pd - u*dlt
+    int dmin = 0, dmax = 0;
+    for (int ph = 0; ph < u; ++ph)
+      for (int j = 0; j < k; ++j) {
+        int num = ph + pd - j;
+        if (num % u != 0) continue;
+        int dlt = num / u;
+        dmin = dlt < dmin ? dlt : dmin; dmax = dlt > dmax ? dlt : dmax;
+      }
+    PackedConv& pc = st.ups;
+    pc.Cin = Cin; pc.N = u * Cout; pc.NT = pick_nt(pc.N); pc.k = dmax - dmin + 1; pc.dil = 1; pc.pad = -dmin; pc.gate = false;
+    pc.flop_per_pos = 2.0 * Cin * Cout * k;          // per INPUT position
+    if (pc.pad > kHaloRows || dmax > kHaloRows) { ok = false; L.err = "upsample taps exceed halo"; break; }
+    pc.w_off = h_w.size();
+    h_w.resize(h_w.size() + (size_t)pc.N * pc.k * Cin, 0.f);
+    float* dst = h_w.data() + pc.w_off;
+    for (int ph = 0; ph < u; ++ph)
+      for (int co = 0; co < Cout; ++co)
+        for (int jj = 0; jj < pc.k; ++jj) {
+          int dlt = jj + dmin, j = ph + pd - u * dlt;
+          if (j < 0 || j >= k) continue;
+          for (int ci = 0; ci < Cin; ++ci)
+            dst[((size_t)(ph * Cout + co) * pc.k + jj) * Cin + ci] = w->v[((size_t)ci * Cout + co) * k + j];
+        }
+    pc.bias_off = h_bias.size();
+    for (int ph = 0; ph < u; ++ph) for (int co = 0; co < Cout; ++co) h_bias.push_back(b->v[co]);
+    while (h_bias.size() % 4) h_bias.push_back(0.f);
+    flop_per_frame += pc.flop_per_pos * pos_per_frame;
+    pos_per_frame *= u;
+
+    st.rb.resize(c.n_resblock_kernels);
+    for (int j = 0; j < c.n_resblock_kernels && ok; ++j) {
+      const int kk = c.resblock_kernel_sizes[j];
+      const std::string rp = "dec.resblocks." + std::to_string(i * c.n_resblock_kernels + j) + ".";
+      for (int d = 0; d < c.n_resblock_dilations && ok; ++d) {
+        const std::string ds = std::to_string(d);
+        ResIter it;
+        const int NT = pick_nt(Cout);
+        const HostTensor* gw = L.weight(rp + "conds." + ds, {Cout, gin});
+        const HostTensor* gb = L.bias(rp + "conds." + ds, Cout);
+        if (!gw || !gb) { ok = false; break; }
+        it.c1 = pack_conv(L.weight(rp + "convs1." + ds, {Cout, Cout, kk}), L.bias(rp + "convs1." + ds, Cout), gate_rows(Cout, NT),
+                          iota_rows(0, Cout), kk, c.resblock_dilation_sizes[j][d], true, NT, gw, gb, 0, Cout);
+        it.c2 = pack_conv(L.weight(rp + "convs2." + ds, {Cout, Cout / 2, kk}), L.bias(rp + "convs2." + ds, Cout), iota_rows(0, Cout),
+                          iota_rows(0, Cout / 2), kk, 1, false, pick_nt(Cout), nullptr, nullptr, 0, Cout / 2);
+        flop_per_frame += (it.c1.flop_per_pos + it.c2.flop_per_pos) * pos_per_frame;
+        st.rb[j].push_back(it);
+      }
+    }
+    stages.push_back(std::move(st));
+    C = Cout;
+  }
+  if (ok) {
+    const HostTensor* w = L.weight("dec.conv_post", {1, C, 7});
+    if (!w) ok = false;
+    else {
+      post_k = 7; post_C = C;
+      h_post.resize((size_t)post_k * C);
+      for (int j = 0; j < post_k; ++j) for (int ci = 0; ci < C; ++ci) h_post[(size_t)j * C + ci] = w->v[(size_t)ci * post_k + j];
+      flop_per_frame += 2.0 * C * post_k * pos_per_frame;
+    }
+  }
+  if (!ok) return fail(VITSB_ERR_WEIGHTS, L.err.empty() ? "weight packing failed" : L.err);
+
+  // ---------------- upload ----------------
+  if (d_w) { cudaFree(d_w); d_w = nullptr; }
+  if (d_bias) { cudaFree(d_bias); d_bias = nullptr; }
+  if (d_condW) { cudaFree(d_condW); d_condW = nullptr; }
+  if (d_condB) { cudaFree(d_condB); d_condB = nullptr; }
+  if (d_post) { cudaFree(d_post); d_post = nullptr; }
+  loaded = false;
+  cudaError_t e = cudaSetDevice(device);
+  auto up = [&](void** dptr, const void* src, size_t bytes) {
+    if (e != cudaSuccess) return;
+    e = cudaMalloc(dptr, bytes ? bytes : 16);
+    if (e == cudaSuccess && bytes) e = cudaMemcpy(*dptr, src, bytes, cudaMemcpyHostToDevice);
+  };
+  if (op == OP_F32) {
+    up(&d_w, h_w.data(), h_w.size() * 4);
+  } else if (op == OP_F16) {
+    std::vector<__half> tmp(h_w.size());
+    for (size_t i = 0; i < h_w.size(); ++i) tmp[i] = __float2half_rn(h_w[i]);
+    up(&d_w, tmp.data(), tmp.size() * 2);
+  } else {
+    std::vector<__nv_bfloat16> tmp(h_w.size());
+    for (size_t i = 0; i < h_w.size(); ++i) tmp[i] = __float2bfloat16_rn(h_w[i]);
+    up(&d_w, tmp.data(), tmp.size() * 2);
+  }
+  up((void**)&d_bias, h_bias.data(), h_bias.size() * 4);
+  up((void**)&d_condW, h_condW.data(), h_condW.size() * 4);
+  up((void**)&d_condB, h_condB.data(), h_condB.size() * 4);
+  up((void**)&d_post, h_post.data(), h_post.size() * 4);
+  if (e != cudaSuccess) return fail(VITSB_ERR_CUDA, std::string("weight upload: ") + cudaGetErrorString(e));
+  std::vector<float>().swap(h_w); std::vector<float>().swap(h_condW);
+  loaded = true;
+  return VITSB_OK;
+}
+
+}  // namespace vitsb

@@ -1,0 +1,184 @@
+"""Host-side mirror of the reference's flow+decoder interface over the C ABI.
+
+`FlowDecoder` owns one `vitsb_handle` (packed weights on one GPU).  Method
+names and argument meaning follow the reference (paths relative to
+emotional-vits/):
+
+  flow_reverse(z_p, g, lengths)   ResidualCouplingBlock.infer / masked forward(reverse=True)  models.py:219-235
+  decode(z, g, lengths, ragged)   Generator.forward                                          models.py:306-318
+  infer_p2(attn, m_p, s_p, g, noise)  SynthesizerTrn.infer_p2                                models.py:568-575
+  synthesize(z_p, g, lengths, ragged) tail of infer_p2 / inference                           models.py:533-534,573-574
+
+PyTorch is plumbing here (device memory, streams); every FLOP of the path runs
+in libvitsb200.so.  There is no CPU fallback: constructing a FlowDecoder
+without a CUDA device or without the built library raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, Optional, Sequence
+
+import torch
+
+from . import lib as L
+
+_TORCH_DT = {torch.float32: L.DT_F32, torch.float16: L.DT_F16, torch.bfloat16: L.DT_BF16}
+
+
+def _hot_items(state_dict):
+    for k, v in state_dict.items():
+        if k.startswith("dec.") or k.startswith("flow."):
+            yield k, v
+
+
+class FlowDecoder:
+    def __init__(self, cfg, state_dict: Dict[str, torch.Tensor], device="cuda:0", precision: str = "fp16"):
+        if not torch.cuda.is_available():
+            raise RuntimeError("vits_b200.FlowDecoder needs a CUDA device (sm_100a); there is no CPU fallback")
+        self.lib = L.load_library()
+        self.device = torch.device(device)
+        if self.device.type != "cuda":
+            raise RuntimeError("vits_b200.FlowDecoder runs on CUDA devices only")
+        self.precision = precision
+        self._cfg_struct = L.make_config(cfg, precision)
+        self.inter_channels = self._cfg_struct.inter_channels
+        self.gin_channels = self._cfg_struct.gin_channels
+        h = C.c_void_p()
+        idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+        self.device = torch.device("cuda", idx)
+        rc = self.lib.vitsb_create(C.byref(self._cfg_struct), idx, C.byref(h))
+        if rc != 0:
+            raise L.VitsbError(rc, self.lib.vitsb_last_error(None).decode())
+        self._h = h
+        self._ws: Optional[torch.Tensor] = None
+        self.load_state_dict(state_dict)
+        self.total_upsample = self.lib.vitsb_total_upsample(self._h)
+        self.flop_per_frame = self.lib.vitsb_flop_per_frame(self._h)
+
+    # -- lifecycle -----------------------------------------------------------
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h is not None and getattr(self, "lib", None) is not None:
+            self.lib.vitsb_destroy(h)
+            self._h = None
+
+    def _check(self, rc: int):
+        if rc != 0:
+            raise L.VitsbError(rc, self.lib.vitsb_last_error(self._h).decode())
+
+    def load_state_dict(self, state_dict: Dict[str, torch.Tensor]):
+        """Accepts the reference checkpoint's `dec.*` / `flow.*` entries, folded
+        or weight-normed (utils.py:54-57, export.py:150-153); other keys are ignored."""
+        keep, descs = [], []
+        for k, v in _hot_items(state_dict):
+            t = v.detach().to("cpu")
+            if t.dtype not in _TORCH_DT:
+                t = t.float()
+            t = t.contiguous()
+            keep.append((k.encode(), t))
+        arr = (L.VitsbTensorDesc * len(keep))()
+        for i, (name, t) in enumerate(keep):
+            arr[i].name = name
+            arr[i].data = t.data_ptr()
+            arr[i].dtype = _TORCH_DT[t.dtype]
+            arr[i].ndim = t.dim()
+            for d in range(t.dim()):
+                arr[i].shape[d] = t.shape[d]
+        self._check(self.lib.vitsb_load_weights(self._h, arr, len(keep)))
+
+    # -- helpers -------------------------------------------------------------
+    def workspace_bytes(self, B: int, T: int) -> int:
+        return int(self.lib.vitsb_workspace_bytes(self._h, B, T))
+
+    def launches_per_call(self, B: int, T: int) -> int:
+        return int(self.lib.vitsb_launches_per_call(self._h, B, T))
+
+    def _workspace(self, B: int, T: int) -> torch.Tensor:
+        need = self.workspace_bytes(B, T)
+        if self._ws is None or self._ws.numel() < need:
+            self._ws = None
+            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+        return self._ws
+
+    def _prep(self, x: torch.Tensor, g: torch.Tensor, lengths):
+        if x.dim() != 3 or x.size(1) != self.inter_channels:
+            raise ValueError(f"expected [B,{self.inter_channels},T], got {tuple(x.shape)}")
+        B, _, T = x.shape
+        if g.dim() == 3:            # tolerate [B,gin,1]
+            g = g.squeeze(-1)
+        if tuple(g.shape) != (B, self.gin_channels):
+            raise ValueError(f"expected g [B,{self.gin_channels}], got {tuple(g.shape)}")
+        x = x.to(self.device, torch.float32).contiguous()
+        g = g.to(self.device, torch.float32).contiguous()
+        lens = None
+        if lengths is not None:
+            lst = [int(v) for v in (lengths.tolist() if torch.is_tensor(lengths) else lengths)]
+            if len(lst) != B:
+                raise ValueError("lengths must have B entries")
+            lens = (C.c_int32 * B)(*lst)
+        return x, g, lens, B, T
+
+    def _stream(self):
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    # -- reference-shaped API --------------------------------------------------
+    @torch.no_grad()
+    def flow_reverse(self, z_p: torch.Tensor, g: torch.Tensor, lengths: Optional[Sequence[int]] = None) -> torch.Tensor:
+        z_p, g, lens, B, T = self._prep(z_p, g, lengths)
+        with torch.cuda.device(self.device):
+            ws = self._workspace(B, T)
+            z = torch.empty_like(z_p)
+            self._check(self.lib.vitsb_flow_reverse(self._h, z_p.data_ptr(), g.data_ptr(), lens, B, T, z.data_ptr(),
+                                                    ws.data_ptr(), ws.numel(), self._stream()))
+        return z
+
+    @torch.no_grad()
+    def decode(self, z: torch.Tensor, g: torch.Tensor, lengths: Optional[Sequence[int]] = None,
+               ragged: bool = True) -> torch.Tensor:
+        z, g, lens, B, T = self._prep(z, g, lengths)
+        with torch.cuda.device(self.device):
+            ws = self._workspace(B, T)
+            wav = torch.empty(B, 1, T * self.total_upsample, dtype=torch.float32, device=self.device)
+            self._check(self.lib.vitsb_decode(self._h, z.data_ptr(), g.data_ptr(), lens, B, T, int(bool(ragged)),
+                                              wav.data_ptr(), ws.data_ptr(), ws.numel(), self._stream()))
+        return wav
+
+    @torch.no_grad()
+    def synthesize(self, z_p: torch.Tensor, g: torch.Tensor, lengths: Optional[Sequence[int]] = None,
+                   ragged: bool = True, return_z: bool = False, out: Optional[torch.Tensor] = None):
+        z_p, g, lens, B, T = self._prep(z_p, g, lengths)
+        with torch.cuda.device(self.device):
+            ws = self._workspace(B, T)
+            wav = out if out is not None else torch.empty(B, 1, T * self.total_upsample, dtype=torch.float32,
+                                                          device=self.device)
+            z = torch.empty_like(z_p) if return_z else None
+            self._check(self.lib.vitsb_synthesize(self._h, z_p.data_ptr(), g.data_ptr(), lens, B, T, int(bool(ragged)),
+                                                  z.data_ptr() if return_z else None, wav.data_ptr(),
+                                                  ws.data_ptr(), ws.numel(), self._stream()))
+        return (wav, z) if return_z else wav
+
+    @torch.no_grad()
+    def infer_p2(self, attn, m_p, s_p, g, noise) -> torch.Tensor:
+        """SynthesizerTrn.infer_p2 (models.py:568-575).  The length-regulation
+        matmuls stay in PyTorch (north star: they hand their tensors across)."""
+        dev = self.device
+        attn, m_p, s_p, noise = (t.to(dev, torch.float32) for t in (attn, m_p, s_p, noise))
+        m = torch.matmul(attn, m_p.transpose(1, 2)).transpose(1, 2)
+        s = torch.matmul(attn, s_p.transpose(1, 2)).transpose(1, 2)
+        z_p = m + noise * s
+        return self.synthesize(z_p, g)
+
+    @torch.no_grad()
+    def synthesize_host(self, z_p_host: torch.Tensor, g_host: torch.Tensor, lengths: Sequence[int],
+                        ragged: bool = True, out_host: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """End-to-end call with HOST buffers (pinned for async copies): H2D of the
+        latents, synthesis, D2H of the waveform, one stream synchronisation."""
+        with torch.cuda.device(self.device):
+            z_p = z_p_host.to(self.device, non_blocking=True)
+            g = g_host.to(self.device, non_blocking=True)
+            wav = self.synthesize(z_p, g, lengths, ragged)
+            if out_host is None:
+                out_host = torch.empty(wav.shape, dtype=torch.float32, pin_memory=True)
+            out_host.copy_(wav, non_blocking=True)
+            torch.cuda.current_stream(self.device).synchronize()
+        return out_host
