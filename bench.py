@@ -1,0 +1,315 @@
+#!/usr/bin/env python
+"""bench.py — generated audio-seconds per second of the flow-reverse + Generator hot path.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--precision fp16|bf16|fp32]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N ...
+
+A step is one `synthesize` pass (reverse flow + decoder)
+over one batch of synthetic latents.  Workload at N=1 is BASELINE.json
+configs[1]: 16 mixed-length utterances (1-10 s, masked/ragged), emotional-vits
+default config, random-init weights at fan-in scale, explicitly injected noise.
+For N>1 the global batch is 16*N utterances sharded by utterance (LPT by
+length), one process per GPU, no collective on the synthesis path (weak scaling).
+
+Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle port of
+the reference path on the host cores instead (see oracle/vits_oracle.py).
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+SR, HOP = 16000, 192
+FRAME_SEC = HOP / SR
+PER_GPU_BATCH = 16
+LEN_LO, LEN_HI = 84, 834          # 1-10 s in 12 ms frames
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--precision", default="fp16", choices=["fp16", "bf16", "fp32"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--profile-out", default=None, help="write the per-launch-family table to this file")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"tflops_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "tflops_burst": d["bf16_tflops"],
+                "hbm_gbs": d["hbm_gbs"], "source": "measured"}
+    return {"tflops_sustained": 1400.0, "tflops_burst": 1590.0, "hbm_gbs": 6650.0, "source": "fallback"}
+
+
+def global_lengths(n_gpus: int):
+    from oracle import fixtures as FX
+    return FX.make_lengths(PER_GPU_BATCH * n_gpus, LEN_LO, LEN_HI, seed=1234 if n_gpus == 1 else 1234 + n_gpus)
+
+
+def lpt_shard(lengths, n):
+    """Longest-processing-time-first assignment of utterances to ranks."""
+    bins = [[] for _ in range(n)]
+    load = [0] * n
+    for i in sorted(range(len(lengths)), key=lambda i: -lengths[i]):
+        r = min(range(n), key=lambda r: (load[r], len(bins[r])))
+        bins[r].append(i)
+        load[r] += lengths[i]
+    return bins
+
+
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._read, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if self.proc:
+            self.proc.terminate()
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ---------------------------------------------------------------------------
+# CPU leg: the oracle port of the reference's own PyTorch path, on host cores
+# ---------------------------------------------------------------------------
+def cpu_oracle_run(lengths, budget_s: float, min_utts: int = 1):
+    """Time per-utterance `flow.infer` + `dec` (models.py:573-574) of the oracle
+    port on as many utterances of the batch as fit in `budget_s`."""
+    import torch
+    from oracle import fixtures as FX
+    from oracle import vits_oracle as O
+    cfg = O.HotPathConfig()
+    sd = FX.make_state_dict(cfg, seed=1234)
+    torch.set_num_threads(os.cpu_count() or 1)
+    lat = FX.make_latents(cfg, lengths, seed=1234)
+    order = sorted(range(len(lengths)), key=lambda i: lengths[i])
+    done_frames, used, n = 0, 0.0, 0
+    with torch.no_grad():
+        O.generator(sd, O.flow_reverse(sd, lat["z_p"][:1, :, :32], lat["g"][:1], cfg), lat["g"][:1], cfg)  # warm-up
+        for i in order:
+            L = lengths[i]
+            t = time.perf_counter()
+            z = O.flow_reverse(sd, lat["z_p"][i:i + 1, :, :L], lat["g"][i:i + 1], cfg)
+            O.generator(sd, z, lat["g"][i:i + 1], cfg)
+            used += time.perf_counter() - t
+            done_frames += L
+            n += 1
+            if used >= budget_s and n >= min_utts:
+                break
+    return {"audio_s": done_frames * FRAME_SEC, "seconds": used, "utts": n, "frames": done_frames,
+            "threads": torch.get_num_threads()}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    lengths = global_lengths(1)
+    total_steps = args.steps + args.warmup
+    budget = max(1.0, min(15.0, 150.0 / max(1, total_steps)))
+    rec = []
+    for s in range(total_steps):
+        r = cpu_oracle_run(lengths, budget)
+        if s >= args.warmup:
+            rec.append(r)
+    audio = sum(r["audio_s"] for r in rec)
+    secs = sum(r["seconds"] for r in rec)
+    val = audio / secs
+    sample = f"{rec[0]['utts']} shortest utterance(s) of the 16-utterance C2 batch per step ({rec[0]['audio_s']:.1f} s audio), " \
+             f"per-utterance fp32 torch-CPU oracle port of flow.infer+dec"
+    out = {"impl": "reference", "metric": "audio-sec/sec (RTF^-1)", "value": val, "unit": "audio-s/s", "n_gpus": args.gpus,
+           "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(1, len(rec)),
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+           "config": {"workload": "C2: emotional-vits base config, 16 mixed-length utterances (1-10 s); bounded sample per step"},
+           "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": rec[0]["threads"], "kind": "port", "sample": sample},
+           "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+           "gpu_launches": 0}
+    print(json.dumps(out), flush=True)
+
+
+# ---------------------------------------------------------------------------
+# GPU leg
+# ---------------------------------------------------------------------------
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from oracle import fixtures as FX            # input/weight generator only (never on the timed path)
+    from oracle.vits_oracle import HotPathConfig
+    from vits_b200 import FlowDecoder
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the b200 arm has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    cfg = HotPathConfig()
+    sd = FX.make_state_dict(cfg, seed=1234)
+    eng = FlowDecoder(cfg, sd, device=dev, precision=args.precision)
+    all_len = global_lengths(world)
+    mine = lpt_shard(all_len, world)[rank]
+    lens = [all_len[i] for i in mine]
+    lat = FX.make_latents(cfg, lens, seed=1234 + rank)
+    B, T = len(lens), max(lens)
+    z_host = lat["z_p"].pin_memory()
+    g_host = lat["g"].pin_memory()
+    z_dev, g_dev = z_host.to(dev), g_host.to(dev)
+    wav_dev = torch.empty(B, 1, T * eng.total_upsample, dtype=torch.float32, device=dev)
+    wav_host = torch.empty(B, 1, T * eng.total_upsample, dtype=torch.float32).pin_memory()
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)       # > 126 MB L2
+    audio_s = sum(lens) * FRAME_SEC
+    frames = sum(lens)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def step_resident():
+        eng.synthesize(z_dev, g_dev, lens, ragged=True, out=wav_dev)
+
+    def step_e2e():
+        eng.synthesize_host(z_host, g_host, lens, ragged=True, out_host=wav_host)
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        evs = []
+        sampler = ClockSampler(local)
+        if rank == 0:
+            sampler.start()
+        for _ in range(steps):
+            flush.fill_(1)                                   # evict L2 between timed iterations (untimed)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            evs.append((a, b))
+        barrier()
+        clocks = sampler.stop() if rank == 0 else None
+        ms = sum(a.elapsed_time(b) for a, b in evs)
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return t.item(), clocks
+
+    ms_res, clocks = timed(step_resident, args.steps, max(3, args.warmup))
+    ms_e2e, _ = timed(step_e2e, args.steps, max(3, args.warmup))
+    tot = torch.tensor([audio_s, frames], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+    audio_all, frames_all = tot[0].item(), tot[1].item()
+
+    # per-launch-family device time (separate, untimed pass): roofline of the dominant kernel
+    eng.profile(True)
+    for _ in range(3):
+        step_resident()
+    table = eng.profile_table()
+    eng.profile(False)
+    conv_rows = [r for r in table if r[3] > 0]
+    conv_ms = sum(r[1] for r in conv_rows) / 3
+    all_ms = sum(r[1] for r in table) / 3
+    conv_flops = sum(r[3] for r in conv_rows) / 3
+    conv_launches = sum(r[2] for r in conv_rows) // 3
+    pk = peaks()
+    achieved_tf = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
+
+    if rank == 0:
+        value = audio_all * args.steps / (ms_res * 1e-3)
+        e2e = audio_all * args.steps / (ms_e2e * 1e-3)
+        traffic = None
+        tf = os.path.join(ROOT, "profiles", "traffic.json")
+        if os.path.exists(tf):
+            traffic = json.load(open(tf)).get("dram_bytes_per_launch")
+        out = {
+            "metric": "audio-sec/sec (RTF^-1)", "value": value, "unit": "audio-s/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_res / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": {"fp16": "f16", "bf16": "bf16", "fp32": "f32"}[args.precision] + " operands, f32 accumulate",
+            "data": "synthetic",
+            "config": {"workload": f"C2: emotional-vits base config, {PER_GPU_BATCH} mixed-length utterances per GPU "
+                                   f"(1-10 s, ragged/masked), flow-reverse + Generator",
+                       "global_batch": PER_GPU_BATCH * world, "valid_audio_s_per_step": audio_all,
+                       "parallelism": f"utterance-sharded replicas x{world} (LPT), no collective",
+                       "l2": "256 MiB flush between timed steps; per-step activation traffic >> 126 MB L2",
+                       "precision": args.precision},
+            "e2e": {"value": e2e, "unit": "audio-s/s", "h2d_bytes_per_step": int(z_host.numel() * 4 + g_host.numel() * 4 + 4 * B) * world,
+                    "d2h_bytes_per_step": int(wav_host.numel() * 4) * world, "ms_per_step": ms_e2e / args.steps},
+            "gpu_launches": eng.launches_per_call(B, T) * args.steps,
+            "clocks": clocks,
+            "roofline": {"bound": "tensor", "kernel": "conv_tc_kernel (tcgen05 implicit-GEMM conv1d, all layers)",
+                         "achieved": achieved_tf, "peak": pk["tflops_sustained"], "unit": "TFLOP/s",
+                         "frac": achieved_tf / pk["tflops_sustained"], "peak_source": pk["source"] + " (sustained cuBLAS bf16)",
+                         "traffic": traffic, "launches_per_step": conv_launches,
+                         "avg_launch_ms": conv_ms / max(1, conv_launches),
+                         "flop_per_launch": conv_flops / max(1, conv_launches),
+                         "kernel_share_of_step": conv_ms / all_ms if all_ms else None,
+                         "step_level_tflops": eng.flop_per_frame * frames_all * args.steps / (ms_res * 1e-3) / 1e12},
+        }
+        if args.profile_out:
+            with open(args.profile_out, "w") as f:
+                f.write(f"# per-launch-family device time, mean of 3 steps, B={B} T_max={T} precision={args.precision}\n")
+                f.write("family,ms_per_step,launches_per_step,algorithmic_gflop_per_step,tflops\n")
+                for name, ms, n, fl in sorted(table, key=lambda r: -r[1]):
+                    f.write(f"{name},{ms / 3:.4f},{n // 3},{fl / 3 / 1e9:.2f},{(fl / (ms * 1e-3) / 1e12) if ms > 0 else 0:.1f}\n")
+        if world == 1 and not args.no_cpu_baseline:
+            r = cpu_oracle_run(lens, 12.0)
+            out["cpu_baseline"] = {"value": r["audio_s"] / r["seconds"], "unit": "audio-s/s", "cores": r["threads"], "kind": "port",
+                                   "sample": f"{r['utts']} shortest utterance(s) of the same batch ({r['audio_s']:.1f} s audio, "
+                                             f"{r['seconds']:.1f} s CPU), per-utterance fp32 torch-CPU oracle port"}
+        print(json.dumps(out), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

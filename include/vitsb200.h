@@ -126,6 +126,14 @@ int vitsb_total_upsample(const vitsb_handle* h);
 int vitsb_launches_per_call(const vitsb_handle* h, int B, int T_max);
 /* Algorithmic FLOP per latent frame (2*Cin*Cout*k per output position). */
 double vitsb_flop_per_frame(const vitsb_handle* h);
+/* Per-launch device timing for bench.py / profiling: while enabled every kernel
+ * launch of a call is bracketed by CUDA events on the call's stream and the call
+ * ends with a stream synchronisation.  vitsb_profile_read returns one row per
+ * launch family (tag: 0 pack, 1 cond, 2 unpack, 3 conv_post, 10-14 flow
+ * pre/in/res/skip/post, 20 conv_pre, 30+s ups, 40+s ResBlock c1, 50+s ResBlock c2
+ * of stage s) with summed milliseconds, launch count and algorithmic FLOP. */
+int vitsb_profile(vitsb_handle* h, int enable);
+int vitsb_profile_read(const vitsb_handle* h, int32_t* tags, double* ms, int64_t* launches, double* flops, int cap);
 /* Library build info: "sm_100a;tcgen05;..." */
 const char* vitsb_build_info(void);
 

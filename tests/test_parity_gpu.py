@@ -1,0 +1,190 @@
+"""GPU parity tests: the CUDA path through the C ABI against (a) the committed
+golden vectors produced by the reference's own modules and (b) the CPU oracle
+on the same seeded inputs.
+
+Tolerances (BASELINE.json north_star): waveform max-abs <= 2e-3 and log-mel L1
+<= 1e-2 on the 16-bit tensor-core path, <= 1e-5 on the fp32-verification build.
+The 16-bit default is fp16 operands (the reference's production dtype,
+infer.py:66): bf16 operand rounding alone gives ~1.2e-2 max-abs on these
+unit-scale fixtures (measured with a pure-PyTorch emulation), so the
+bf16 variant is held to its own measured floor instead.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import fixtures as FX
+from oracle import vits_oracle as O
+from oracle.logmel import log_mel_l1
+
+pytestmark = pytest.mark.gpu
+
+TOL_WAV = {"fp32": 1e-5, "fp16": 2e-3, "bf16": 2.5e-2}
+TOL_Z = {"fp32": 2e-5, "fp16": 1e-2, "bf16": 8e-2}
+TOL_MEL = {"fp32": 1e-4, "fp16": 1e-2, "bf16": 1e-2}
+
+_engines = {}
+
+
+def engine(cfg, sd, prec, key="base"):
+    from vits_b200 import FlowDecoder
+    k = (key, prec)
+    if k not in _engines:
+        _engines[k] = FlowDecoder(cfg, sd, device="cuda:0", precision=prec)
+    return _engines[k]
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16"])
+def test_infer_p2_golden(base_cfg, base_sd, golden_dir, prec):
+    gold = np.load(os.path.join(golden_dir, "base_p2_T33.npz"))
+    inp = FX.make_p2_inputs(base_cfg, 33, seed=1234)
+    eng = engine(base_cfg, base_sd, prec)
+    o = eng.infer_p2(*(inp[k].cuda() for k in ("attn", "m_p", "s_p", "g", "noise"))).cpu()
+    assert o.shape == (1, 1, 33 * 192)
+    ref = torch.from_numpy(gold["o"])
+    assert (o - ref).abs().max().item() <= TOL_WAV[prec]
+    assert log_mel_l1(o[:, 0], ref[:, 0]) <= TOL_MEL[prec]
+    z = eng.flow_reverse(torch.from_numpy(gold["z_p"]).cuda(), inp["g"].cuda()).cpu()
+    assert (z - torch.from_numpy(gold["z"])).abs().max().item() <= TOL_Z[prec]
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16"])
+def test_tiny_lengths_golden(base_cfg, base_sd, golden_dir, prec):
+    gold = np.load(os.path.join(golden_dir, "base_tiny.npz"))
+    eng = engine(base_cfg, base_sd, prec)
+    for T in (1, 2, 5):
+        lat = FX.make_latents(base_cfg, [T], seed=100 + T)
+        wav, z = eng.synthesize(lat["z_p"].cuda(), lat["g"].cuda(), return_z=True)
+        assert (z.cpu().numpy() - gold[f"z_T{T}"]).__abs__().max() <= TOL_Z[prec]
+        assert (wav.cpu().numpy() - gold[f"o_T{T}"]).__abs__().max() <= TOL_WAV[prec]
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16"])
+def test_batch_golden_ragged_and_padded(base_cfg, base_sd, golden_dir, prec):
+    gold = np.load(os.path.join(golden_dir, "base_batch3.npz"))
+    lens = [int(x) for x in gold["lengths"]]
+    lat = FX.make_latents(base_cfg, lens, seed=77)
+    eng = engine(base_cfg, base_sd, prec)
+    zp, g = lat["z_p"].cuda(), lat["g"].cuda()
+    wav, z = eng.synthesize(zp, g, lens, ragged=True, return_z=True)
+    wav, z = wav.cpu().numpy(), z.cpu().numpy()
+    for b, L in enumerate(lens):      # row b == the reference's B=1 infer on its own length
+        assert np.abs(z[b:b + 1, :, :L] - gold[f"z_row{b}"]).max() <= TOL_Z[prec]
+        assert np.abs(wav[b:b + 1, :, :L * 192] - gold[f"o_row{b}"]).max() <= TOL_WAV[prec]
+        assert np.abs(wav[b, :, L * 192:]).sum() == 0 and np.abs(z[b, :, L:]).sum() == 0
+    # padded semantics == SynthesizerTrn.inference (masked flow, unmasked decoder)
+    wavp = eng.synthesize(zp, g, lens, ragged=False).cpu().numpy()
+    assert np.abs(wavp - gold["o_padded"]).max() <= TOL_WAV[prec]
+    zm = eng.flow_reverse(zp, g, lens).cpu().numpy()
+    assert np.abs(zm - gold["z_padded"]).max() <= TOL_Z[prec]
+    # standalone decode() of the golden z equals the golden waveform
+    od = eng.decode(torch.from_numpy(gold["z_padded"]).cuda(), g, lens, ragged=False).cpu().numpy()
+    assert np.abs(od - gold["o_padded"]).max() <= TOL_WAV[prec]
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16"])
+def test_adapt_shape_set_golden(adapt_cfg, golden_dir, prec):
+    gold = np.load(os.path.join(golden_dir, "adapt_T19.npz"))
+    sd = FX.make_state_dict(adapt_cfg, seed=4321)
+    eng = engine(adapt_cfg, sd, prec, key="adapt")
+    lat = FX.make_latents(adapt_cfg, [19], seed=5, noise_scale=0.382)
+    wav, z = eng.synthesize(lat["z_p"].cuda(), lat["g"].cuda(), return_z=True)
+    assert wav.shape == (1, 1, 19 * 96)
+    assert np.abs(z.cpu().numpy() - gold["z"]).max() <= TOL_Z[prec]
+    assert np.abs(wav.cpu().numpy() - gold["o"]).max() <= TOL_WAV[prec]
+
+
+def test_weight_norm_state_dict_packs_identically(base_cfg, base_sd):
+    from vits_b200 import FlowDecoder
+    sd_wn = FX.make_state_dict(base_cfg, seed=1234, weight_norm=True)
+    a = engine(base_cfg, base_sd, "fp32")
+    b = FlowDecoder(base_cfg, sd_wn, device="cuda:0", precision="fp32")
+    lat = FX.make_latents(base_cfg, [40], seed=9)
+    wa = a.synthesize(lat["z_p"].cuda(), lat["g"].cuda())
+    wb = b.synthesize(lat["z_p"].cuda(), lat["g"].cuda())
+    assert (wa - wb).abs().max().item() <= 1e-5
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16"])
+def test_c1_single_utterance_vs_oracle(base_cfg, base_sd, prec):
+    """BASELINE config 1: one ~5 s utterance (T=417)."""
+    lat = FX.make_latents(base_cfg, [417], seed=1234)
+    with torch.no_grad():
+        z_ref = O.flow_reverse(base_sd, lat["z_p"], lat["g"], base_cfg)
+        o_ref = O.generator(base_sd, z_ref, lat["g"], base_cfg)
+    eng = engine(base_cfg, base_sd, prec)
+    wav = eng.synthesize(lat["z_p"].cuda(), lat["g"].cuda()).cpu()
+    assert (wav - o_ref).abs().max().item() <= TOL_WAV[prec]
+    assert log_mel_l1(wav[:, 0], o_ref[:, 0]) <= TOL_MEL[prec]
+
+
+def test_c2_batch16_properties(base_cfg, base_sd):
+    """BASELINE config 2 at full size (16 mixed-length utterances, 1-10 s) through
+    size-independent properties: determinism, row independence (row b of the
+    ragged batch == the B=1 call on that row, bit for bit), zero beyond len,
+    fp16 within tolerance of the fp32-verification path."""
+    lens = FX.make_lengths(16, 84, 834, seed=1234)
+    lat = FX.make_latents(base_cfg, lens, seed=1234)
+    zp, g = lat["z_p"].cuda(), lat["g"].cuda()
+    e16, e32 = engine(base_cfg, base_sd, "fp16"), engine(base_cfg, base_sd, "fp32")
+    w1 = e16.synthesize(zp, g, lens, ragged=True)
+    w2 = e16.synthesize(zp, g, lens, ragged=True)
+    assert torch.equal(w1, w2)
+    for b in (0, 7, 15):
+        L = lens[b]
+        wb = e16.synthesize(zp[b:b + 1, :, :L].contiguous(), g[b:b + 1])
+        assert torch.equal(wb[0, 0], w1[b, 0, :L * 192])
+        assert w1[b, 0, L * 192:].abs().sum().item() == 0
+    w32 = e32.synthesize(zp, g, lens, ragged=True)
+    assert (w1 - w32).abs().max().item() <= 2e-3
+    assert not torch.isnan(w1).any()
+    # spot-check one row against the CPU oracle
+    b = int(np.argmin(lens))
+    with torch.no_grad():
+        zr = O.flow_reverse(base_sd, lat["z_p"][b:b + 1, :, :lens[b]], lat["g"][b:b + 1], base_cfg)
+        orr = O.generator(base_sd, zr, lat["g"][b:b + 1], base_cfg)
+    assert (w32[b:b + 1, :, :lens[b] * 192].cpu() - orr).abs().max().item() <= 1e-5
+
+
+def test_c3_long_form(base_cfg, base_sd):
+    """BASELINE config 3: 60 s single utterance (T=5000)."""
+    lat = FX.make_latents(base_cfg, [5000], seed=3)
+    zp, g = lat["z_p"].cuda(), lat["g"].cuda()
+    w16 = engine(base_cfg, base_sd, "fp16").synthesize(zp, g)
+    w32 = engine(base_cfg, base_sd, "fp32").synthesize(zp, g)
+    assert w16.shape == (1, 1, 960000)
+    assert (w16 - w32).abs().max().item() <= 2e-3
+    # time-locality: the first 2 s do not depend on what follows them (receptive field << 1 s)
+    ws = engine(base_cfg, base_sd, "fp32").synthesize(zp[:, :, :400].contiguous(), g)
+    assert (ws[0, 0, :32000] - w32[0, 0, :32000]).abs().max().item() <= 1e-5
+
+
+def test_c5_distinct_speakers_per_row(base_cfg, base_sd):
+    """BASELINE config 5: every row has its own g; rows must not leak conditioning."""
+    lens = [50, 50, 50, 50]
+    lat = FX.make_latents(base_cfg, lens, seed=11)
+    zp = lat["z_p"][:1].repeat(4, 1, 1).cuda()          # same latent, 4 different speakers
+    g = lat["g"].cuda()
+    e = engine(base_cfg, base_sd, "fp16")
+    w = e.synthesize(zp, g, lens)
+    for b in range(4):
+        wb = e.synthesize(zp[b:b + 1], g[b:b + 1])
+        assert torch.equal(wb[0], w[b])
+    assert (w[0] - w[1]).abs().max().item() > 1e-2
+
+
+def test_error_paths(base_cfg, base_sd):
+    from vits_b200 import lib as L
+    e = engine(base_cfg, base_sd, "fp16")
+    lat = FX.make_latents(base_cfg, [10], seed=1)
+    with pytest.raises(ValueError):
+        e.synthesize(lat["z_p"][:, :100].cuda(), lat["g"].cuda())
+    with pytest.raises(L.VitsbError):
+        e.synthesize(lat["z_p"].cuda(), lat["g"].cuda(), [11])       # len > T_max
+    bad = dict(base_sd)
+    bad.pop("dec.conv_post.weight")
+    from vits_b200 import FlowDecoder
+    with pytest.raises(L.VitsbError):
+        FlowDecoder(base_cfg, bad, device="cuda:0")

@@ -80,6 +80,27 @@ int vitsb_launches_per_call(const vitsb_handle* h, int B, int T_max) {
 
 double vitsb_flop_per_frame(const vitsb_handle* h) { return h ? h->eng.flop_per_frame : 0.0; }
 
+int vitsb_profile(vitsb_handle* h, int enable) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  h->eng.profile = enable != 0;
+  h->eng.prof.clear();
+  return VITSB_OK;
+}
+
+int vitsb_profile_read(const vitsb_handle* h, int32_t* tags, double* ms, int64_t* launches, double* flops, int cap) {
+  if (!h) return 0;
+  int n = 0;
+  for (const auto& kv : h->eng.prof) {
+    if (n >= cap) break;
+    if (tags) tags[n] = kv.first;
+    if (ms) ms[n] = kv.second.ms;
+    if (launches) launches[n] = kv.second.launches;
+    if (flops) flops[n] = kv.second.flops;
+    ++n;
+  }
+  return n;
+}
+
 const char* vitsb_build_info(void) {
   return "vitsb200;arch=sm_100a;tensor=tcgen05.mma.kind::f16+TMEM;copy=TMA(cp.async.bulk.tensor);verify=fp32-ffma;cpu_fallback=none";
 }

@@ -66,6 +66,11 @@ struct Engine {
   float* d_condB = nullptr;
   float* d_post = nullptr;
 
+  // optional per-launch timing (cudaEvent pairs around every launch, read back after a sync)
+  bool profile = false;
+  struct ProfRow { double ms = 0; long long launches = 0; double flops = 0; };
+  std::map<int, ProfRow> prof;     // keyed by launch tag (see engine_run.cu)
+
   ~Engine();
   int fail(int code, const std::string& msg) { err = msg; return code; }
 

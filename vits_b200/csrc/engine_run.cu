@@ -47,11 +47,30 @@ WsLayout Engine::layout(int B, int T) const {
 
 namespace {
 
+// launch tags for the profile table
+enum Tag { T_PACK = 0, T_COND = 1, T_UNPACK = 2, T_POST = 3, T_FLOW_PRE = 10, T_FLOW_IN = 11, T_FLOW_RES = 12,
+           T_FLOW_SKIP = 13, T_FLOW_POST = 14, T_CONV_PRE = 20, T_UPS = 30, T_RB_C1 = 40, T_RB_C2 = 50 };
+
+struct ProfEv { int tag; double flops; cudaEvent_t a, b; };
+
 struct Ctx {
   Engine* e;
   cudaStream_t stream;
   bool dry;
   int launches = 0;
+  std::vector<ProfEv> evs;
+  double valid_frames = 0;   // sum_b min(len[b], T) (host-side, for algorithmic FLOP attribution)
+  void ev_begin(int tag, double flops) {
+    if (dry || !e->profile) return;
+    ProfEv p{tag, flops, nullptr, nullptr};
+    cudaEventCreate(&p.a); cudaEventCreate(&p.b);
+    cudaEventRecord(p.a, stream);
+    evs.push_back(p);
+  }
+  void ev_end() {
+    if (dry || !e->profile) return;
+    cudaEventRecord(evs.back().b, stream);
+  }
   cudaError_t err = cudaSuccess;
   int B, T;
   const int* len_flow;   // device lens used for masking (nullptr = all rows live)
@@ -60,9 +79,10 @@ struct Ctx {
 
   bool ok() const { return err == cudaSuccess; }
 
-  void conv(const PackedConv& p, const void* in, int L, int len_mul, const int* len, const Epilogue& ep_in) {
+  void conv(int tag, const PackedConv& p, const void* in, int L, int len_mul, const int* len, const Epilogue& ep_in) {
     ++launches;
     if (dry || !ok()) return;
+    ev_begin(tag, p.flop_per_pos * (len ? valid_frames : (double)B * T) * len_mul);
     ConvArgs a{};
     a.in = in; a.in_ld = p.Cin; a.in_bstride = (long long)L * p.Cin; a.Cin = p.Cin;
     a.w = reinterpret_cast<const char*>(e->d_w) + p.w_off * op_bytes(e->op);
@@ -73,6 +93,7 @@ struct Ctx {
     if (p.cond_off >= 0) { a.epi.bias = cond + p.cond_off; a.epi.bias_bstride = e->Ncond; }
     else { a.epi.bias = e->d_bias + p.bias_off; a.epi.bias_bstride = 0; }
     err = e->op == OP_F32 ? launch_conv_f32(a, stream) : launch_conv_tc(a, e->op, stream);
+    ev_end();
   }
 };
 
@@ -118,7 +139,11 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
   cx.len_flow = len ? d_len : nullptr;
   cx.len_dec = (len && ragged) ? d_len : nullptr;
 
-#define AUX_LAUNCH(expr) do { ++cx.launches; if (!dry && cx.ok()) cx.err = (expr); } while (0)
+#define AUX_LAUNCH(tag, expr) do { ++cx.launches; if (!dry && cx.ok()) { cx.ev_begin(tag, 0.0); cx.err = (expr); cx.ev_end(); } } while (0)
+  if (!dry) {
+    if (len) for (int b = 0; b < B; ++b) cx.valid_frames += len[b];
+    else cx.valid_frames = (double)B * T;
+  }
 
   if (!dry) {
     cudaError_t e0 = cudaSetDevice(device);
@@ -126,45 +151,45 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
     if (len) cx.err = cudaMemcpyAsync(d_len, len, sizeof(int) * B, cudaMemcpyHostToDevice, stream);
   }
   // seam: channel-major fp32 -> time-major (masked beyond len)
-  AUX_LAUNCH(launch_pack_time_major(z_in, B, IC, T, cx.len_flow, (what & RUN_FLOW) ? F(W.zf) : nullptr, P(W.zop), op, stream));
+  AUX_LAUNCH(T_PACK, launch_pack_time_major(z_in, B, IC, T, cx.len_flow, (what & RUN_FLOW) ? F(W.zf) : nullptr, P(W.zop), op, stream));
   // all conditioning Linears of the call: flow cond_layers (modules.py:161) + ResBlock conds (modules.py:254)
-  AUX_LAUNCH(launch_cond_gemv(d_condW, d_condB, g, B, Ncond, cfg.gin_channels, F(W.cond), stream));
+  AUX_LAUNCH(T_COND, launch_cond_gemv(d_condW, d_condB, g, B, Ncond, cfg.gin_channels, F(W.cond), stream));
 
   if (what & RUN_FLOW) {
     for (const Coupling& cp : couplings) {
       // h = pre(x0)                                                   modules.py:364
       { Epilogue ep = epi_base(); set_out_f32(ep, F(W.hf), H, T); set_out_op(ep, P(W.hop), H, T, 1.f);
-        cx.conv(cp.pre, P(W.zop), T, 1, cx.len_flow, ep); }
+        cx.conv(T_FLOW_PRE, cp.pre, P(W.zop), T, 1, cx.len_flow, ep); }
       const int nl = (int)cp.in_layers.size();
       for (int l = 0; l < nl; ++l) {
         // acts = tanh(a)*sigmoid(b), a,b = in_layer(h) + cond slice     modules.py:163-172
         { Epilogue ep = epi_base(); set_out_op(ep, P(W.acts), H, T, 1.f);
-          cx.conv(cp.in_layers[l], P(W.hop), T, 1, cx.len_flow, ep); }
+          cx.conv(T_FLOW_IN, cp.in_layers[l], P(W.hop), T, 1, cx.len_flow, ep); }
         if (l < nl - 1) {
           // h += res_skip[:H]                                           modules.py:176-178
           Epilogue ep = epi_base(); set_res(ep, F(W.hf), H, T); set_out_f32(ep, F(W.hf), H, T); set_out_op(ep, P(W.hop), H, T, 1.f);
-          cx.conv(cp.res[l], P(W.acts), T, 1, cx.len_flow, ep);
+          cx.conv(T_FLOW_RES, cp.res[l], P(W.acts), T, 1, cx.len_flow, ep);
         }
         // output += res_skip[H:] (all of it on the last layer)          modules.py:179-181
         { Epilogue ep = epi_base();
           if (l > 0) set_accum(ep, F(W.skipf), H, T);
           if (l < nl - 1) set_out_f32(ep, F(W.skipf), H, T); else set_out_op(ep, P(W.skipop), H, T, 1.f);
-          cx.conv(cp.skip[l], P(W.acts), T, 1, cx.len_flow, ep); }
+          cx.conv(T_FLOW_SKIP, cp.skip[l], P(W.acts), T, 1, cx.len_flow, ep); }
       }
       // x1 = x1 - post(out)   (mean-only, logs == 0)                    modules.py:366-372
       { Epilogue ep = epi_base(); ep.alpha = -1.f; ep.beta = 1.f;
         ep.res = F(W.zf) + cp.coff; ep.res_ld = IC; ep.res_bstride = (long long)T * IC;
         ep.out_f32 = F(W.zf) + cp.coff; ep.out_f32_ld = IC; ep.out_f32_bstride = (long long)T * IC;
         ep.out_op = reinterpret_cast<char*>(P(W.zop)) + (size_t)cp.coff * ob; ep.out_op_ld = IC; ep.out_op_bstride = (long long)T * IC;
-        cx.conv(cp.post, P(W.skipop), T, 1, cx.len_flow, ep); }
+        cx.conv(T_FLOW_POST, cp.post, P(W.skipop), T, 1, cx.len_flow, ep); }
     }
-    if (z_out) AUX_LAUNCH(launch_unpack_channel_major(F(W.zf), B, IC, T, z_out, stream));
+    if (z_out) AUX_LAUNCH(T_UNPACK, launch_unpack_channel_major(F(W.zf), B, IC, T, z_out, stream));
   }
 
   if (what & RUN_DEC) {
     // x = conv_pre(z); the next op's leaky_relu(0.1) is folded into the operand copy   models.py:307-309
     { Epilogue ep = epi_base(); set_out_op(ep, P(W.nxt_op), conv_pre.N, T, 0.1f);
-      cx.conv(conv_pre, P(W.zop), T, 1, cx.len_dec, ep); }
+      cx.conv(T_CONV_PRE, conv_pre, P(W.zop), T, 1, cx.len_dec, ep); }
     int L = T;              // rows per batch item at the current rate
     int mul = 1;            // valid rows = len * mul
     const int ns = (int)stages.size();
@@ -174,7 +199,7 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
       // x = ups[i](leaky_relu(x)): phase-stacked conv, output row t holds out[u*t .. u*t+u-1]   models.py:310
       { Epilogue ep = epi_base();
         set_out_f32(ep, F(W.xin_f), st.ups.N, L); set_out_op(ep, P(W.xin_op), st.ups.N, L, 0.1f);
-        cx.conv(st.ups, P(W.nxt_op), L, mul, cx.len_dec, ep); }
+        cx.conv(T_UPS + s, st.ups, P(W.nxt_op), L, mul, cx.len_dec, ep); }
       L = Lo; mul *= st.u;
       const int nk = (int)st.rb.size();
       const float inv = 1.0f / nk;
@@ -187,7 +212,7 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
           const float* xin_f = d == 0 ? F(W.xin_f) : F(W.xb_f);
           // xt = tanh(.)*sigmoid(.) of c1(leaky_relu(x)) + cond           modules.py:252-257
           { Epilogue ep = epi_base(); set_out_op(ep, P(W.g_op), C / 2, L, 1.f);
-            cx.conv(it.c1, xin_op, L, mul, cx.len_dec, ep); }
+            cx.conv(T_RB_C1 + s, it.c1, xin_op, L, mul, cx.len_dec, ep); }
           // x = c2(xt) + x                                                modules.py:258-259
           Epilogue ep = epi_base();
           set_res(ep, xin_f, C, L);
@@ -200,15 +225,26 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
             if (j < nk - 1) set_out_f32(ep, F(W.acc_f), C, L);
             else set_out_op(ep, P(W.nxt_op), C, L, next_slope);
           }
-          cx.conv(it.c2, P(W.g_op), L, mul, cx.len_dec, ep);
+          cx.conv(T_RB_C2 + s, it.c2, P(W.g_op), L, mul, cx.len_dec, ep);
         }
       }
     }
     // tanh(conv_post(leaky_relu(x, 0.01)))                                 models.py:315-317
-    AUX_LAUNCH(launch_conv_post(P(W.nxt_op), op, B, L, post_C, post_k, d_post, cx.len_dec, mul, wav, stream));
+    AUX_LAUNCH(T_POST, launch_conv_post(P(W.nxt_op), op, B, L, post_C, post_k, d_post, cx.len_dec, mul, wav, stream));
   }
 #undef AUX_LAUNCH
   if (launches) *launches = cx.launches;
+  if (!cx.evs.empty()) {
+    cudaStreamSynchronize(stream);
+    for (ProfEv& p : cx.evs) {
+      float ms = 0.f;
+      if (p.b && cudaEventElapsedTime(&ms, p.a, p.b) == cudaSuccess) {
+        ProfRow& r = prof[p.tag];
+        r.ms += ms; r.launches += 1; r.flops += p.flops;
+      }
+      cudaEventDestroy(p.a); if (p.b) cudaEventDestroy(p.b);
+    }
+  }
   if (!cx.ok()) return fail(VITSB_ERR_CUDA, std::string("launch failed: ") + cudaGetErrorString(cx.err));
   return VITSB_OK;
 }

@@ -93,6 +93,26 @@ class FlowDecoder:
     def launches_per_call(self, B: int, T: int) -> int:
         return int(self.lib.vitsb_launches_per_call(self._h, B, T))
 
+    TAG_NAMES = {0: "pack", 1: "cond_gemv", 2: "unpack", 3: "conv_post", 10: "flow.pre", 11: "flow.in_layers",
+                 12: "flow.res", 13: "flow.skip", 14: "flow.post", 20: "conv_pre"}
+
+    def profile(self, enable: bool):
+        self._check(self.lib.vitsb_profile(self._h, int(enable)))
+
+    def profile_table(self):
+        """[(name, ms, launches, algorithmic flop)] accumulated since profile(True)."""
+        cap = 64
+        tags, ms = (C.c_int32 * cap)(), (C.c_double * cap)()
+        n_l, fl = (C.c_int64 * cap)(), (C.c_double * cap)()
+        n = self.lib.vitsb_profile_read(self._h, tags, ms, n_l, fl, cap)
+        rows = []
+        for i in range(n):
+            t = tags[i]
+            name = self.TAG_NAMES.get(t) or (f"ups.{t - 30}" if 30 <= t < 40 else
+                                             f"resblock.c1.s{t - 40}" if 40 <= t < 50 else f"resblock.c2.s{t - 50}")
+            rows.append((name, ms[i], int(n_l[i]), fl[i]))
+        return rows
+
     def _workspace(self, B: int, T: int) -> torch.Tensor:
         need = self.workspace_bytes(B, T)
         if self._ws is None or self._ws.numel() < need:

@@ -49,6 +49,9 @@ SYMBOLS = {
     "vitsb_total_upsample": (C.c_int, [_P]),
     "vitsb_launches_per_call": (C.c_int, [_P, C.c_int, C.c_int]),
     "vitsb_flop_per_frame": (C.c_double, [_P]),
+    "vitsb_profile": (C.c_int, [_P, C.c_int]),
+    "vitsb_profile_read": (C.c_int, [_P, C.POINTER(C.c_int32), C.POINTER(C.c_double), C.POINTER(C.c_int64),
+                                     C.POINTER(C.c_double), C.c_int]),
     "vitsb_build_info": (C.c_char_p, []),
     "vitsb_selftest_conv": (C.c_int, [C.c_int] * 9 + [C.c_uint32, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
 }
@@ -83,7 +86,7 @@ class VitsbError(RuntimeError):
 
 def make_config(cfg, precision: str) -> VitsbConfig:
     """cfg: any object with the hot-path attribute names of configs/base.json
-    (e.g. the reference's HParams `hps.model`, or oracle HotPathConfig)."""
+    (e.g. the reference HParams `hps.model`, a dict, or a dataclass)."""
     def get(name, default=None):
         if isinstance(cfg, dict):
             return cfg.get(name, default)
