@@ -10,7 +10,7 @@ namespace vitsb {
 // ---------------------------------------------------------------------------
 template <typename OpT>
 __global__ void pack_time_major_kernel(const float* __restrict__ src, int C, int T, const int* __restrict__ len,
-                                       float* __restrict__ dst_f32, OpT* __restrict__ dst_op) {
+                                       float* __restrict__ dst_f32, OpT* __restrict__ dst_op, int split) {
   __shared__ float tile[32][33];
   const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
   const int valid = len ? len[b] : T;
@@ -26,17 +26,26 @@ __global__ void pack_time_major_kernel(const float* __restrict__ src, int C, int
       float v = tile[threadIdx.x][i];
       long long o = ((long long)b * T + t) * C + c;
       if (dst_f32) dst_f32[o] = v;
-      if (dst_op) dst_op[o] = to_op<OpT>(v);
+      if (dst_op) {
+        if (split) {                       // row = [hi(C) | lo(C)], see common.h
+          long long os = ((long long)b * T + t) * (2 * C) + c;
+          OpT hi = to_op<OpT>(v);
+          dst_op[os] = hi;
+          dst_op[os + C] = to_op<OpT>(v - from_op<OpT>(hi));
+        } else {
+          dst_op[o] = to_op<OpT>(v);
+        }
+      }
     }
   }
 }
 
 cudaError_t launch_pack_time_major(const float* src, int B, int C, int T, const int* len,
-                                   float* dst_f32, void* dst_op, int op, cudaStream_t stream) {
+                                   float* dst_f32, void* dst_op, int op, int split, cudaStream_t stream) {
   dim3 grid(ceil_div(T, 32), ceil_div(C, 32), B), block(32, 8);
-  if (op == OP_F16) pack_time_major_kernel<__half><<<grid, block, 0, stream>>>(src, C, T, len, dst_f32, (__half*)dst_op);
-  else if (op == OP_BF16) pack_time_major_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(src, C, T, len, dst_f32, (__nv_bfloat16*)dst_op);
-  else pack_time_major_kernel<float><<<grid, block, 0, stream>>>(src, C, T, len, dst_f32, (float*)dst_op);
+  if (op == OP_F16) pack_time_major_kernel<__half><<<grid, block, 0, stream>>>(src, C, T, len, dst_f32, (__half*)dst_op, split);
+  else if (op == OP_BF16) pack_time_major_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(src, C, T, len, dst_f32, (__nv_bfloat16*)dst_op, split);
+  else pack_time_major_kernel<float><<<grid, block, 0, stream>>>(src, C, T, len, dst_f32, (float*)dst_op, 0);
   return cudaGetLastError();
 }
 
@@ -104,14 +113,14 @@ cudaError_t launch_cond_gemv(const float* W, const float* bias, const float* g, 
 }
 
 // ---------------------------------------------------------------------------
-// conv_post (Conv1d C->1, k taps, no bias) + tanh.  HBM-bound: reads C op
-// values and writes one fp32 sample per output position.  The input already
-// carries the preceding leaky-relu (slope 0.01), fused by the last MRF epilogue.
+// leaky_relu(slope) + conv_post (Conv1d C->1, k taps, no bias) + tanh.  HBM-bound:
+// reads C fp32 values (the MRF accumulator of the last stage, never rounded to
+// 16 bits: conv_post sits right before the output and its input rounding would
+// be the single largest error term) and writes one fp32 sample per position.
 // ---------------------------------------------------------------------------
 constexpr int kPostTile = 256;
-template <typename OpT>
 __global__ void __launch_bounds__(kPostTile)
-conv_post_kernel(const OpT* __restrict__ in, int L, int C, int k, const float* __restrict__ w,
+conv_post_kernel(const float* __restrict__ in, int L, int C, int k, float slope, const float* __restrict__ w,
                  const int* __restrict__ len, int len_mul, float* __restrict__ wav) {
   extern __shared__ float sm[];
   const int pad = (k - 1) / 2;
@@ -126,10 +135,11 @@ conv_post_kernel(const OpT* __restrict__ in, int L, int C, int k, const float* _
     if (t < L) wav[(long long)b * L + t] = 0.f;
     return;
   }
-  const OpT* src = in + (long long)b * L * C;
+  const float* src = in + (long long)b * L * C;
   for (int i = threadIdx.x; i < rows * C; i += kPostTile) {
     int r = i / C, c = i - r * C, t = t0 + r - pad;
-    tile[r * ldc + c] = (t >= 0 && t < L) ? from_op<OpT>(src[(long long)t * C + c]) : 0.f;
+    float x = (t >= 0 && t < L) ? src[(long long)t * C + c] : 0.f;
+    tile[r * ldc + c] = x >= 0.f ? x : slope * x;
   }
   for (int i = threadIdx.x; i < k * C; i += kPostTile) ws[i] = w[i];
   __syncthreads();
@@ -145,13 +155,11 @@ conv_post_kernel(const OpT* __restrict__ in, int L, int C, int k, const float* _
   wav[(long long)b * L + t] = t < valid ? tanhf(acc) : 0.f;
 }
 
-cudaError_t launch_conv_post(const void* in, int op, int B, int L, int C, int k, const float* w,
+cudaError_t launch_conv_post(const float* in, int B, int L, int C, int k, float slope, const float* w,
                              const int* len, int len_mul, float* wav, cudaStream_t stream) {
   dim3 grid(ceil_div(L, kPostTile), B);
   size_t smem = (size_t)((kPostTile + k - 1) * (C + 1) + k * C) * sizeof(float);
-  if (op == OP_F16) conv_post_kernel<__half><<<grid, kPostTile, smem, stream>>>((const __half*)in, L, C, k, w, len, len_mul, wav);
-  else if (op == OP_BF16) conv_post_kernel<__nv_bfloat16><<<grid, kPostTile, smem, stream>>>((const __nv_bfloat16*)in, L, C, k, w, len, len_mul, wav);
-  else conv_post_kernel<float><<<grid, kPostTile, smem, stream>>>((const float*)in, L, C, k, w, len, len_mul, wav);
+  conv_post_kernel<<<grid, kPostTile, smem, stream>>>(in, L, C, k, slope, w, len, len_mul, wav);
   return cudaGetLastError();
 }
 

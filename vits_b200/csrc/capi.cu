@@ -148,7 +148,7 @@ int vitsb_selftest_conv(int device, int precision, int Cin, int N, int k, int di
   cudaMemcpy(d_len, len.data(), B * 4, cudaMemcpyHostToDevice);
   cudaMemset(d_o1, 0xff, n_out * 4); cudaMemset(d_o2, 0xff, n_out * 4);
   ConvArgs a{};
-  a.in_ld = Cin; a.in_bstride = (long long)L * Cin; a.Cin = Cin; a.N = N; a.NT = NT; a.k = k; a.dil = dil; a.pad = (k - 1) / 2 * dil;
+  a.in_ld = Cin; a.in_cols = Cin; a.in_bstride = (long long)L * Cin; a.Cin = Cin; a.N = N; a.NT = NT; a.k = k; a.dil = dil; a.pad = (k - 1) / 2 * dil;
   a.L = L; a.B = B; a.len = d_len; a.len_mul = 1;
   a.epi.bias = d_bias; a.epi.bias_bstride = N; a.epi.alpha = gate ? 1.f : 0.5f; a.epi.beta = 0.75f; a.epi.out_slope = 0.1f;
   a.epi.gate = gate;

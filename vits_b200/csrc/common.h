@@ -22,6 +22,13 @@ constexpr int kHaloRows = 32;    // >= largest one-sided receptive field of any 
 //   gate: v = tanh(v_a) * sigmoid(v_b), (a, b) = packed columns (c, c + NT/2) of one N tile
 //   rows t >= len[b]*len_mul are stored as zero (masked / ragged semantics)
 //   out_f32[b,t,n] = v ; out_op[b,t,n] = op_t( v >= 0 ? v : out_slope * v )
+//
+// Split precision (16-bit paths only).  The convs whose operand rounding dominates
+// the waveform error (the whole flow, conv_pre, the upsamplers)
+// run as x*W ~= xh*Wh + xl*Wh + xh*Wl with x = xh + xl, W = Wh + Wl in the operand
+// type: the activation row is stored as [hi(C) | lo(C)], the packed weights per tap
+// as [Wh | Wh | Wl], and the K loop reads activation columns modulo 2C, i.e.
+// (hi, lo, hi) against (Wh, Wh, Wl).
 struct Epilogue {
   const float* bias;     long long bias_bstride;      // per-batch stride (0 = shared)
   float alpha, beta;
@@ -31,13 +38,15 @@ struct Epilogue {
   void*  out_op;         int out_op_ld;  long long out_op_bstride;
   float out_slope;       // leaky-relu slope folded into the operand copy (1.0 = identity)
   int gate;              // 1: gated (tanh*sigmoid) epilogue, output has N/2 channels
+  int out_op_split;      // >0: also store lo = op_t(x - float(hi)) at column offset +out_op_split (2-term split operand)
 };
 
 struct ConvArgs {
   const void* in;        // op_t [B][L][in_ld]
   long long in_bstride;  // elements
   int in_ld;             // row pitch in elements
-  int Cin;               // channels consumed per tap (multiple of 16)
+  int Cin;               // K per tap (multiple of 16); 3*in_cols/2 for split-precision convs
+  int in_cols;           // physical columns of an input row; K block kc reads columns (kc*BK) % in_cols
   const void* w;         // op_t [N][k*Cin]  K-major
   int N;                 // GEMM N (packed output columns)
   int NT;                // N tile (<=256, multiple of 16); gate pairs live inside one tile

@@ -62,7 +62,7 @@ conv_f32_kernel(const ConvArgs a) {
     const bool row_ok = (trow >= 0) && (trow < a.L);
     for (int c0 = 0; c0 < a.Cin; c0 += FT_K) {
       float4 av = make_float4(0.f, 0.f, 0.f, 0.f), bv = av;
-      if (row_ok) av = *reinterpret_cast<const float4*>(in + (long long)trow * a.in_ld + c0 + lk);
+      if (row_ok) av = *reinterpret_cast<const float4*>(in + (long long)trow * a.in_ld + (c0 % a.in_cols) + lk);
       if (my_wrow >= 0) bv = *reinterpret_cast<const float4*>(w + (long long)my_wrow * Ktot + j * a.Cin + c0 + lk);
       __syncthreads();
       As[lk + 0][lr] = av.x; As[lk + 1][lr] = av.y; As[lk + 2][lr] = av.z; As[lk + 3][lr] = av.w;

@@ -43,27 +43,36 @@ template <> struct Pack16<__half> {
     __half2 h = __floats2half2_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&h);
   }
+  __device__ static __forceinline__ float2 unpack2(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
 };
 template <> struct Pack16<__nv_bfloat16> {
   __device__ static __forceinline__ uint32_t pack2(float a, float b) {
     __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
     return *reinterpret_cast<uint32_t*>(&h);
   }
+  __device__ static __forceinline__ float2 unpack2(uint32_t u) { return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u)); }
 };
 
 template <typename OpT>
-__device__ __forceinline__ void store_op16(OpT* dst, const float (&v)[16], float slope) {
-  uint32_t p[8];
+__device__ __forceinline__ void store_op16(OpT* dst, const float (&v)[16], float slope, int split) {
+  uint32_t p[8], q[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
     float x = v[2 * i], y = v[2 * i + 1];
     x = x >= 0.f ? x : slope * x;
     y = y >= 0.f ? y : slope * y;
     p[i] = Pack16<OpT>::pack2(x, y);
+    const float2 hi = Pack16<OpT>::unpack2(p[i]);
+    q[i] = Pack16<OpT>::pack2(x - hi.x, y - hi.y);
   }
   uint4* d = reinterpret_cast<uint4*>(dst);
   d[0] = make_uint4(p[0], p[1], p[2], p[3]);
   d[1] = make_uint4(p[4], p[5], p[6], p[7]);
+  if (split > 0) {
+    uint4* l = reinterpret_cast<uint4*>(dst + split);
+    l[0] = make_uint4(q[0], q[1], q[2], q[3]);
+    l[1] = make_uint4(q[4], q[5], q[6], q[7]);
+  }
 }
 
 __device__ __forceinline__ void load16(const float* src, float (&v)[16]) {
@@ -81,7 +90,7 @@ __device__ __forceinline__ void store16(float* dst, const float (&v)[16]) {
 }
 
 template <typename OpT>
-__global__ void __launch_bounds__(kTcThreads, 1)
+__global__ void __launch_bounds__(kTcThreads)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const ConvArgs a, const TcGeom g) {
   const int b = blockIdx.z;
@@ -127,7 +136,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         ptx::mbar_wait(empty_bar(s), ph ^ 1u);
         ptx::mbar_expect_tx(full_bar(s), tx_bytes);
         const int j = it / g.kchunks, kc = it - j * g.kchunks;
-        ptx::tma_load_3d(sA + s * g.a_bytes, &tmA, full_bar(s), kc * g.BK, t0 + j * a.dil - a.pad, b);
+        ptx::tma_load_3d(sA + s * g.a_bytes, &tmA, full_bar(s), (kc * g.BK) % a.in_cols, t0 + j * a.dil - a.pad, b);
         ptx::tma_load_2d(sB + s * g.b_stride, &tmB, full_bar(s), j * a.Cin + kc * g.BK, ntile * a.NT);
       }
     }
@@ -184,7 +193,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (in_range) {
           if (ep.out_f32)
             store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + (long long)ntile * half + c0, v);
-          if (ep.out_op) store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + orow_op + c0, v, ep.out_slope);
+          if (ep.out_op) store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + orow_op + c0, v, ep.out_slope, ep.out_op_split);
         }
       }
     } else {
@@ -218,7 +227,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + n0 + c0, v);
           if (ep.out_op)
             store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + (long long)b * ep.out_op_bstride +
-                                (long long)t * ep.out_op_ld + n0 + c0, v, ep.out_slope);
+                                (long long)t * ep.out_op_ld + n0 + c0, v, ep.out_slope, ep.out_op_split);
         }
       }
     }
@@ -254,6 +263,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 bool conv_tc_supported(int Cin, int in_ld, int N, int NT, int k) {
+  // (in_cols, when different from Cin, must be a multiple of the K block; checked in make_geom)
   if (!(Cin == 16 || Cin == 32 || (Cin % 64 == 0 && Cin > 0))) return false;
   if (in_ld % 8 != 0) return false;                       // 16-byte row pitch for TMA
   if (NT < 16 || NT > kMaxTileN || NT % 16 != 0 || N % NT != 0) return false;
@@ -265,15 +275,24 @@ static bool make_geom(const ConvArgs& a, int op, TcGeom* g) {
   if (!conv_tc_supported(a.Cin, a.in_ld, a.N, a.NT, a.k)) return false;
   if (a.epi.gate && (a.NT % 32 != 0)) return false;
   g->BK = a.Cin >= 64 ? 64 : a.Cin;
+  if (a.in_cols <= 0 || a.in_cols % g->BK != 0) return false;
   g->kchunks = a.Cin / g->BK;
   g->iters = a.k * g->kchunks;
   g->a_bytes = kTileM * g->BK * 2;
   g->b_bytes = a.NT * g->BK * 2;
   g->b_stride = (g->b_bytes + 1023u) & ~1023u;
-  const uint32_t budget = 192 * 1024;
-  int st = budget / (g->a_bytes + g->b_stride);
-  if (st > 8) st = 8;
-  if (st > g->iters) st = g->iters;
+  // Pipeline depth vs occupancy: one tile per CTA means a CTA's epilogue only overlaps
+  // another CTA's main loop, so prefer the smallest smem footprint that still gives a
+  // >=3-deep ring (several co-resident CTAs per SM) over one deep ring per SM.
+  const uint32_t stage = g->a_bytes + g->b_stride;
+  const uint32_t budgets[4] = {40 * 1024, 72 * 1024, 110 * 1024, 192 * 1024};
+  int st = 1;
+  for (int i = 0; i < 4; ++i) {
+    st = (int)(budgets[i] / stage);
+    if (st > 8) st = 8;
+    if (st > g->iters) st = g->iters;
+    if (st >= (g->iters < 3 ? g->iters : 3)) break;
+  }
   if (st < 1) st = 1;
   g->stages = st;
   uint32_t cols = 32;
@@ -294,7 +313,7 @@ cudaError_t launch_conv_tc(const ConvArgs& a, int op, cudaStream_t stream) {
                                : (g.BK == 32 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B);
   CUtensorMap tmA, tmB;
   {
-    cuuint64_t dims[3] = {(cuuint64_t)a.Cin, (cuuint64_t)a.L, (cuuint64_t)a.B};
+    cuuint64_t dims[3] = {(cuuint64_t)a.in_cols, (cuuint64_t)a.L, (cuuint64_t)a.B};
     cuuint64_t strides[2] = {(cuuint64_t)a.in_ld * 2, (cuuint64_t)a.in_bstride * 2};
     cuuint32_t box[3] = {(cuuint32_t)g.BK, (cuuint32_t)kTileM, 1};
     cuuint32_t estr[3] = {1, 1, 1};

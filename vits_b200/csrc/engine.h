@@ -11,8 +11,10 @@ namespace vitsb {
 
 // One implicit-GEMM conv after packing.
 struct PackedConv {
-  int Cin = 0, N = 0, NT = 0, k = 1, dil = 1, pad = 0;
+  int Cin = 0, N = 0, NT = 0, k = 1, dil = 1, pad = 0;   // Cin = K per tap in the packed weights
+  int in_cols = 0;         // physical columns of an input row (2*C for split-precision convs, else Cin)
   bool gate = false;
+  bool split = false;      // 3-term split precision: rows [hi|lo], weights [Wh|Wh|Wl] per tap (common.h)
   size_t w_off = 0;        // element offset into the operand-typed weight pool, [N][k*Cin] K-major
   size_t bias_off = 0;     // offset into the static fp32 bias pool (packed column order)
   int cond_off = -1;       // >=0: bias = per-call conditioning vector at this column (conv bias folded in)
@@ -45,6 +47,7 @@ struct Engine {
   int device = 0;
   int op = OP_F16;
   std::string err;
+  bool split16 = false;    // 16-bit paths: flow + conv_pre + upsamplers run split-precision
 
   // packed model
   bool loaded = false;

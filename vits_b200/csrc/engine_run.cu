@@ -26,12 +26,13 @@ WsLayout Engine::layout(int B, int T) const {
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes); return o; };
   const size_t BT = (size_t)B * T;
   const size_t H = cfg.hidden_channels, IC = cfg.inter_channels;
+  const size_t sm = split16 ? 2 : 1;             // split-precision operand rows are [hi | lo]
   w.len = take(sizeof(int) * (size_t)B);
   w.cond = take(sizeof(float) * (size_t)B * (Ncond > 0 ? Ncond : 1));
-  w.zf = take(4 * BT * IC);  w.zop = take(ob * BT * IC);
-  w.hf = take(4 * BT * H);   w.hop = take(ob * BT * H);
-  w.acts = take(ob * BT * H);
-  w.skipf = take(4 * BT * H); w.skipop = take(ob * BT * H);
+  w.zf = take(4 * BT * IC);  w.zop = take(ob * BT * IC * sm);
+  w.hf = take(4 * BT * H);   w.hop = take(ob * BT * H * sm);
+  w.acts = take(ob * BT * H * sm);
+  w.skipf = take(4 * BT * H); w.skipop = take(ob * BT * H * sm);
   // decoder: elements per frame of the widest stage tensor
   size_t E = cfg.upsample_initial_channel;     // conv_pre output lives in nxt_op
   size_t pos = 1; int C = cfg.upsample_initial_channel;
@@ -40,7 +41,7 @@ WsLayout Engine::layout(int B, int T) const {
     if (pos * C > E) E = pos * C;
   }
   w.xin_f = take(4 * BT * E); w.xb_f = take(4 * BT * E); w.acc_f = take(4 * BT * E);
-  w.xin_op = take(ob * BT * E); w.xb_op = take(ob * BT * E); w.g_op = take(ob * BT * E / 2 + 16); w.nxt_op = take(ob * BT * E);
+  w.xin_op = take(ob * BT * E); w.xb_op = take(ob * BT * E); w.g_op = take(ob * BT * E / 2 + 16); w.nxt_op = take(ob * BT * E * sm);
   w.total = off;
   return w;
 }
@@ -84,7 +85,7 @@ struct Ctx {
     if (dry || !ok()) return;
     ev_begin(tag, p.flop_per_pos * (len ? valid_frames : (double)B * T) * len_mul);
     ConvArgs a{};
-    a.in = in; a.in_ld = p.Cin; a.in_bstride = (long long)L * p.Cin; a.Cin = p.Cin;
+    a.in = in; a.in_ld = p.in_cols; a.in_cols = p.in_cols; a.in_bstride = (long long)L * p.in_cols; a.Cin = p.Cin;
     a.w = reinterpret_cast<const char*>(e->d_w) + p.w_off * op_bytes(e->op);
     a.N = p.N; a.NT = p.NT; a.k = p.k; a.dil = p.dil; a.pad = p.pad; a.L = L; a.B = B;
     a.len = len; a.len_mul = len_mul;
@@ -108,6 +109,11 @@ void set_accum(Epilogue& ep, const float* p, int ld, long long L) { ep.accum = p
 void set_out_f32(Epilogue& ep, float* p, int ld, long long L) { ep.out_f32 = p; ep.out_f32_ld = ld; ep.out_f32_bstride = L * ld; }
 void set_out_op(Epilogue& ep, void* p, int ld, long long L, float slope) {
   ep.out_op = p; ep.out_op_ld = ld; ep.out_op_bstride = L * ld; ep.out_slope = slope;
+}
+// split-precision operand target: logical C columns, physical row [hi(C) | lo(C)]
+void set_out_op_split(Epilogue& ep, void* p, int C, long long L, float slope, bool split) {
+  const int ld = split ? 2 * C : C;
+  ep.out_op = p; ep.out_op_ld = ld; ep.out_op_bstride = L * ld; ep.out_slope = slope; ep.out_op_split = split ? C : 0;
 }
 
 }  // namespace
@@ -151,36 +157,38 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
     if (len) cx.err = cudaMemcpyAsync(d_len, len, sizeof(int) * B, cudaMemcpyHostToDevice, stream);
   }
   // seam: channel-major fp32 -> time-major (masked beyond len)
-  AUX_LAUNCH(T_PACK, launch_pack_time_major(z_in, B, IC, T, cx.len_flow, (what & RUN_FLOW) ? F(W.zf) : nullptr, P(W.zop), op, stream));
+  AUX_LAUNCH(T_PACK, launch_pack_time_major(z_in, B, IC, T, cx.len_flow, (what & RUN_FLOW) ? F(W.zf) : nullptr, P(W.zop), op, split16 ? 1 : 0, stream));
   // all conditioning Linears of the call: flow cond_layers (modules.py:161) + ResBlock conds (modules.py:254)
   AUX_LAUNCH(T_COND, launch_cond_gemv(d_condW, d_condB, g, B, Ncond, cfg.gin_channels, F(W.cond), stream));
 
   if (what & RUN_FLOW) {
     for (const Coupling& cp : couplings) {
       // h = pre(x0)                                                   modules.py:364
-      { Epilogue ep = epi_base(); set_out_f32(ep, F(W.hf), H, T); set_out_op(ep, P(W.hop), H, T, 1.f);
+      { Epilogue ep = epi_base(); set_out_f32(ep, F(W.hf), H, T); set_out_op_split(ep, P(W.hop), H, T, 1.f, split16);
         cx.conv(T_FLOW_PRE, cp.pre, P(W.zop), T, 1, cx.len_flow, ep); }
       const int nl = (int)cp.in_layers.size();
       for (int l = 0; l < nl; ++l) {
         // acts = tanh(a)*sigmoid(b), a,b = in_layer(h) + cond slice     modules.py:163-172
-        { Epilogue ep = epi_base(); set_out_op(ep, P(W.acts), H, T, 1.f);
+        { Epilogue ep = epi_base(); set_out_op_split(ep, P(W.acts), H, T, 1.f, split16);
           cx.conv(T_FLOW_IN, cp.in_layers[l], P(W.hop), T, 1, cx.len_flow, ep); }
         if (l < nl - 1) {
           // h += res_skip[:H]                                           modules.py:176-178
-          Epilogue ep = epi_base(); set_res(ep, F(W.hf), H, T); set_out_f32(ep, F(W.hf), H, T); set_out_op(ep, P(W.hop), H, T, 1.f);
+          Epilogue ep = epi_base(); set_res(ep, F(W.hf), H, T); set_out_f32(ep, F(W.hf), H, T); set_out_op_split(ep, P(W.hop), H, T, 1.f, split16);
           cx.conv(T_FLOW_RES, cp.res[l], P(W.acts), T, 1, cx.len_flow, ep);
         }
         // output += res_skip[H:] (all of it on the last layer)          modules.py:179-181
         { Epilogue ep = epi_base();
           if (l > 0) set_accum(ep, F(W.skipf), H, T);
-          if (l < nl - 1) set_out_f32(ep, F(W.skipf), H, T); else set_out_op(ep, P(W.skipop), H, T, 1.f);
+          if (l < nl - 1) set_out_f32(ep, F(W.skipf), H, T); else set_out_op_split(ep, P(W.skipop), H, T, 1.f, split16);
           cx.conv(T_FLOW_SKIP, cp.skip[l], P(W.acts), T, 1, cx.len_flow, ep); }
       }
       // x1 = x1 - post(out)   (mean-only, logs == 0)                    modules.py:366-372
       { Epilogue ep = epi_base(); ep.alpha = -1.f; ep.beta = 1.f;
         ep.res = F(W.zf) + cp.coff; ep.res_ld = IC; ep.res_bstride = (long long)T * IC;
         ep.out_f32 = F(W.zf) + cp.coff; ep.out_f32_ld = IC; ep.out_f32_bstride = (long long)T * IC;
-        ep.out_op = reinterpret_cast<char*>(P(W.zop)) + (size_t)cp.coff * ob; ep.out_op_ld = IC; ep.out_op_bstride = (long long)T * IC;
+        const int zld = split16 ? 2 * IC : IC;
+        ep.out_op = reinterpret_cast<char*>(P(W.zop)) + (size_t)cp.coff * ob; ep.out_op_ld = zld; ep.out_op_bstride = (long long)T * zld;
+        ep.out_op_split = split16 ? IC : 0;
         cx.conv(T_FLOW_POST, cp.post, P(W.skipop), T, 1, cx.len_flow, ep); }
     }
     if (z_out) AUX_LAUNCH(T_UNPACK, launch_unpack_channel_major(F(W.zf), B, IC, T, z_out, stream));
@@ -188,7 +196,7 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
 
   if (what & RUN_DEC) {
     // x = conv_pre(z); the next op's leaky_relu(0.1) is folded into the operand copy   models.py:307-309
-    { Epilogue ep = epi_base(); set_out_op(ep, P(W.nxt_op), conv_pre.N, T, 0.1f);
+    { Epilogue ep = epi_base(); set_out_op_split(ep, P(W.nxt_op), conv_pre.N, T, 0.1f, split16);
       cx.conv(T_CONV_PRE, conv_pre, P(W.zop), T, 1, cx.len_dec, ep); }
     int L = T;              // rows per batch item at the current rate
     int mul = 1;            // valid rows = len * mul
@@ -203,7 +211,7 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
       L = Lo; mul *= st.u;
       const int nk = (int)st.rb.size();
       const float inv = 1.0f / nk;
-      const float next_slope = s + 1 < ns ? 0.1f : 0.01f;      // models.py:309 vs models.py:315
+      const float next_slope = 0.1f;                           // models.py:309 (the 0.01 of models.py:315 is in conv_post)
       for (int j = 0; j < nk; ++j) {
         const int ni = (int)st.rb[j].size();
         for (int d = 0; d < ni; ++d) {
@@ -222,15 +230,15 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
             // MRF: xs += branch; x = xs / num_kernels                      models.py:311-314
             ep.alpha = inv; ep.beta = inv;
             if (j > 0) set_accum(ep, F(W.acc_f), C, L);
-            if (j < nk - 1) set_out_f32(ep, F(W.acc_f), C, L);
-            else set_out_op(ep, P(W.nxt_op), C, L, next_slope);
+            if (j < nk - 1 || s == ns - 1) set_out_f32(ep, F(W.acc_f), C, L);   // last stage: conv_post reads fp32
+            else set_out_op_split(ep, P(W.nxt_op), C, L, next_slope, split16);
           }
           cx.conv(T_RB_C2 + s, it.c2, P(W.g_op), L, mul, cx.len_dec, ep);
         }
       }
     }
     // tanh(conv_post(leaky_relu(x, 0.01)))                                 models.py:315-317
-    AUX_LAUNCH(T_POST, launch_conv_post(P(W.nxt_op), op, B, L, post_C, post_k, d_post, cx.len_dec, mul, wav, stream));
+    AUX_LAUNCH(T_POST, launch_conv_post(F(W.acc_f), B, L, post_C, post_k, 0.01f, d_post, cx.len_dec, mul, wav, stream));
   }
 #undef AUX_LAUNCH
   if (launches) *launches = cx.launches;

@@ -66,6 +66,7 @@ int Engine::validate_config() {
     if (dr < 1 || pad > kHaloRows) return bad("flow dilation");
   }
   op = c.precision == VITSB_PREC_FP32 ? OP_F32 : (c.precision == VITSB_PREC_BF16 ? OP_BF16 : OP_F16);
+  split16 = op != OP_F32;
   up_total = 1;
   for (int i = 0; i < c.n_upsamples; ++i) up_total *= c.upsample_rates[i];
   return VITSB_OK;
@@ -161,11 +162,25 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
   bool ok = true;
 
   // generic Conv1d packer.  rows[n] = source out-channel; cols[cp] = source in-channel or -1 (zero)
+  // operand-type rounding on the host (for the split-precision hi/lo decomposition)
+  auto op_round = [&](float v) -> float {
+    return op == OP_BF16 ? __bfloat162float(__float2bfloat16_rn(v)) : __half2float(__float2half_rn(v));
+  };
+  // writes one packed weight value; split convs get [Wh | Wh | Wl] per tap
+  auto put_w = [&](float* dst, const PackedConv& p, int nn, int j, int cp, int C, float v) {
+    if (!p.split) { dst[((size_t)nn * p.k + j) * p.Cin + cp] = v; return; }
+    const float hi = op_round(v), lo = op_round(v - hi);
+    float* row = dst + ((size_t)nn * p.k + j) * p.Cin;
+    row[cp] = hi; row[C + cp] = hi; row[2 * C + cp] = lo;
+  };
   auto pack_conv = [&](const HostTensor* w, const HostTensor* b, const std::vector<int>& rows, const std::vector<int>& cols,
                        int k, int dil, bool gate, int NT, const HostTensor* condW, const HostTensor* condB, int cond_row0,
-                       int true_cin) -> PackedConv {
+                       int true_cin, bool split) -> PackedConv {
     PackedConv p;
-    p.Cin = (int)cols.size(); p.N = (int)rows.size(); p.NT = NT; p.k = k; p.dil = dil; p.pad = (k - 1) / 2 * dil; p.gate = gate;
+    const int C = (int)cols.size();
+    p.split = split && split16;
+    p.Cin = p.split ? 3 * C : C; p.in_cols = p.split ? 2 * C : C;
+    p.N = (int)rows.size(); p.NT = NT; p.k = k; p.dil = dil; p.pad = (k - 1) / 2 * dil; p.gate = gate;
     p.flop_per_pos = 2.0 * true_cin * p.N * k;
     if (!w || !b) { ok = false; return p; }
     const int Cin_src = (int)w->shape[1];
@@ -174,8 +189,8 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
     float* dst = h_w.data() + p.w_off;
     for (int nn = 0; nn < p.N; ++nn)
       for (int j = 0; j < k; ++j)
-        for (int cp = 0; cp < p.Cin; ++cp)
-          if (cols[cp] >= 0) dst[((size_t)nn * k + j) * p.Cin + cp] = w->v[((size_t)rows[nn] * Cin_src + cols[cp]) * k + j];
+        for (int cp = 0; cp < C; ++cp)
+          if (cols[cp] >= 0) put_w(dst, p, nn, j, cp, C, w->v[((size_t)rows[nn] * Cin_src + cols[cp]) * k + j]);
     if (condW) {
       p.cond_off = Ncond;
       h_condW.resize((size_t)(Ncond + p.N) * gin);
@@ -205,7 +220,7 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
       std::vector<int> cols(IC, -1);
       for (int cl = 0; cl < half; ++cl) cols[flipped ? IC - 1 - cl : cl] = cl;
       cp.pre = pack_conv(L.weight(p + "pre", {H, half, 1}), L.bias(p + "pre", H), iota_rows(0, H), cols, 1, 1, false, pick_nt(H),
-                         nullptr, nullptr, 0, half);
+                         nullptr, nullptr, 0, half, true);
     }
     const HostTensor* cw = L.weight(p + "enc.cond_layer", {2 * H * nl, gin});
     const HostTensor* cb = L.bias(p + "enc.cond_layer", 2 * H * nl);
@@ -216,15 +231,15 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
       const int NT = pick_nt(2 * H);
       std::vector<int> cols = iota_rows(0, H);
       cp.in_layers.push_back(pack_conv(L.weight(p + "enc.in_layers." + li, {2 * H, H, fk}), L.bias(p + "enc.in_layers." + li, 2 * H),
-                                       gate_rows(2 * H, NT), cols, fk, dil, true, NT, cw, cb, l * 2 * H, H));
+                                       gate_rows(2 * H, NT), cols, fk, dil, true, NT, cw, cb, l * 2 * H, H, true));
       const int rs = l < nl - 1 ? 2 * H : H;
       const HostTensor* rw = L.weight(p + "enc.res_skip_layers." + li, {rs, H, 1});
       const HostTensor* rb = L.bias(p + "enc.res_skip_layers." + li, rs);
       if (l < nl - 1) {
-        cp.res.push_back(pack_conv(rw, rb, iota_rows(0, H), cols, 1, 1, false, pick_nt(H), nullptr, nullptr, 0, H));
-        cp.skip.push_back(pack_conv(rw, rb, iota_rows(H, H), cols, 1, 1, false, pick_nt(H), nullptr, nullptr, 0, H));
+        cp.res.push_back(pack_conv(rw, rb, iota_rows(0, H), cols, 1, 1, false, pick_nt(H), nullptr, nullptr, 0, H, true));
+        cp.skip.push_back(pack_conv(rw, rb, iota_rows(H, H), cols, 1, 1, false, pick_nt(H), nullptr, nullptr, 0, H, true));
       } else {
-        cp.skip.push_back(pack_conv(rw, rb, iota_rows(0, H), cols, 1, 1, false, pick_nt(H), nullptr, nullptr, 0, H));
+        cp.skip.push_back(pack_conv(rw, rb, iota_rows(0, H), cols, 1, 1, false, pick_nt(H), nullptr, nullptr, 0, H, true));
       }
       dil *= c.flow_dilation_rate[fi];
     }
@@ -234,7 +249,7 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
       for (int r = 0; r < half; ++r) rows[r] = flipped ? half - 1 - r : r;
       cp.coff = flipped ? 0 : half;
       cp.post = pack_conv(L.weight(p + "post", {half, H, 1}), L.bias(p + "post", half), rows, iota_rows(0, H), 1, 1, false,
-                          pick_nt(half), nullptr, nullptr, 0, H);
+                          pick_nt(half), nullptr, nullptr, 0, H, true);
     }
     if (!ok) break;
     flop_per_frame += cp.pre.flop_per_pos + cp.post.flop_per_pos;
@@ -248,7 +263,7 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
   int C = c.upsample_initial_channel;
   if (ok) {
     conv_pre = pack_conv(L.weight("dec.conv_pre", {C, IC, 7}), L.bias("dec.conv_pre", C), iota_rows(0, C), iota_rows(0, IC), 7, 1,
-                         false, pick_nt(C), nullptr, nullptr, 0, IC);
+                         false, pick_nt(C), nullptr, nullptr, 0, IC, true);
     flop_per_frame += conv_pre.flop_per_pos;
   }
   int pos_per_frame = 1;
@@ -269,11 +284,13 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
         dmin = dlt < dmin ? dlt : dmin; dmax = dlt > dmax ? dlt : dmax;
       }
     PackedConv& pc = st.ups;
-    pc.Cin = Cin; pc.N = u * Cout; pc.NT = pick_nt(pc.N); pc.k = dmax - dmin + 1; pc.dil = 1; pc.pad = -dmin; pc.gate = false;
+    pc.split = split16;
+    pc.Cin = pc.split ? 3 * Cin : Cin; pc.in_cols = pc.split ? 2 * Cin : Cin;
+    pc.N = u * Cout; pc.NT = pick_nt(pc.N); pc.k = dmax - dmin + 1; pc.dil = 1; pc.pad = -dmin; pc.gate = false;
     pc.flop_per_pos = 2.0 * Cin * Cout * k;          // per INPUT position
     if (pc.pad > kHaloRows || dmax > kHaloRows) { ok = false; L.err = "upsample taps exceed halo"; break; }
     pc.w_off = h_w.size();
-    h_w.resize(h_w.size() + (size_t)pc.N * pc.k * Cin, 0.f);
+    h_w.resize(h_w.size() + (size_t)pc.N * pc.k * pc.Cin, 0.f);
     float* dst = h_w.data() + pc.w_off;
     for (int ph = 0; ph < u; ++ph)
       for (int co = 0; co < Cout; ++co)
@@ -281,7 +298,7 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
           int dlt = jj + dmin, j = ph + pd - u * dlt;
           if (j < 0 || j >= k) continue;
           for (int ci = 0; ci < Cin; ++ci)
-            dst[((size_t)(ph * Cout + co) * pc.k + jj) * Cin + ci] = w->v[((size_t)ci * Cout + co) * k + j];
+            put_w(dst, pc, ph * Cout + co, jj, ci, Cin, w->v[((size_t)ci * Cout + co) * k + j]);
         }
     pc.bias_off = h_bias.size();
     for (int ph = 0; ph < u; ++ph) for (int co = 0; co < Cout; ++co) h_bias.push_back(b->v[co]);
@@ -301,9 +318,9 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
         const HostTensor* gb = L.bias(rp + "conds." + ds, Cout);
         if (!gw || !gb) { ok = false; break; }
         it.c1 = pack_conv(L.weight(rp + "convs1." + ds, {Cout, Cout, kk}), L.bias(rp + "convs1." + ds, Cout), gate_rows(Cout, NT),
-                          iota_rows(0, Cout), kk, c.resblock_dilation_sizes[j][d], true, NT, gw, gb, 0, Cout);
+                          iota_rows(0, Cout), kk, c.resblock_dilation_sizes[j][d], true, NT, gw, gb, 0, Cout, false);
         it.c2 = pack_conv(L.weight(rp + "convs2." + ds, {Cout, Cout / 2, kk}), L.bias(rp + "convs2." + ds, Cout), iota_rows(0, Cout),
-                          iota_rows(0, Cout / 2), kk, 1, false, pick_nt(Cout), nullptr, nullptr, 0, Cout / 2);
+                          iota_rows(0, Cout / 2), kk, 1, false, pick_nt(Cout), nullptr, nullptr, 0, Cout / 2, false);
         flop_per_frame += (it.c1.flop_per_pos + it.c2.flop_per_pos) * pos_per_frame;
         st.rb[j].push_back(it);
       }
