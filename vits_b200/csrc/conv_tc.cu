@@ -18,6 +18,7 @@
 #include "common.h"
 #include "kernels.h"
 #include "ptx.h"
+#include "tc_common.cuh"
 
 #include <mutex>
 
@@ -36,58 +37,6 @@ struct TcGeom {
 };
 
 constexpr int kTcThreads = 192;
-
-template <typename OpT> struct Pack16;   // 16 floats -> 16 OpT (32 bytes) as two uint4
-template <> struct Pack16<__half> {
-  __device__ static __forceinline__ uint32_t pack2(float a, float b) {
-    __half2 h = __floats2half2_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-  }
-  __device__ static __forceinline__ float2 unpack2(uint32_t u) { return __half22float2(*reinterpret_cast<__half2*>(&u)); }
-};
-template <> struct Pack16<__nv_bfloat16> {
-  __device__ static __forceinline__ uint32_t pack2(float a, float b) {
-    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&h);
-  }
-  __device__ static __forceinline__ float2 unpack2(uint32_t u) { return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u)); }
-};
-
-template <typename OpT>
-__device__ __forceinline__ void store_op16(OpT* dst, const float (&v)[16], float slope, int split) {
-  uint32_t p[8], q[8];
-#pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    float x = v[2 * i], y = v[2 * i + 1];
-    x = x >= 0.f ? x : slope * x;
-    y = y >= 0.f ? y : slope * y;
-    p[i] = Pack16<OpT>::pack2(x, y);
-    const float2 hi = Pack16<OpT>::unpack2(p[i]);
-    q[i] = Pack16<OpT>::pack2(x - hi.x, y - hi.y);
-  }
-  uint4* d = reinterpret_cast<uint4*>(dst);
-  d[0] = make_uint4(p[0], p[1], p[2], p[3]);
-  d[1] = make_uint4(p[4], p[5], p[6], p[7]);
-  if (split > 0) {
-    uint4* l = reinterpret_cast<uint4*>(dst + split);
-    l[0] = make_uint4(q[0], q[1], q[2], q[3]);
-    l[1] = make_uint4(q[4], q[5], q[6], q[7]);
-  }
-}
-
-__device__ __forceinline__ void load16(const float* src, float (&v)[16]) {
-  const float4* s = reinterpret_cast<const float4*>(src);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    float4 x = s[i];
-    v[4 * i] = x.x; v[4 * i + 1] = x.y; v[4 * i + 2] = x.z; v[4 * i + 3] = x.w;
-  }
-}
-__device__ __forceinline__ void store16(float* dst, const float (&v)[16]) {
-  float4* d = reinterpret_cast<float4*>(dst);
-#pragma unroll
-  for (int i = 0; i < 4; ++i) d[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
-}
 
 template <typename OpT>
 __global__ void __launch_bounds__(kTcThreads)
@@ -163,74 +112,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncwarp();
   } else {
     // ===== epilogue: TMEM -> registers -> fused math -> global =====
-    const Epilogue& ep = a.epi;
-    const int q = warp & 3;                       // TMEM lane quarter this warp may access
-    const int row = q * 32 + lane;
-    const int t = t0 + row;
-    const bool in_range = t < a.L;
-    const bool live = t < valid;
     ptx::mbar_wait(accum_bar, 0);
     ptx::tc_fence_after();
-    const uint32_t trow = tmem_base + (static_cast<uint32_t>(q * 32) << 16);
-    const float* bias = ep.bias + (long long)b * ep.bias_bstride + (long long)ntile * a.NT;
-    if (ep.gate) {
-      const int half = a.NT >> 1;
-      const long long orow_op = (long long)b * ep.out_op_bstride + (long long)t * ep.out_op_ld + (long long)ntile * half;
-      for (int c0 = 0; c0 < half; c0 += 16) {
-        uint32_t ra[16], rb[16];
-        ptx::tmem_ld16(trow + c0, ra);
-        ptx::tmem_ld16(trow + half + c0, rb);
-        ptx::tmem_ld_wait();
-        float ba[16], bb[16], v[16];
-        load16(bias + c0, ba);
-        load16(bias + half + c0, bb);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float xa = ep.alpha * (__uint_as_float(ra[i]) + ba[i]);
-          float xb = ep.alpha * (__uint_as_float(rb[i]) + bb[i]);
-          v[i] = live ? gate_fn<false>(xa, xb) : 0.f;
-        }
-        if (in_range) {
-          if (ep.out_f32)
-            store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + (long long)ntile * half + c0, v);
-          if (ep.out_op) store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + orow_op + c0, v, ep.out_slope, ep.out_op_split);
-        }
-      }
-    } else {
-      const long long n0 = (long long)ntile * a.NT;
-      for (int c0 = 0; c0 < a.NT; c0 += 16) {
-        uint32_t r[16];
-        ptx::tmem_ld16(trow + c0, r);
-        ptx::tmem_ld_wait();
-        float bv[16], v[16];
-        load16(bias + c0, bv);
-#pragma unroll
-        for (int i = 0; i < 16; ++i) v[i] = ep.alpha * (__uint_as_float(r[i]) + bv[i]);
-        if (in_range) {
-          if (ep.res) {
-            float x[16];
-            load16(ep.res + (long long)b * ep.res_bstride + (long long)t * ep.res_ld + n0 + c0, x);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = fmaf(ep.beta, x[i], v[i]);
-          }
-          if (ep.accum) {
-            float x[16];
-            load16(ep.accum + (long long)b * ep.accum_bstride + (long long)t * ep.accum_ld + n0 + c0, x);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] += x[i];
-          }
-          if (!live) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = 0.f;
-          }
-          if (ep.out_f32)
-            store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + n0 + c0, v);
-          if (ep.out_op)
-            store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + (long long)b * ep.out_op_bstride +
-                                (long long)t * ep.out_op_ld + n0 + c0, v, ep.out_slope, ep.out_op_split);
-        }
-      }
-    }
+    tc_epilogue<OpT>(a, b, t0, ntile, valid, tmem_base, warp & 3, lane);
   }
 
   // ---- teardown: all TMEM reads done before dealloc ----
