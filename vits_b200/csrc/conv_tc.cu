@@ -20,6 +20,7 @@
 #include "ptx.h"
 #include "tc_common.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 namespace vitsb {
@@ -129,11 +130,10 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
 // ---------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+typedef TmaEncodeFn EncodeTiledFn;
+static EncodeTiledFn get_encode_fn() { return tma_encode_fn(); }
 
-static EncodeTiledFn get_encode_fn() {
+TmaEncodeFn tma_encode_fn() {
   static EncodeTiledFn fn = nullptr;
   static std::once_flag once;
   std::call_once(once, [] {
@@ -186,7 +186,17 @@ static bool make_geom(const ConvArgs& a, int op, TcGeom* g) {
   return true;
 }
 
+static int tc_mode() {
+  static int mode = -1;
+  if (mode < 0) { const char* e = getenv("VITSB_TC_MODE"); mode = e ? atoi(e) : 0; }
+  return mode;
+}
+
 cudaError_t launch_conv_tc(const ConvArgs& a, int op, cudaStream_t stream) {
+  if (tc_mode() > 0) {
+    cudaError_t e = launch_conv_tc2(a, op, tc_mode(), stream);
+    if (e != cudaErrorNotSupported) return e;
+  }
   TcGeom g;
   if (op == OP_F32 || !make_geom(a, op, &g)) return cudaErrorNotSupported;
   EncodeTiledFn enc = get_encode_fn();
@@ -216,16 +226,13 @@ cudaError_t launch_conv_tc(const ConvArgs& a, int op, cudaStream_t stream) {
   }
   const size_t smem = 1024 + (size_t)g.stages * (g.a_bytes + g.b_stride) + 8 * (2 * g.stages + 1) + 16;
   dim3 grid(ceil_div(a.L, kTileM), a.N / a.NT, a.B);
-  cudaError_t e;
-  if (op == OP_BF16) {
-    e = cudaFuncSetAttribute(conv_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (e != cudaSuccess) return e;
-    conv_tc_kernel<__nv_bfloat16><<<grid, kTcThreads, smem, stream>>>(tmA, tmB, a, g);
-  } else {
-    e = cudaFuncSetAttribute(conv_tc_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-    if (e != cudaSuccess) return e;
-    conv_tc_kernel<__half><<<grid, kTcThreads, smem, stream>>>(tmA, tmB, a, g);
-  }
+  static std::once_flag once;
+  std::call_once(once, [] {
+    cudaFuncSetAttribute(conv_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    cudaFuncSetAttribute(conv_tc_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  });
+  if (op == OP_BF16) conv_tc_kernel<__nv_bfloat16><<<grid, kTcThreads, smem, stream>>>(tmA, tmB, a, g);
+  else conv_tc_kernel<__half><<<grid, kTcThreads, smem, stream>>>(tmA, tmB, a, g);
   return cudaGetLastError();
 }
 

@@ -38,7 +38,7 @@ struct Stage {             // ups[i] + its MRF (num_kernels ResBlock2 x iteratio
 struct WsLayout {
   size_t len = 0, cond = 0;
   size_t zf = 0, zop = 0, hf = 0, hop = 0, acts = 0, skipf = 0, skipop = 0;   // flow
-  size_t xin_f = 0, xb_f = 0, acc_f = 0, xin_op = 0, xb_op = 0, g_op = 0, nxt_op = 0;  // decoder
+  size_t xin_f = 0, xb_f = 0, acc_f = 0, xin_op = 0, xb_op = 0, xb2_op = 0, g_op = 0, nxt_op = 0;  // decoder
   size_t total = 0;
 };
 
@@ -47,7 +47,8 @@ struct Engine {
   int device = 0;
   int op = OP_F16;
   std::string err;
-  bool split16 = false;    // 16-bit paths: flow + conv_pre + upsamplers run split-precision
+  bool split16 = false;
+  bool rb_fused = false;   // 16-bit paths: ResBlock iterations run as the fused persistent kernel (rb_fused.cu)    // 16-bit paths: flow + conv_pre + upsamplers run split-precision
 
   // packed model
   bool loaded = false;

@@ -41,7 +41,7 @@ WsLayout Engine::layout(int B, int T) const {
     if (pos * C > E) E = pos * C;
   }
   w.xin_f = take(4 * BT * E); w.xb_f = take(4 * BT * E); w.acc_f = take(4 * BT * E);
-  w.xin_op = take(ob * BT * E); w.xb_op = take(ob * BT * E); w.g_op = take(ob * BT * E / 2 + 16); w.nxt_op = take(ob * BT * E * sm);
+  w.xin_op = take(ob * BT * E); w.xb_op = take(ob * BT * E); w.xb2_op = take(rb_fused ? ob * BT * E : 16); w.g_op = take(ob * BT * E / 2 + 16); w.nxt_op = take(ob * BT * E * sm);
   w.total = off;
   return w;
 }
@@ -50,7 +50,7 @@ namespace {
 
 // launch tags for the profile table
 enum Tag { T_PACK = 0, T_COND = 1, T_UNPACK = 2, T_POST = 3, T_FLOW_PRE = 10, T_FLOW_IN = 11, T_FLOW_RES = 12,
-           T_FLOW_SKIP = 13, T_FLOW_POST = 14, T_CONV_PRE = 20, T_UPS = 30, T_RB_C1 = 40, T_RB_C2 = 50 };
+           T_FLOW_SKIP = 13, T_FLOW_POST = 14, T_CONV_PRE = 20, T_UPS = 30, T_RB_C1 = 40, T_RB_C2 = 50, T_RB_FUSED = 60 };
 
 struct ProfEv { int tag; double flops; cudaEvent_t a, b; };
 
@@ -206,7 +206,8 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
       const int C = st.C, Lo = L * st.u;
       // x = ups[i](leaky_relu(x)): phase-stacked conv, output row t holds out[u*t .. u*t+u-1]   models.py:310
       { Epilogue ep = epi_base();
-        set_out_f32(ep, F(W.xin_f), st.ups.N, L); set_out_op(ep, P(W.xin_op), st.ups.N, L, 0.1f);
+        if (!rb_fused) set_out_f32(ep, F(W.xin_f), st.ups.N, L);
+        set_out_op(ep, P(W.xin_op), st.ups.N, L, 0.1f);
         cx.conv(T_UPS + s, st.ups, P(W.nxt_op), L, mul, cx.len_dec, ep); }
       L = Lo; mul *= st.u;
       const int nk = (int)st.rb.size();
@@ -216,6 +217,38 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
         const int ni = (int)st.rb[j].size();
         for (int d = 0; d < ni; ++d) {
           const ResIter& it = st.rb[j][d];
+          if (rb_fused) {
+            // whole iteration in one kernel; the residual stream is y = op(leaky_relu(x)) only (rb_fused.cu)
+            ++cx.launches;
+            if (dry || !cx.ok()) continue;
+            RbLaunch rl{};
+            void* ping = (d & 1) ? P(W.xb2_op) : P(W.xb_op);        // out of iteration d
+            void* pong = (d & 1) ? P(W.xb_op) : P(W.xb2_op);        // out of iteration d-1
+            rl.y_in = d == 0 ? P(W.xin_op) : pong;
+            rl.w1 = reinterpret_cast<const char*>(d_w) + it.c1.w_off * ob;
+            rl.w2 = reinterpret_cast<const char*>(d_w) + it.c2.w_off * ob;
+            rl.C = C; rl.k = it.c1.k; rl.dil = it.c1.dil; rl.B = B;
+            RbArgs& ra = rl.a;
+            ra.L = L; ra.B = B; ra.len = cx.len_dec; ra.len_mul = mul;
+            ra.bias1 = cx.cond + it.c1.cond_off; ra.bias1_bstride = Ncond;
+            ra.bias2 = d_bias + it.c2.bias_off;
+            ra.scale = 1.f;
+            if (d < ni - 1) {
+              ra.y_out = ping;
+            } else {                                                 // MRF (models.py:311-314)
+              ra.scale = inv;
+              ra.acc = F(W.acc_f);
+              ra.acc_mode = (j > 0 ? RB_ACC_READ : 0) | (j < nk - 1 ? RB_ACC_STORE : RB_EMIT_NEXT);
+              if (j == nk - 1) {
+                if (s == ns - 1) ra.nxt_f32 = F(W.acc_f);            // conv_post reads fp32
+                else { ra.nxt_op = P(W.nxt_op); ra.nxt_split = split16 ? 1 : 0; }
+              }
+            }
+            cx.ev_begin(T_RB_FUSED + s, (it.c1.flop_per_pos + it.c2.flop_per_pos) * (cx.len_dec ? cx.valid_frames : (double)B * T) * mul);
+            cx.err = launch_rb_fused(rl, op, stream);
+            cx.ev_end();
+            continue;
+          }
           const void* xin_op = d == 0 ? P(W.xin_op) : P(W.xb_op);
           const float* xin_f = d == 0 ? F(W.xin_f) : F(W.xb_f);
           // xt = tanh(.)*sigmoid(.) of c1(leaky_relu(x)) + cond           modules.py:252-257

@@ -15,6 +15,7 @@
 //   - every conditioning Linear stacked into one [Ncond][gin] matrix in packed
 //     column order, conv bias folded into its bias.
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "engine.h"
@@ -67,6 +68,17 @@ int Engine::validate_config() {
   }
   op = c.precision == VITSB_PREC_FP32 ? OP_F32 : (c.precision == VITSB_PREC_BF16 ? OP_BF16 : OP_F16);
   split16 = op != OP_F32;
+  {
+    const char* ev = getenv("VITSB_RB_FUSED");
+    rb_fused = op != OP_F32 && !(ev && ev[0] == '0');
+    int Cs = c.upsample_initial_channel;
+    for (int i = 0; i < c.n_upsamples && rb_fused; ++i) {
+      Cs /= 2;
+      for (int j = 0; j < c.n_resblock_kernels; ++j)
+        for (int d = 0; d < c.n_resblock_dilations; ++d)
+          if (!rb_fused_supported(Cs, c.resblock_kernel_sizes[j], c.resblock_dilation_sizes[j][d], 1)) rb_fused = false;
+    }
+  }
   up_total = 1;
   for (int i = 0; i < c.n_upsamples; ++i) up_total *= c.upsample_rates[i];
   return VITSB_OK;

@@ -1,5 +1,7 @@
 // Launch entry points of every kernel in the library.
 #pragma once
+#include <cuda.h>
+
 #include "common.h"
 
 namespace vitsb {
@@ -14,6 +16,37 @@ cudaError_t launch_conv_f32(const ConvArgs& a, cudaStream_t stream);
 // Returns cudaErrorNotSupported for shapes outside its envelope.
 cudaError_t launch_conv_tc(const ConvArgs& a, int op, cudaStream_t stream);
 bool conv_tc_supported(int Cin, int in_ld, int N, int NT, int k);
+// conv_tc2.cu — slab variant (A rows staged once per channel block, taps = descriptor row shifts)
+cudaError_t launch_conv_tc2(const ConvArgs& a, int op, int mode, cudaStream_t stream);
+// rb_fused.cu — fused ResBlock2 iteration (c1 -> gate -> c2 -> residual) as one persistent kernel
+enum { RB_ACC_READ = 1, RB_ACC_STORE = 2, RB_EMIT_NEXT = 4 };
+struct RbArgs {
+  void* y_out;             // op_t [B][L][C] = leaky_relu(x_new, 0.1) (mid iterations) or null
+  float* acc;              // fp32 [B][L][C] MRF accumulator (models.py:311-314)
+  int acc_mode;            // RB_ACC_READ: v += acc; RB_ACC_STORE: acc = v; RB_EMIT_NEXT: write nxt_*
+  void* nxt_op;            // op_t leaky_relu(v, 0.1): [B][L][2C] hi|lo if nxt_split else [B][L][C]
+  int nxt_split;
+  float* nxt_f32;          // fp32 [B][L][C] = v (conv_post input)
+  float scale;             // v = scale * (c2 + bias2 + x)
+  const float* bias1; long long bias1_bstride;   // per-batch conditioning + conv bias, gate-packed order
+  const float* bias2;
+  int L, B;
+  const int* len; int len_mul;
+};
+struct RbLaunch {
+  const void* y_in;        // op_t [B][L][C] = leaky_relu(x, 0.1)
+  const void* w1;          // op_t [C][k*C]    (gate-packed rows)
+  const void* w2;          // op_t [C][k*C/2]
+  int C, k, dil, B;
+  RbArgs a;
+};
+bool rb_fused_supported(int C, int k, int dil, int B);
+cudaError_t launch_rb_fused(const RbLaunch& L, int op, cudaStream_t stream);
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link-time libcuda dependency)
+typedef CUresult (*TmaEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+TmaEncodeFn tma_encode_fn();
 
 // aux_kernels.cu
 // [B][C][T] fp32 channel-major -> time-major fp32 (+ operand copy), rows >= len[b] zeroed

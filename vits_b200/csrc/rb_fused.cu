@@ -1,0 +1,431 @@
+// Fused ResBlock2 iteration (modules.py:250-260) as ONE persistent tcgen05 kernel:
+//
+//     y_in = leaky_relu(x)  (16-bit, time-major)          [single HBM read]
+//       -> c1: dilated conv C->C (implicit GEMM, taps = row-shifted views of one smem slab)
+//       -> + cond bias, tanh(a)*sigmoid(b)  -> G tile (C/2 ch) written to SHARED memory
+//       -> c2: conv C/2->C over the smem G tile (taps = row-shifted views again)
+//       -> + bias + x (recovered from the same smem slab) -> leaky_relu -> y_out   [single HBM write]
+//
+// The residual stream lives in HBM only as y = fp16(leaky_relu(x, 0.1)); leaky_relu is
+// invertible (x = y >= 0 ? y : 10*y), so the one tensor serves both as the next conv's
+// operand and as the residual.  Per iteration and element the kernel moves 2 B in + 2 B
+// out instead of the 14 B of the layer-at-a-time plan (fp16 operand + fp32 residual
+// copies + the G round trip).
+//
+// Output rows per tile: T_out = 128 - (k-1): c1 computes the 128 G rows
+// [t0-p2, t0-p2+128) that c2's taps need for outputs [t0, t0+T_out), p2 = (k-1)/2.
+//
+// Roles (320 threads): warp 0 TMA producer (activation slabs + streamed weight boxes),
+// warp 1 MMA issuer, warps 2-5 epilogue-1 (gate -> smem), warps 6-9 epilogue-2
+// (residual, store).  With C <= 128 slabs, G tiles and both TMEM accumulators are
+// double-buffered and the MMA order is c1(i+1), c2(i): four pipeline stages
+// (c1 | gate | c2 | store) run concurrently on consecutive tiles.
+#include "common.h"
+#include "kernels.h"
+#include "ptx.h"
+#include "tc_common.cuh"
+
+#include <mutex>
+
+namespace vitsb {
+
+struct RbGeom {
+  int C, k, dil;
+  int p1, p2, T_out;
+  int BK1, nCB1, rb1;        // c1: channels per block, blocks, row bytes (= swizzle span)
+  int BK2, nCB2, rb2;        // c2 (input C/2)
+  int R1, RG;                // slab rows (mult. of 8), G buffer rows (mult. of 8)
+  int nBuf;                  // 1 or 2: slabs / G tiles / accumulators
+  int nW;                    // weight ring slots
+  uint32_t slab_bytes;       // per channel block
+  uint32_t g_bytes;          // per channel block
+  uint32_t w_slot;           // bytes per ring slot
+  uint32_t w1_tx, w2_tx;     // bytes per weight box
+  uint32_t tmem_cols, idesc;
+  int total_tiles;           // upper bound (exact count is recomputed on device from len)
+};
+
+constexpr int kRbThreads = 320;
+constexpr int kRbMaxB = 512;
+
+// Swizzle<B,4,3> on a byte address whose buffer base is 1024-aligned: XOR bits [4,4+B) with bits [7,7+B)
+__device__ __forceinline__ uint32_t swz_addr(uint32_t addr, int rowbytes) {
+  const uint32_t mask = rowbytes == 128 ? 7u : (rowbytes == 64 ? 3u : 1u);
+  return addr ^ (((addr >> 7) & mask) << 4);
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+
+template <typename OpT>
+__global__ void __launch_bounds__(kRbThreads, 1)
+rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmW1,
+                const __grid_constant__ CUtensorMap tmW2, const RbArgs a, const RbGeom g) {
+  extern __shared__ uint8_t smem_raw[];
+  __shared__ int s_tile_prefix[kRbMaxB + 1];
+  __shared__ uint32_t s_tmem;
+
+  const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t sSlab = smem_base;                                            // [nBuf][nCB1][slab_bytes]
+  const uint32_t sG = sSlab + g.nBuf * g.nCB1 * g.slab_bytes;                  // [nBuf][nCB2][g_bytes]
+  const uint32_t sW = sG + g.nBuf * g.nCB2 * g.g_bytes;                        // [nW][w_slot]
+  const uint32_t bars = sW + g.nW * g.w_slot;
+  // barrier map
+  auto slab_full = [&](int i) { return bars + 8u * i; };
+  auto slab_empty = [&](int i) { return bars + 8u * (2 + i); };
+  auto acc1_full = [&](int i) { return bars + 8u * (4 + i); };
+  auto acc1_empty = [&](int i) { return bars + 8u * (6 + i); };
+  auto acc2_full = [&](int i) { return bars + 8u * (8 + i); };
+  auto acc2_empty = [&](int i) { return bars + 8u * (10 + i); };
+  auto g_full = [&](int i) { return bars + 8u * (12 + i); };
+  auto g_empty = [&](int i) { return bars + 8u * (14 + i); };
+  auto w_full = [&](int i) { return bars + 8u * (16 + i); };
+  auto w_empty = [&](int i) { return bars + 8u * (16 + g.nW + i); };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // ---- tile table: tiles of batch row b cover output rows [0, min(L, valid_b + halo)) ----
+  if (threadIdx.x == 0) {
+    int acc = 0;
+    for (int b = 0; b < a.B; ++b) {
+      s_tile_prefix[b] = acc;
+      int valid = a.len ? a.len[b] * a.len_mul : a.L;
+      int rows = valid + kHaloRows < a.L ? valid + kHaloRows : a.L;
+      acc += (rows + g.T_out - 1) / g.T_out;
+    }
+    s_tile_prefix[a.B] = acc;
+  }
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tmap(&tmY); ptx::prefetch_tmap(&tmW1); ptx::prefetch_tmap(&tmW2);
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(slab_full(i), 1);  ptx::mbar_init(slab_empty(i), 5);   // 1 MMA commit + 4 epilogue-2 warps
+      ptx::mbar_init(acc1_full(i), 1);  ptx::mbar_init(acc1_empty(i), 4);
+      ptx::mbar_init(acc2_full(i), 1);  ptx::mbar_init(acc2_empty(i), 4);
+      ptx::mbar_init(g_full(i), 4);     ptx::mbar_init(g_empty(i), 1);
+    }
+    for (int i = 0; i < g.nW; ++i) { ptx::mbar_init(w_full(i), 1); ptx::mbar_init(w_empty(i), 1); }
+    ptx::mbar_fence_init();
+  }
+  if (warp == 1) ptx::tmem_alloc(ptx::smem_u32(&s_tmem), g.tmem_cols);
+  ptx::tc_fence_before();
+  __syncthreads();
+  ptx::tc_fence_after();
+  const uint32_t tmem_base = s_tmem;
+  const int total_tiles = s_tile_prefix[a.B];
+  const int my_tiles = total_tiles > (int)blockIdx.x ? (total_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+
+  // tile n of this CTA -> (b, t0)
+  auto tile_coords = [&](int n, int& b, int& t0) {
+    const int tile = blockIdx.x + n * gridDim.x;
+    int lo = 0, hi = a.B;                       // largest b with prefix[b] <= tile
+    while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (s_tile_prefix[mid] <= tile) lo = mid; else hi = mid; }
+    b = lo;
+    t0 = (tile - s_tile_prefix[lo]) * g.T_out;
+  };
+  const uint32_t acc1_col = 0, acc2_col = g.nBuf * g.C;       // TMEM columns: [acc1 x nBuf][acc2 x nBuf]
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // =================== TMA producer ===================
+      int wc = 0;                                // weight boxes issued so far
+      auto load_w1 = [&]() {
+        for (int cb = 0; cb < g.nCB1; ++cb)
+          for (int j = 0; j < g.k; ++j, ++wc) {
+            const int s = wc % g.nW;
+            ptx::mbar_wait(w_empty(s), ((wc / g.nW) & 1) ^ 1u);
+            ptx::mbar_expect_tx(w_full(s), g.w1_tx);
+            ptx::tma_load_2d(sW + s * g.w_slot, &tmW1, w_full(s), j * g.C + cb * g.BK1, 0);
+          }
+      };
+      auto load_w2 = [&]() {
+        for (int cb = 0; cb < g.nCB2; ++cb)
+          for (int j = 0; j < g.k; ++j, ++wc) {
+            const int s = wc % g.nW;
+            ptx::mbar_wait(w_empty(s), ((wc / g.nW) & 1) ^ 1u);
+            ptx::mbar_expect_tx(w_full(s), g.w2_tx);
+            ptx::tma_load_2d(sW + s * g.w_slot, &tmW2, w_full(s), j * (g.C / 2) + cb * g.BK2, 0);
+          }
+      };
+      auto load_slab = [&](int n) {
+        int b, t0; tile_coords(n, b, t0);
+        const int s = n % g.nBuf;
+        ptx::mbar_wait(slab_empty(s), ((n / g.nBuf) & 1) ^ 1u);
+        ptx::mbar_expect_tx(slab_full(s), g.nCB1 * g.R1 * g.rb1);
+        for (int cb = 0; cb < g.nCB1; ++cb)
+          ptx::tma_load_3d(sSlab + (s * g.nCB1 + cb) * g.slab_bytes, &tmY, slab_full(s), cb * g.BK1, t0 - g.p2 - g.p1, b);
+      };
+      for (int n = 0; n <= my_tiles; ++n) {
+        if (g.nBuf == 2) {                       // pipelined order: c1(n), c2(n-1)
+          if (n < my_tiles) { load_slab(n); load_w1(); }
+          if (n >= 1) load_w2();
+        } else {                                 // sequential order: c2(n-1), c1(n)
+          if (n >= 1) load_w2();
+          if (n < my_tiles) { load_slab(n); load_w1(); }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // =================== MMA issuer ===================
+      int wc = 0;
+      auto do_c1 = [&](int n) {
+        const int s = n % g.nBuf;
+        ptx::mbar_wait(slab_full(s), (n / g.nBuf) & 1);
+        ptx::mbar_wait(acc1_empty(s), ((n / g.nBuf) & 1) ^ 1u);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc1_col + s * g.C;
+        for (int cb = 0; cb < g.nCB1; ++cb) {
+          const uint32_t abase = sSlab + (s * g.nCB1 + cb) * g.slab_bytes;
+          for (int j = 0; j < g.k; ++j, ++wc) {
+            const int ws = wc % g.nW;
+            ptx::mbar_wait(w_full(ws), (wc / g.nW) & 1);
+            ptx::tc_fence_after();
+            const uint32_t bbase = sW + ws * g.w_slot;
+            for (int kk = 0; kk < g.BK1 / 16; ++kk) {
+              const uint64_t ad = ptx::umma_smem_desc(abase + (j * g.dil) * g.rb1 + kk * 32, g.rb1, 0);
+              const uint64_t bd = ptx::umma_smem_desc(bbase + kk * 32, g.rb1, 0);
+              ptx::umma_f16(d_tmem, ad, bd, g.idesc, (cb | j | kk) != 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(w_empty(ws));
+          }
+        }
+        ptx::umma_commit(acc1_full(s));
+        ptx::umma_commit(slab_empty(s));         // 1 of 5 arrivals: c1 no longer reads the slab
+      };
+      auto do_c2 = [&](int n) {
+        const int s = n % g.nBuf;
+        ptx::mbar_wait(g_full(s), (n / g.nBuf) & 1);
+        ptx::mbar_wait(acc2_empty(s), ((n / g.nBuf) & 1) ^ 1u);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc2_col + s * g.C;
+        for (int cb = 0; cb < g.nCB2; ++cb) {
+          const uint32_t abase = sG + (s * g.nCB2 + cb) * g.g_bytes;
+          for (int j = 0; j < g.k; ++j, ++wc) {
+            const int ws = wc % g.nW;
+            ptx::mbar_wait(w_full(ws), (wc / g.nW) & 1);
+            ptx::tc_fence_after();
+            const uint32_t bbase = sW + ws * g.w_slot;
+            for (int kk = 0; kk < g.BK2 / 16; ++kk) {
+              const uint64_t ad = ptx::umma_smem_desc(abase + j * g.rb2 + kk * 32, g.rb2, 0);
+              const uint64_t bd = ptx::umma_smem_desc(bbase + kk * 32, g.rb2, 0);
+              ptx::umma_f16(d_tmem, ad, bd, g.idesc, (cb | j | kk) != 0 ? 1u : 0u);
+            }
+            ptx::umma_commit(w_empty(ws));
+          }
+        }
+        ptx::umma_commit(acc2_full(s));
+        ptx::umma_commit(g_empty(s));
+      };
+      for (int n = 0; n <= my_tiles; ++n) {
+        if (g.nBuf == 2) {
+          if (n < my_tiles) do_c1(n);
+          if (n >= 1) do_c2(n - 1);
+        } else {
+          if (n >= 1) do_c2(n - 1);
+          if (n < my_tiles) do_c1(n);
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp < 6) {
+    // =================== epilogue 1: gate -> G tile in shared memory ===================
+    const int q = warp & 3, r = q * 32 + lane;
+    const int half = g.C >> 1;
+    for (int n = 0; n < my_tiles; ++n) {
+      int b, t0; tile_coords(n, b, t0);
+      const int s = n % g.nBuf;
+      const int valid = a.len ? a.len[b] * a.len_mul : a.L;
+      const int t = t0 - g.p2 + r;
+      const bool live = t >= 0 && t < valid;     // G outside the sequence is the conv's zero padding
+      ptx::mbar_wait(acc1_full(s), (n / g.nBuf) & 1);
+      ptx::mbar_wait(g_empty(s), ((n / g.nBuf) & 1) ^ 1u);
+      ptx::tc_fence_after();
+      const uint32_t trow = tmem_base + acc1_col + s * g.C + (static_cast<uint32_t>(q * 32) << 16);
+      const float* bias = a.bias1 + (long long)b * a.bias1_bstride;
+      for (int c0 = 0; c0 < half; c0 += 16) {
+        uint32_t ra[16], rb[16];
+        ptx::tmem_ld16(trow + c0, ra);
+        ptx::tmem_ld16(trow + half + c0, rb);
+        ptx::tmem_ld_wait();
+        float ba[16], bb[16];
+        load16(bias + c0, ba);
+        load16(bias + half + c0, bb);
+        uint32_t p[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float v0 = live ? gate_fn<false>(__uint_as_float(ra[2 * i]) + ba[2 * i], __uint_as_float(rb[2 * i]) + bb[2 * i]) : 0.f;
+          float v1 = live ? gate_fn<false>(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1]) : 0.f;
+          p[i] = Pack16<OpT>::pack2(v0, v1);
+        }
+        // channel c0..c0+15 of row r -> block cb2, two 16-byte chunks, swizzled like a TMA write would
+        const int cb2 = c0 / g.BK2, cin = c0 - cb2 * g.BK2;
+        const uint32_t rowaddr = sG + (s * g.nCB2 + cb2) * g.g_bytes + r * g.rb2 + cin * 2;
+        st_shared_v4(swz_addr(rowaddr, g.rb2), p[0], p[1], p[2], p[3]);
+        st_shared_v4(swz_addr(rowaddr + 16, g.rb2), p[4], p[5], p[6], p[7]);
+      }
+      fence_proxy_async_smem();                  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) { ptx::mbar_arrive(g_full(s)); ptx::mbar_arrive(acc1_empty(s)); }
+    }
+  } else {
+    // =================== epilogue 2: bias + residual + leaky_relu -> global ===================
+    const int q = warp & 3, r = q * 32 + lane;
+    for (int n = 0; n < my_tiles; ++n) {
+      int b, t0; tile_coords(n, b, t0);
+      const int s = n % g.nBuf;
+      const int valid = a.len ? a.len[b] * a.len_mul : a.L;
+      const int t = t0 + r;
+      const bool in_range = r < g.T_out && t < a.L;
+      const bool live = t < valid;
+      ptx::mbar_wait(acc2_full(s), (n / g.nBuf) & 1);
+      ptx::mbar_wait(slab_full(s), (n / g.nBuf) & 1);      // acquire the TMA-written slab for the residual reads
+      ptx::tc_fence_after();
+      const uint32_t trow = tmem_base + acc2_col + s * g.C + (static_cast<uint32_t>(q * 32) << 16);
+      const long long orow = ((long long)b * a.L + t) * g.C;
+      const int srow = r + g.p2 + g.p1;          // slab row holding y_in[t]
+      for (int c0 = 0; c0 < g.C; c0 += 16) {
+        uint32_t ra[16];
+        ptx::tmem_ld16(trow + c0, ra);
+        ptx::tmem_ld_wait();
+        if (in_range) {
+          float bv[16], v[16];
+          load16(a.bias2 + c0, bv);
+          const int cb = c0 / g.BK1, cin = c0 - cb * g.BK1;
+          const uint32_t yaddr = sSlab + (s * g.nCB1 + cb) * g.slab_bytes + srow * g.rb1 + cin * 2;
+          const uint4 y0 = ld_shared_v4(swz_addr(yaddr, g.rb1)), y1 = ld_shared_v4(swz_addr(yaddr + 16, g.rb1));
+          const uint32_t yw[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const float2 y = Pack16<OpT>::unpack2(yw[i]);
+            const float x0 = y.x >= 0.f ? y.x : 10.f * y.x;       // inverse of leaky_relu(., 0.1)
+            const float x1 = y.y >= 0.f ? y.y : 10.f * y.y;
+            v[2 * i] = a.scale * (__uint_as_float(ra[2 * i]) + bv[2 * i] + x0);
+            v[2 * i + 1] = a.scale * (__uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1] + x1);
+          }
+          if (a.acc_mode & RB_ACC_READ) {
+            float x[16];
+            load16(a.acc + orow + c0, x);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] += x[i];
+          }
+          if (!live) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) v[i] = 0.f;
+          }
+          if (a.acc_mode & RB_ACC_STORE) store16(a.acc + orow + c0, v);
+          if (a.acc_mode & RB_EMIT_NEXT) {
+            if (a.nxt_f32) store16(a.nxt_f32 + orow + c0, v);
+            if (a.nxt_op) store_op16<OpT>(reinterpret_cast<OpT*>(a.nxt_op) + (a.nxt_split ? 2 : 1) * orow + c0, v, 0.1f,
+                                          a.nxt_split ? g.C : 0);
+          }
+          if (a.y_out) store_op16<OpT>(reinterpret_cast<OpT*>(a.y_out) + orow + c0, v, 0.1f, 0);
+        }
+      }
+      ptx::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) { ptx::mbar_arrive(acc2_empty(s)); ptx::mbar_arrive(slab_empty(s)); }
+    }
+  }
+
+  ptx::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    ptx::tc_fence_after();
+    ptx::tmem_dealloc(tmem_base, g.tmem_cols);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------
+bool rb_fused_supported(int C, int k, int dil, int B) {
+  if (!(C == 32 || (C % 64 == 0 && C >= 64 && C <= 256))) return false;
+  if (k % 2 != 1 || k < 1 || dil < 1 || B > kRbMaxB) return false;
+  if (kTileM - (k - 1) < 32) return false;
+  if (((kTileM + (k - 1) * dil + 7) & ~7) > 256) return false;
+  return true;
+}
+
+cudaError_t launch_rb_fused(const RbLaunch& L, int op, cudaStream_t stream) {
+  if (op == OP_F32 || !rb_fused_supported(L.C, L.k, L.dil, L.B)) return cudaErrorNotSupported;
+  RbGeom g{};
+  g.C = L.C; g.k = L.k; g.dil = L.dil;
+  g.p2 = (L.k - 1) / 2; g.p1 = (L.k - 1) * L.dil / 2; g.T_out = kTileM - (L.k - 1);
+  g.BK1 = L.C >= 64 ? 64 : L.C; g.nCB1 = L.C / g.BK1; g.rb1 = g.BK1 * 2;
+  const int C2 = L.C / 2;
+  g.BK2 = C2 >= 64 ? 64 : C2; g.nCB2 = C2 / g.BK2; g.rb2 = g.BK2 * 2;
+  g.R1 = (kTileM + (L.k - 1) * L.dil + 7) & ~7;
+  g.RG = (kTileM + (L.k - 1) + 7) & ~7;
+  g.slab_bytes = ((uint32_t)g.R1 * g.rb1 + 1023u) & ~1023u;
+  g.g_bytes = ((uint32_t)g.RG * g.rb2 + 1023u) & ~1023u;
+  g.w1_tx = (uint32_t)L.C * g.rb1; g.w2_tx = (uint32_t)L.C * g.rb2;
+  g.w_slot = (g.w1_tx + 1023u) & ~1023u;
+  const uint32_t budget = 220 * 1024;
+  for (g.nBuf = (4 * L.C <= 512) ? 2 : 1; g.nBuf >= 1; --g.nBuf) {
+    const uint32_t fixed = 1024 + g.nBuf * (g.nCB1 * g.slab_bytes + g.nCB2 * g.g_bytes) + 512;
+    if (fixed + 2 * g.w_slot > budget) continue;
+    g.nW = (int)((budget - fixed) / g.w_slot);
+    if (g.nW > 8) g.nW = 8;
+    break;
+  }
+  if (g.nBuf < 1) return cudaErrorNotSupported;
+  uint32_t cols = 32;
+  while (cols < (uint32_t)(2 * g.nBuf * L.C)) cols <<= 1;
+  g.tmem_cols = cols;
+  g.idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM, L.C);
+
+  TmaEncodeFn enc = tma_encode_fn();
+  if (!enc) return cudaErrorNotSupported;
+  const CUtensorMapDataType dt = op == OP_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+  auto swz = [](int rb) { return rb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (rb == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B); };
+  CUtensorMap tmY, tmW1, tmW2;
+  cuuint32_t estr[3] = {1, 1, 1};
+  {
+    cuuint64_t dims[3] = {(cuuint64_t)L.C, (cuuint64_t)L.a.L, (cuuint64_t)L.B};
+    cuuint64_t strides[2] = {(cuuint64_t)L.C * 2, (cuuint64_t)L.a.L * L.C * 2};
+    cuuint32_t box[3] = {(cuuint32_t)g.BK1, (cuuint32_t)g.R1, 1};
+    if (enc(&tmY, dt, 3, const_cast<void*>(L.y_in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(g.rb1),
+            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return cudaErrorInvalidValue;
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)L.k * L.C, (cuuint64_t)L.C};
+    cuuint64_t strides[1] = {(cuuint64_t)L.k * L.C * 2};
+    cuuint32_t box[2] = {(cuuint32_t)g.BK1, (cuuint32_t)L.C};
+    if (enc(&tmW1, dt, 2, const_cast<void*>(L.w1), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(g.rb1),
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return cudaErrorInvalidValue;
+  }
+  {
+    cuuint64_t dims[2] = {(cuuint64_t)L.k * C2, (cuuint64_t)L.C};
+    cuuint64_t strides[1] = {(cuuint64_t)L.k * C2 * 2};
+    cuuint32_t box[2] = {(cuuint32_t)g.BK2, (cuuint32_t)L.C};
+    if (enc(&tmW2, dt, 2, const_cast<void*>(L.w2), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(g.rb2),
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return cudaErrorInvalidValue;
+  }
+  const size_t smem = 1024 + (size_t)g.nBuf * (g.nCB1 * g.slab_bytes + g.nCB2 * g.g_bytes) + (size_t)g.nW * g.w_slot + 8 * (16 + 2 * g.nW) + 64;
+  static int num_sms = 0;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    cudaFuncSetAttribute(rb_fused_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    cudaFuncSetAttribute(rb_fused_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    int dev = 0; cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+  });
+  // upper bound on tiles -> grid (persistent: at most one CTA per SM)
+  const long long max_tiles = (long long)L.B * ((L.a.L + g.T_out - 1) / g.T_out);
+  int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
+  if (grid < 1) grid = 1;
+  if (op == OP_BF16) rb_fused_kernel<__nv_bfloat16><<<grid, kRbThreads, smem, stream>>>(tmY, tmW1, tmW2, L.a, g);
+  else rb_fused_kernel<__half><<<grid, kRbThreads, smem, stream>>>(tmY, tmW1, tmW2, L.a, g);
+  return cudaGetLastError();
+}
+
+}  // namespace vitsb

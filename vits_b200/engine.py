@@ -109,7 +109,8 @@ class FlowDecoder:
         for i in range(n):
             t = tags[i]
             name = self.TAG_NAMES.get(t) or (f"ups.{t - 30}" if 30 <= t < 40 else
-                                             f"resblock.c1.s{t - 40}" if 40 <= t < 50 else f"resblock.c2.s{t - 50}")
+                                             f"resblock.c1.s{t - 40}" if 40 <= t < 50 else
+                                             f"resblock.c2.s{t - 50}" if 50 <= t < 60 else f"resblock.fused.s{t - 60}")
             rows.append((name, ms[i], int(n_l[i]), fl[i]))
         return rows
 
