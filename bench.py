@@ -72,6 +72,18 @@ def lpt_shard(lengths, n):
     return bins
 
 
+def reduce_job(audio_s, frames, ms, world, device):
+    """Whole-job aggregation for N ranks: audio and frames SUM over ranks, time MAX over ranks."""
+    import torch
+    import torch.distributed as dist
+    tot = torch.tensor([audio_s, frames], dtype=torch.float64, device=device)
+    t = torch.tensor([ms], dtype=torch.float64, device=device)
+    if world > 1:
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return tot[0].item(), int(round(tot[1].item())), t.item()
+
+
 class ClockSampler:
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
@@ -236,17 +248,11 @@ def run_b200(args):
         t1 = sampler.mark()
         clocks = sampler.stop(t0, t1) if rank == 0 else None
         ms = sum(a.elapsed_time(b) for a, b in evs)
-        t = torch.tensor([ms], dtype=torch.float64, device=dev)
-        if world > 1:
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return t.item(), clocks
+        return reduce_job(0.0, 0, ms, world, dev)[2], clocks
 
     ms_res, clocks = timed(step_resident, args.steps, max(3, args.warmup))
     ms_e2e, _ = timed(step_e2e, args.steps, max(3, args.warmup))
-    tot = torch.tensor([audio_s, frames], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
-    audio_all, frames_all = tot[0].item(), tot[1].item()
+    audio_all, frames_all, _ = reduce_job(audio_s, frames, 0.0, world, dev)
 
     # per-launch-family device time (separate, untimed pass): roofline of the dominant kernel
     eng.profile(True)

@@ -61,7 +61,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   // generic pointer to the TMEM-address slot
   uint32_t* tmem_slot_ptr = reinterpret_cast<uint32_t*>(smem_raw + (tmem_slot - ptx::smem_u32(smem_raw)));
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
@@ -76,40 +76,46 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   ptx::tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
+  // Role loops are warp-uniform; only the single-thread instructions are predicated on one
+  // elected lane (see ptx::elect_one) so that descriptors / coordinates stay in uniform registers.
+  const int iters = g.iters, stages = g.stages, kchunks = g.kchunks, BK = g.BK;
+  const uint32_t a_bytes = g.a_bytes, b_stride = g.b_stride;
   if (warp == 0) {
-    if (lane == 0) {
-      // ===== TMA producer =====
-      const uint32_t tx_bytes = g.a_bytes + g.b_bytes;
-      for (int it = 0; it < g.iters; ++it) {
-        const int s = it % g.stages;
-        const uint32_t ph = (it / g.stages) & 1;
-        ptx::mbar_wait(empty_bar(s), ph ^ 1u);
+    // ===== TMA producer =====
+    const bool leader = ptx::elect_one();
+    const uint32_t tx_bytes = g.a_bytes + g.b_bytes;
+    const int in_cols = a.in_cols, dil = a.dil, row0 = t0 - a.pad, Cin = a.Cin, n0 = ntile * a.NT;
+    for (int it = 0; it < iters; ++it) {
+      const int s = it % stages;
+      const uint32_t ph = (it / stages) & 1;
+      ptx::mbar_wait(empty_bar(s), ph ^ 1u);
+      if (leader) {
         ptx::mbar_expect_tx(full_bar(s), tx_bytes);
-        const int j = it / g.kchunks, kc = it - j * g.kchunks;
-        ptx::tma_load_3d(sA + s * g.a_bytes, &tmA, full_bar(s), (kc * g.BK) % a.in_cols, t0 + j * a.dil - a.pad, b);
-        ptx::tma_load_2d(sB + s * g.b_stride, &tmB, full_bar(s), j * a.Cin + kc * g.BK, ntile * a.NT);
+        const int j = it / kchunks, kc = it - j * kchunks;
+        ptx::tma_load_3d(sA + s * a_bytes, &tmA, full_bar(s), (kc * BK) % in_cols, row0 + j * dil, b);
+        ptx::tma_load_2d(sB + s * b_stride, &tmB, full_bar(s), j * Cin + kc * BK, n0);
       }
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ===== MMA issuer =====
-      const uint32_t swz = g.BK * 2;
-      for (int it = 0; it < g.iters; ++it) {
-        const int s = it % g.stages;
-        const uint32_t ph = (it / g.stages) & 1;
-        ptx::mbar_wait(full_bar(s), ph);
-        ptx::tc_fence_after();
-        const uint32_t abase = sA + s * g.a_bytes, bbase = sB + s * g.b_stride;
-        for (int kk = 0; kk < g.BK / 16; ++kk) {
-          const uint64_t ad = ptx::umma_smem_desc(abase + kk * 32, swz, 0);
-          const uint64_t bd = ptx::umma_smem_desc(bbase + kk * 32, swz, 0);
-          ptx::umma_f16(tmem_base, ad, bd, g.idesc, (it | kk) != 0 ? 1u : 0u);
-        }
+    // ===== MMA issuer =====
+    const bool leader = ptx::elect_one();
+    const uint64_t dhi = ptx::umma_smem_desc(0, BK * 2, 0);
+    const uint32_t idesc = g.idesc;
+    const int nk = BK / 16;
+    for (int it = 0; it < iters; ++it) {
+      const int s = it % stages;
+      const uint32_t ph = (it / stages) & 1;
+      ptx::mbar_wait(full_bar(s), ph);
+      ptx::tc_fence_after();
+      const uint64_t ad0 = dhi | ((sA + s * a_bytes) >> 4), bd0 = dhi | ((sB + s * b_stride) >> 4);
+      if (leader) {
+        for (int kk = 0; kk < nk; ++kk)
+          ptx::umma_f16(tmem_base, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (it | kk) != 0 ? 1u : 0u);
         ptx::umma_commit(empty_bar(s));           // frees the smem stage when these MMAs retire
       }
-      ptx::umma_commit(accum_bar);                // accumulator complete
     }
+    if (leader) ptx::umma_commit(accum_bar);      // accumulator complete
     __syncwarp();
   } else {
     // ===== epilogue: TMEM -> registers -> fused math -> global =====

@@ -13,6 +13,18 @@ __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
 
+// One elected lane of a fully active warp (same lane for the lifetime of the role loop).
+// Role loops run warp-uniformly (all 32 lanes wait on the mbarriers and compute the
+// descriptors, so ptxas keeps them in uniform registers) and only the single-thread
+// instructions (TMA, tcgen05.mma, tcgen05.commit) are predicated on the elected lane;
+// a whole loop under `if (lane == 0)` makes ptxas wrap every UTCHMMA/UTMALDG in a
+// uniform-register waterfall, which the MMA-issuing thread cannot afford.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t p;
+  asm volatile("{\n.reg .pred P;\nelect.sync _|P, 0xffffffff;\nselp.u32 %0, 1, 0, P;\n}\n" : "=r"(p));
+  return p != 0;
+}
+
 // ---------------- mbarrier ----------------
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
   asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");

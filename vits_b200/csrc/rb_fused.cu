@@ -15,9 +15,9 @@
 // Output rows per tile: T_out = 128 - (k-1): c1 computes the 128 G rows
 // [t0-p2, t0-p2+128) that c2's taps need for outputs [t0, t0+T_out), p2 = (k-1)/2.
 //
-// Roles (320 threads): warp 0 TMA producer (activation slabs + streamed weight boxes),
-// warp 1 MMA issuer, warps 2-5 epilogue-1 (gate -> smem), warps 6-9 epilogue-2
-// (residual, store).  With C <= 128 slabs, G tiles and both TMEM accumulators are
+// Roles (352 threads): warp 0 activation-slab TMA producer, warp 1 MMA issuer, warps 2-5
+// epilogue-1 (gate -> smem), warps 6-9 epilogue-2 (residual, store), warp 10 weight TMA
+// producer (all boxes resident when they fit in smem — C <= 64 — else a streamed ring).  With C <= 128 slabs, G tiles and both TMEM accumulators are
 // double-buffered and the MMA order is c1(i+1), c2(i): four pipeline stages
 // (c1 | gate | c2 | store) run concurrently on consecutive tiles.
 #include "common.h"
@@ -25,6 +25,7 @@
 #include "ptx.h"
 #include "tc_common.cuh"
 
+#include <cstdio>
 #include <mutex>
 
 namespace vitsb {
@@ -35,8 +36,10 @@ struct RbGeom {
   int BK1, nCB1, rb1;        // c1: channels per block, blocks, row bytes (= swizzle span)
   int BK2, nCB2, rb2;        // c2 (input C/2)
   int R1, RG;                // slab rows (mult. of 8), G buffer rows (mult. of 8)
-  int nBuf;                  // 1 or 2: slabs / G tiles / accumulators
-  int nW;                    // weight ring slots
+  int nSlab;                 // activation slab buffers (1..4)
+  int nBuf;                  // 1 or 2: G tiles / TMEM accumulators
+  int nW;                    // weight ring slots (streamed mode)
+  int stationary;            // 1: all k*(nCB1+nCB2) weight boxes stay resident in smem, loaded once per CTA
   uint32_t slab_bytes;       // per channel block
   uint32_t g_bytes;          // per channel block
   uint32_t w_slot;           // bytes per ring slot
@@ -45,7 +48,7 @@ struct RbGeom {
   int total_tiles;           // upper bound (exact count is recomputed on device from len)
 };
 
-constexpr int kRbThreads = 320;
+constexpr int kRbThreads = 352;   // 11 warps: slab TMA, MMA, 4x gate epilogue, 4x store epilogue, weight TMA
 constexpr int kRbMaxB = 512;
 
 // Swizzle<B,4,3> on a byte address whose buffer base is 1024-aligned: XOR bits [4,4+B) with bits [7,7+B)
@@ -73,23 +76,26 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   __shared__ uint32_t s_tmem;
 
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t sSlab = smem_base;                                            // [nBuf][nCB1][slab_bytes]
-  const uint32_t sG = sSlab + g.nBuf * g.nCB1 * g.slab_bytes;                  // [nBuf][nCB2][g_bytes]
-  const uint32_t sW = sG + g.nBuf * g.nCB2 * g.g_bytes;                        // [nW][w_slot]
-  const uint32_t bars = sW + g.nW * g.w_slot;
+  const uint32_t sSlab = smem_base;                                            // [nSlab][nCB1][slab_bytes]
+  const uint32_t sG = sSlab + g.nSlab * g.nCB1 * g.slab_bytes;                 // [nBuf][nCB2][g_bytes]
+  const uint32_t sW = sG + g.nBuf * g.nCB2 * g.g_bytes;                        // ring [nW][w_slot] or all boxes
+  const int nbox1 = g.k * g.nCB1, nbox2 = g.k * g.nCB2;
+  const uint32_t w_bytes = g.stationary ? nbox1 * g.w1_tx + nbox2 * g.w2_tx : g.nW * g.w_slot;
+  const uint32_t bars = sW + w_bytes;
   // barrier map
   auto slab_full = [&](int i) { return bars + 8u * i; };
-  auto slab_empty = [&](int i) { return bars + 8u * (2 + i); };
-  auto acc1_full = [&](int i) { return bars + 8u * (4 + i); };
-  auto acc1_empty = [&](int i) { return bars + 8u * (6 + i); };
-  auto acc2_full = [&](int i) { return bars + 8u * (8 + i); };
-  auto acc2_empty = [&](int i) { return bars + 8u * (10 + i); };
-  auto g_full = [&](int i) { return bars + 8u * (12 + i); };
-  auto g_empty = [&](int i) { return bars + 8u * (14 + i); };
-  auto w_full = [&](int i) { return bars + 8u * (16 + i); };
-  auto w_empty = [&](int i) { return bars + 8u * (16 + g.nW + i); };
+  auto slab_empty = [&](int i) { return bars + 8u * (4 + i); };
+  auto acc1_full = [&](int i) { return bars + 8u * (8 + i); };
+  auto acc1_empty = [&](int i) { return bars + 8u * (10 + i); };
+  auto acc2_full = [&](int i) { return bars + 8u * (12 + i); };
+  auto acc2_empty = [&](int i) { return bars + 8u * (14 + i); };
+  auto g_full = [&](int i) { return bars + 8u * (16 + i); };
+  auto g_empty = [&](int i) { return bars + 8u * (18 + i); };
+  const uint32_t w_all = bars + 8u * 20;
+  auto w_full = [&](int i) { return bars + 8u * (21 + i); };
+  auto w_empty = [&](int i) { return bars + 8u * (21 + g.nW + i); };
 
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform role id
 
   // ---- tile table: tiles of batch row b cover output rows [0, min(L, valid_b + halo)) ----
   if (threadIdx.x == 0) {
@@ -104,8 +110,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   }
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmY); ptx::prefetch_tmap(&tmW1); ptx::prefetch_tmap(&tmW2);
+    for (int i = 0; i < 4; ++i) { ptx::mbar_init(slab_full(i), 1); ptx::mbar_init(slab_empty(i), 5); }   // 1 MMA commit + 4 epilogue-2 warps
+    ptx::mbar_init(w_all, 1);
     for (int i = 0; i < 2; ++i) {
-      ptx::mbar_init(slab_full(i), 1);  ptx::mbar_init(slab_empty(i), 5);   // 1 MMA commit + 4 epilogue-2 warps
       ptx::mbar_init(acc1_full(i), 1);  ptx::mbar_init(acc1_empty(i), 4);
       ptx::mbar_init(acc2_full(i), 1);  ptx::mbar_init(acc2_empty(i), 4);
       ptx::mbar_init(g_full(i), 4);     ptx::mbar_init(g_empty(i), 1);
@@ -131,107 +138,142 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   };
   const uint32_t acc1_col = 0, acc2_col = g.nBuf * g.C;       // TMEM columns: [acc1 x nBuf][acc2 x nBuf]
 
+  const bool pipelined = g.nBuf == 2 && g.nSlab >= 2;        // MMA order c1(n), c2(n-1); else c2(n-1), c1(n)
   if (warp == 0) {
-    if (lane == 0) {
-      // =================== TMA producer ===================
-      int wc = 0;                                // weight boxes issued so far
-      auto load_w1 = [&]() {
+    // =================== activation-slab TMA producer ===================
+    const bool leader = ptx::elect_one();
+    const int nSlab = g.nSlab, nCB1 = g.nCB1, BK1 = g.BK1, halo = g.p2 + g.p1;
+    const uint32_t slab_tx = g.nCB1 * g.R1 * g.rb1, slab_bytes = g.slab_bytes;
+    for (int n = 0; n < my_tiles; ++n) {
+      int b, t0; tile_coords(n, b, t0);
+      const int s = n % nSlab;
+      ptx::mbar_wait(slab_empty(s), ((n / nSlab) & 1) ^ 1u);
+      if (leader) {
+        ptx::mbar_expect_tx(slab_full(s), slab_tx);
+        for (int cb = 0; cb < nCB1; ++cb)
+          ptx::tma_load_3d(sSlab + (s * nCB1 + cb) * slab_bytes, &tmY, slab_full(s), cb * BK1, t0 - halo, b);
+      }
+    }
+    __syncwarp();
+  } else if (warp == 10) {
+    if (lane == 0 && my_tiles > 0) {
+      // =================== weight TMA producer ===================
+      if (g.stationary) {
+        // every (conv, channel block, tap) box stays resident: one barrier, loaded once per CTA
+        ptx::mbar_expect_tx(w_all, nbox1 * g.w1_tx + nbox2 * g.w2_tx);
         for (int cb = 0; cb < g.nCB1; ++cb)
-          for (int j = 0; j < g.k; ++j, ++wc) {
-            const int s = wc % g.nW;
-            ptx::mbar_wait(w_empty(s), ((wc / g.nW) & 1) ^ 1u);
-            ptx::mbar_expect_tx(w_full(s), g.w1_tx);
-            ptx::tma_load_2d(sW + s * g.w_slot, &tmW1, w_full(s), j * g.C + cb * g.BK1, 0);
-          }
-      };
-      auto load_w2 = [&]() {
+          for (int j = 0; j < g.k; ++j)
+            ptx::tma_load_2d(sW + (cb * g.k + j) * g.w1_tx, &tmW1, w_all, j * g.C + cb * g.BK1, 0);
         for (int cb = 0; cb < g.nCB2; ++cb)
-          for (int j = 0; j < g.k; ++j, ++wc) {
-            const int s = wc % g.nW;
-            ptx::mbar_wait(w_empty(s), ((wc / g.nW) & 1) ^ 1u);
-            ptx::mbar_expect_tx(w_full(s), g.w2_tx);
-            ptx::tma_load_2d(sW + s * g.w_slot, &tmW2, w_full(s), j * (g.C / 2) + cb * g.BK2, 0);
-          }
-      };
-      auto load_slab = [&](int n) {
-        int b, t0; tile_coords(n, b, t0);
-        const int s = n % g.nBuf;
-        ptx::mbar_wait(slab_empty(s), ((n / g.nBuf) & 1) ^ 1u);
-        ptx::mbar_expect_tx(slab_full(s), g.nCB1 * g.R1 * g.rb1);
-        for (int cb = 0; cb < g.nCB1; ++cb)
-          ptx::tma_load_3d(sSlab + (s * g.nCB1 + cb) * g.slab_bytes, &tmY, slab_full(s), cb * g.BK1, t0 - g.p2 - g.p1, b);
-      };
-      for (int n = 0; n <= my_tiles; ++n) {
-        if (g.nBuf == 2) {                       // pipelined order: c1(n), c2(n-1)
-          if (n < my_tiles) { load_slab(n); load_w1(); }
-          if (n >= 1) load_w2();
-        } else {                                 // sequential order: c2(n-1), c1(n)
-          if (n >= 1) load_w2();
-          if (n < my_tiles) { load_slab(n); load_w1(); }
+          for (int j = 0; j < g.k; ++j)
+            ptx::tma_load_2d(sW + nbox1 * g.w1_tx + (cb * g.k + j) * g.w2_tx, &tmW2, w_all, j * (g.C / 2) + cb * g.BK2, 0);
+      } else {
+        int wc = 0;                                // weight boxes issued so far, in MMA consumption order
+        auto load_w1 = [&]() {
+          for (int cb = 0; cb < g.nCB1; ++cb)
+            for (int j = 0; j < g.k; ++j, ++wc) {
+              const int s = wc % g.nW;
+              ptx::mbar_wait(w_empty(s), ((wc / g.nW) & 1) ^ 1u);
+              ptx::mbar_expect_tx(w_full(s), g.w1_tx);
+              ptx::tma_load_2d(sW + s * g.w_slot, &tmW1, w_full(s), j * g.C + cb * g.BK1, 0);
+            }
+        };
+        auto load_w2 = [&]() {
+          for (int cb = 0; cb < g.nCB2; ++cb)
+            for (int j = 0; j < g.k; ++j, ++wc) {
+              const int s = wc % g.nW;
+              ptx::mbar_wait(w_empty(s), ((wc / g.nW) & 1) ^ 1u);
+              ptx::mbar_expect_tx(w_full(s), g.w2_tx);
+              ptx::tma_load_2d(sW + s * g.w_slot, &tmW2, w_full(s), j * (g.C / 2) + cb * g.BK2, 0);
+            }
+        };
+        for (int n = 0; n <= my_tiles; ++n) {
+          if (pipelined) { if (n < my_tiles) load_w1(); if (n >= 1) load_w2(); }
+          else           { if (n >= 1) load_w2(); if (n < my_tiles) load_w1(); }
         }
       }
     }
     __syncwarp();
   } else if (warp == 1) {
-    if (lane == 0) {
-      // =================== MMA issuer ===================
+    if (my_tiles > 0) {
+      // =================== MMA issuer (warp-uniform loop, elected lane issues) ===================
+      const bool leader = ptx::elect_one();
+      const int kTaps = g.k, nCB1 = g.nCB1, nCB2 = g.nCB2, nSlab = g.nSlab, nBuf = g.nBuf, nW = g.nW, C = g.C;
+      const bool stationary = g.stationary != 0;
+      const uint32_t slab_bytes = g.slab_bytes, g_bytes = g.g_bytes, w1_tx = g.w1_tx, w2_tx = g.w2_tx, w_slot = g.w_slot;
       int wc = 0;
+      const uint64_t dhi1 = ptx::umma_smem_desc(0, g.rb1, 0), dhi2 = ptx::umma_smem_desc(0, g.rb2, 0);
+      const uint32_t tap_stride1 = g.dil * g.rb1, tap_stride2 = g.rb2, idesc = g.idesc;
+      const int nk1 = g.BK1 / 16, nk2 = g.BK2 / 16;
+      if (g.stationary) { ptx::mbar_wait(w_all, 0); ptx::tc_fence_after(); }
       auto do_c1 = [&](int n) {
-        const int s = n % g.nBuf;
-        ptx::mbar_wait(slab_full(s), (n / g.nBuf) & 1);
-        ptx::mbar_wait(acc1_empty(s), ((n / g.nBuf) & 1) ^ 1u);
+        const int ss = n % nSlab, s = n % nBuf;
+        ptx::mbar_wait(slab_full(ss), (n / nSlab) & 1);
+        ptx::mbar_wait(acc1_empty(s), ((n / nBuf) & 1) ^ 1u);
         ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc1_col + s * g.C;
-        for (int cb = 0; cb < g.nCB1; ++cb) {
-          const uint32_t abase = sSlab + (s * g.nCB1 + cb) * g.slab_bytes;
-          for (int j = 0; j < g.k; ++j, ++wc) {
-            const int ws = wc % g.nW;
-            ptx::mbar_wait(w_full(ws), (wc / g.nW) & 1);
-            ptx::tc_fence_after();
-            const uint32_t bbase = sW + ws * g.w_slot;
-            for (int kk = 0; kk < g.BK1 / 16; ++kk) {
-              const uint64_t ad = ptx::umma_smem_desc(abase + (j * g.dil) * g.rb1 + kk * 32, g.rb1, 0);
-              const uint64_t bd = ptx::umma_smem_desc(bbase + kk * 32, g.rb1, 0);
-              ptx::umma_f16(d_tmem, ad, bd, g.idesc, (cb | j | kk) != 0 ? 1u : 0u);
+        const uint32_t d_tmem = tmem_base + acc1_col + s * C;
+        for (int cb = 0; cb < nCB1; ++cb) {
+          const uint32_t abase = sSlab + (ss * nCB1 + cb) * slab_bytes;
+          for (int j = 0; j < kTaps; ++j, ++wc) {
+            uint32_t bbase;
+            int ws = 0;
+            if (stationary) {
+              bbase = sW + (cb * kTaps + j) * w1_tx;
+            } else {
+              ws = wc % nW;
+              ptx::mbar_wait(w_full(ws), (wc / nW) & 1);
+              ptx::tc_fence_after();
+              bbase = sW + ws * w_slot;
             }
-            ptx::umma_commit(w_empty(ws));
+            // descriptors differ only in their 14-bit start-address field (16-byte units)
+            const uint64_t ad0 = dhi1 | ((abase + tap_stride1 * j) >> 4), bd0 = dhi1 | (bbase >> 4);
+            if (leader) {
+              for (int kk = 0; kk < nk1; ++kk)
+                ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
+              if (!stationary) ptx::umma_commit(w_empty(ws));
+            }
           }
         }
-        ptx::umma_commit(acc1_full(s));
-        ptx::umma_commit(slab_empty(s));         // 1 of 5 arrivals: c1 no longer reads the slab
+        if (leader) {
+          ptx::umma_commit(acc1_full(s));
+          ptx::umma_commit(slab_empty(ss));      // 1 of 5 arrivals: c1 no longer reads the slab
+        }
       };
       auto do_c2 = [&](int n) {
-        const int s = n % g.nBuf;
-        ptx::mbar_wait(g_full(s), (n / g.nBuf) & 1);
-        ptx::mbar_wait(acc2_empty(s), ((n / g.nBuf) & 1) ^ 1u);
+        const int s = n % nBuf;
+        ptx::mbar_wait(g_full(s), (n / nBuf) & 1);
+        ptx::mbar_wait(acc2_empty(s), ((n / nBuf) & 1) ^ 1u);
         ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc2_col + s * g.C;
-        for (int cb = 0; cb < g.nCB2; ++cb) {
-          const uint32_t abase = sG + (s * g.nCB2 + cb) * g.g_bytes;
-          for (int j = 0; j < g.k; ++j, ++wc) {
-            const int ws = wc % g.nW;
-            ptx::mbar_wait(w_full(ws), (wc / g.nW) & 1);
-            ptx::tc_fence_after();
-            const uint32_t bbase = sW + ws * g.w_slot;
-            for (int kk = 0; kk < g.BK2 / 16; ++kk) {
-              const uint64_t ad = ptx::umma_smem_desc(abase + j * g.rb2 + kk * 32, g.rb2, 0);
-              const uint64_t bd = ptx::umma_smem_desc(bbase + kk * 32, g.rb2, 0);
-              ptx::umma_f16(d_tmem, ad, bd, g.idesc, (cb | j | kk) != 0 ? 1u : 0u);
+        const uint32_t d_tmem = tmem_base + acc2_col + s * C;
+        for (int cb = 0; cb < nCB2; ++cb) {
+          const uint32_t abase = sG + (s * nCB2 + cb) * g_bytes;
+          for (int j = 0; j < kTaps; ++j, ++wc) {
+            uint32_t bbase;
+            int ws = 0;
+            if (stationary) {
+              bbase = sW + nbox1 * w1_tx + (cb * kTaps + j) * w2_tx;
+            } else {
+              ws = wc % nW;
+              ptx::mbar_wait(w_full(ws), (wc / nW) & 1);
+              ptx::tc_fence_after();
+              bbase = sW + ws * w_slot;
             }
-            ptx::umma_commit(w_empty(ws));
+            const uint64_t ad0 = dhi2 | ((abase + tap_stride2 * j) >> 4), bd0 = dhi2 | (bbase >> 4);
+            if (leader) {
+              for (int kk = 0; kk < nk2; ++kk)
+                ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
+              if (!stationary) ptx::umma_commit(w_empty(ws));
+            }
           }
         }
-        ptx::umma_commit(acc2_full(s));
-        ptx::umma_commit(g_empty(s));
+        if (leader) {
+          ptx::umma_commit(acc2_full(s));
+          ptx::umma_commit(g_empty(s));
+        }
       };
       for (int n = 0; n <= my_tiles; ++n) {
-        if (g.nBuf == 2) {
-          if (n < my_tiles) do_c1(n);
-          if (n >= 1) do_c2(n - 1);
-        } else {
-          if (n >= 1) do_c2(n - 1);
-          if (n < my_tiles) do_c1(n);
-        }
+        if (pipelined) { if (n < my_tiles) do_c1(n); if (n >= 1) do_c2(n - 1); }
+        else           { if (n >= 1) do_c2(n - 1); if (n < my_tiles) do_c1(n); }
       }
     }
     __syncwarp();
@@ -276,18 +318,18 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       __syncwarp();
       if (lane == 0) { ptx::mbar_arrive(g_full(s)); ptx::mbar_arrive(acc1_empty(s)); }
     }
-  } else {
+  } else if (warp < 10) {
     // =================== epilogue 2: bias + residual + leaky_relu -> global ===================
     const int q = warp & 3, r = q * 32 + lane;
     for (int n = 0; n < my_tiles; ++n) {
       int b, t0; tile_coords(n, b, t0);
-      const int s = n % g.nBuf;
+      const int s = n % g.nBuf, ss = n % g.nSlab;
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
       const int t = t0 + r;
       const bool in_range = r < g.T_out && t < a.L;
       const bool live = t < valid;
       ptx::mbar_wait(acc2_full(s), (n / g.nBuf) & 1);
-      ptx::mbar_wait(slab_full(s), (n / g.nBuf) & 1);      // acquire the TMA-written slab for the residual reads
+      ptx::mbar_wait(slab_full(ss), (n / g.nSlab) & 1);      // acquire the TMA-written slab for the residual reads
       ptx::tc_fence_after();
       const uint32_t trow = tmem_base + acc2_col + s * g.C + (static_cast<uint32_t>(q * 32) << 16);
       const long long orow = ((long long)b * a.L + t) * g.C;
@@ -300,7 +342,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           float bv[16], v[16];
           load16(a.bias2 + c0, bv);
           const int cb = c0 / g.BK1, cin = c0 - cb * g.BK1;
-          const uint32_t yaddr = sSlab + (s * g.nCB1 + cb) * g.slab_bytes + srow * g.rb1 + cin * 2;
+          const uint32_t yaddr = sSlab + (ss * g.nCB1 + cb) * g.slab_bytes + srow * g.rb1 + cin * 2;
           const uint4 y0 = ld_shared_v4(swz_addr(yaddr, g.rb1)), y1 = ld_shared_v4(swz_addr(yaddr + 16, g.rb1));
           const uint32_t yw[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
 #pragma unroll
@@ -332,7 +374,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) { ptx::mbar_arrive(acc2_empty(s)); ptx::mbar_arrive(slab_empty(s)); }
+      if (lane == 0) { ptx::mbar_arrive(acc2_empty(s)); ptx::mbar_arrive(slab_empty(ss)); }
     }
   }
 
@@ -370,14 +412,24 @@ cudaError_t launch_rb_fused(const RbLaunch& L, int op, cudaStream_t stream) {
   g.w1_tx = (uint32_t)L.C * g.rb1; g.w2_tx = (uint32_t)L.C * g.rb2;
   g.w_slot = (g.w1_tx + 1023u) & ~1023u;
   const uint32_t budget = 220 * 1024;
-  for (g.nBuf = (4 * L.C <= 512) ? 2 : 1; g.nBuf >= 1; --g.nBuf) {
-    const uint32_t fixed = 1024 + g.nBuf * (g.nCB1 * g.slab_bytes + g.nCB2 * g.g_bytes) + 512;
-    if (fixed + 2 * g.w_slot > budget) continue;
-    g.nW = (int)((budget - fixed) / g.w_slot);
+  const uint32_t nbox1 = L.k * g.nCB1, nbox2 = L.k * g.nCB2;
+  const uint32_t w_all_bytes = nbox1 * g.w1_tx + nbox2 * g.w2_tx;
+  g.nBuf = (4 * L.C <= 512) ? 2 : 1;
+  const uint32_t slab_set = g.nCB1 * g.slab_bytes, g_set = g.nCB2 * g.g_bytes;
+  const uint32_t fixed = 1024 + 512 + g.nBuf * g_set;
+  g.stationary = 0; g.nW = 0; g.nSlab = 0;
+  if (fixed + w_all_bytes + 2 * slab_set <= budget) {
+    // small stages: weights resident, deep activation prefetch
+    g.stationary = 1;
+    g.nSlab = (int)((budget - fixed - w_all_bytes) / slab_set);
+    if (g.nSlab > 4) g.nSlab = 4;
+  } else {
+    g.nSlab = g.nBuf == 2 ? 2 : 1;
+    if (fixed + g.nSlab * slab_set + 2 * g.w_slot > budget) { g.nSlab = 1; }
+    if (fixed + g.nSlab * slab_set + 2 * g.w_slot > budget) return cudaErrorNotSupported;
+    g.nW = (int)((budget - fixed - g.nSlab * slab_set) / g.w_slot);
     if (g.nW > 8) g.nW = 8;
-    break;
   }
-  if (g.nBuf < 1) return cudaErrorNotSupported;
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * g.nBuf * L.C)) cols <<= 1;
   g.tmem_cols = cols;
@@ -394,28 +446,30 @@ cudaError_t launch_rb_fused(const RbLaunch& L, int op, cudaStream_t stream) {
     cuuint64_t strides[2] = {(cuuint64_t)L.C * 2, (cuuint64_t)L.a.L * L.C * 2};
     cuuint32_t box[3] = {(cuuint32_t)g.BK1, (cuuint32_t)g.R1, 1};
     if (enc(&tmY, dt, 3, const_cast<void*>(L.y_in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(g.rb1),
-            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return cudaErrorInvalidValue;
+            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", L.C, L.k); return cudaErrorInvalidValue; }
   }
   {
     cuuint64_t dims[2] = {(cuuint64_t)L.k * L.C, (cuuint64_t)L.C};
     cuuint64_t strides[1] = {(cuuint64_t)L.k * L.C * 2};
     cuuint32_t box[2] = {(cuuint32_t)g.BK1, (cuuint32_t)L.C};
     if (enc(&tmW1, dt, 2, const_cast<void*>(L.w1), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(g.rb1),
-            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return cudaErrorInvalidValue;
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", L.C, L.k); return cudaErrorInvalidValue; }
   }
   {
     cuuint64_t dims[2] = {(cuuint64_t)L.k * C2, (cuuint64_t)L.C};
     cuuint64_t strides[1] = {(cuuint64_t)L.k * C2 * 2};
     cuuint32_t box[2] = {(cuuint32_t)g.BK2, (cuuint32_t)L.C};
     if (enc(&tmW2, dt, 2, const_cast<void*>(L.w2), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(g.rb2),
-            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) return cudaErrorInvalidValue;
+            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", L.C, L.k); return cudaErrorInvalidValue; }
   }
-  const size_t smem = 1024 + (size_t)g.nBuf * (g.nCB1 * g.slab_bytes + g.nCB2 * g.g_bytes) + (size_t)g.nW * g.w_slot + 8 * (16 + 2 * g.nW) + 64;
+  const size_t smem = 1024 + (size_t)g.nSlab * slab_set + (size_t)g.nBuf * g_set + (g.stationary ? (size_t)w_all_bytes : (size_t)g.nW * g.w_slot) + 8 * (21 + 2 * g.nW) + 64;
   static int num_sms = 0;
   static std::once_flag once;
   std::call_once(once, [] {
-    cudaFuncSetAttribute(rb_fused_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
-    cudaFuncSetAttribute(rb_fused_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 226 * 1024);
+    // opt-in limit is 227 KB per CTA INCLUDING the kernel's static shared memory (tile table)
+    cudaError_t e1 = cudaFuncSetAttribute(rb_fused_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 222 * 1024);
+    cudaError_t e2 = cudaFuncSetAttribute(rb_fused_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 222 * 1024);
+    if (e1 != cudaSuccess || e2 != cudaSuccess) fprintf(stderr, "rb_fused: cudaFuncSetAttribute failed: %s\n", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
     int dev = 0; cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
   });
@@ -425,7 +479,11 @@ cudaError_t launch_rb_fused(const RbLaunch& L, int op, cudaStream_t stream) {
   if (grid < 1) grid = 1;
   if (op == OP_BF16) rb_fused_kernel<__nv_bfloat16><<<grid, kRbThreads, smem, stream>>>(tmY, tmW1, tmW2, L.a, g);
   else rb_fused_kernel<__half><<<grid, kRbThreads, smem, stream>>>(tmY, tmW1, tmW2, L.a, g);
-  return cudaGetLastError();
+  cudaError_t le = cudaGetLastError();
+  if (le != cudaSuccess)
+    fprintf(stderr, "rb_fused launch failed (%s): C=%d k=%d dil=%d grid=%d smem=%zu nSlab=%d nBuf=%d nW=%d stat=%d tmem=%u\n", cudaGetErrorString(le),
+            L.C, L.k, L.dil, grid, smem, g.nSlab, g.nBuf, g.nW, g.stationary, g.tmem_cols);
+  return le;
 }
 
 }  // namespace vitsb
