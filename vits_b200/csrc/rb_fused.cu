@@ -9,17 +9,27 @@
 // The residual stream lives in HBM only as y = fp16(leaky_relu(x, 0.1)); leaky_relu is
 // invertible (x = y >= 0 ? y : 10*y), so the one tensor serves both as the next conv's
 // operand and as the residual.  Per iteration and element the kernel moves 2 B in + 2 B
-// out instead of the 14 B of the layer-at-a-time plan (fp16 operand + fp32 residual
-// copies + the G round trip).
+// out instead of the 14 B of the layer-at-a-time plan.
 //
 // Output rows per tile: T_out = 128 - (k-1): c1 computes the 128 G rows
 // [t0-p2, t0-p2+128) that c2's taps need for outputs [t0, t0+T_out), p2 = (k-1)/2.
 //
-// Roles (352 threads): warp 0 activation-slab TMA producer, warp 1 MMA issuer, warps 2-5
-// epilogue-1 (gate -> smem), warps 6-9 epilogue-2 (residual, store), warp 10 weight TMA
-// producer (all boxes resident when they fit in smem — C <= 64 — else a streamed ring).  With C <= 128 slabs, G tiles and both TMEM accumulators are
-// double-buffered and the MMA order is c1(i+1), c2(i): four pipeline stages
-// (c1 | gate | c2 | store) run concurrently on consecutive tiles.
+// The kernel is specialised at compile time on (C, k) — 4 stages x 3 kernel sizes of the
+// reference config — so that the two MMA-issuing warps run straight-line code: every UMMA
+// descriptor is `base + compile-time offset`, no per-tap constant reloads or integer
+// division (the first version spent ~500 cycles of uniform-datapath instructions per tap
+// around 128 cycles of tensor work; profiles/r01_c_ncu_rb_fused_full_summary.txt).
+//
+// Roles (13 warps, 416 threads):
+//   warp 0      activation-slab TMA producer
+//   warp 1      c1 MMA issuer          warp 2   c2 MMA issuer
+//   warp 3      c1 weight TMA producer warp 12  c2 weight TMA producer
+//   warps 4-7   epilogue 1: TMEM -> bias + cond + gate -> G tile in smem (swizzled like TMA)
+//   warps 8-11  epilogue 2: TMEM -> bias + residual + leaky_relu -> global (+ MRF accumulate)
+// Weights are resident in smem when they fit (C <= 64) and streamed through two
+// independent rings (one per conv, so neither issuer can starve the other) otherwise.
+// With C <= 128 slabs, G tiles and both TMEM accumulators are double-buffered:
+// c1(n+1) | gate(n) | c2(n) | store(n-1) overlap on consecutive tiles.
 #include "common.h"
 #include "kernels.h"
 #include "ptx.h"
@@ -30,30 +40,44 @@
 
 namespace vitsb {
 
-struct RbGeom {
-  int C, k, dil;
-  int p1, p2, T_out;
-  int BK1, nCB1, rb1;        // c1: channels per block, blocks, row bytes (= swizzle span)
-  int BK2, nCB2, rb2;        // c2 (input C/2)
-  int R1, RG;                // slab rows (mult. of 8), G buffer rows (mult. of 8)
-  int nSlab;                 // activation slab buffers (1..4)
-  int nBuf;                  // 1 or 2: G tiles / TMEM accumulators
-  int nW;                    // weight ring slots (streamed mode)
-  int stationary;            // 1: all k*(nCB1+nCB2) weight boxes stay resident in smem, loaded once per CTA
-  uint32_t slab_bytes;       // per channel block
-  uint32_t g_bytes;          // per channel block
-  uint32_t w_slot;           // bytes per ring slot
-  uint32_t w1_tx, w2_tx;     // bytes per weight box
-  uint32_t tmem_cols, idesc;
-  int total_tiles;           // upper bound (exact count is recomputed on device from len)
+constexpr int kRbThreads = 416;
+constexpr int kRbMaxB = 512;
+constexpr uint32_t kRbSmemBudget = 220 * 1024;
+
+template <int C, int KT>
+struct RbT {
+  static constexpr int C2 = C / 2;
+  static constexpr int BK1 = C >= 64 ? 64 : C, nCB1 = C / BK1, rb1 = BK1 * 2, NK1 = BK1 / 16;
+  static constexpr int BK2 = C2 >= 64 ? 64 : C2, nCB2 = C2 / BK2, rb2 = BK2 * 2, NK2 = BK2 / 16;
+  static constexpr int P2 = (KT - 1) / 2, T_OUT = kTileM - (KT - 1);
+  static constexpr int RG = (kTileM + (KT - 1) + 7) & ~7;
+  static constexpr uint32_t G_BYTES = ((uint32_t)RG * rb2 + 1023u) & ~1023u;     // per channel block
+  // C = 256: every MMA / weight box covers NMMA = 128 of the 256 output columns (two N halves per (cb, tap)),
+  // so a ring slot is 16 KB instead of 32 KB and more boxes fit next to the 4-block slab
+  static constexpr int NS = C > 128 ? C / 128 : 1, NMMA = C / NS;
+  static constexpr uint32_t W1_TX = (uint32_t)NMMA * rb1, W2_TX = (uint32_t)NMMA * rb2;  // bytes per (cb, tap, half) weight box
+  static constexpr int NBOX1 = KT * nCB1 * NS, NBOX2 = KT * nCB2 * NS;
+  static constexpr uint32_t W_ALL = NBOX1 * W1_TX + NBOX2 * W2_TX;
+  static constexpr int NBUF = (4 * C <= 512) ? 2 : 1;                             // G tiles / TMEM accumulator sets
+  static constexpr uint32_t G_SET = nCB2 * G_BYTES;
+  static constexpr bool STATIONARY = C <= 64;                                     // W_ALL <= 135 KB
+  static constexpr uint32_t TMEM_COLS = (2 * NBUF * C <= 32) ? 32 : (2 * NBUF * C <= 64 ? 64 : (2 * NBUF * C <= 128 ? 128 : (2 * NBUF * C <= 256 ? 256 : 512)));
 };
 
-constexpr int kRbThreads = 352;   // 11 warps: slab TMA, MMA, 4x gate epilogue, 4x store epilogue, weight TMA
-constexpr int kRbMaxB = 512;
+// run-time geometry (depends on the dilation and the smem left after the fixed parts)
+struct RbRt {
+  int dil, p1;               // c1 dilation, (k-1)*dil/2
+  int R1;                    // slab rows (multiple of 8)
+  uint32_t slab_bytes;       // per channel block (multiple of 1024)
+  int nSlab;                 // activation slab buffers (1..4)
+  int nW1, nW2;              // weight ring slots (streamed mode)
+  uint32_t idesc;
+};
 
 // Swizzle<B,4,3> on a byte address whose buffer base is 1024-aligned: XOR bits [4,4+B) with bits [7,7+B)
-__device__ __forceinline__ uint32_t swz_addr(uint32_t addr, int rowbytes) {
-  const uint32_t mask = rowbytes == 128 ? 7u : (rowbytes == 64 ? 3u : 1u);
+template <int ROWBYTES>
+__device__ __forceinline__ uint32_t swz_addr(uint32_t addr) {
+  constexpr uint32_t mask = ROWBYTES == 128 ? 7u : (ROWBYTES == 64 ? 3u : 1u);
   return addr ^ (((addr >> 7) & mask) << 4);
 }
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
@@ -66,23 +90,38 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
 }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
+// ring / buffer cursor without integer division
+struct Cursor {
+  int idx; uint32_t phase;
+  __device__ __forceinline__ void next(int n) { if (++idx == n) { idx = 0; phase ^= 1u; } }
+};
 
-template <typename OpT>
+// tanh(a) * sigmoid(b) with 3 MUFU ops (2x ex2, 1x rcp):
+//   tanh(a) = (1 - e^{-2a}) / (1 + e^{-2a}),  sigmoid(b) = 1 / (1 + e^{-b})
+// a is clamped at -20 (tanh == -1 in fp32 there) and b at -40 so the product of the
+// denominators stays below 2^126 (the __fdividef range).
+__device__ __forceinline__ float gate3(float a, float b) {
+  const float ea = exp2f(-2.885390081777927f * fmaxf(a, -20.f));
+  const float eb = exp2f(-1.4426950408889634f * fmaxf(b, -40.f));
+  return __fdividef(1.0f - ea, (1.0f + ea) * (1.0f + eb));
+}
+
+template <typename OpT, int C, int KT>
 __global__ void __launch_bounds__(kRbThreads, 1)
 rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmW1,
-                const __grid_constant__ CUtensorMap tmW2, const RbArgs a, const RbGeom g) {
+                const __grid_constant__ CUtensorMap tmW2, const RbArgs a, const RbRt rt) {
+  using G = RbT<C, KT>;
   extern __shared__ uint8_t smem_raw[];
   __shared__ int s_tile_prefix[kRbMaxB + 1];
   __shared__ uint32_t s_tmem;
 
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
+  const uint32_t slab_set = G::nCB1 * rt.slab_bytes;
   const uint32_t sSlab = smem_base;                                            // [nSlab][nCB1][slab_bytes]
-  const uint32_t sG = sSlab + g.nSlab * g.nCB1 * g.slab_bytes;                 // [nBuf][nCB2][g_bytes]
-  const uint32_t sW = sG + g.nBuf * g.nCB2 * g.g_bytes;                        // ring [nW][w_slot] or all boxes
-  const int nbox1 = g.k * g.nCB1, nbox2 = g.k * g.nCB2;
-  const uint32_t w_bytes = g.stationary ? nbox1 * g.w1_tx + nbox2 * g.w2_tx : g.nW * g.w_slot;
-  const uint32_t bars = sW + w_bytes;
-  // barrier map
+  const uint32_t sG = sSlab + rt.nSlab * slab_set;                             // [NBUF][nCB2][G_BYTES]
+  const uint32_t sW1 = sG + G::NBUF * G::G_SET;                                // all boxes, or ring 1
+  const uint32_t sW2 = sW1 + (G::STATIONARY ? G::NBOX1 * G::W1_TX : rt.nW1 * G::W1_TX);   // c2 boxes, or ring 2
+  const uint32_t bars = sW2 + (G::STATIONARY ? G::NBOX2 * G::W2_TX : rt.nW2 * G::W2_TX);
   auto slab_full = [&](int i) { return bars + 8u * i; };
   auto slab_empty = [&](int i) { return bars + 8u * (4 + i); };
   auto acc1_full = [&](int i) { return bars + 8u * (8 + i); };
@@ -92,8 +131,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   auto g_full = [&](int i) { return bars + 8u * (16 + i); };
   auto g_empty = [&](int i) { return bars + 8u * (18 + i); };
   const uint32_t w_all = bars + 8u * 20;
-  auto w_full = [&](int i) { return bars + 8u * (21 + i); };
-  auto w_empty = [&](int i) { return bars + 8u * (21 + g.nW + i); };
+  auto w1_full = [&](int i) { return bars + 8u * (21 + i); };
+  auto w1_empty = [&](int i) { return bars + 8u * (29 + i); };
+  auto w2_full = [&](int i) { return bars + 8u * (37 + i); };
+  auto w2_empty = [&](int i) { return bars + 8u * (45 + i); };
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform role id
 
@@ -104,7 +145,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       s_tile_prefix[b] = acc;
       int valid = a.len ? a.len[b] * a.len_mul : a.L;
       int rows = valid + kHaloRows < a.L ? valid + kHaloRows : a.L;
-      acc += (rows + g.T_out - 1) / g.T_out;
+      acc += (rows + G::T_OUT - 1) / G::T_OUT;
     }
     s_tile_prefix[a.B] = acc;
   }
@@ -117,233 +158,273 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       ptx::mbar_init(acc2_full(i), 1);  ptx::mbar_init(acc2_empty(i), 4);
       ptx::mbar_init(g_full(i), 4);     ptx::mbar_init(g_empty(i), 1);
     }
-    for (int i = 0; i < g.nW; ++i) { ptx::mbar_init(w_full(i), 1); ptx::mbar_init(w_empty(i), 1); }
+    for (int i = 0; i < 8; ++i) {
+      ptx::mbar_init(w1_full(i), 1); ptx::mbar_init(w1_empty(i), 1);
+      ptx::mbar_init(w2_full(i), 1); ptx::mbar_init(w2_empty(i), 1);
+    }
     ptx::mbar_fence_init();
   }
-  if (warp == 1) ptx::tmem_alloc(ptx::smem_u32(&s_tmem), g.tmem_cols);
+  if (warp == 1) ptx::tmem_alloc(ptx::smem_u32(&s_tmem), G::TMEM_COLS);
   ptx::tc_fence_before();
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = s_tmem;
   const int total_tiles = s_tile_prefix[a.B];
   const int my_tiles = total_tiles > (int)blockIdx.x ? (total_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  constexpr uint32_t acc1_col = 0, acc2_col = G::NBUF * C;       // TMEM columns: [acc1 x NBUF][acc2 x NBUF]
 
-  // tile n of this CTA -> (b, t0)
-  auto tile_coords = [&](int n, int& b, int& t0) {
-    const int tile = blockIdx.x + n * gridDim.x;
-    int lo = 0, hi = a.B;                       // largest b with prefix[b] <= tile
-    while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (s_tile_prefix[mid] <= tile) lo = mid; else hi = mid; }
-    b = lo;
-    t0 = (tile - s_tile_prefix[lo]) * g.T_out;
-  };
-  const uint32_t acc1_col = 0, acc2_col = g.nBuf * g.C;       // TMEM columns: [acc1 x nBuf][acc2 x nBuf]
+  // static round-robin schedule; b only grows along a CTA's tile sequence
+  int cur_tile = blockIdx.x, cur_b = 0;
+  auto tile_seek = [&]() { while (s_tile_prefix[cur_b + 1] <= cur_tile) ++cur_b; };
+  auto tile_next = [&]() { cur_tile += gridDim.x; };
 
-  const bool pipelined = g.nBuf == 2 && g.nSlab >= 2;        // MMA order c1(n), c2(n-1); else c2(n-1), c1(n)
   if (warp == 0) {
     // =================== activation-slab TMA producer ===================
     const bool leader = ptx::elect_one();
-    const int nSlab = g.nSlab, nCB1 = g.nCB1, BK1 = g.BK1, halo = g.p2 + g.p1;
-    const uint32_t slab_tx = g.nCB1 * g.R1 * g.rb1, slab_bytes = g.slab_bytes;
-    for (int n = 0; n < my_tiles; ++n) {
-      int b, t0; tile_coords(n, b, t0);
-      const int s = n % nSlab;
-      ptx::mbar_wait(slab_empty(s), ((n / nSlab) & 1) ^ 1u);
+    const int halo = G::P2 + rt.p1, nSlab = rt.nSlab;
+    const uint32_t slab_tx = G::nCB1 * (uint32_t)rt.R1 * G::rb1, slab_bytes = rt.slab_bytes;
+    Cursor sl{0, 0};
+    for (int n = 0; n < my_tiles; ++n, tile_next()) {
+      tile_seek();
+      const int t0 = (cur_tile - s_tile_prefix[cur_b]) * G::T_OUT;
+      ptx::mbar_wait(slab_empty(sl.idx), sl.phase ^ 1u);
       if (leader) {
-        ptx::mbar_expect_tx(slab_full(s), slab_tx);
-        for (int cb = 0; cb < nCB1; ++cb)
-          ptx::tma_load_3d(sSlab + (s * nCB1 + cb) * slab_bytes, &tmY, slab_full(s), cb * BK1, t0 - halo, b);
+        ptx::mbar_expect_tx(slab_full(sl.idx), slab_tx);
+#pragma unroll
+        for (int cb = 0; cb < G::nCB1; ++cb)
+          ptx::tma_load_3d(sSlab + sl.idx * slab_set + cb * slab_bytes, &tmY, slab_full(sl.idx), cb * G::BK1, t0 - halo, cur_b);
       }
+      sl.next(nSlab);
     }
     __syncwarp();
-  } else if (warp == 10) {
-    if (lane == 0 && my_tiles > 0) {
-      // =================== weight TMA producer ===================
-      if (g.stationary) {
-        // every (conv, channel block, tap) box stays resident: one barrier, loaded once per CTA
-        ptx::mbar_expect_tx(w_all, nbox1 * g.w1_tx + nbox2 * g.w2_tx);
-        for (int cb = 0; cb < g.nCB1; ++cb)
-          for (int j = 0; j < g.k; ++j)
-            ptx::tma_load_2d(sW + (cb * g.k + j) * g.w1_tx, &tmW1, w_all, j * g.C + cb * g.BK1, 0);
-        for (int cb = 0; cb < g.nCB2; ++cb)
-          for (int j = 0; j < g.k; ++j)
-            ptx::tma_load_2d(sW + nbox1 * g.w1_tx + (cb * g.k + j) * g.w2_tx, &tmW2, w_all, j * (g.C / 2) + cb * g.BK2, 0);
-      } else {
-        int wc = 0;                                // weight boxes issued so far, in MMA consumption order
-        auto load_w1 = [&]() {
-          for (int cb = 0; cb < g.nCB1; ++cb)
-            for (int j = 0; j < g.k; ++j, ++wc) {
-              const int s = wc % g.nW;
-              ptx::mbar_wait(w_empty(s), ((wc / g.nW) & 1) ^ 1u);
-              ptx::mbar_expect_tx(w_full(s), g.w1_tx);
-              ptx::tma_load_2d(sW + s * g.w_slot, &tmW1, w_full(s), j * g.C + cb * g.BK1, 0);
-            }
-        };
-        auto load_w2 = [&]() {
-          for (int cb = 0; cb < g.nCB2; ++cb)
-            for (int j = 0; j < g.k; ++j, ++wc) {
-              const int s = wc % g.nW;
-              ptx::mbar_wait(w_empty(s), ((wc / g.nW) & 1) ^ 1u);
-              ptx::mbar_expect_tx(w_full(s), g.w2_tx);
-              ptx::tma_load_2d(sW + s * g.w_slot, &tmW2, w_full(s), j * (g.C / 2) + cb * g.BK2, 0);
-            }
-        };
-        for (int n = 0; n <= my_tiles; ++n) {
-          if (pipelined) { if (n < my_tiles) load_w1(); if (n >= 1) load_w2(); }
-          else           { if (n >= 1) load_w2(); if (n < my_tiles) load_w1(); }
-        }
+  } else if (warp == 3) {
+    // =================== c1 weight TMA producer (or: all resident weights, once) ===================
+    const bool leader = ptx::elect_one();
+    if (G::STATIONARY) {
+      if (leader && my_tiles > 0) {
+        ptx::mbar_expect_tx(w_all, G::W_ALL);
+        static_assert(!G::STATIONARY || G::NS == 1, "resident weights use whole-N boxes");
+        for (int cb = 0; cb < G::nCB1; ++cb)
+          for (int j = 0; j < KT; ++j)
+            ptx::tma_load_2d(sW1 + (cb * KT + j) * G::W1_TX, &tmW1, w_all, j * C + cb * G::BK1, 0);
+        for (int cb = 0; cb < G::nCB2; ++cb)
+          for (int j = 0; j < KT; ++j)
+            ptx::tma_load_2d(sW2 + (cb * KT + j) * G::W2_TX, &tmW2, w_all, j * G::C2 + cb * G::BK2, 0);
       }
+    } else {
+      const int nW1 = rt.nW1;
+      Cursor wr{0, 0};
+      for (int n = 0; n < my_tiles; ++n)
+        for (int cb = 0; cb < G::nCB1; ++cb)
+          for (int j = 0; j < KT; ++j)
+            for (int h = 0; h < G::NS; ++h) {
+              ptx::mbar_wait(w1_empty(wr.idx), wr.phase ^ 1u);
+              if (leader) {
+                ptx::mbar_expect_tx(w1_full(wr.idx), G::W1_TX);
+                ptx::tma_load_2d(sW1 + wr.idx * G::W1_TX, &tmW1, w1_full(wr.idx), j * C + cb * G::BK1, h * G::NMMA);
+              }
+              wr.next(nW1);
+            }
     }
     __syncwarp();
-  } else if (warp == 1) {
-    if (my_tiles > 0) {
-      // =================== MMA issuer (warp-uniform loop, elected lane issues) ===================
+  } else if (warp == 12) {
+    // =================== c2 weight TMA producer (streamed mode only) ===================
+    if (!G::STATIONARY) {
       const bool leader = ptx::elect_one();
-      const int kTaps = g.k, nCB1 = g.nCB1, nCB2 = g.nCB2, nSlab = g.nSlab, nBuf = g.nBuf, nW = g.nW, C = g.C;
-      const bool stationary = g.stationary != 0;
-      const uint32_t slab_bytes = g.slab_bytes, g_bytes = g.g_bytes, w1_tx = g.w1_tx, w2_tx = g.w2_tx, w_slot = g.w_slot;
-      int wc = 0;
-      const uint64_t dhi1 = ptx::umma_smem_desc(0, g.rb1, 0), dhi2 = ptx::umma_smem_desc(0, g.rb2, 0);
-      const uint32_t tap_stride1 = g.dil * g.rb1, tap_stride2 = g.rb2, idesc = g.idesc;
-      const int nk1 = g.BK1 / 16, nk2 = g.BK2 / 16;
-      if (g.stationary) { ptx::mbar_wait(w_all, 0); ptx::tc_fence_after(); }
-      auto do_c1 = [&](int n) {
-        const int ss = n % nSlab, s = n % nBuf;
-        ptx::mbar_wait(slab_full(ss), (n / nSlab) & 1);
-        ptx::mbar_wait(acc1_empty(s), ((n / nBuf) & 1) ^ 1u);
-        ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc1_col + s * C;
-        for (int cb = 0; cb < nCB1; ++cb) {
-          const uint32_t abase = sSlab + (ss * nCB1 + cb) * slab_bytes;
-          for (int j = 0; j < kTaps; ++j, ++wc) {
-            uint32_t bbase;
-            int ws = 0;
-            if (stationary) {
-              bbase = sW + (cb * kTaps + j) * w1_tx;
-            } else {
-              ws = wc % nW;
-              ptx::mbar_wait(w_full(ws), (wc / nW) & 1);
-              ptx::tc_fence_after();
-              bbase = sW + ws * w_slot;
+      const int nW2 = rt.nW2;
+      Cursor wr{0, 0};
+      for (int n = 0; n < my_tiles; ++n)
+        for (int cb = 0; cb < G::nCB2; ++cb)
+          for (int j = 0; j < KT; ++j)
+            for (int h = 0; h < G::NS; ++h) {
+              ptx::mbar_wait(w2_empty(wr.idx), wr.phase ^ 1u);
+              if (leader) {
+                ptx::mbar_expect_tx(w2_full(wr.idx), G::W2_TX);
+                ptx::tma_load_2d(sW2 + wr.idx * G::W2_TX, &tmW2, w2_full(wr.idx), j * G::C2 + cb * G::BK2, h * G::NMMA);
+              }
+              wr.next(nW2);
             }
+      __syncwarp();
+    }
+  } else if (warp == 1) {
+    // =================== c1 MMA issuer (warp-uniform loop, elected lane issues) ===================
+    if (my_tiles > 0) {
+      const bool leader = ptx::elect_one();
+      const int nSlab = rt.nSlab, nW1 = rt.nW1;
+      const uint32_t slab_bytes = rt.slab_bytes, idesc = rt.idesc;
+      const uint32_t tap16 = ((uint32_t)rt.dil * G::rb1) >> 4;                  // tap stride in 16-byte units
+      const uint64_t dhi = ptx::umma_smem_desc(0, G::rb1, 0);
+      Cursor sl{0, 0}, ab{0, 0}, wr{0, 0};
+      if (G::STATIONARY) { ptx::mbar_wait(w_all, 0); ptx::tc_fence_after(); }
+      for (int n = 0; n < my_tiles; ++n) {
+        ptx::mbar_wait(slab_full(sl.idx), sl.phase);
+        ptx::mbar_wait(acc1_empty(ab.idx), ab.phase ^ 1u);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc1_col + ab.idx * C;
+        const uint32_t a16 = (sSlab + sl.idx * slab_set) >> 4;
+#pragma unroll
+        for (int cb = 0; cb < G::nCB1; ++cb) {
+#pragma unroll
+          for (int j = 0; j < KT; ++j) {
             // descriptors differ only in their 14-bit start-address field (16-byte units)
-            const uint64_t ad0 = dhi1 | ((abase + tap_stride1 * j) >> 4), bd0 = dhi1 | (bbase >> 4);
-            if (leader) {
-              for (int kk = 0; kk < nk1; ++kk)
-                ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
-              if (!stationary) ptx::umma_commit(w_empty(ws));
+            const uint64_t ad0 = dhi | (uint64_t)(a16 + cb * (slab_bytes >> 4) + j * tap16);
+#pragma unroll
+            for (int h = 0; h < G::NS; ++h) {
+              uint32_t b16;
+              if (G::STATIONARY) {
+                b16 = (sW1 + (cb * KT + j) * G::W1_TX) >> 4;
+              } else {
+                ptx::mbar_wait(w1_full(wr.idx), wr.phase);
+                ptx::tc_fence_after();
+                b16 = (sW1 + wr.idx * G::W1_TX) >> 4;
+              }
+              const uint64_t bd0 = dhi | (uint64_t)b16;
+              if (leader) {
+#pragma unroll
+                for (int kk = 0; kk < G::NK1; ++kk)
+                  ptx::umma_f16(d_tmem + h * G::NMMA, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
+                if (!G::STATIONARY) ptx::umma_commit(w1_empty(wr.idx));
+              }
+              if (!G::STATIONARY) wr.next(nW1);
             }
           }
         }
         if (leader) {
-          ptx::umma_commit(acc1_full(s));
-          ptx::umma_commit(slab_empty(ss));      // 1 of 5 arrivals: c1 no longer reads the slab
+          ptx::umma_commit(acc1_full(ab.idx));
+          ptx::umma_commit(slab_empty(sl.idx));      // 1 of 5 arrivals: c1 no longer reads the slab
         }
-      };
-      auto do_c2 = [&](int n) {
-        const int s = n % nBuf;
-        ptx::mbar_wait(g_full(s), (n / nBuf) & 1);
-        ptx::mbar_wait(acc2_empty(s), ((n / nBuf) & 1) ^ 1u);
-        ptx::tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc2_col + s * C;
-        for (int cb = 0; cb < nCB2; ++cb) {
-          const uint32_t abase = sG + (s * nCB2 + cb) * g_bytes;
-          for (int j = 0; j < kTaps; ++j, ++wc) {
-            uint32_t bbase;
-            int ws = 0;
-            if (stationary) {
-              bbase = sW + nbox1 * w1_tx + (cb * kTaps + j) * w2_tx;
-            } else {
-              ws = wc % nW;
-              ptx::mbar_wait(w_full(ws), (wc / nW) & 1);
-              ptx::tc_fence_after();
-              bbase = sW + ws * w_slot;
-            }
-            const uint64_t ad0 = dhi2 | ((abase + tap_stride2 * j) >> 4), bd0 = dhi2 | (bbase >> 4);
-            if (leader) {
-              for (int kk = 0; kk < nk2; ++kk)
-                ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
-              if (!stationary) ptx::umma_commit(w_empty(ws));
-            }
-          }
-        }
-        if (leader) {
-          ptx::umma_commit(acc2_full(s));
-          ptx::umma_commit(g_empty(s));
-        }
-      };
-      for (int n = 0; n <= my_tiles; ++n) {
-        if (pipelined) { if (n < my_tiles) do_c1(n); if (n >= 1) do_c2(n - 1); }
-        else           { if (n >= 1) do_c2(n - 1); if (n < my_tiles) do_c1(n); }
+        sl.next(nSlab); ab.next(G::NBUF);
       }
     }
     __syncwarp();
-  } else if (warp < 6) {
+  } else if (warp == 2) {
+    // =================== c2 MMA issuer ===================
+    if (my_tiles > 0) {
+      const bool leader = ptx::elect_one();
+      const int nW2 = rt.nW2;
+      const uint32_t idesc = rt.idesc;
+      const uint64_t dhi = ptx::umma_smem_desc(0, G::rb2, 0);
+      Cursor gb{0, 0}, wr{0, 0};
+      if (G::STATIONARY) { ptx::mbar_wait(w_all, 0); ptx::tc_fence_after(); }
+      for (int n = 0; n < my_tiles; ++n) {
+        ptx::mbar_wait(g_full(gb.idx), gb.phase);
+        ptx::mbar_wait(acc2_empty(gb.idx), gb.phase ^ 1u);
+        ptx::tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc2_col + gb.idx * C;
+        const uint32_t a16 = (sG + gb.idx * G::G_SET) >> 4;
+#pragma unroll
+        for (int cb = 0; cb < G::nCB2; ++cb) {
+#pragma unroll
+          for (int j = 0; j < KT; ++j) {
+            const uint64_t ad0 = dhi | (uint64_t)(a16 + cb * (G::G_BYTES >> 4) + j * (G::rb2 >> 4));
+#pragma unroll
+            for (int h = 0; h < G::NS; ++h) {
+              uint32_t b16;
+              if (G::STATIONARY) {
+                b16 = (sW2 + (cb * KT + j) * G::W2_TX) >> 4;
+              } else {
+                ptx::mbar_wait(w2_full(wr.idx), wr.phase);
+                ptx::tc_fence_after();
+                b16 = (sW2 + wr.idx * G::W2_TX) >> 4;
+              }
+              const uint64_t bd0 = dhi | (uint64_t)b16;
+              if (leader) {
+#pragma unroll
+                for (int kk = 0; kk < G::NK2; ++kk)
+                  ptx::umma_f16(d_tmem + h * G::NMMA, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
+                if (!G::STATIONARY) ptx::umma_commit(w2_empty(wr.idx));
+              }
+              if (!G::STATIONARY) wr.next(nW2);
+            }
+          }
+        }
+        if (leader) {
+          ptx::umma_commit(acc2_full(gb.idx));
+          ptx::umma_commit(g_empty(gb.idx));
+        }
+        gb.next(G::NBUF);
+      }
+    }
+    __syncwarp();
+  } else if (warp >= 4 && warp < 8) {
     // =================== epilogue 1: gate -> G tile in shared memory ===================
     const int q = warp & 3, r = q * 32 + lane;
-    const int half = g.C >> 1;
-    for (int n = 0; n < my_tiles; ++n) {
-      int b, t0; tile_coords(n, b, t0);
-      const int s = n % g.nBuf;
+    Cursor gb{0, 0};
+    for (int n = 0; n < my_tiles; ++n, tile_next()) {
+      tile_seek();
+      const int b = cur_b, t0 = (cur_tile - s_tile_prefix[cur_b]) * G::T_OUT;
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
-      const int t = t0 - g.p2 + r;
+      const int t = t0 - G::P2 + r;
       const bool live = t >= 0 && t < valid;     // G outside the sequence is the conv's zero padding
-      ptx::mbar_wait(acc1_full(s), (n / g.nBuf) & 1);
-      ptx::mbar_wait(g_empty(s), ((n / g.nBuf) & 1) ^ 1u);
-      ptx::tc_fence_after();
-      const uint32_t trow = tmem_base + acc1_col + s * g.C + (static_cast<uint32_t>(q * 32) << 16);
       const float* bias = a.bias1 + (long long)b * a.bias1_bstride;
-      for (int c0 = 0; c0 < half; c0 += 16) {
+      const int s = gb.idx;
+      ptx::mbar_wait(acc1_full(s), gb.phase);
+      ptx::mbar_wait(g_empty(s), gb.phase ^ 1u);
+      ptx::tc_fence_after();
+      const uint32_t trow = tmem_base + acc1_col + s * C + (static_cast<uint32_t>(q * 32) << 16);
+      const uint32_t grow = sG + s * G::G_SET + r * G::rb2;
+#pragma unroll
+      for (int c0 = 0; c0 < G::C2; c0 += 16) {
+        float ba[16], bb[16];
+        load16(bias + c0, ba);                   // issued before the TMEM loads so both latencies overlap
+        load16(bias + G::C2 + c0, bb);
         uint32_t ra[16], rb[16];
         ptx::tmem_ld16(trow + c0, ra);
-        ptx::tmem_ld16(trow + half + c0, rb);
+        ptx::tmem_ld16(trow + G::C2 + c0, rb);
         ptx::tmem_ld_wait();
-        float ba[16], bb[16];
-        load16(bias + c0, ba);
-        load16(bias + half + c0, bb);
         uint32_t p[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          float v0 = live ? gate_fn<false>(__uint_as_float(ra[2 * i]) + ba[2 * i], __uint_as_float(rb[2 * i]) + bb[2 * i]) : 0.f;
-          float v1 = live ? gate_fn<false>(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1]) : 0.f;
-          p[i] = Pack16<OpT>::pack2(v0, v1);
+          float v0 = gate3(__uint_as_float(ra[2 * i]) + ba[2 * i], __uint_as_float(rb[2 * i]) + bb[2 * i]);
+          float v1 = gate3(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1]);
+          p[i] = live ? Pack16<OpT>::pack2(v0, v1) : 0u;
         }
         // channel c0..c0+15 of row r -> block cb2, two 16-byte chunks, swizzled like a TMA write would
-        const int cb2 = c0 / g.BK2, cin = c0 - cb2 * g.BK2;
-        const uint32_t rowaddr = sG + (s * g.nCB2 + cb2) * g.g_bytes + r * g.rb2 + cin * 2;
-        st_shared_v4(swz_addr(rowaddr, g.rb2), p[0], p[1], p[2], p[3]);
-        st_shared_v4(swz_addr(rowaddr + 16, g.rb2), p[4], p[5], p[6], p[7]);
+        constexpr int dummy = 0; (void)dummy;
+        const int cb2 = c0 / G::BK2, cin = c0 - cb2 * G::BK2;
+        const uint32_t rowaddr = grow + cb2 * G::G_BYTES + cin * 2;
+        st_shared_v4(swz_addr<G::rb2>(rowaddr), p[0], p[1], p[2], p[3]);
+        st_shared_v4(swz_addr<G::rb2>(rowaddr + 16), p[4], p[5], p[6], p[7]);
       }
       fence_proxy_async_smem();                  // generic-proxy smem writes -> visible to the tensor core (async proxy)
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) { ptx::mbar_arrive(g_full(s)); ptx::mbar_arrive(acc1_empty(s)); }
+      gb.next(G::NBUF);
     }
-  } else if (warp < 10) {
+  } else if (warp >= 8 && warp < 12) {
     // =================== epilogue 2: bias + residual + leaky_relu -> global ===================
     const int q = warp & 3, r = q * 32 + lane;
-    for (int n = 0; n < my_tiles; ++n) {
-      int b, t0; tile_coords(n, b, t0);
-      const int s = n % g.nBuf, ss = n % g.nSlab;
+    const int nSlab = rt.nSlab;
+    const uint32_t slab_bytes = rt.slab_bytes;
+    const int srow = r + G::P2 + rt.p1;          // slab row holding y_in[t]
+    Cursor ab{0, 0}, sl{0, 0};
+    for (int n = 0; n < my_tiles; ++n, tile_next()) {
+      tile_seek();
+      const int b = cur_b, t0 = (cur_tile - s_tile_prefix[cur_b]) * G::T_OUT;
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
       const int t = t0 + r;
-      const bool in_range = r < g.T_out && t < a.L;
+      const bool in_range = r < G::T_OUT && t < a.L;
       const bool live = t < valid;
-      ptx::mbar_wait(acc2_full(s), (n / g.nBuf) & 1);
-      ptx::mbar_wait(slab_full(ss), (n / g.nSlab) & 1);      // acquire the TMA-written slab for the residual reads
+      const int s = ab.idx, ss = sl.idx;
+      ptx::mbar_wait(acc2_full(s), ab.phase);
+      ptx::mbar_wait(slab_full(ss), sl.phase);      // acquire the TMA-written slab for the residual reads
       ptx::tc_fence_after();
-      const uint32_t trow = tmem_base + acc2_col + s * g.C + (static_cast<uint32_t>(q * 32) << 16);
-      const long long orow = ((long long)b * a.L + t) * g.C;
-      const int srow = r + g.p2 + g.p1;          // slab row holding y_in[t]
-      for (int c0 = 0; c0 < g.C; c0 += 16) {
+      const uint32_t trow = tmem_base + acc2_col + s * C + (static_cast<uint32_t>(q * 32) << 16);
+      const long long orow = ((long long)b * a.L + t) * C;
+      const uint32_t yrow = sSlab + ss * slab_set + srow * G::rb1;
+#pragma unroll
+      for (int c0 = 0; c0 < C; c0 += 16) {
+        float bv[16];
+        load16(a.bias2 + c0, bv);
+        const int cb = c0 / G::BK1, cin = c0 - cb * G::BK1;
+        const uint32_t yaddr = yrow + cb * slab_bytes + cin * 2;
+        const uint4 y0 = ld_shared_v4(swz_addr<G::rb1>(yaddr)), y1 = ld_shared_v4(swz_addr<G::rb1>(yaddr + 16));
         uint32_t ra[16];
         ptx::tmem_ld16(trow + c0, ra);
         ptx::tmem_ld_wait();
         if (in_range) {
-          float bv[16], v[16];
-          load16(a.bias2 + c0, bv);
-          const int cb = c0 / g.BK1, cin = c0 - cb * g.BK1;
-          const uint32_t yaddr = sSlab + (ss * g.nCB1 + cb) * g.slab_bytes + srow * g.rb1 + cin * 2;
-          const uint4 y0 = ld_shared_v4(swz_addr(yaddr, g.rb1)), y1 = ld_shared_v4(swz_addr(yaddr + 16, g.rb1));
+          float v[16];
           const uint32_t yw[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
@@ -367,7 +448,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           if (a.acc_mode & RB_EMIT_NEXT) {
             if (a.nxt_f32) store16(a.nxt_f32 + orow + c0, v);
             if (a.nxt_op) store_op16<OpT>(reinterpret_cast<OpT*>(a.nxt_op) + (a.nxt_split ? 2 : 1) * orow + c0, v, 0.1f,
-                                          a.nxt_split ? g.C : 0);
+                                          a.nxt_split ? C : 0);
           }
           if (a.y_out) store_op16<OpT>(reinterpret_cast<OpT*>(a.y_out) + orow + c0, v, 0.1f, 0);
         }
@@ -375,6 +456,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) { ptx::mbar_arrive(acc2_empty(s)); ptx::mbar_arrive(slab_empty(ss)); }
+      ab.next(G::NBUF); sl.next(nSlab);
     }
   }
 
@@ -382,7 +464,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, g.tmem_cols);
+    ptx::tmem_dealloc(tmem_base, G::TMEM_COLS);
   }
 }
 
@@ -390,50 +472,44 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 // host side
 // ---------------------------------------------------------------------------
 bool rb_fused_supported(int C, int k, int dil, int B) {
-  if (!(C == 32 || (C % 64 == 0 && C >= 64 && C <= 256))) return false;
-  if (k % 2 != 1 || k < 1 || dil < 1 || B > kRbMaxB) return false;
-  if (kTileM - (k - 1) < 32) return false;
-  if (((kTileM + (k - 1) * dil + 7) & ~7) > 256) return false;
+  if (!(C == 32 || C == 64 || C == 128 || C == 256)) return false;
+  if (!(k == 3 || k == 7 || k == 11)) return false;
+  if (dil < 1 || B > kRbMaxB) return false;
+  if (((kTileM + (k - 1) * dil + 7) & ~7) > 256) return false;   // TMA box rows
   return true;
 }
 
-cudaError_t launch_rb_fused(const RbLaunch& L, int op, cudaStream_t stream) {
-  if (op == OP_F32 || !rb_fused_supported(L.C, L.k, L.dil, L.B)) return cudaErrorNotSupported;
-  RbGeom g{};
-  g.C = L.C; g.k = L.k; g.dil = L.dil;
-  g.p2 = (L.k - 1) / 2; g.p1 = (L.k - 1) * L.dil / 2; g.T_out = kTileM - (L.k - 1);
-  g.BK1 = L.C >= 64 ? 64 : L.C; g.nCB1 = L.C / g.BK1; g.rb1 = g.BK1 * 2;
-  const int C2 = L.C / 2;
-  g.BK2 = C2 >= 64 ? 64 : C2; g.nCB2 = C2 / g.BK2; g.rb2 = g.BK2 * 2;
-  g.R1 = (kTileM + (L.k - 1) * L.dil + 7) & ~7;
-  g.RG = (kTileM + (L.k - 1) + 7) & ~7;
-  g.slab_bytes = ((uint32_t)g.R1 * g.rb1 + 1023u) & ~1023u;
-  g.g_bytes = ((uint32_t)g.RG * g.rb2 + 1023u) & ~1023u;
-  g.w1_tx = (uint32_t)L.C * g.rb1; g.w2_tx = (uint32_t)L.C * g.rb2;
-  g.w_slot = (g.w1_tx + 1023u) & ~1023u;
-  const uint32_t budget = 220 * 1024;
-  const uint32_t nbox1 = L.k * g.nCB1, nbox2 = L.k * g.nCB2;
-  const uint32_t w_all_bytes = nbox1 * g.w1_tx + nbox2 * g.w2_tx;
-  g.nBuf = (4 * L.C <= 512) ? 2 : 1;
-  const uint32_t slab_set = g.nCB1 * g.slab_bytes, g_set = g.nCB2 * g.g_bytes;
-  const uint32_t fixed = 1024 + 512 + g.nBuf * g_set;
-  g.stationary = 0; g.nW = 0; g.nSlab = 0;
-  if (fixed + w_all_bytes + 2 * slab_set <= budget) {
-    // small stages: weights resident, deep activation prefetch
-    g.stationary = 1;
-    g.nSlab = (int)((budget - fixed - w_all_bytes) / slab_set);
-    if (g.nSlab > 4) g.nSlab = 4;
+namespace {
+
+template <typename OpT, int C, int KT>
+cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
+  using G = RbT<C, KT>;
+  RbRt rt{};
+  rt.dil = L.dil; rt.p1 = (KT - 1) * L.dil / 2;
+  rt.R1 = (kTileM + (KT - 1) * L.dil + 7) & ~7;
+  rt.slab_bytes = ((uint32_t)rt.R1 * G::rb1 + 1023u) & ~1023u;
+  const uint32_t slab_set = G::nCB1 * rt.slab_bytes;
+  const uint32_t fixed = 1024 + 512 + G::NBUF * G::G_SET;
+  if (G::STATIONARY) {
+    if (fixed + G::W_ALL + 2 * slab_set > kRbSmemBudget) return cudaErrorNotSupported;
+    rt.nSlab = (int)((kRbSmemBudget - fixed - G::W_ALL) / slab_set);
+    if (rt.nSlab > 4) rt.nSlab = 4;
   } else {
-    g.nSlab = g.nBuf == 2 ? 2 : 1;
-    if (fixed + g.nSlab * slab_set + 2 * g.w_slot > budget) { g.nSlab = 1; }
-    if (fixed + g.nSlab * slab_set + 2 * g.w_slot > budget) return cudaErrorNotSupported;
-    g.nW = (int)((budget - fixed - g.nSlab * slab_set) / g.w_slot);
-    if (g.nW > 8) g.nW = 8;
+    // streamed weights: at least 2 ring slots per conv, then as many slabs as NBUF can use, rest to the rings (2:1)
+    rt.nSlab = G::NBUF == 2 ? 2 : 1;
+    if (fixed + rt.nSlab * slab_set + 2 * G::W1_TX + 2 * G::W2_TX > kRbSmemBudget) rt.nSlab = 1;
+    if (fixed + rt.nSlab * slab_set + 2 * G::W1_TX + 2 * G::W2_TX > kRbSmemBudget) return cudaErrorNotSupported;
+    uint32_t left = kRbSmemBudget - fixed - rt.nSlab * slab_set;
+    rt.nW1 = 2; rt.nW2 = 2; left -= 2 * G::W1_TX + 2 * G::W2_TX;
+    while (true) {
+      bool grew = false;
+      if (rt.nW1 < 8 && left >= G::W1_TX) { ++rt.nW1; left -= G::W1_TX; grew = true; }
+      if (rt.nW1 < 8 && left >= G::W1_TX) { ++rt.nW1; left -= G::W1_TX; grew = true; }
+      if (rt.nW2 < 8 && left >= G::W2_TX) { ++rt.nW2; left -= G::W2_TX; grew = true; }
+      if (!grew) break;
+    }
   }
-  uint32_t cols = 32;
-  while (cols < (uint32_t)(2 * g.nBuf * L.C)) cols <<= 1;
-  g.tmem_cols = cols;
-  g.idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM, L.C);
+  rt.idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM, G::NMMA);
 
   TmaEncodeFn enc = tma_encode_fn();
   if (!enc) return cudaErrorNotSupported;
@@ -441,49 +517,69 @@ cudaError_t launch_rb_fused(const RbLaunch& L, int op, cudaStream_t stream) {
   auto swz = [](int rb) { return rb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (rb == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B); };
   CUtensorMap tmY, tmW1, tmW2;
   cuuint32_t estr[3] = {1, 1, 1};
+  bool ok = true;
   {
-    cuuint64_t dims[3] = {(cuuint64_t)L.C, (cuuint64_t)L.a.L, (cuuint64_t)L.B};
-    cuuint64_t strides[2] = {(cuuint64_t)L.C * 2, (cuuint64_t)L.a.L * L.C * 2};
-    cuuint32_t box[3] = {(cuuint32_t)g.BK1, (cuuint32_t)g.R1, 1};
-    if (enc(&tmY, dt, 3, const_cast<void*>(L.y_in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(g.rb1),
-            CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", L.C, L.k); return cudaErrorInvalidValue; }
+    cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)L.a.L, (cuuint64_t)L.B};
+    cuuint64_t strides[2] = {(cuuint64_t)C * 2, (cuuint64_t)L.a.L * C * 2};
+    cuuint32_t box[3] = {(cuuint32_t)G::BK1, (cuuint32_t)rt.R1, 1};
+    ok &= enc(&tmY, dt, 3, const_cast<void*>(L.y_in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(G::rb1),
+              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
   }
   {
-    cuuint64_t dims[2] = {(cuuint64_t)L.k * L.C, (cuuint64_t)L.C};
-    cuuint64_t strides[1] = {(cuuint64_t)L.k * L.C * 2};
-    cuuint32_t box[2] = {(cuuint32_t)g.BK1, (cuuint32_t)L.C};
-    if (enc(&tmW1, dt, 2, const_cast<void*>(L.w1), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(g.rb1),
-            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", L.C, L.k); return cudaErrorInvalidValue; }
+    cuuint64_t dims[2] = {(cuuint64_t)KT * C, (cuuint64_t)C};
+    cuuint64_t strides[1] = {(cuuint64_t)KT * C * 2};
+    cuuint32_t box[2] = {(cuuint32_t)G::BK1, (cuuint32_t)G::NMMA};
+    ok &= enc(&tmW1, dt, 2, const_cast<void*>(L.w1), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(G::rb1),
+              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
   }
   {
-    cuuint64_t dims[2] = {(cuuint64_t)L.k * C2, (cuuint64_t)L.C};
-    cuuint64_t strides[1] = {(cuuint64_t)L.k * C2 * 2};
-    cuuint32_t box[2] = {(cuuint32_t)g.BK2, (cuuint32_t)L.C};
-    if (enc(&tmW2, dt, 2, const_cast<void*>(L.w2), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(g.rb2),
-            CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", L.C, L.k); return cudaErrorInvalidValue; }
+    cuuint64_t dims[2] = {(cuuint64_t)KT * G::C2, (cuuint64_t)C};
+    cuuint64_t strides[1] = {(cuuint64_t)KT * G::C2 * 2};
+    cuuint32_t box[2] = {(cuuint32_t)G::BK2, (cuuint32_t)G::NMMA};
+    ok &= enc(&tmW2, dt, 2, const_cast<void*>(L.w2), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(G::rb2),
+              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
   }
-  const size_t smem = 1024 + (size_t)g.nSlab * slab_set + (size_t)g.nBuf * g_set + (g.stationary ? (size_t)w_all_bytes : (size_t)g.nW * g.w_slot) + 8 * (21 + 2 * g.nW) + 64;
+  if (!ok) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", C, KT); return cudaErrorInvalidValue; }
+  const size_t wbytes = G::STATIONARY ? (size_t)G::W_ALL : (size_t)rt.nW1 * G::W1_TX + (size_t)rt.nW2 * G::W2_TX;
+  const size_t smem = 1024 + (size_t)rt.nSlab * slab_set + (size_t)G::NBUF * G::G_SET + wbytes + 8 * 53 + 64;
   static int num_sms = 0;
-  static std::once_flag once;
+  static std::once_flag once;     // one flag per template instantiation
+  static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
     // opt-in limit is 227 KB per CTA INCLUDING the kernel's static shared memory (tile table)
-    cudaError_t e1 = cudaFuncSetAttribute(rb_fused_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 222 * 1024);
-    cudaError_t e2 = cudaFuncSetAttribute(rb_fused_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 222 * 1024);
-    if (e1 != cudaSuccess || e2 != cudaSuccess) fprintf(stderr, "rb_fused: cudaFuncSetAttribute failed: %s\n", cudaGetErrorString(e1 != cudaSuccess ? e1 : e2));
+    attr_err = cudaFuncSetAttribute(rb_fused_kernel<OpT, C, KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
     int dev = 0; cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
   });
+  if (attr_err != cudaSuccess) { fprintf(stderr, "rb_fused: cudaFuncSetAttribute failed: %s\n", cudaGetErrorString(attr_err)); return attr_err; }
   // upper bound on tiles -> grid (persistent: at most one CTA per SM)
-  const long long max_tiles = (long long)L.B * ((L.a.L + g.T_out - 1) / g.T_out);
+  const long long max_tiles = (long long)L.B * ((L.a.L + G::T_OUT - 1) / G::T_OUT);
   int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
   if (grid < 1) grid = 1;
-  if (op == OP_BF16) rb_fused_kernel<__nv_bfloat16><<<grid, kRbThreads, smem, stream>>>(tmY, tmW1, tmW2, L.a, g);
-  else rb_fused_kernel<__half><<<grid, kRbThreads, smem, stream>>>(tmY, tmW1, tmW2, L.a, g);
+  rb_fused_kernel<OpT, C, KT><<<grid, kRbThreads, smem, stream>>>(tmY, tmW1, tmW2, L.a, rt);
   cudaError_t le = cudaGetLastError();
   if (le != cudaSuccess)
-    fprintf(stderr, "rb_fused launch failed (%s): C=%d k=%d dil=%d grid=%d smem=%zu nSlab=%d nBuf=%d nW=%d stat=%d tmem=%u\n", cudaGetErrorString(le),
-            L.C, L.k, L.dil, grid, smem, g.nSlab, g.nBuf, g.nW, g.stationary, g.tmem_cols);
+    fprintf(stderr, "rb_fused launch failed (%s): C=%d k=%d dil=%d grid=%d smem=%zu nSlab=%d nW=%d/%d\n", cudaGetErrorString(le),
+            C, KT, L.dil, grid, smem, rt.nSlab, rt.nW1, rt.nW2);
   return le;
+}
+
+template <typename OpT>
+cudaError_t dispatch(const RbLaunch& L, int op, cudaStream_t s) {
+#define VITSB_RB_CASE(CC, KK) if (L.C == CC && L.k == KK) return launch_t<OpT, CC, KK>(L, op, s);
+  VITSB_RB_CASE(32, 3) VITSB_RB_CASE(32, 7) VITSB_RB_CASE(32, 11)
+  VITSB_RB_CASE(64, 3) VITSB_RB_CASE(64, 7) VITSB_RB_CASE(64, 11)
+  VITSB_RB_CASE(128, 3) VITSB_RB_CASE(128, 7) VITSB_RB_CASE(128, 11)
+  VITSB_RB_CASE(256, 3) VITSB_RB_CASE(256, 7) VITSB_RB_CASE(256, 11)
+#undef VITSB_RB_CASE
+  return cudaErrorNotSupported;
+}
+
+}  // namespace
+
+cudaError_t launch_rb_fused(const RbLaunch& L, int op, cudaStream_t stream) {
+  if (op == OP_F32 || !rb_fused_supported(L.C, L.k, L.dil, L.B)) return cudaErrorNotSupported;
+  return op == OP_BF16 ? dispatch<__nv_bfloat16>(L, op, stream) : dispatch<__half>(L, op, stream);
 }
 
 }  // namespace vitsb
