@@ -32,6 +32,7 @@ struct RbArgs {
   const float* bias2;
   int L, B;
   const int* len; int len_mul;
+  const void* y_res;       // = RbLaunch::y_in (set by launch_rb_fused): residual rows re-read from global when C >= 64
 };
 struct RbLaunch {
   const void* y_in;        // op_t [B][L][C] = leaky_relu(x, 0.1)

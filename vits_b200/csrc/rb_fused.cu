@@ -20,16 +20,21 @@
 // division (the first version spent ~500 cycles of uniform-datapath instructions per tap
 // around 128 cycles of tensor work; profiles/r01_c_ncu_rb_fused_full_summary.txt).
 //
-// Roles (13 warps, 416 threads):
+// Roles (12 warps, 384 threads):
 //   warp 0      activation-slab TMA producer
-//   warp 1      c1 MMA issuer          warp 2   c2 MMA issuer
-//   warp 3      c1 weight TMA producer warp 12  c2 weight TMA producer
+//   warp 1      c1 MMA issuer (and c2 in streamed-weight mode)
+//   warp 2      c2 MMA issuer (resident-weight mode: small N needs two issuing threads)
+//   warp 3      weight TMA producer
 //   warps 4-7   epilogue 1: TMEM -> bias + cond + gate -> G tile in smem (swizzled like TMA)
 //   warps 8-11  epilogue 2: TMEM -> bias + residual + leaky_relu -> global (+ MRF accumulate)
-// Weights are resident in smem when they fit (C <= 64) and streamed through two
-// independent rings (one per conv, so neither issuer can starve the other) otherwise.
-// With C <= 128 slabs, G tiles and both TMEM accumulators are double-buffered:
+// Weights are resident in smem when they fit (C <= 64) and streamed through one ring in
+// the issuing warp's fixed order otherwise.  G tiles and both TMEM accumulators are
+// NBUF-deep (4 for C <= 64, where a tile is ~500 tensor cycles and the mbarrier / commit
+// round trips between the four stages dominate; 2 for C = 128; 1 for C = 256):
 // c1(n+1) | gate(n) | c2(n) | store(n-1) overlap on consecutive tiles.
+// For C >= 64 the store epilogue re-reads the residual rows from global memory (L2 hits:
+// TMA fetched them microseconds earlier), so a slab is released as soon as c1's MMAs
+// retire and 2-3 slabs are enough to keep loads ahead of the tensor pipe.
 #include "common.h"
 #include "kernels.h"
 #include "ptx.h"
@@ -40,7 +45,7 @@
 
 namespace vitsb {
 
-constexpr int kRbThreads = 416;
+constexpr int kRbThreads = 384;
 constexpr int kRbMaxB = 512;
 constexpr uint32_t kRbSmemBudget = 220 * 1024;
 
@@ -52,16 +57,16 @@ struct RbT {
   static constexpr int P2 = (KT - 1) / 2, T_OUT = kTileM - (KT - 1);
   static constexpr int RG = (kTileM + (KT - 1) + 7) & ~7;
   static constexpr uint32_t G_BYTES = ((uint32_t)RG * rb2 + 1023u) & ~1023u;     // per channel block
-  // C = 256: every MMA / weight box covers NMMA = 128 of the 256 output columns (two N halves per (cb, tap)),
-  // so a ring slot is 16 KB instead of 32 KB and more boxes fit next to the 4-block slab
-  static constexpr int NS = C > 128 ? C / 128 : 1, NMMA = C / NS;
-  static constexpr uint32_t W1_TX = (uint32_t)NMMA * rb1, W2_TX = (uint32_t)NMMA * rb2;  // bytes per (cb, tap, half) weight box
-  static constexpr int NBOX1 = KT * nCB1 * NS, NBOX2 = KT * nCB2 * NS;
+  static constexpr uint32_t W1_TX = (uint32_t)C * rb1, W2_TX = (uint32_t)C * rb2;  // bytes per (cb, tap) weight box
+  static constexpr uint32_t W_SLOT = W1_TX > W2_TX ? W1_TX : W2_TX;               // ring slot (streamed mode)
+  static constexpr int NBOX1 = KT * nCB1, NBOX2 = KT * nCB2;
   static constexpr uint32_t W_ALL = NBOX1 * W1_TX + NBOX2 * W2_TX;
-  static constexpr int NBUF = (4 * C <= 512) ? 2 : 1;                             // G tiles / TMEM accumulator sets
+  static constexpr int NBUF = C <= 64 ? 4 : (C <= 128 ? 2 : 1);                   // G tiles / TMEM accumulator sets
   static constexpr uint32_t G_SET = nCB2 * G_BYTES;
-  static constexpr bool STATIONARY = C <= 64;                                     // W_ALL <= 135 KB
-  static constexpr uint32_t TMEM_COLS = (2 * NBUF * C <= 32) ? 32 : (2 * NBUF * C <= 64 ? 64 : (2 * NBUF * C <= 128 ? 128 : (2 * NBUF * C <= 256 ? 256 : 512)));
+  static constexpr bool STATIONARY = C <= 64;                                     // W_ALL <= 135 KB: resident weights, two issuers
+  static constexpr bool RES_GLOBAL = C >= 64;                                     // residual rows re-read from global (L2)
+  static constexpr uint32_t TMEM_COLS = 2 * NBUF * C <= 256 ? 256 : 512;
+  static_assert(2 * NBUF * C <= 512, "TMEM columns");
 };
 
 // run-time geometry (depends on the dilation and the smem left after the fixed parts)
@@ -69,8 +74,8 @@ struct RbRt {
   int dil, p1;               // c1 dilation, (k-1)*dil/2
   int R1;                    // slab rows (multiple of 8)
   uint32_t slab_bytes;       // per channel block (multiple of 1024)
-  int nSlab;                 // activation slab buffers (1..4)
-  int nW1, nW2;              // weight ring slots (streamed mode)
+  int nSlab;                 // activation slab buffers (1..8)
+  int nW;                    // weight ring slots (streamed mode, 2..8)
   uint32_t idesc;
 };
 
@@ -96,17 +101,33 @@ struct Cursor {
   __device__ __forceinline__ void next(int n) { if (++idx == n) { idx = 0; phase ^= 1u; } }
 };
 
-// tanh(a) * sigmoid(b) with 3 MUFU ops (2x ex2, 1x rcp):
-//   tanh(a) = (1 - e^{-2a}) / (1 + e^{-2a}),  sigmoid(b) = 1 / (1 + e^{-b})
-// a is clamped at -20 (tanh == -1 in fp32 there) and b at -40 so the product of the
-// denominators stays below 2^126 (the __fdividef range).
-__device__ __forceinline__ float gate3(float a, float b) {
-  const float ea = exp2f(-2.885390081777927f * fmaxf(a, -20.f));
-  const float eb = exp2f(-1.4426950408889634f * fmaxf(b, -40.f));
+// tanh(a) * sigmoid(b) for the G tile (rounded to the 16-bit operand type right after).
+//   default: 2 MUFU.TANH, sigmoid(b) = 0.5 + 0.5 tanh(b/2); tanh.approx has ~2^-11 relative
+//   error, the same size as the fp16 rounding of the result (parity measured in tests).
+//   VITSB_GATE_EXACT: 2x ex2 + rcp, ~1e-6 relative: (1 - e^-2a) / ((1 + e^-2a)(1 + e^-b)),
+//   a clamped at -20 and b at -40 so the denominator stays inside the __fdividef range.
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float gate_fast(float a, float b) {
+#ifdef VITSB_GATE_EXACT
+  const float ea = ex2_approx(-2.885390081777927f * fmaxf(a, -20.f));
+  const float eb = ex2_approx(-1.4426950408889634f * fmaxf(b, -40.f));
   return __fdividef(1.0f - ea, (1.0f + ea) * (1.0f + eb));
+#else
+  const float th = 0.5f * tanh_approx(a);
+  return fmaf(th, tanh_approx(0.5f * b), th);
+#endif
 }
 
-template <typename OpT, int C, int KT>
+template <typename OpT, int C, int KT, bool LAST>
 __global__ void __launch_bounds__(kRbThreads, 1)
 rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmW1,
                 const __grid_constant__ CUtensorMap tmW2, const RbArgs a, const RbRt rt) {
@@ -119,22 +140,20 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   const uint32_t slab_set = G::nCB1 * rt.slab_bytes;
   const uint32_t sSlab = smem_base;                                            // [nSlab][nCB1][slab_bytes]
   const uint32_t sG = sSlab + rt.nSlab * slab_set;                             // [NBUF][nCB2][G_BYTES]
-  const uint32_t sW1 = sG + G::NBUF * G::G_SET;                                // all boxes, or ring 1
-  const uint32_t sW2 = sW1 + (G::STATIONARY ? G::NBOX1 * G::W1_TX : rt.nW1 * G::W1_TX);   // c2 boxes, or ring 2
-  const uint32_t bars = sW2 + (G::STATIONARY ? G::NBOX2 * G::W2_TX : rt.nW2 * G::W2_TX);
+  const uint32_t sW = sG + G::NBUF * G::G_SET;                                 // all boxes (c1 then c2), or the ring
+  const uint32_t sW2 = sW + G::NBOX1 * G::W1_TX;                               // resident mode: c2 boxes
+  const uint32_t bars = sW + (G::STATIONARY ? G::W_ALL : rt.nW * G::W_SLOT);
   auto slab_full = [&](int i) { return bars + 8u * i; };
-  auto slab_empty = [&](int i) { return bars + 8u * (4 + i); };
-  auto acc1_full = [&](int i) { return bars + 8u * (8 + i); };
-  auto acc1_empty = [&](int i) { return bars + 8u * (10 + i); };
-  auto acc2_full = [&](int i) { return bars + 8u * (12 + i); };
-  auto acc2_empty = [&](int i) { return bars + 8u * (14 + i); };
-  auto g_full = [&](int i) { return bars + 8u * (16 + i); };
-  auto g_empty = [&](int i) { return bars + 8u * (18 + i); };
-  const uint32_t w_all = bars + 8u * 20;
-  auto w1_full = [&](int i) { return bars + 8u * (21 + i); };
-  auto w1_empty = [&](int i) { return bars + 8u * (29 + i); };
-  auto w2_full = [&](int i) { return bars + 8u * (37 + i); };
-  auto w2_empty = [&](int i) { return bars + 8u * (45 + i); };
+  auto slab_empty = [&](int i) { return bars + 8u * (8 + i); };
+  auto acc1_full = [&](int i) { return bars + 8u * (16 + i); };
+  auto acc1_empty = [&](int i) { return bars + 8u * (20 + i); };
+  auto acc2_full = [&](int i) { return bars + 8u * (24 + i); };
+  auto acc2_empty = [&](int i) { return bars + 8u * (28 + i); };
+  auto g_full = [&](int i) { return bars + 8u * (32 + i); };
+  auto g_empty = [&](int i) { return bars + 8u * (36 + i); };
+  const uint32_t w_all = bars + 8u * 40;
+  auto w_full = [&](int i) { return bars + 8u * (41 + i); };
+  auto w_empty = [&](int i) { return bars + 8u * (49 + i); };
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform role id
 
@@ -151,17 +170,15 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   }
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmY); ptx::prefetch_tmap(&tmW1); ptx::prefetch_tmap(&tmW2);
-    for (int i = 0; i < 4; ++i) { ptx::mbar_init(slab_full(i), 1); ptx::mbar_init(slab_empty(i), 5); }   // 1 MMA commit + 4 epilogue-2 warps
+    // slab release: c1's MMA commit, plus the 4 store-epilogue warps when they read the residual from the slab
+    for (int i = 0; i < 8; ++i) { ptx::mbar_init(slab_full(i), 1); ptx::mbar_init(slab_empty(i), G::RES_GLOBAL ? 1 : 5); }
     ptx::mbar_init(w_all, 1);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 4; ++i) {
       ptx::mbar_init(acc1_full(i), 1);  ptx::mbar_init(acc1_empty(i), 4);
       ptx::mbar_init(acc2_full(i), 1);  ptx::mbar_init(acc2_empty(i), 4);
       ptx::mbar_init(g_full(i), 4);     ptx::mbar_init(g_empty(i), 1);
     }
-    for (int i = 0; i < 8; ++i) {
-      ptx::mbar_init(w1_full(i), 1); ptx::mbar_init(w1_empty(i), 1);
-      ptx::mbar_init(w2_full(i), 1); ptx::mbar_init(w2_empty(i), 1);
-    }
+    for (int i = 0; i < 8; ++i) { ptx::mbar_init(w_full(i), 1); ptx::mbar_init(w_empty(i), 1); }
     ptx::mbar_fence_init();
   }
   if (warp == 1) ptx::tmem_alloc(ptx::smem_u32(&s_tmem), G::TMEM_COLS);
@@ -198,65 +215,64 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     }
     __syncwarp();
   } else if (warp == 3) {
-    // =================== c1 weight TMA producer (or: all resident weights, once) ===================
+    // =================== weight TMA producer ===================
     const bool leader = ptx::elect_one();
     if (G::STATIONARY) {
+      // every (conv, channel block, tap) box stays resident: one barrier, loaded once per CTA
       if (leader && my_tiles > 0) {
         ptx::mbar_expect_tx(w_all, G::W_ALL);
-        static_assert(!G::STATIONARY || G::NS == 1, "resident weights use whole-N boxes");
         for (int cb = 0; cb < G::nCB1; ++cb)
           for (int j = 0; j < KT; ++j)
-            ptx::tma_load_2d(sW1 + (cb * KT + j) * G::W1_TX, &tmW1, w_all, j * C + cb * G::BK1, 0);
+            ptx::tma_load_2d(sW + (cb * KT + j) * G::W1_TX, &tmW1, w_all, j * C + cb * G::BK1, 0);
         for (int cb = 0; cb < G::nCB2; ++cb)
           for (int j = 0; j < KT; ++j)
             ptx::tma_load_2d(sW2 + (cb * KT + j) * G::W2_TX, &tmW2, w_all, j * G::C2 + cb * G::BK2, 0);
       }
     } else {
-      const int nW1 = rt.nW1;
+      // one ring, filled in the issuing warp's consumption order: c1(0), [c1(n), c2(n-1)]..., c2(last)
+      const int nW = rt.nW;
       Cursor wr{0, 0};
-      for (int n = 0; n < my_tiles; ++n)
+      auto load_w1 = [&]() {
         for (int cb = 0; cb < G::nCB1; ++cb)
-          for (int j = 0; j < KT; ++j)
-            for (int h = 0; h < G::NS; ++h) {
-              ptx::mbar_wait(w1_empty(wr.idx), wr.phase ^ 1u);
-              if (leader) {
-                ptx::mbar_expect_tx(w1_full(wr.idx), G::W1_TX);
-                ptx::tma_load_2d(sW1 + wr.idx * G::W1_TX, &tmW1, w1_full(wr.idx), j * C + cb * G::BK1, h * G::NMMA);
-              }
-              wr.next(nW1);
+          for (int j = 0; j < KT; ++j) {
+            ptx::mbar_wait(w_empty(wr.idx), wr.phase ^ 1u);
+            if (leader) {
+              ptx::mbar_expect_tx(w_full(wr.idx), G::W1_TX);
+              ptx::tma_load_2d(sW + wr.idx * G::W_SLOT, &tmW1, w_full(wr.idx), j * C + cb * G::BK1, 0);
             }
+            wr.next(nW);
+          }
+      };
+      auto load_w2 = [&]() {
+        for (int cb = 0; cb < G::nCB2; ++cb)
+          for (int j = 0; j < KT; ++j) {
+            ptx::mbar_wait(w_empty(wr.idx), wr.phase ^ 1u);
+            if (leader) {
+              ptx::mbar_expect_tx(w_full(wr.idx), G::W2_TX);
+              ptx::tma_load_2d(sW + wr.idx * G::W_SLOT, &tmW2, w_full(wr.idx), j * G::C2 + cb * G::BK2, 0);
+            }
+            wr.next(nW);
+          }
+      };
+      for (int n = 0; n <= my_tiles; ++n) {
+        if (n < my_tiles) load_w1();
+        if (n >= 1) load_w2();
+      }
     }
     __syncwarp();
-  } else if (warp == 12) {
-    // =================== c2 weight TMA producer (streamed mode only) ===================
-    if (!G::STATIONARY) {
+  } else if (warp == 1 || warp == 2) {
+    // =================== MMA issuers (warp-uniform loops, elected lane issues) ===================
+    // resident weights: warp 1 issues c1, warp 2 issues c2, independently;
+    // streamed weights: warp 1 issues both in ring order c1(n), c2(n-1); warp 2 idles.
+    if (my_tiles > 0 && (warp == 1 || G::STATIONARY)) {
       const bool leader = ptx::elect_one();
-      const int nW2 = rt.nW2;
-      Cursor wr{0, 0};
-      for (int n = 0; n < my_tiles; ++n)
-        for (int cb = 0; cb < G::nCB2; ++cb)
-          for (int j = 0; j < KT; ++j)
-            for (int h = 0; h < G::NS; ++h) {
-              ptx::mbar_wait(w2_empty(wr.idx), wr.phase ^ 1u);
-              if (leader) {
-                ptx::mbar_expect_tx(w2_full(wr.idx), G::W2_TX);
-                ptx::tma_load_2d(sW2 + wr.idx * G::W2_TX, &tmW2, w2_full(wr.idx), j * G::C2 + cb * G::BK2, h * G::NMMA);
-              }
-              wr.next(nW2);
-            }
-      __syncwarp();
-    }
-  } else if (warp == 1) {
-    // =================== c1 MMA issuer (warp-uniform loop, elected lane issues) ===================
-    if (my_tiles > 0) {
-      const bool leader = ptx::elect_one();
-      const int nSlab = rt.nSlab, nW1 = rt.nW1;
+      const int nSlab = rt.nSlab, nW = rt.nW;
       const uint32_t slab_bytes = rt.slab_bytes, idesc = rt.idesc;
-      const uint32_t tap16 = ((uint32_t)rt.dil * G::rb1) >> 4;                  // tap stride in 16-byte units
-      const uint64_t dhi = ptx::umma_smem_desc(0, G::rb1, 0);
-      Cursor sl{0, 0}, ab{0, 0}, wr{0, 0};
+      const uint32_t tap16 = ((uint32_t)rt.dil * G::rb1) >> 4;                  // c1 tap stride in 16-byte units
+      const uint64_t dhi1 = ptx::umma_smem_desc(0, G::rb1, 0), dhi2 = ptx::umma_smem_desc(0, G::rb2, 0);
+      Cursor sl{0, 0}, ab{0, 0}, gb{0, 0}, wr{0, 0};
       if (G::STATIONARY) { ptx::mbar_wait(w_all, 0); ptx::tc_fence_after(); }
-      for (int n = 0; n < my_tiles; ++n) {
+      auto do_c1 = [&]() {
         ptx::mbar_wait(slab_full(sl.idx), sl.phase);
         ptx::mbar_wait(acc1_empty(ab.idx), ab.phase ^ 1u);
         ptx::tc_fence_after();
@@ -266,47 +282,32 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         for (int cb = 0; cb < G::nCB1; ++cb) {
 #pragma unroll
           for (int j = 0; j < KT; ++j) {
-            // descriptors differ only in their 14-bit start-address field (16-byte units)
-            const uint64_t ad0 = dhi | (uint64_t)(a16 + cb * (slab_bytes >> 4) + j * tap16);
-#pragma unroll
-            for (int h = 0; h < G::NS; ++h) {
-              uint32_t b16;
-              if (G::STATIONARY) {
-                b16 = (sW1 + (cb * KT + j) * G::W1_TX) >> 4;
-              } else {
-                ptx::mbar_wait(w1_full(wr.idx), wr.phase);
-                ptx::tc_fence_after();
-                b16 = (sW1 + wr.idx * G::W1_TX) >> 4;
-              }
-              const uint64_t bd0 = dhi | (uint64_t)b16;
-              if (leader) {
-#pragma unroll
-                for (int kk = 0; kk < G::NK1; ++kk)
-                  ptx::umma_f16(d_tmem + h * G::NMMA, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
-                if (!G::STATIONARY) ptx::umma_commit(w1_empty(wr.idx));
-              }
-              if (!G::STATIONARY) wr.next(nW1);
+            uint32_t b16;
+            if (G::STATIONARY) {
+              b16 = (sW + (cb * KT + j) * G::W1_TX) >> 4;
+            } else {
+              ptx::mbar_wait(w_full(wr.idx), wr.phase);
+              ptx::tc_fence_after();
+              b16 = (sW + wr.idx * G::W_SLOT) >> 4;
             }
+            // descriptors differ only in their 14-bit start-address field (16-byte units)
+            const uint64_t ad0 = dhi1 | (uint64_t)(a16 + cb * (slab_bytes >> 4) + j * tap16), bd0 = dhi1 | (uint64_t)b16;
+            if (leader) {
+#pragma unroll
+              for (int kk = 0; kk < G::NK1; ++kk)
+                ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
+              if (!G::STATIONARY) ptx::umma_commit(w_empty(wr.idx));
+            }
+            if (!G::STATIONARY) wr.next(nW);
           }
         }
         if (leader) {
           ptx::umma_commit(acc1_full(ab.idx));
-          ptx::umma_commit(slab_empty(sl.idx));      // 1 of 5 arrivals: c1 no longer reads the slab
+          ptx::umma_commit(slab_empty(sl.idx));      // c1 no longer reads the slab
         }
         sl.next(nSlab); ab.next(G::NBUF);
-      }
-    }
-    __syncwarp();
-  } else if (warp == 2) {
-    // =================== c2 MMA issuer ===================
-    if (my_tiles > 0) {
-      const bool leader = ptx::elect_one();
-      const int nW2 = rt.nW2;
-      const uint32_t idesc = rt.idesc;
-      const uint64_t dhi = ptx::umma_smem_desc(0, G::rb2, 0);
-      Cursor gb{0, 0}, wr{0, 0};
-      if (G::STATIONARY) { ptx::mbar_wait(w_all, 0); ptx::tc_fence_after(); }
-      for (int n = 0; n < my_tiles; ++n) {
+      };
+      auto do_c2 = [&]() {
         ptx::mbar_wait(g_full(gb.idx), gb.phase);
         ptx::mbar_wait(acc2_empty(gb.idx), gb.phase ^ 1u);
         ptx::tc_fence_after();
@@ -316,26 +317,22 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         for (int cb = 0; cb < G::nCB2; ++cb) {
 #pragma unroll
           for (int j = 0; j < KT; ++j) {
-            const uint64_t ad0 = dhi | (uint64_t)(a16 + cb * (G::G_BYTES >> 4) + j * (G::rb2 >> 4));
-#pragma unroll
-            for (int h = 0; h < G::NS; ++h) {
-              uint32_t b16;
-              if (G::STATIONARY) {
-                b16 = (sW2 + (cb * KT + j) * G::W2_TX) >> 4;
-              } else {
-                ptx::mbar_wait(w2_full(wr.idx), wr.phase);
-                ptx::tc_fence_after();
-                b16 = (sW2 + wr.idx * G::W2_TX) >> 4;
-              }
-              const uint64_t bd0 = dhi | (uint64_t)b16;
-              if (leader) {
-#pragma unroll
-                for (int kk = 0; kk < G::NK2; ++kk)
-                  ptx::umma_f16(d_tmem + h * G::NMMA, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
-                if (!G::STATIONARY) ptx::umma_commit(w2_empty(wr.idx));
-              }
-              if (!G::STATIONARY) wr.next(nW2);
+            uint32_t b16;
+            if (G::STATIONARY) {
+              b16 = (sW2 + (cb * KT + j) * G::W2_TX) >> 4;
+            } else {
+              ptx::mbar_wait(w_full(wr.idx), wr.phase);
+              ptx::tc_fence_after();
+              b16 = (sW + wr.idx * G::W_SLOT) >> 4;
             }
+            const uint64_t ad0 = dhi2 | (uint64_t)(a16 + cb * (G::G_BYTES >> 4) + j * (G::rb2 >> 4)), bd0 = dhi2 | (uint64_t)b16;
+            if (leader) {
+#pragma unroll
+              for (int kk = 0; kk < G::NK2; ++kk)
+                ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
+              if (!G::STATIONARY) ptx::umma_commit(w_empty(wr.idx));
+            }
+            if (!G::STATIONARY) wr.next(nW);
           }
         }
         if (leader) {
@@ -343,12 +340,23 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           ptx::umma_commit(g_empty(gb.idx));
         }
         gb.next(G::NBUF);
+      };
+      if (G::STATIONARY) {
+        if (warp == 1) { for (int n = 0; n < my_tiles; ++n) do_c1(); }
+        else           { for (int n = 0; n < my_tiles; ++n) do_c2(); }
+      } else {
+        for (int n = 0; n <= my_tiles; ++n) {
+          if (n < my_tiles) do_c1();
+          if (n >= 1) do_c2();
+        }
       }
     }
     __syncwarp();
   } else if (warp >= 4 && warp < 8) {
     // =================== epilogue 1: gate -> G tile in shared memory ===================
     const int q = warp & 3, r = q * 32 + lane;
+    constexpr int NCH = G::C2 / 16;              // 16-gate chunks per row
+    constexpr bool kBiasRegs = G::C2 <= 32;      // whole cond/bias row preloaded before the accumulator wait
     Cursor gb{0, 0};
     for (int n = 0; n < my_tiles; ++n, tile_next()) {
       tile_seek();
@@ -357,6 +365,14 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const int t = t0 - G::P2 + r;
       const bool live = t >= 0 && t < valid;     // G outside the sequence is the conv's zero padding
       const float* bias = a.bias1 + (long long)b * a.bias1_bstride;
+      float pa[kBiasRegs ? G::C2 : 16], pb[kBiasRegs ? G::C2 : 16];
+      if (kBiasRegs) {
+#pragma unroll
+        for (int c = 0; c < NCH; ++c) {
+          load16(bias + 16 * c, *reinterpret_cast<float(*)[16]>(&pa[kBiasRegs ? 16 * c : 0]));
+          load16(bias + G::C2 + 16 * c, *reinterpret_cast<float(*)[16]>(&pb[kBiasRegs ? 16 * c : 0]));
+        }
+      }
       const int s = gb.idx;
       ptx::mbar_wait(acc1_full(s), gb.phase);
       ptx::mbar_wait(g_empty(s), gb.phase ^ 1u);
@@ -364,10 +380,14 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const uint32_t trow = tmem_base + acc1_col + s * C + (static_cast<uint32_t>(q * 32) << 16);
       const uint32_t grow = sG + s * G::G_SET + r * G::rb2;
 #pragma unroll
-      for (int c0 = 0; c0 < G::C2; c0 += 16) {
-        float ba[16], bb[16];
-        load16(bias + c0, ba);                   // issued before the TMEM loads so both latencies overlap
-        load16(bias + G::C2 + c0, bb);
+      for (int c = 0; c < NCH; ++c) {
+        const int c0 = 16 * c;
+        if (!kBiasRegs) {
+          load16(bias + c0, *reinterpret_cast<float(*)[16]>(&pa[0]));       // issued before the TMEM loads so both latencies overlap
+          load16(bias + G::C2 + c0, *reinterpret_cast<float(*)[16]>(&pb[0]));
+        }
+        const float* ba = &pa[kBiasRegs ? c0 : 0];
+        const float* bb = &pb[kBiasRegs ? c0 : 0];
         uint32_t ra[16], rb[16];
         ptx::tmem_ld16(trow + c0, ra);
         ptx::tmem_ld16(trow + G::C2 + c0, rb);
@@ -375,12 +395,11 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         uint32_t p[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          float v0 = gate3(__uint_as_float(ra[2 * i]) + ba[2 * i], __uint_as_float(rb[2 * i]) + bb[2 * i]);
-          float v1 = gate3(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1]);
+          const float v0 = gate_fast(__uint_as_float(ra[2 * i]) + ba[2 * i], __uint_as_float(rb[2 * i]) + bb[2 * i]);
+          const float v1 = gate_fast(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1]);
           p[i] = live ? Pack16<OpT>::pack2(v0, v1) : 0u;
         }
         // channel c0..c0+15 of row r -> block cb2, two 16-byte chunks, swizzled like a TMA write would
-        constexpr int dummy = 0; (void)dummy;
         const int cb2 = c0 / G::BK2, cin = c0 - cb2 * G::BK2;
         const uint32_t rowaddr = grow + cb2 * G::G_BYTES + cin * 2;
         st_shared_v4(swz_addr<G::rb2>(rowaddr), p[0], p[1], p[2], p[3]);
@@ -394,10 +413,14 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     }
   } else if (warp >= 8 && warp < 12) {
     // =================== epilogue 2: bias + residual + leaky_relu -> global ===================
+    // LAST = false: mid iteration, y_out = op(leaky_relu(c2 + bias + x)) only.
+    // LAST = true : last iteration of a branch: v = scale * (c2 + bias + x) [+ acc]; acc / next-stage stores (MRF).
     const int q = warp & 3, r = q * 32 + lane;
     const int nSlab = rt.nSlab;
     const uint32_t slab_bytes = rt.slab_bytes;
     const int srow = r + G::P2 + rt.p1;          // slab row holding y_in[t]
+    constexpr int NCH = C / 16;                  // 16-column chunks per row
+    constexpr int PF = NCH < 8 ? NCH : 8;        // residual chunks kept in flight (2 x uint4 each)
     Cursor ab{0, 0}, sl{0, 0};
     for (int n = 0; n < my_tiles; ++n, tile_next()) {
       tile_seek();
@@ -407,33 +430,62 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const bool in_range = r < G::T_OUT && t < a.L;
       const bool live = t < valid;
       const int s = ab.idx, ss = sl.idx;
+      const long long orow = ((long long)b * a.L + t) * C;
+      const uint4* yres = reinterpret_cast<const uint4*>(reinterpret_cast<const OpT*>(a.y_res) + orow);
+      const uint32_t yrow = sSlab + ss * slab_set + srow * G::rb1;
+      // residual rows: issued before the accumulator wait so their latency hides behind c2
+      uint4 yq[PF][2];
+      auto load_y = [&](int c, uint4 (&dst)[2]) {
+        if (G::RES_GLOBAL) {
+          dst[0] = dst[1] = make_uint4(0u, 0u, 0u, 0u);
+          if (in_range) { dst[0] = __ldg(yres + 2 * c); dst[1] = __ldg(yres + 2 * c + 1); }
+        } else {
+          const int c0 = 16 * c, cb = c0 / G::BK1, cin = c0 - cb * G::BK1;
+          const uint32_t yaddr = yrow + cb * slab_bytes + cin * 2;
+          dst[0] = ld_shared_v4(swz_addr<G::rb1>(yaddr)); dst[1] = ld_shared_v4(swz_addr<G::rb1>(yaddr + 16));
+        }
+      };
+      if (!G::RES_GLOBAL) ptx::mbar_wait(slab_full(ss), sl.phase);      // acquire the TMA-written slab for the residual reads
+#pragma unroll
+      for (int c = 0; c < PF; ++c) load_y(c, yq[c]);
       ptx::mbar_wait(acc2_full(s), ab.phase);
-      ptx::mbar_wait(slab_full(ss), sl.phase);      // acquire the TMA-written slab for the residual reads
       ptx::tc_fence_after();
       const uint32_t trow = tmem_base + acc2_col + s * C + (static_cast<uint32_t>(q * 32) << 16);
-      const long long orow = ((long long)b * a.L + t) * C;
-      const uint32_t yrow = sSlab + ss * slab_set + srow * G::rb1;
 #pragma unroll
-      for (int c0 = 0; c0 < C; c0 += 16) {
+      for (int c = 0; c < NCH; ++c) {
+        const int c0 = 16 * c;
         float bv[16];
         load16(a.bias2 + c0, bv);
-        const int cb = c0 / G::BK1, cin = c0 - cb * G::BK1;
-        const uint32_t yaddr = yrow + cb * slab_bytes + cin * 2;
-        const uint4 y0 = ld_shared_v4(swz_addr<G::rb1>(yaddr)), y1 = ld_shared_v4(swz_addr<G::rb1>(yaddr + 16));
         uint32_t ra[16];
         ptx::tmem_ld16(trow + c0, ra);
         ptx::tmem_ld_wait();
-        if (in_range) {
-          float v[16];
-          const uint32_t yw[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+        const uint4 y0 = yq[c % PF][0], y1 = yq[c % PF][1];
+        if (c + PF < NCH) load_y(c + PF, yq[c % PF]);
+        const uint32_t yw[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
+        float v[16];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const float2 y = Pack16<OpT>::unpack2(yw[i]);
-            const float x0 = y.x >= 0.f ? y.x : 10.f * y.x;       // inverse of leaky_relu(., 0.1)
-            const float x1 = y.y >= 0.f ? y.y : 10.f * y.y;
-            v[2 * i] = a.scale * (__uint_as_float(ra[2 * i]) + bv[2 * i] + x0);
-            v[2 * i + 1] = a.scale * (__uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1] + x1);
+        for (int i = 0; i < 8; ++i) {
+          const float2 y = Pack16<OpT>::unpack2(yw[i]);
+          // inverse of leaky_relu(., 0.1): x = y >= 0 ? y : 10 y = min(y, 10 y)
+          v[2 * i] = (__uint_as_float(ra[2 * i]) + bv[2 * i]) + fminf(y.x, 10.f * y.x);
+          v[2 * i + 1] = (__uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1]) + fminf(y.y, 10.f * y.y);
+        }
+        if (!LAST) {
+          if (in_range) {
+            uint32_t pk[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              // leaky_relu(v, 0.1) = max(v, 0.1 v); rows beyond len[b] are stored as zeros
+              const uint32_t w = Pack16<OpT>::pack2(fmaxf(v[2 * i], 0.1f * v[2 * i]), fmaxf(v[2 * i + 1], 0.1f * v[2 * i + 1]));
+              pk[i] = live ? w : 0u;
+            }
+            uint4* d = reinterpret_cast<uint4*>(reinterpret_cast<OpT*>(a.y_out) + orow + c0);
+            d[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+            d[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
           }
+        } else if (in_range) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] *= a.scale;
           if (a.acc_mode & RB_ACC_READ) {
             float x[16];
             load16(a.acc + orow + c0, x);
@@ -455,7 +507,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) { ptx::mbar_arrive(acc2_empty(s)); ptx::mbar_arrive(slab_empty(ss)); }
+      if (lane == 0) {
+        ptx::mbar_arrive(acc2_empty(s));
+        if (!G::RES_GLOBAL) ptx::mbar_arrive(slab_empty(ss));
+      }
       ab.next(G::NBUF); sl.next(nSlab);
     }
   }
@@ -481,7 +536,7 @@ bool rb_fused_supported(int C, int k, int dil, int B) {
 
 namespace {
 
-template <typename OpT, int C, int KT>
+template <typename OpT, int C, int KT, bool LAST>
 cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   using G = RbT<C, KT>;
   RbRt rt{};
@@ -493,23 +548,17 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   if (G::STATIONARY) {
     if (fixed + G::W_ALL + 2 * slab_set > kRbSmemBudget) return cudaErrorNotSupported;
     rt.nSlab = (int)((kRbSmemBudget - fixed - G::W_ALL) / slab_set);
-    if (rt.nSlab > 4) rt.nSlab = 4;
+    const int want = G::RES_GLOBAL ? 4 : G::NBUF + 2;   // slab lifetime: load + c1 only, or the whole 4-stage pipeline
+    if (rt.nSlab > want) rt.nSlab = want;
   } else {
-    // streamed weights: at least 2 ring slots per conv, then as many slabs as NBUF can use, rest to the rings (2:1)
-    rt.nSlab = G::NBUF == 2 ? 2 : 1;
-    if (fixed + rt.nSlab * slab_set + 2 * G::W1_TX + 2 * G::W2_TX > kRbSmemBudget) rt.nSlab = 1;
-    if (fixed + rt.nSlab * slab_set + 2 * G::W1_TX + 2 * G::W2_TX > kRbSmemBudget) return cudaErrorNotSupported;
-    uint32_t left = kRbSmemBudget - fixed - rt.nSlab * slab_set;
-    rt.nW1 = 2; rt.nW2 = 2; left -= 2 * G::W1_TX + 2 * G::W2_TX;
-    while (true) {
-      bool grew = false;
-      if (rt.nW1 < 8 && left >= G::W1_TX) { ++rt.nW1; left -= G::W1_TX; grew = true; }
-      if (rt.nW1 < 8 && left >= G::W1_TX) { ++rt.nW1; left -= G::W1_TX; grew = true; }
-      if (rt.nW2 < 8 && left >= G::W2_TX) { ++rt.nW2; left -= G::W2_TX; grew = true; }
-      if (!grew) break;
-    }
+    // streamed weights: slabs first (2 when the accumulators are double-buffered), the rest to the ring
+    rt.nSlab = G::NBUF >= 2 ? 2 : 1;
+    if (fixed + rt.nSlab * slab_set + 2 * G::W_SLOT > kRbSmemBudget) rt.nSlab = 1;
+    if (fixed + rt.nSlab * slab_set + 2 * G::W_SLOT > kRbSmemBudget) return cudaErrorNotSupported;
+    rt.nW = (int)((kRbSmemBudget - fixed - rt.nSlab * slab_set) / G::W_SLOT);
+    if (rt.nW > 8) rt.nW = 8;
   }
-  rt.idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM, G::NMMA);
+  rt.idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM, C);
 
   TmaEncodeFn enc = tma_encode_fn();
   if (!enc) return cudaErrorNotSupported;
@@ -528,26 +577,26 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   {
     cuuint64_t dims[2] = {(cuuint64_t)KT * C, (cuuint64_t)C};
     cuuint64_t strides[1] = {(cuuint64_t)KT * C * 2};
-    cuuint32_t box[2] = {(cuuint32_t)G::BK1, (cuuint32_t)G::NMMA};
+    cuuint32_t box[2] = {(cuuint32_t)G::BK1, (cuuint32_t)C};
     ok &= enc(&tmW1, dt, 2, const_cast<void*>(L.w1), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(G::rb1),
               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
   }
   {
     cuuint64_t dims[2] = {(cuuint64_t)KT * G::C2, (cuuint64_t)C};
     cuuint64_t strides[1] = {(cuuint64_t)KT * G::C2 * 2};
-    cuuint32_t box[2] = {(cuuint32_t)G::BK2, (cuuint32_t)G::NMMA};
+    cuuint32_t box[2] = {(cuuint32_t)G::BK2, (cuuint32_t)C};
     ok &= enc(&tmW2, dt, 2, const_cast<void*>(L.w2), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(G::rb2),
               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
   }
   if (!ok) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", C, KT); return cudaErrorInvalidValue; }
-  const size_t wbytes = G::STATIONARY ? (size_t)G::W_ALL : (size_t)rt.nW1 * G::W1_TX + (size_t)rt.nW2 * G::W2_TX;
-  const size_t smem = 1024 + (size_t)rt.nSlab * slab_set + (size_t)G::NBUF * G::G_SET + wbytes + 8 * 53 + 64;
+  const size_t wbytes = G::STATIONARY ? (size_t)G::W_ALL : (size_t)rt.nW * G::W_SLOT;
+  const size_t smem = 1024 + (size_t)rt.nSlab * slab_set + (size_t)G::NBUF * G::G_SET + wbytes + 8 * 57 + 64;
   static int num_sms = 0;
   static std::once_flag once;     // one flag per template instantiation
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
     // opt-in limit is 227 KB per CTA INCLUDING the kernel's static shared memory (tile table)
-    attr_err = cudaFuncSetAttribute(rb_fused_kernel<OpT, C, KT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+    attr_err = cudaFuncSetAttribute(rb_fused_kernel<OpT, C, KT, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
     int dev = 0; cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
   });
@@ -556,17 +605,21 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   const long long max_tiles = (long long)L.B * ((L.a.L + G::T_OUT - 1) / G::T_OUT);
   int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
   if (grid < 1) grid = 1;
-  rb_fused_kernel<OpT, C, KT><<<grid, kRbThreads, smem, stream>>>(tmY, tmW1, tmW2, L.a, rt);
+  RbArgs args = L.a;
+  args.y_res = L.y_in;
+  rb_fused_kernel<OpT, C, KT, LAST><<<grid, kRbThreads, smem, stream>>>(tmY, tmW1, tmW2, args, rt);
   cudaError_t le = cudaGetLastError();
   if (le != cudaSuccess)
-    fprintf(stderr, "rb_fused launch failed (%s): C=%d k=%d dil=%d grid=%d smem=%zu nSlab=%d nW=%d/%d\n", cudaGetErrorString(le),
-            C, KT, L.dil, grid, smem, rt.nSlab, rt.nW1, rt.nW2);
+    fprintf(stderr, "rb_fused launch failed (%s): C=%d k=%d dil=%d grid=%d smem=%zu nSlab=%d nW=%d\n", cudaGetErrorString(le),
+            C, KT, L.dil, grid, smem, rt.nSlab, rt.nW);
   return le;
 }
 
 template <typename OpT>
 cudaError_t dispatch(const RbLaunch& L, int op, cudaStream_t s) {
-#define VITSB_RB_CASE(CC, KK) if (L.C == CC && L.k == KK) return launch_t<OpT, CC, KK>(L, op, s);
+  // mid iterations only write y_out; anything else (MRF accumulate / next-stage emit / scale) takes the general epilogue
+  const bool last = L.a.acc_mode != 0 || L.a.scale != 1.f || !L.a.y_out;
+#define VITSB_RB_CASE(CC, KK) if (L.C == CC && L.k == KK) return last ? launch_t<OpT, CC, KK, true>(L, op, s) : launch_t<OpT, CC, KK, false>(L, op, s);
   VITSB_RB_CASE(32, 3) VITSB_RB_CASE(32, 7) VITSB_RB_CASE(32, 11)
   VITSB_RB_CASE(64, 3) VITSB_RB_CASE(64, 7) VITSB_RB_CASE(64, 11)
   VITSB_RB_CASE(128, 3) VITSB_RB_CASE(128, 7) VITSB_RB_CASE(128, 11)
