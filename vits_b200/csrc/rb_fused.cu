@@ -20,13 +20,14 @@
 // division (the first version spent ~500 cycles of uniform-datapath instructions per tap
 // around 128 cycles of tensor work; profiles/r01_c_ncu_rb_fused_full_summary.txt).
 //
-// Roles (12 warps, 384 threads):
+// Roles (12 or 20 warps; the second epilogue group exists when there are >= 2 accumulator sets):
 //   warp 0      activation-slab TMA producer
 //   warp 1      c1 MMA issuer (and c2 in streamed-weight mode)
 //   warp 2      c2 MMA issuer (resident-weight mode: small N needs two issuing threads)
 //   warp 3      weight TMA producer
 //   warps 4-7   epilogue 1: TMEM -> bias + cond + gate -> G tile in smem (swizzled like TMA)
 //   warps 8-11  epilogue 2: TMEM -> bias + residual + leaky_relu -> global (+ MRF accumulate)
+//   warps 12-15 / 16-19  second gate / store group: the two groups take alternate tiles
 // Weights are resident in smem when they fit (C <= 64) and streamed through one ring in
 // the issuing warp's fixed order otherwise.  G tiles and both TMEM accumulators are
 // NBUF-deep (4 for C <= 64, where a tile is ~500 tensor cycles and the mbarrier / commit
@@ -45,7 +46,6 @@
 
 namespace vitsb {
 
-constexpr int kRbThreads = 384;
 constexpr int kRbMaxB = 512;
 constexpr uint32_t kRbSmemBudget = 220 * 1024;
 
@@ -66,6 +66,10 @@ struct RbT {
   static constexpr bool STATIONARY = C <= 64;                                     // W_ALL <= 135 KB: resident weights, two issuers
   static constexpr bool RES_GLOBAL = C >= 64;                                     // residual rows re-read from global (L2)
   static constexpr uint32_t TMEM_COLS = 2 * NBUF * C <= 256 ? 256 : 512;
+  // epilogue warp groups: with >= 2 accumulator sets, two groups of (4 gate + 4 store) warps take alternate
+  // tiles - the epilogues are latency / issue bound (one warp per scheduler reaches IPC ~0.3), not MUFU bound
+  static constexpr int NGRP = NBUF >= 2 ? 2 : 1;
+  static constexpr int THREADS = 128 + NGRP * 256;
   static_assert(2 * NBUF * C <= 512, "TMEM columns");
 };
 
@@ -128,7 +132,7 @@ __device__ __forceinline__ float gate_fast(float a, float b) {
 }
 
 template <typename OpT, int C, int KT, bool LAST>
-__global__ void __launch_bounds__(kRbThreads, 1)
+__global__ void __launch_bounds__((RbT<C, KT>::THREADS), 1)
 rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmW1,
                 const __grid_constant__ CUtensorMap tmW2, const RbArgs a, const RbRt rt) {
   using G = RbT<C, KT>;
@@ -191,9 +195,13 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   constexpr uint32_t acc1_col = 0, acc2_col = G::NBUF * C;       // TMEM columns: [acc1 x NBUF][acc2 x NBUF]
 
   // static round-robin schedule; b only grows along a CTA's tile sequence
-  int cur_tile = blockIdx.x, cur_b = 0;
+  // epilogue group of this warp (warps 4-11: group 0, warps 12-19: group 1) and its tile stride
+  const int grp = warp >= 12 ? 1 : 0;
+  const bool is_epi = warp >= 4;
+  const int tstep = is_epi ? G::NGRP : 1;
+  int cur_tile = blockIdx.x + (is_epi ? grp : 0) * gridDim.x, cur_b = 0;
   auto tile_seek = [&]() { while (s_tile_prefix[cur_b + 1] <= cur_tile) ++cur_b; };
-  auto tile_next = [&]() { cur_tile += gridDim.x; };
+  auto tile_next = [&]() { cur_tile += tstep * gridDim.x; };
 
   if (warp == 0) {
     // =================== activation-slab TMA producer ===================
@@ -352,13 +360,13 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       }
     }
     __syncwarp();
-  } else if (warp >= 4 && warp < 8) {
+  } else if ((warp >= 4 && warp < 8) || (warp >= 12 && warp < 16)) {
     // =================== epilogue 1: gate -> G tile in shared memory ===================
     const int q = warp & 3, r = q * 32 + lane;
     constexpr int NCH = G::C2 / 16;              // 16-gate chunks per row
     constexpr bool kBiasRegs = G::C2 <= 32;      // whole cond/bias row preloaded before the accumulator wait
-    Cursor gb{0, 0};
-    for (int n = 0; n < my_tiles; ++n, tile_next()) {
+    for (int n = grp; n < my_tiles; n += G::NGRP, tile_next()) {
+      const Cursor gb{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
       tile_seek();
       const int b = cur_b, t0 = (cur_tile - s_tile_prefix[cur_b]) * G::T_OUT;
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
@@ -409,9 +417,8 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) { ptx::mbar_arrive(g_full(s)); ptx::mbar_arrive(acc1_empty(s)); }
-      gb.next(G::NBUF);
     }
-  } else if (warp >= 8 && warp < 12) {
+  } else if (warp >= 8) {
     // =================== epilogue 2: bias + residual + leaky_relu -> global ===================
     // LAST = false: mid iteration, y_out = op(leaky_relu(c2 + bias + x)) only.
     // LAST = true : last iteration of a branch: v = scale * (c2 + bias + x) [+ acc]; acc / next-stage stores (MRF).
@@ -420,9 +427,11 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     const uint32_t slab_bytes = rt.slab_bytes;
     const int srow = r + G::P2 + rt.p1;          // slab row holding y_in[t]
     constexpr int NCH = C / 16;                  // 16-column chunks per row
-    constexpr int PF = NCH < 8 ? NCH : 8;        // residual chunks kept in flight (2 x uint4 each)
-    Cursor ab{0, 0}, sl{0, 0};
-    for (int n = 0; n < my_tiles; ++n, tile_next()) {
+    constexpr int PF = NCH < 4 ? NCH : 4;        // residual chunks kept in flight (2 x uint4 each)
+    Cursor sl{0, 0};
+    if (grp == 1) sl.next(nSlab);
+    for (int n = grp; n < my_tiles; n += G::NGRP, tile_next()) {
+      const Cursor ab{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
       tile_seek();
       const int b = cur_b, t0 = (cur_tile - s_tile_prefix[cur_b]) * G::T_OUT;
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
@@ -511,7 +520,8 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         ptx::mbar_arrive(acc2_empty(s));
         if (!G::RES_GLOBAL) ptx::mbar_arrive(slab_empty(ss));
       }
-      ab.next(G::NBUF); sl.next(nSlab);
+#pragma unroll
+      for (int i = 0; i < G::NGRP; ++i) sl.next(nSlab);
     }
   }
 
@@ -607,7 +617,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   if (grid < 1) grid = 1;
   RbArgs args = L.a;
   args.y_res = L.y_in;
-  rb_fused_kernel<OpT, C, KT, LAST><<<grid, kRbThreads, smem, stream>>>(tmY, tmW1, tmW2, args, rt);
+  rb_fused_kernel<OpT, C, KT, LAST><<<grid, G::THREADS, smem, stream>>>(tmY, tmW1, tmW2, args, rt);
   cudaError_t le = cudaGetLastError();
   if (le != cudaSuccess)
     fprintf(stderr, "rb_fused launch failed (%s): C=%d k=%d dil=%d grid=%d smem=%zu nSlab=%d nW=%d\n", cudaGetErrorString(le),
