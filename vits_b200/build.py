@@ -9,7 +9,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libvitsb200.so")
-SOURCES = ["conv_f32.cu", "aux_kernels.cu", "conv_tc.cu", "conv_tc2.cu", "rb_fused.cu", "engine_weights.cu", "engine_run.cu", "capi.cu"]
+SOURCES = ["conv_f32.cu", "aux_kernels.cu", "conv_tc.cu", "rb_fused.cu", "engine_weights.cu", "engine_run.cu", "capi.cu"]
 NVCC_FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
               "-Xcompiler", "-fPIC", "-shared", "-cudart", "static"]
 

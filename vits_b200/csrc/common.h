@@ -56,6 +56,10 @@ struct ConvArgs {
   const int* len;        // device [B] valid frames
   int len_mul;           // valid rows = len[b] * len_mul
   Epilogue epi;
+  // Two convs that read the same input fused into one launch (WN res_skip, modules.py:174-181):
+  // N tiles with first column >= n_split use epi_b, with columns counted from n_split.  0 = single epilogue.
+  int n_split;
+  Epilogue epi_b;
 };
 
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

@@ -80,10 +80,18 @@ struct Ctx {
 
   bool ok() const { return err == cudaSuccess; }
 
-  void conv(int tag, const PackedConv& p, const void* in, int L, int len_mul, const int* len, const Epilogue& ep_in) {
+  // p2 / ep2: a second conv over the same input whose packed weights and biases directly follow p's
+  // (WN res_skip halves): one launch, N tiles >= p.N take ep2 (tensor-core path only)
+  static bool mergeable(const PackedConv& p, const PackedConv& q) {
+    return q.w_off == p.w_off + (size_t)p.N * p.k * p.Cin && q.bias_off == p.bias_off + (size_t)p.N && q.NT == p.NT &&
+           q.Cin == p.Cin && q.k == p.k && q.dil == p.dil && q.pad == p.pad && q.in_cols == p.in_cols && !p.gate && !q.gate &&
+           p.cond_off < 0 && q.cond_off < 0;
+  }
+  void conv(int tag, const PackedConv& p, const void* in, int L, int len_mul, const int* len, const Epilogue& ep_in,
+            const PackedConv* p2 = nullptr, const Epilogue* ep2 = nullptr) {
     ++launches;
     if (dry || !ok()) return;
-    ev_begin(tag, p.flop_per_pos * (len ? valid_frames : (double)B * T) * len_mul);
+    ev_begin(tag, (p.flop_per_pos + (p2 ? p2->flop_per_pos : 0.0)) * (len ? valid_frames : (double)B * T) * len_mul);
     ConvArgs a{};
     a.in = in; a.in_ld = p.in_cols; a.in_cols = p.in_cols; a.in_bstride = (long long)L * p.in_cols; a.Cin = p.Cin;
     a.w = reinterpret_cast<const char*>(e->d_w) + p.w_off * op_bytes(e->op);
@@ -93,6 +101,11 @@ struct Ctx {
     a.epi.gate = p.gate ? 1 : 0;
     if (p.cond_off >= 0) { a.epi.bias = cond + p.cond_off; a.epi.bias_bstride = e->Ncond; }
     else { a.epi.bias = e->d_bias + p.bias_off; a.epi.bias_bstride = 0; }
+    if (p2) {
+      a.N = p.N + p2->N; a.n_split = p.N;
+      a.epi_b = *ep2; a.epi_b.gate = 0;
+      a.epi_b.bias = e->d_bias + p2->bias_off; a.epi_b.bias_bstride = 0;
+    }
     err = e->op == OP_F32 ? launch_conv_f32(a, stream) : launch_conv_tc(a, e->op, stream);
     ev_end();
   }
@@ -171,16 +184,18 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
         // acts = tanh(a)*sigmoid(b), a,b = in_layer(h) + cond slice     modules.py:163-172
         { Epilogue ep = epi_base(); set_out_op_split(ep, P(W.acts), H, T, 1.f, split16);
           cx.conv(T_FLOW_IN, cp.in_layers[l], P(W.hop), T, 1, cx.len_flow, ep); }
-        if (l < nl - 1) {
-          // h += res_skip[:H]                                           modules.py:176-178
-          Epilogue ep = epi_base(); set_res(ep, F(W.hf), H, T); set_out_f32(ep, F(W.hf), H, T); set_out_op_split(ep, P(W.hop), H, T, 1.f, split16);
-          cx.conv(T_FLOW_RES, cp.res[l], P(W.acts), T, 1, cx.len_flow, ep);
-        }
+        // h += res_skip[:H]                                             modules.py:176-178
+        Epilogue epr = epi_base(); set_res(epr, F(W.hf), H, T); set_out_f32(epr, F(W.hf), H, T); set_out_op_split(epr, P(W.hop), H, T, 1.f, split16);
         // output += res_skip[H:] (all of it on the last layer)          modules.py:179-181
-        { Epilogue ep = epi_base();
-          if (l > 0) set_accum(ep, F(W.skipf), H, T);
-          if (l < nl - 1) set_out_f32(ep, F(W.skipf), H, T); else set_out_op_split(ep, P(W.skipop), H, T, 1.f, split16);
-          cx.conv(T_FLOW_SKIP, cp.skip[l], P(W.acts), T, 1, cx.len_flow, ep); }
+        Epilogue eps = epi_base();
+        if (l > 0) set_accum(eps, F(W.skipf), H, T);
+        if (l < nl - 1) set_out_f32(eps, F(W.skipf), H, T); else set_out_op_split(eps, P(W.skipop), H, T, 1.f, split16);
+        if (l < nl - 1 && op != OP_F32 && Ctx::mergeable(cp.res[l], cp.skip[l])) {
+          cx.conv(T_FLOW_RES, cp.res[l], P(W.acts), T, 1, cx.len_flow, epr, &cp.skip[l], &eps);   // both halves, one launch
+        } else {
+          if (l < nl - 1) cx.conv(T_FLOW_RES, cp.res[l], P(W.acts), T, 1, cx.len_flow, epr);
+          cx.conv(T_FLOW_SKIP, cp.skip[l], P(W.acts), T, 1, cx.len_flow, eps);
+        }
       }
       // x1 = x1 - post(out)   (mean-only, logs == 0)                    modules.py:366-372
       { Epilogue ep = epi_base(); ep.alpha = -1.f; ep.beta = 1.f;

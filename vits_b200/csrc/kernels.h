@@ -16,8 +16,6 @@ cudaError_t launch_conv_f32(const ConvArgs& a, cudaStream_t stream);
 // Returns cudaErrorNotSupported for shapes outside its envelope.
 cudaError_t launch_conv_tc(const ConvArgs& a, int op, cudaStream_t stream);
 bool conv_tc_supported(int Cin, int in_ld, int N, int NT, int k);
-// conv_tc2.cu — slab variant (A rows staged once per channel block, taps = descriptor row shifts)
-cudaError_t launch_conv_tc2(const ConvArgs& a, int op, int mode, cudaStream_t stream);
 // rb_fused.cu — fused ResBlock2 iteration (c1 -> gate -> c2 -> residual) as one persistent kernel
 enum { RB_ACC_READ = 1, RB_ACC_STORE = 2, RB_EMIT_NEXT = 4 };
 struct RbArgs {

@@ -63,9 +63,8 @@ __device__ __forceinline__ void store16(float* dst, const float (&v)[16]) {
 // Must be called by all 32 lanes (tcgen05.ld is .sync.aligned) after the
 // accumulator-ready barrier and a tcgen05.fence::after_thread_sync.
 template <typename OpT>
-__device__ __forceinline__ void tc_epilogue(const ConvArgs& a, int b, int t0, int ntile, int valid,
+__device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& ep, int b, int t0, int ntile, int valid,
                                             uint32_t tmem_acc, int q, int lane) {
-    const Epilogue& ep = a.epi;
     const int row = q * 32 + lane;
     const int t = t0 + row;
     const bool in_range = t < a.L;
