@@ -49,7 +49,9 @@ struct ConvArgs {
   int in_cols;           // physical columns of an input row; K block kc reads columns (kc*BK) % in_cols
   const void* w;         // op_t [N][k*Cin]  K-major
   int N;                 // GEMM N (packed output columns)
-  int NT;                // N tile (<=256, multiple of 16); gate pairs live inside one tile
+  int NT;                // N tile (<=256, multiple of 16); the tensor-core launcher may pick a smaller divisor (wave balance)
+  int gate_group;        // gated convs: packed columns come in groups of gate_group = [tanh half | sigmoid half]; 0 -> NT
+  int m_tiles;           // host-known number of 128-row tiles that will run (ragged lengths); 0 -> B * ceil(L / 128)
   int k, dil, pad;       // tap j reads input row t + j*dil - pad
   int L;                 // rows per batch item
   int B;

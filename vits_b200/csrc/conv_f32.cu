@@ -41,7 +41,7 @@ conv_f32_kernel(const ConvArgs a) {
     if (!ep.gate) { int n = nblk * FT_N + c; return n < a.N ? n : -1; }
     int gc = nblk * 32 + (c & 31);
     if (gc >= n_out_total) return -1;
-    return packed_col_for_gate(gc, a.NT, c >> 5);
+    return packed_col_for_gate(gc, a.gate_group > 0 ? a.gate_group : a.NT, c >> 5);
   };
 
   float acc[4][4];
@@ -94,7 +94,8 @@ conv_f32_kernel(const ConvArgs a) {
         const int c = tx + 16 * h;                 // smem col of tanh part; sigmoid part at c+32
         const int gc = nblk * 32 + c;
         if (gc >= n_out_total) continue;
-        const int na = packed_col_for_gate(gc, a.NT, 0), nb = packed_col_for_gate(gc, a.NT, 1);
+        const int GG = a.gate_group > 0 ? a.gate_group : a.NT;
+        const int na = packed_col_for_gate(gc, GG, 0), nb = packed_col_for_gate(gc, GG, 1);
         float va = ep.alpha * (acc[i][h] + bias[na]);
         float vb = ep.alpha * (acc[i][h + 2] + bias[nb]);
         float v = live ? gate_fn<true>(va, vb) : 0.f;

@@ -25,6 +25,7 @@
 #include "tc_common.cuh"
 
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 namespace vitsb {
@@ -35,7 +36,7 @@ struct TcGeom {
   int stages;        // smem ring depth (<= 8)
   int nNT;           // N tiles
   uint32_t a_bytes;  // 128 * BK * 2
-  uint32_t b_bytes;  // NT * BK * 2
+  uint32_t b_bytes;  // per CTA: (NT / CTAs per item) * BK * 2
   uint32_t b_stride; // smem bytes per B stage (b_bytes rounded to 1024)
   uint32_t tmem_cols;
   uint32_t idesc;
@@ -44,7 +45,11 @@ struct TcGeom {
 constexpr int kTcThreads = 320;
 constexpr int kTcMaxB = 512;
 
-template <typename OpT>
+// TWO = true: CTA-pair mode (cluster of 2, tcgen05 cta_group::2).  A work item is a PAIR of time tiles
+// (pair p = m-tiles 2p and 2p+1 of the flattened (batch row, time tile) list; rank r of the pair owns
+// m-tile 2p+r) times one N tile.  Each CTA loads its own A box and HALF of the B box (NT/2 weight rows),
+// so the L2 -> smem weight traffic per SM halves - these convs are L2-bound on weights at M = 128.
+template <typename OpT, bool TWO>
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                const ConvArgs a, const TcGeom g) {
@@ -62,6 +67,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   auto acc_empty = [&](int i) { return bars + 8u * (18 + i); };
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform
+  const int rank = TWO ? (int)ptx::cluster_ctarank() : 0;
+  const int ncl = TWO ? 2 : 1;                                                                // CTAs per work item
+  const int cl_id = blockIdx.x / ncl, n_cl = gridDim.x / ncl;
 
   if (threadIdx.x == 0) {
     int acc = 0;
@@ -77,27 +85,33 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
     for (int s = 0; s < 8; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full(i), 1); ptx::mbar_init(acc_empty(i), 4); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full(i), 1); ptx::mbar_init(acc_empty(i), 4 * ncl); }
     ptx::mbar_fence_init();
   }
-  if (warp == 1) ptx::tmem_alloc(ptx::smem_u32(&s_tmem), g.tmem_cols);
+  if (warp == 1) { if (TWO) ptx::tmem_alloc_2sm(ptx::smem_u32(&s_tmem), g.tmem_cols); else ptx::tmem_alloc(ptx::smem_u32(&s_tmem), g.tmem_cols); }
   ptx::tc_fence_before();
-  __syncthreads();
+  if (TWO) ptx::cluster_sync_all(); else __syncthreads();    // barrier inits visible to the peer before any remote signal
   ptx::tc_fence_after();
   const uint32_t tmem_base = s_tmem;
 
   const int nNT = g.nNT;
-  const int total_tiles = s_prefix[a.B] * nNT;
-  const int my_tiles = total_tiles > (int)blockIdx.x ? (total_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const int n_mt = s_prefix[a.B];                            // real m-tiles
+  const int n_q = (n_mt + ncl - 1) / ncl;                    // m-tile groups (pairs)
+  const int total_items = n_q * nNT;
+  const int my_items = total_items > cl_id ? (total_items - 1 - cl_id) / n_cl + 1 : 0;
 
-  // tile -> (b, t0, ntile): N tile fastest, then time tile, then batch row; b only grows along a CTA's sequence
+  // item -> (b, t0, ntile) of THIS CTA: N tile fastest, then time tile, then batch row; b only grows.
+  // An odd m-tile count leaves rank 1 of the last pair without a tile: live = false (it still runs the protocol).
   int cur_b = 0;
-  auto coords = [&](int tile, int& b, int& t0, int& ntile) {
-    const int q = tile / nNT;
-    ntile = tile - q * nNT;
-    while (s_prefix[cur_b + 1] <= q) ++cur_b;
+  auto coords = [&](int item, int& b, int& t0, int& ntile, bool& live) {
+    const int q = item / nNT;
+    ntile = item - q * nNT;
+    int mt = q * ncl + rank;
+    live = mt < n_mt;
+    if (!live) mt = n_mt - 1;
+    while (s_prefix[cur_b + 1] <= mt) ++cur_b;
     b = cur_b;
-    t0 = (q - s_prefix[cur_b]) * kTileM;
+    t0 = (mt - s_prefix[cur_b]) * kTileM;
   };
 
   // Role loops are warp-uniform; only the single-thread instructions are predicated on one
@@ -105,23 +119,30 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int stages = g.stages, kchunks = g.kchunks, BK = g.BK, ktaps = a.k;
   const uint32_t a_bytes = g.a_bytes, b_stride = g.b_stride;
   if (warp == 0) {
-    // ===== TMA producer =====
+    // ===== TMA producer (both CTAs of a pair; the leader arms the barrier for both) =====
     const bool leader = ptx::elect_one();
-    const uint32_t tx_bytes = g.a_bytes + g.b_bytes;
+    const uint32_t tx_bytes = (g.a_bytes + g.b_bytes) * ncl;
     const int in_cols = a.in_cols, dil = a.dil, Cin = a.Cin;
     int s = 0; uint32_t ph = 0;
-    for (int n = 0; n < my_tiles; ++n) {
-      int b, t0, ntile;
-      coords(blockIdx.x + n * gridDim.x, b, t0, ntile);
-      const int row0 = t0 - a.pad, n0 = ntile * a.NT;
+    for (int n = 0; n < my_items; ++n) {
+      int b, t0, ntile; bool live;
+      coords(cl_id + n * n_cl, b, t0, ntile, live);
+      const int row0 = (live ? t0 : a.L + 1024) - a.pad;      // dead tile: every row out of range -> TMA zero fill
+      const int n0 = ntile * a.NT + rank * (a.NT / ncl);
       for (int j = 0; j < ktaps; ++j) {
         int col = 0;                                  // (kc * BK) % in_cols without the division
         for (int kc = 0; kc < kchunks; ++kc) {
           ptx::mbar_wait(empty_bar(s), ph ^ 1u);
           if (leader) {
-            ptx::mbar_expect_tx(full_bar(s), tx_bytes);
-            ptx::tma_load_3d(sA + s * a_bytes, &tmA, full_bar(s), col, row0 + j * dil, b);
-            ptx::tma_load_2d(sB + s * b_stride, &tmB, full_bar(s), j * Cin + kc * BK, n0);
+            if (TWO) {
+              if (rank == 0) ptx::mbar_expect_tx(full_bar(s), tx_bytes);
+              ptx::tma_load_3d_2sm(sA + s * a_bytes, &tmA, full_bar(s), col, row0 + j * dil, b);
+              ptx::tma_load_2d_2sm(sB + s * b_stride, &tmB, full_bar(s), j * Cin + kc * BK, n0);
+            } else {
+              ptx::mbar_expect_tx(full_bar(s), tx_bytes);
+              ptx::tma_load_3d(sA + s * a_bytes, &tmA, full_bar(s), col, row0 + j * dil, b);
+              ptx::tma_load_2d(sB + s * b_stride, &tmB, full_bar(s), j * Cin + kc * BK, n0);
+            }
           }
           col += BK; if (col >= in_cols) col -= in_cols;
           if (++s == stages) { s = 0; ph ^= 1u; }
@@ -130,62 +151,64 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     }
     __syncwarp();
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    const bool leader = ptx::elect_one();
-    const uint64_t dhi = ptx::umma_smem_desc(0, BK * 2, 0);
-    const uint32_t idesc = g.idesc;
-    const int nk = BK / 16, iters = ktaps * kchunks;
-    const uint32_t a16 = a_bytes >> 4, b16 = b_stride >> 4;
-    int s = 0; uint32_t ph = 0;
-    for (int n = 0; n < my_tiles; ++n) {
-      const int buf = n & 1;
-      ptx::mbar_wait(acc_empty(buf), ((n >> 1) & 1) ^ 1u);
-      ptx::tc_fence_after();
-      const uint32_t d_tmem = tmem_base + buf * a.NT;
-      for (int it = 0; it < iters; ++it) {
-        ptx::mbar_wait(full_bar(s), ph);
+    // ===== MMA issuer (leader CTA only in pair mode) =====
+    if (rank == 0) {
+      const bool leader = ptx::elect_one();
+      const uint64_t dhi = ptx::umma_smem_desc(0, BK * 2, 0);
+      const uint32_t idesc = g.idesc;
+      const int nk = BK / 16, iters = ktaps * kchunks;
+      const uint32_t a16 = a_bytes >> 4, b16 = b_stride >> 4;
+      const uint32_t sA16 = (sA & 0x3FFFFu) >> 4, sB16 = (sB & 0x3FFFFu) >> 4;
+      int s = 0; uint32_t ph = 0;
+      for (int n = 0; n < my_items; ++n) {
+        const int buf = n & 1;
+        ptx::mbar_wait(acc_empty(buf), ((n >> 1) & 1) ^ 1u);
         ptx::tc_fence_after();
-        const uint64_t ad0 = dhi | (uint64_t)((sA >> 4) + s * a16), bd0 = dhi | (uint64_t)((sB >> 4) + s * b16);
-        if (leader) {
-          if (nk == 4) {
-#pragma unroll
-            for (int kk = 0; kk < 4; ++kk)
-              ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (it | kk) != 0 ? 1u : 0u);
-          } else {
-            for (int kk = 0; kk < nk; ++kk)
-              ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (it | kk) != 0 ? 1u : 0u);
+        const uint32_t d_tmem = tmem_base + buf * a.NT;
+        for (int it = 0; it < iters; ++it) {
+          ptx::mbar_wait(full_bar(s), ph);
+          ptx::tc_fence_after();
+          const uint64_t ad0 = dhi | (uint64_t)(sA16 + s * a16), bd0 = dhi | (uint64_t)(sB16 + s * b16);
+          if (leader) {
+#pragma unroll 4
+            for (int kk = 0; kk < nk; ++kk) {
+              if (TWO) ptx::umma_f16_2sm(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (it | kk) != 0 ? 1u : 0u);
+              else ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (it | kk) != 0 ? 1u : 0u);
+            }
+            if (TWO) ptx::umma_commit_2sm(empty_bar(s)); else ptx::umma_commit(empty_bar(s));   // frees the smem stage (both CTAs)
           }
-          ptx::umma_commit(empty_bar(s));           // frees the smem stage when these MMAs retire
+          if (++s == stages) { s = 0; ph ^= 1u; }
         }
-        if (++s == stages) { s = 0; ph ^= 1u; }
+        if (leader) { if (TWO) ptx::umma_commit_2sm(acc_full(buf)); else ptx::umma_commit(acc_full(buf)); }   // accumulator complete
       }
-      if (leader) ptx::umma_commit(acc_full(buf));  // accumulator complete
     }
     __syncwarp();
   } else {
     // ===== epilogue groups: TMEM -> registers -> fused math -> global =====
     const int grp = warp >= 6 ? 1 : 0;
-    for (int n = grp; n < my_tiles; n += 2) {
-      int b, t0, ntile;
-      coords(blockIdx.x + n * gridDim.x, b, t0, ntile);
+    for (int n = grp; n < my_items; n += 2) {
+      int b, t0, ntile; bool live;
+      coords(cl_id + n * n_cl, b, t0, ntile, live);
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
       ptx::mbar_wait(acc_full(grp), (n >> 1) & 1);
       ptx::tc_fence_after();
-      const int nsplit_tile = a.n_split > 0 ? a.n_split / a.NT : nNT;
-      if (ntile < nsplit_tile) tc_epilogue<OpT>(a, a.epi, b, t0, ntile, valid, tmem_base + grp * a.NT, warp & 3, lane);
-      else tc_epilogue<OpT>(a, a.epi_b, b, t0, ntile - nsplit_tile, valid, tmem_base + grp * a.NT, warp & 3, lane);
+      if (live) {
+        const int nsplit_tile = a.n_split > 0 ? a.n_split / a.NT : nNT;
+        if (ntile < nsplit_tile) tc_epilogue<OpT>(a, a.epi, b, t0, ntile, valid, tmem_base + grp * a.NT, warp & 3, lane);
+        else tc_epilogue<OpT>(a, a.epi_b, b, t0, ntile - nsplit_tile, valid, tmem_base + grp * a.NT, warp & 3, lane);
+      }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(acc_empty(grp));
+      if (lane == 0) { if (TWO) ptx::mbar_arrive_leader(acc_empty(grp)); else ptx::mbar_arrive(acc_empty(grp)); }
     }
   }
 
-  // ---- teardown: all TMEM reads done before dealloc ----
+  // ---- teardown: all TMEM reads (and, in pair mode, the peer's) done before dealloc ----
   ptx::tc_fence_before();
-  __syncthreads();
+  if (TWO) ptx::cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, g.tmem_cols);
+    if (TWO) ptx::tmem_dealloc_2sm(tmem_base, g.tmem_cols); else ptx::tmem_dealloc(tmem_base, g.tmem_cols);
   }
 }
 
@@ -214,7 +237,7 @@ bool conv_tc_supported(int Cin, int in_ld, int N, int NT, int k) {
   return true;
 }
 
-static bool make_geom(const ConvArgs& a, int op, TcGeom* g) {
+static bool make_geom(const ConvArgs& a, int op, int ncl, TcGeom* g) {
   if (!conv_tc_supported(a.Cin, a.in_ld, a.N, a.NT, a.k)) return false;
   if (a.epi.gate && (a.NT % 32 != 0)) return false;
   if (a.B > kTcMaxB) return false;
@@ -224,7 +247,7 @@ static bool make_geom(const ConvArgs& a, int op, TcGeom* g) {
   g->kchunks = a.Cin / g->BK;
   g->nNT = a.N / a.NT;
   g->a_bytes = kTileM * g->BK * 2;
-  g->b_bytes = a.NT * g->BK * 2;
+  g->b_bytes = (a.NT / ncl) * g->BK * 2;
   g->b_stride = (g->b_bytes + 1023u) & ~1023u;
   // one persistent CTA per SM: as deep a ring as fits (<= 8 stages, no deeper than two tiles' worth)
   const uint32_t stage = g->a_bytes + g->b_stride;
@@ -237,13 +260,51 @@ static bool make_geom(const ConvArgs& a, int op, TcGeom* g) {
   uint32_t cols = 32;
   while (cols < (uint32_t)(2 * a.NT)) cols <<= 1;
   g->tmem_cols = cols;
-  g->idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM, a.NT);
+  g->idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM * ncl, a.NT);
   return true;
 }
 
-cudaError_t launch_conv_tc(const ConvArgs& a, int op, cudaStream_t stream) {
+static bool pair_mode_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("VITSB_TC_PAIR"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v == 1;
+}
+
+// Wave balance: one output tile is 128 rows x NT columns and a CTA (pair) runs its tiles back to back,
+// so the kernel lasts ceil(items / groups) tiles.  With ~75 time tiles per call (16 utterances) NT = 256
+// gives 150 tiles on 148 SMs - two waves, the second almost empty.  Pick the N tile that minimises
+// waves x (NT + fixed per-tile cost) among the divisors the packing allows.
+static int pick_launch_nt(const ConvArgs& a, int num_sms, bool pair_ok) {
+  if (a.epi.gate && a.gate_group <= 0) return a.NT;          // gate pairs are packed per NT: fixed
+  const int unit = a.epi.gate ? a.gate_group : 32;
+  const int q = a.m_tiles > 0 ? a.m_tiles : a.B * ceil_div(a.L, kTileM);
+  int best = a.NT; double best_cost = 1e30;
+  for (int nt = a.NT; nt >= unit; nt -= unit) {
+    if (a.N % nt != 0 || nt % unit != 0 || (a.n_split > 0 && a.n_split % nt != 0)) continue;
+    const int ncl = (pair_ok && nt % 32 == 0) ? 2 : 1;
+    const long long items = (long long)ceil_div(q, ncl) * (a.N / nt);
+    const int groups = num_sms / ncl;
+    const double waves = (double)((items + groups - 1) / groups);
+    const double cost = waves * (nt + 40.0);
+    if (cost < best_cost - 1e-9) { best_cost = cost; best = nt; }
+  }
+  return best;
+}
+
+cudaError_t launch_conv_tc(const ConvArgs& a_in, int op, cudaStream_t stream) {
+  if (op == OP_F32) return cudaErrorNotSupported;
+  static int num_sms = 0;
+  if (num_sms == 0) {
+    int dev = 0; cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    if (num_sms <= 0) num_sms = 148;
+  }
+  ConvArgs a = a_in;
+  a.NT = pick_launch_nt(a_in, num_sms, pair_mode_enabled());
+  // CTA-pair mode whenever each CTA's half of the weight box is a whole number of 8-row swizzle atoms
+  const int ncl = (pair_mode_enabled() && a.NT % 32 == 0 && a.NT >= 32) ? 2 : 1;
   TcGeom g;
-  if (op == OP_F32 || !make_geom(a, op, &g)) return cudaErrorNotSupported;
+  if (!make_geom(a, op, ncl, &g)) return cudaErrorNotSupported;
   TmaEncodeFn enc = tma_encode_fn();
   if (!enc) return cudaErrorNotSupported;
 
@@ -263,33 +324,49 @@ cudaError_t launch_conv_tc(const ConvArgs& a, int op, cudaStream_t stream) {
   {
     cuuint64_t dims[2] = {(cuuint64_t)a.k * a.Cin, (cuuint64_t)a.N};
     cuuint64_t strides[1] = {(cuuint64_t)a.k * a.Cin * 2};
-    cuuint32_t box[2] = {(cuuint32_t)g.BK, (cuuint32_t)a.NT};
+    cuuint32_t box[2] = {(cuuint32_t)g.BK, (cuuint32_t)(a.NT / ncl)};
     cuuint32_t estr[2] = {1, 1};
     CUresult r = enc(&tmB, dt, 2, const_cast<void*>(a.w), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
   }
   const size_t smem = 1024 + (size_t)g.stages * (g.a_bytes + g.b_stride) + 8 * 20 + 16;
-  static int num_sms = 0;
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    cudaError_t e1 = cudaFuncSetAttribute(conv_tc_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024);
-    cudaError_t e2 = cudaFuncSetAttribute(conv_tc_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024);
-    attr_err = e1 != cudaSuccess ? e1 : e2;
-    int dev = 0; cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaError_t e[4] = {
+        cudaFuncSetAttribute(conv_tc_kernel<__nv_bfloat16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024),
+        cudaFuncSetAttribute(conv_tc_kernel<__half, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024),
+        cudaFuncSetAttribute(conv_tc_kernel<__nv_bfloat16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024),
+        cudaFuncSetAttribute(conv_tc_kernel<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024)};
+    for (cudaError_t x : e) if (x != cudaSuccess) attr_err = x;
   });
   if (attr_err != cudaSuccess) return attr_err;
-  const long long max_tiles = (long long)a.B * ceil_div(a.L, kTileM) * g.nNT;
-  int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
-  if (grid < 1) grid = 1;
-  if (op == OP_BF16) conv_tc_kernel<__nv_bfloat16><<<grid, kTcThreads, smem, stream>>>(tmA, tmB, a, g);
-  else conv_tc_kernel<__half><<<grid, kTcThreads, smem, stream>>>(tmA, tmB, a, g);
-  cudaError_t le = cudaGetLastError();
+  const long long max_items = (long long)ceil_div(a.m_tiles > 0 ? a.m_tiles : a.B * ceil_div(a.L, kTileM), ncl) * g.nNT;
+  const int max_groups = num_sms / ncl;
+  int groups = (int)(max_items < max_groups ? max_items : max_groups);
+  if (groups < 1) groups = 1;
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(groups * ncl, 1, 1);
+  cfg.blockDim = dim3(kTcThreads, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = ncl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  cudaError_t le;
+  if (ncl == 2) {
+    le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, conv_tc_kernel<__nv_bfloat16, true>, tmA, tmB, a, g)
+                       : cudaLaunchKernelEx(&cfg, conv_tc_kernel<__half, true>, tmA, tmB, a, g);
+  } else {
+    le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, conv_tc_kernel<__nv_bfloat16, false>, tmA, tmB, a, g)
+                       : cudaLaunchKernelEx(&cfg, conv_tc_kernel<__half, false>, tmA, tmB, a, g);
+  }
+  if (le == cudaSuccess) le = cudaGetLastError();
   if (le != cudaSuccess)
-    fprintf(stderr, "conv_tc launch failed (%s): Cin=%d N=%d NT=%d k=%d grid=%d smem=%zu stages=%d\n", cudaGetErrorString(le),
-            a.Cin, a.N, a.NT, a.k, grid, smem, g.stages);
+    fprintf(stderr, "conv_tc launch failed (%s): Cin=%d N=%d NT=%d k=%d grid=%d x%d smem=%zu stages=%d\n", cudaGetErrorString(le),
+            a.Cin, a.N, a.NT, a.k, groups, ncl, smem, g.stages);
   return le;
 }
 

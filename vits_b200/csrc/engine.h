@@ -14,6 +14,7 @@ struct PackedConv {
   int Cin = 0, N = 0, NT = 0, k = 1, dil = 1, pad = 0;   // Cin = K per tap in the packed weights
   int in_cols = 0;         // physical columns of an input row (2*C for split-precision convs, else Cin)
   bool gate = false;
+  int gate_group = 0;      // gated: packed columns in groups of gate_group = [tanh | sigmoid] halves (0 -> NT)
   bool split = false;      // 3-term split precision: rows [hi|lo], weights [Wh|Wh|Wl] per tap (common.h)
   size_t w_off = 0;        // element offset into the operand-typed weight pool, [N][k*Cin] K-major
   size_t bias_off = 0;     // offset into the static fp32 bias pool (packed column order)

@@ -78,6 +78,18 @@ struct Ctx {
   const int* len_dec;
   const float* cond;     // device [B][Ncond]
 
+  const int32_t* h_len = nullptr;   // host copy of len (tile counts for the launcher's wave balancing)
+  int m_tiles(int L, int len_mul, bool ragged) const {
+    if (!ragged || !h_len) return B * ((L + kTileM - 1) / kTileM);
+    int q = 0;
+    for (int b = 0; b < B; ++b) {
+      long long rows = (long long)h_len[b] * len_mul + kHaloRows;
+      if (rows > L) rows = L;
+      q += (int)((rows + kTileM - 1) / kTileM);
+    }
+    return q;
+  }
+
   bool ok() const { return err == cudaSuccess; }
 
   // p2 / ep2: a second conv over the same input whose packed weights and biases directly follow p's
@@ -96,6 +108,7 @@ struct Ctx {
     a.in = in; a.in_ld = p.in_cols; a.in_cols = p.in_cols; a.in_bstride = (long long)L * p.in_cols; a.Cin = p.Cin;
     a.w = reinterpret_cast<const char*>(e->d_w) + p.w_off * op_bytes(e->op);
     a.N = p.N; a.NT = p.NT; a.k = p.k; a.dil = p.dil; a.pad = p.pad; a.L = L; a.B = B;
+    a.gate_group = p.gate_group; a.m_tiles = m_tiles(L, len_mul, len != nullptr);
     a.len = len; a.len_mul = len_mul;
     a.epi = ep_in;
     a.epi.gate = p.gate ? 1 : 0;
@@ -154,6 +167,7 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
   Ctx cx{this, stream, dry};
   cx.B = B; cx.T = T;
   cx.cond = F(W.cond);
+  cx.h_len = len;
   int* d_len = reinterpret_cast<int*>(base + W.len);
   cx.len_flow = len ? d_len : nullptr;
   cx.len_dec = (len && ragged) ? d_len : nullptr;

@@ -241,9 +241,11 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
     for (int l = 0; l < nl && ok; ++l) {
       const std::string li = std::to_string(l);
       const int NT = pick_nt(2 * H);
+      const int GG = (NT % 64 == 0) ? 64 : NT;   // gate pairs packed in 64-column groups: the launcher may run any NT that is a multiple of it
       std::vector<int> cols = iota_rows(0, H);
       cp.in_layers.push_back(pack_conv(L.weight(p + "enc.in_layers." + li, {2 * H, H, fk}), L.bias(p + "enc.in_layers." + li, 2 * H),
-                                       gate_rows(2 * H, NT), cols, fk, dil, true, NT, cw, cb, l * 2 * H, H, true));
+                                       gate_rows(2 * H, GG), cols, fk, dil, true, NT, cw, cb, l * 2 * H, H, true));
+      cp.in_layers.back().gate_group = GG;
       const int rs = l < nl - 1 ? 2 * H : H;
       const HostTensor* rw = L.weight(p + "enc.res_skip_layers." + li, {rs, H, 1});
       const HostTensor* rb = L.bias(p + "enc.res_skip_layers." + li, rs);

@@ -72,26 +72,30 @@ __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& e
     const uint32_t trow = tmem_acc + (static_cast<uint32_t>(q * 32) << 16);
     const float* bias = ep.bias + (long long)b * ep.bias_bstride + (long long)ntile * a.NT;
     if (ep.gate) {
-      const int half = a.NT >> 1;
-      const long long orow_op = (long long)b * ep.out_op_bstride + (long long)t * ep.out_op_ld + (long long)ntile * half;
-      for (int c0 = 0; c0 < half; c0 += 16) {
-        uint32_t ra[16], rb[16];
-        ptx::tmem_ld16(trow + c0, ra);
-        ptx::tmem_ld16(trow + half + c0, rb);
-        ptx::tmem_ld_wait();
-        float ba[16], bb[16], v[16];
-        load16(bias + c0, ba);
-        load16(bias + half + c0, bb);
+      // packed columns: groups of GG = [tanh GG/2 | sigmoid GG/2]; output channel = packed gate index
+      const int GG = a.gate_group > 0 ? a.gate_group : a.NT, gh = GG >> 1;
+      const long long orow_op = (long long)b * ep.out_op_bstride + (long long)t * ep.out_op_ld + (long long)ntile * (a.NT >> 1);
+      for (int g0 = 0; g0 < a.NT; g0 += GG) {
+        for (int c0 = 0; c0 < gh; c0 += 16) {
+          uint32_t ra[16], rb[16];
+          ptx::tmem_ld16(trow + g0 + c0, ra);
+          ptx::tmem_ld16(trow + g0 + gh + c0, rb);
+          ptx::tmem_ld_wait();
+          float ba[16], bb[16], v[16];
+          load16(bias + g0 + c0, ba);
+          load16(bias + g0 + gh + c0, bb);
 #pragma unroll
-        for (int i = 0; i < 16; ++i) {
-          float xa = ep.alpha * (__uint_as_float(ra[i]) + ba[i]);
-          float xb = ep.alpha * (__uint_as_float(rb[i]) + bb[i]);
-          v[i] = live ? gate_fn<false>(xa, xb) : 0.f;
-        }
-        if (in_range) {
-          if (ep.out_f32)
-            store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + (long long)ntile * half + c0, v);
-          if (ep.out_op) store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + orow_op + c0, v, ep.out_slope, ep.out_op_split);
+          for (int i = 0; i < 16; ++i) {
+            float xa = ep.alpha * (__uint_as_float(ra[i]) + ba[i]);
+            float xb = ep.alpha * (__uint_as_float(rb[i]) + bb[i]);
+            v[i] = live ? gate_fn<false>(xa, xb) : 0.f;
+          }
+          const int oc = (g0 >> 1) + c0;       // output column inside this tile's NT/2 gate channels
+          if (in_range) {
+            if (ep.out_f32)
+              store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + (long long)ntile * (a.NT >> 1) + oc, v);
+            if (ep.out_op) store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + orow_op + oc, v, ep.out_slope, ep.out_op_split);
+          }
         }
       }
     } else {
