@@ -57,7 +57,12 @@ struct RbT {
   static constexpr int P2 = (KT - 1) / 2, T_OUT = kTileM - (KT - 1);
   static constexpr int RG = (kTileM + (KT - 1) + 7) & ~7;
   static constexpr uint32_t G_BYTES = ((uint32_t)RG * rb2 + 1023u) & ~1023u;     // per channel block
-  static constexpr uint32_t W1_TX = (uint32_t)C * rb1, W2_TX = (uint32_t)C * rb2;  // bytes per (cb, tap) weight box
+  // CTA-pair mode (cluster of 2, tcgen05 cta_group::2) for the streamed-weight sizes: one UMMA covers the
+  // 128-row tiles of BOTH CTAs (M = 256) and each CTA holds half of the weight rows, so the L2 -> smem
+  // weight stream per SM halves (at M = 128 it needs ~64 B/clk/SM, above what L2 can feed 148 SMs)
+  static constexpr bool PAIR = C >= 128;
+  static constexpr int NCL = PAIR ? 2 : 1;
+  static constexpr uint32_t W1_TX = (uint32_t)(C / NCL) * rb1, W2_TX = (uint32_t)(C / NCL) * rb2;  // bytes per (cb, tap) weight box, per CTA
   static constexpr uint32_t W_SLOT = W1_TX > W2_TX ? W1_TX : W2_TX;               // ring slot (streamed mode)
   static constexpr int NBOX1 = KT * nCB1, NBOX2 = KT * nCB2;
   static constexpr uint32_t W_ALL = NBOX1 * W1_TX + NBOX2 * W2_TX;
@@ -160,6 +165,8 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   auto w_empty = [&](int i) { return bars + 8u * (49 + i); };
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform role id
+  const int rank = G::PAIR ? (int)ptx::cluster_ctarank() : 0;
+  const int unit_id = blockIdx.x / G::NCL, n_units = gridDim.x / G::NCL;     // a unit = one CTA, or one CTA pair
 
   // ---- tile table: tiles of batch row b cover output rows [0, min(L, valid_b + halo)) ----
   if (threadIdx.x == 0) {
@@ -178,20 +185,22 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     for (int i = 0; i < 8; ++i) { ptx::mbar_init(slab_full(i), 1); ptx::mbar_init(slab_empty(i), G::RES_GLOBAL ? 1 : 5); }
     ptx::mbar_init(w_all, 1);
     for (int i = 0; i < 4; ++i) {
-      ptx::mbar_init(acc1_full(i), 1);  ptx::mbar_init(acc1_empty(i), 4);
-      ptx::mbar_init(acc2_full(i), 1);  ptx::mbar_init(acc2_empty(i), 4);
-      ptx::mbar_init(g_full(i), 4);     ptx::mbar_init(g_empty(i), 1);
+      // pair mode: the leader's copies collect the arrivals of both CTAs' epilogue warps
+      ptx::mbar_init(acc1_full(i), 1);  ptx::mbar_init(acc1_empty(i), 4 * G::NCL);
+      ptx::mbar_init(acc2_full(i), 1);  ptx::mbar_init(acc2_empty(i), 4 * G::NCL);
+      ptx::mbar_init(g_full(i), 4 * G::NCL);     ptx::mbar_init(g_empty(i), 1);
     }
     for (int i = 0; i < 8; ++i) { ptx::mbar_init(w_full(i), 1); ptx::mbar_init(w_empty(i), 1); }
     ptx::mbar_fence_init();
   }
-  if (warp == 1) ptx::tmem_alloc(ptx::smem_u32(&s_tmem), G::TMEM_COLS);
+  if (warp == 1) { if (G::PAIR) ptx::tmem_alloc_2sm(ptx::smem_u32(&s_tmem), G::TMEM_COLS); else ptx::tmem_alloc(ptx::smem_u32(&s_tmem), G::TMEM_COLS); }
   ptx::tc_fence_before();
-  __syncthreads();
+  if (G::PAIR) ptx::cluster_sync_all(); else __syncthreads();      // barrier inits visible to the peer before any remote signal
   ptx::tc_fence_after();
   const uint32_t tmem_base = s_tmem;
   const int total_tiles = s_tile_prefix[a.B];
-  const int my_tiles = total_tiles > (int)blockIdx.x ? (total_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const int total_units = (total_tiles + G::NCL - 1) / G::NCL;      // pair mode: tiles 2u and 2u+1 (the last may be missing)
+  const int my_tiles = total_units > unit_id ? (total_units - 1 - unit_id) / n_units + 1 : 0;
   constexpr uint32_t acc1_col = 0, acc2_col = G::NBUF * C;       // TMEM columns: [acc1 x NBUF][acc2 x NBUF]
 
   // static round-robin schedule; b only grows along a CTA's tile sequence
@@ -199,9 +208,16 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   const int grp = warp >= 12 ? 1 : 0;
   const bool is_epi = warp >= 4;
   const int tstep = is_epi ? G::NGRP : 1;
-  int cur_tile = blockIdx.x + (is_epi ? grp : 0) * gridDim.x, cur_b = 0;
-  auto tile_seek = [&]() { while (s_tile_prefix[cur_b + 1] <= cur_tile) ++cur_b; };
-  auto tile_next = [&]() { cur_tile += tstep * gridDim.x; };
+  int cur_unit = unit_id + (is_epi ? grp : 0) * n_units, cur_b = 0, cur_tile = 0;
+  bool cur_dead = false;                          // pair mode, odd tile count: rank 1 of the last pair runs the protocol on zeros
+  auto tile_seek = [&]() {
+    const int t = G::PAIR ? cur_unit * 2 + rank : cur_unit;
+    cur_dead = t >= total_tiles;
+    cur_tile = cur_dead ? total_tiles - 1 : t;
+    while (s_tile_prefix[cur_b + 1] <= cur_tile) ++cur_b;
+  };
+  auto tile_t0 = [&]() { return cur_dead ? a.L + 4096 : (cur_tile - s_tile_prefix[cur_b]) * G::T_OUT; };   // dead: every row out of range
+  auto tile_next = [&]() { cur_unit += tstep * n_units; };
 
   if (warp == 0) {
     // =================== activation-slab TMA producer ===================
@@ -211,13 +227,15 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     Cursor sl{0, 0};
     for (int n = 0; n < my_tiles; ++n, tile_next()) {
       tile_seek();
-      const int t0 = (cur_tile - s_tile_prefix[cur_b]) * G::T_OUT;
+      const int t0 = tile_t0();
       ptx::mbar_wait(slab_empty(sl.idx), sl.phase ^ 1u);
       if (leader) {
-        ptx::mbar_expect_tx(slab_full(sl.idx), slab_tx);
+        if (rank == 0) ptx::mbar_expect_tx(slab_full(sl.idx), slab_tx * G::NCL);      // pair: both CTAs' slabs land on the leader's barrier
 #pragma unroll
-        for (int cb = 0; cb < G::nCB1; ++cb)
-          ptx::tma_load_3d(sSlab + sl.idx * slab_set + cb * slab_bytes, &tmY, slab_full(sl.idx), cb * G::BK1, t0 - halo, cur_b);
+        for (int cb = 0; cb < G::nCB1; ++cb) {
+          if (G::PAIR) ptx::tma_load_3d_2sm(sSlab + sl.idx * slab_set + cb * slab_bytes, &tmY, slab_full(sl.idx), cb * G::BK1, t0 - halo, cur_b);
+          else ptx::tma_load_3d(sSlab + sl.idx * slab_set + cb * slab_bytes, &tmY, slab_full(sl.idx), cb * G::BK1, t0 - halo, cur_b);
+        }
       }
       sl.next(nSlab);
     }
@@ -245,8 +263,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           for (int j = 0; j < KT; ++j) {
             ptx::mbar_wait(w_empty(wr.idx), wr.phase ^ 1u);
             if (leader) {
-              ptx::mbar_expect_tx(w_full(wr.idx), G::W1_TX);
-              ptx::tma_load_2d(sW + wr.idx * G::W_SLOT, &tmW1, w_full(wr.idx), j * C + cb * G::BK1, 0);
+              if (rank == 0) ptx::mbar_expect_tx(w_full(wr.idx), G::W1_TX * G::NCL);
+              if (G::PAIR) ptx::tma_load_2d_2sm(sW + wr.idx * G::W_SLOT, &tmW1, w_full(wr.idx), j * C + cb * G::BK1, rank * (C / 2));
+              else ptx::tma_load_2d(sW + wr.idx * G::W_SLOT, &tmW1, w_full(wr.idx), j * C + cb * G::BK1, 0);
             }
             wr.next(nW);
           }
@@ -256,8 +275,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           for (int j = 0; j < KT; ++j) {
             ptx::mbar_wait(w_empty(wr.idx), wr.phase ^ 1u);
             if (leader) {
-              ptx::mbar_expect_tx(w_full(wr.idx), G::W2_TX);
-              ptx::tma_load_2d(sW + wr.idx * G::W_SLOT, &tmW2, w_full(wr.idx), j * G::C2 + cb * G::BK2, 0);
+              if (rank == 0) ptx::mbar_expect_tx(w_full(wr.idx), G::W2_TX * G::NCL);
+              if (G::PAIR) ptx::tma_load_2d_2sm(sW + wr.idx * G::W_SLOT, &tmW2, w_full(wr.idx), j * G::C2 + cb * G::BK2, rank * (C / 2));
+              else ptx::tma_load_2d(sW + wr.idx * G::W_SLOT, &tmW2, w_full(wr.idx), j * G::C2 + cb * G::BK2, 0);
             }
             wr.next(nW);
           }
@@ -272,7 +292,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     // =================== MMA issuers (warp-uniform loops, elected lane issues) ===================
     // resident weights: warp 1 issues c1, warp 2 issues c2, independently;
     // streamed weights: warp 1 issues both in ring order c1(n), c2(n-1); warp 2 idles.
-    if (my_tiles > 0 && (warp == 1 || G::STATIONARY)) {
+    if (my_tiles > 0 && (warp == 1 || G::STATIONARY) && rank == 0) {
       const bool leader = ptx::elect_one();
       const int nSlab = rt.nSlab, nW = rt.nW;
       const uint32_t slab_bytes = rt.slab_bytes, idesc = rt.idesc;
@@ -280,38 +300,43 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const uint64_t dhi1 = ptx::umma_smem_desc(0, G::rb1, 0), dhi2 = ptx::umma_smem_desc(0, G::rb2, 0);
       Cursor sl{0, 0}, ab{0, 0}, gb{0, 0}, wr{0, 0};
       if (G::STATIONARY) { ptx::mbar_wait(w_all, 0); ptx::tc_fence_after(); }
+      // pair mode: one instruction drives both CTAs' tensor cores; commits arrive on both CTAs' barrier copies
+      auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t id, uint32_t acc) {
+        if (G::PAIR) ptx::umma_f16_2sm(d, ad, bd, id, acc); else ptx::umma_f16(d, ad, bd, id, acc);
+      };
+      auto commit = [&](uint32_t bar) { if (G::PAIR) ptx::umma_commit_2sm(bar); else ptx::umma_commit(bar); };
       auto do_c1 = [&]() {
         ptx::mbar_wait(slab_full(sl.idx), sl.phase);
         ptx::mbar_wait(acc1_empty(ab.idx), ab.phase ^ 1u);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc1_col + ab.idx * C;
-        const uint32_t a16 = (sSlab + sl.idx * slab_set) >> 4;
+        const uint32_t a16 = ((sSlab + sl.idx * slab_set) & 0x3FFFFu) >> 4;
 #pragma unroll
         for (int cb = 0; cb < G::nCB1; ++cb) {
 #pragma unroll
           for (int j = 0; j < KT; ++j) {
             uint32_t b16;
             if (G::STATIONARY) {
-              b16 = (sW + (cb * KT + j) * G::W1_TX) >> 4;
+              b16 = ((sW + (cb * KT + j) * G::W1_TX) & 0x3FFFFu) >> 4;
             } else {
               ptx::mbar_wait(w_full(wr.idx), wr.phase);
               ptx::tc_fence_after();
-              b16 = (sW + wr.idx * G::W_SLOT) >> 4;
+              b16 = ((sW + wr.idx * G::W_SLOT) & 0x3FFFFu) >> 4;
             }
             // descriptors differ only in their 14-bit start-address field (16-byte units)
             const uint64_t ad0 = dhi1 | (uint64_t)(a16 + cb * (slab_bytes >> 4) + j * tap16), bd0 = dhi1 | (uint64_t)b16;
             if (leader) {
 #pragma unroll
               for (int kk = 0; kk < G::NK1; ++kk)
-                ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
-              if (!G::STATIONARY) ptx::umma_commit(w_empty(wr.idx));
+                mma(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
+              if (!G::STATIONARY) commit(w_empty(wr.idx));
             }
             if (!G::STATIONARY) wr.next(nW);
           }
         }
         if (leader) {
-          ptx::umma_commit(acc1_full(ab.idx));
-          ptx::umma_commit(slab_empty(sl.idx));      // c1 no longer reads the slab
+          commit(acc1_full(ab.idx));
+          commit(slab_empty(sl.idx));                // c1 no longer reads the slab
         }
         sl.next(nSlab); ab.next(G::NBUF);
       };
@@ -320,32 +345,32 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         ptx::mbar_wait(acc2_empty(gb.idx), gb.phase ^ 1u);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc2_col + gb.idx * C;
-        const uint32_t a16 = (sG + gb.idx * G::G_SET) >> 4;
+        const uint32_t a16 = ((sG + gb.idx * G::G_SET) & 0x3FFFFu) >> 4;
 #pragma unroll
         for (int cb = 0; cb < G::nCB2; ++cb) {
 #pragma unroll
           for (int j = 0; j < KT; ++j) {
             uint32_t b16;
             if (G::STATIONARY) {
-              b16 = (sW2 + (cb * KT + j) * G::W2_TX) >> 4;
+              b16 = ((sW2 + (cb * KT + j) * G::W2_TX) & 0x3FFFFu) >> 4;
             } else {
               ptx::mbar_wait(w_full(wr.idx), wr.phase);
               ptx::tc_fence_after();
-              b16 = (sW + wr.idx * G::W_SLOT) >> 4;
+              b16 = ((sW + wr.idx * G::W_SLOT) & 0x3FFFFu) >> 4;
             }
             const uint64_t ad0 = dhi2 | (uint64_t)(a16 + cb * (G::G_BYTES >> 4) + j * (G::rb2 >> 4)), bd0 = dhi2 | (uint64_t)b16;
             if (leader) {
 #pragma unroll
               for (int kk = 0; kk < G::NK2; ++kk)
-                ptx::umma_f16(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
-              if (!G::STATIONARY) ptx::umma_commit(w_empty(wr.idx));
+                mma(d_tmem, ad0 + 2 * kk, bd0 + 2 * kk, idesc, (cb | j | kk) != 0 ? 1u : 0u);
+              if (!G::STATIONARY) commit(w_empty(wr.idx));
             }
             if (!G::STATIONARY) wr.next(nW);
           }
         }
         if (leader) {
-          ptx::umma_commit(acc2_full(gb.idx));
-          ptx::umma_commit(g_empty(gb.idx));
+          commit(acc2_full(gb.idx));
+          commit(g_empty(gb.idx));
         }
         gb.next(G::NBUF);
       };
@@ -368,7 +393,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     for (int n = grp; n < my_tiles; n += G::NGRP, tile_next()) {
       const Cursor gb{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
       tile_seek();
-      const int b = cur_b, t0 = (cur_tile - s_tile_prefix[cur_b]) * G::T_OUT;
+      const int b = cur_b, t0 = tile_t0();
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
       const int t = t0 - G::P2 + r;
       const bool live = t >= 0 && t < valid;     // G outside the sequence is the conv's zero padding
@@ -413,10 +438,14 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         st_shared_v4(swz_addr<G::rb2>(rowaddr), p[0], p[1], p[2], p[3]);
         st_shared_v4(swz_addr<G::rb2>(rowaddr + 16), p[4], p[5], p[6], p[7]);
       }
-      fence_proxy_async_smem();                  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+      if (G::PAIR) asm volatile("fence.proxy.async;" ::: "memory");   // the leader's tensor core reads this CTA's G tile
+      else fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the tensor core (async proxy)
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) { ptx::mbar_arrive(g_full(s)); ptx::mbar_arrive(acc1_empty(s)); }
+      if (lane == 0) {
+        if (G::PAIR) { ptx::mbar_arrive_leader(g_full(s)); ptx::mbar_arrive_leader(acc1_empty(s)); }
+        else { ptx::mbar_arrive(g_full(s)); ptx::mbar_arrive(acc1_empty(s)); }
+      }
     }
   } else if (warp >= 8) {
     // =================== epilogue 2: bias + residual + leaky_relu -> global ===================
@@ -433,7 +462,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     for (int n = grp; n < my_tiles; n += G::NGRP, tile_next()) {
       const Cursor ab{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
       tile_seek();
-      const int b = cur_b, t0 = (cur_tile - s_tile_prefix[cur_b]) * G::T_OUT;
+      const int b = cur_b, t0 = tile_t0();
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
       const int t = t0 + r;
       const bool in_range = r < G::T_OUT && t < a.L;
@@ -517,7 +546,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) {
-        ptx::mbar_arrive(acc2_empty(s));
+        if (G::PAIR) ptx::mbar_arrive_leader(acc2_empty(s)); else ptx::mbar_arrive(acc2_empty(s));
         if (!G::RES_GLOBAL) ptx::mbar_arrive(slab_empty(ss));
       }
 #pragma unroll
@@ -526,10 +555,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   }
 
   ptx::tc_fence_before();
-  __syncthreads();
+  if (G::PAIR) ptx::cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, G::TMEM_COLS);
+    if (G::PAIR) ptx::tmem_dealloc_2sm(tmem_base, G::TMEM_COLS); else ptx::tmem_dealloc(tmem_base, G::TMEM_COLS);
   }
 }
 
@@ -568,7 +597,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
     rt.nW = (int)((kRbSmemBudget - fixed - rt.nSlab * slab_set) / G::W_SLOT);
     if (rt.nW > 8) rt.nW = 8;
   }
-  rt.idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM, C);
+  rt.idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM * G::NCL, C);
 
   TmaEncodeFn enc = tma_encode_fn();
   if (!enc) return cudaErrorNotSupported;
@@ -587,14 +616,14 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   {
     cuuint64_t dims[2] = {(cuuint64_t)KT * C, (cuuint64_t)C};
     cuuint64_t strides[1] = {(cuuint64_t)KT * C * 2};
-    cuuint32_t box[2] = {(cuuint32_t)G::BK1, (cuuint32_t)C};
+    cuuint32_t box[2] = {(cuuint32_t)G::BK1, (cuuint32_t)(C / G::NCL)};
     ok &= enc(&tmW1, dt, 2, const_cast<void*>(L.w1), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(G::rb1),
               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
   }
   {
     cuuint64_t dims[2] = {(cuuint64_t)KT * G::C2, (cuuint64_t)C};
     cuuint64_t strides[1] = {(cuuint64_t)KT * G::C2 * 2};
-    cuuint32_t box[2] = {(cuuint32_t)G::BK2, (cuuint32_t)C};
+    cuuint32_t box[2] = {(cuuint32_t)G::BK2, (cuuint32_t)(C / G::NCL)};
     ok &= enc(&tmW2, dt, 2, const_cast<void*>(L.w2), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(G::rb2),
               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
   }
@@ -613,12 +642,24 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   if (attr_err != cudaSuccess) { fprintf(stderr, "rb_fused: cudaFuncSetAttribute failed: %s\n", cudaGetErrorString(attr_err)); return attr_err; }
   // upper bound on tiles -> grid (persistent: at most one CTA per SM)
   const long long max_tiles = (long long)L.B * ((L.a.L + G::T_OUT - 1) / G::T_OUT);
-  int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
-  if (grid < 1) grid = 1;
+  const long long max_units = (max_tiles + G::NCL - 1) / G::NCL;
+  const int sm_units = num_sms / G::NCL;
+  int units = (int)(max_units < sm_units ? max_units : sm_units);
+  if (units < 1) units = 1;
+  const int grid = units * G::NCL;
   RbArgs args = L.a;
   args.y_res = L.y_in;
-  rb_fused_kernel<OpT, C, KT, LAST><<<grid, G::THREADS, smem, stream>>>(tmY, tmW1, tmW2, args, rt);
-  cudaError_t le = cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(G::THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = G::NCL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  cfg.attrs = at; cfg.numAttrs = 1;
+  cudaError_t le = cudaLaunchKernelEx(&cfg, rb_fused_kernel<OpT, C, KT, LAST>, tmY, tmW1, tmW2, args, rt);
+  if (le == cudaSuccess) le = cudaGetLastError();
   if (le != cudaSuccess)
     fprintf(stderr, "rb_fused launch failed (%s): C=%d k=%d dil=%d grid=%d smem=%zu nSlab=%d nW=%d\n", cudaGetErrorString(le),
             C, KT, L.dil, grid, smem, rt.nSlab, rt.nW);
