@@ -30,6 +30,7 @@ struct RbArgs {
   const float* bias2;
   int L, B;
   const int* len; int len_mul;
+  long long* trace;        // debug: clock64 timeline of CTA 0 (VITSB_RB_TRACE), normally null
   const void* y_res;       // = RbLaunch::y_in (set by launch_rb_fused): residual rows re-read from global when C >= 64
 };
 struct RbLaunch {

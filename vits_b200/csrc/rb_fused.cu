@@ -42,6 +42,7 @@
 #include "tc_common.cuh"
 
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 namespace vitsb {
@@ -86,6 +87,7 @@ struct RbRt {
   int nSlab;                 // activation slab buffers (1..8)
   int nW;                    // weight ring slots (streamed mode, 2..8)
   uint32_t idesc;
+  int dbg;                   // VITSB_RB_DBG ablation mask (timing experiments only; results are wrong when set)
 };
 
 // Swizzle<B,4,3> on a byte address whose buffer base is 1024-aligned: XOR bits [4,4+B) with bits [7,7+B)
@@ -101,6 +103,21 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
   return v;
+}
+// Prefetching global load that the compiler may not sink to its first use (plain __ldg of read-only data is
+// free to move across the memory-clobbering tcgen05 asm statements, which silently undoes a software prefetch).
+__device__ __forceinline__ uint4 ldg_nc_v4_pinned(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+// 16 consecutive floats from shared memory (all lanes read the same address: broadcast, conflict-free)
+__device__ __forceinline__ void lds16(uint32_t addr, float (&v)[16]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint4 x = ld_shared_v4(addr + 16 * i);
+    v[4 * i] = __uint_as_float(x.x); v[4 * i + 1] = __uint_as_float(x.y); v[4 * i + 2] = __uint_as_float(x.z); v[4 * i + 3] = __uint_as_float(x.w);
+  }
 }
 __device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
@@ -144,6 +161,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   extern __shared__ uint8_t smem_raw[];
   __shared__ int s_tile_prefix[kRbMaxB + 1];
   __shared__ uint32_t s_tmem;
+  // Bias vectors staged in shared memory: with ~220 KB of the SM's 256 KB carved out as smem the L1 is a few KB
+  // and the residual stream flushes it, so per-chunk bias loads from global paid an L2 round trip each.
+  __shared__ __align__(16) float s_bias2[C];            // conv2 bias
+  __shared__ __align__(16) float s_bias1[2][C];         // per epilogue group: conv1 bias + conditioning of the current batch row
 
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t slab_set = G::nCB1 * rt.slab_bytes;
@@ -179,6 +200,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     }
     s_tile_prefix[a.B] = acc;
   }
+  for (int i = threadIdx.x; i < C; i += blockDim.x) s_bias2[i] = a.bias2[i];
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmY); ptx::prefetch_tmap(&tmW1); ptx::prefetch_tmap(&tmW2);
     // slab release: c1's MMA commit, plus the 4 store-epilogue warps when they read the residual from the slab
@@ -198,9 +220,13 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   if (G::PAIR) ptx::cluster_sync_all(); else __syncthreads();      // barrier inits visible to the peer before any remote signal
   ptx::tc_fence_after();
   const uint32_t tmem_base = s_tmem;
+  // timeline trace of CTA 0 (VITSB_RB_TRACE): trace[(role * 16 + tile) * 2 + kind] = clock64()
+  auto trace = [&](int role, int tile, int kind) {
+    if (a.trace && blockIdx.x == 0 && tile < 16 && lane == 0) a.trace[(role * 16 + tile) * 2 + kind] = clock64();
+  };
   const int total_tiles = s_tile_prefix[a.B];
   const int total_units = (total_tiles + G::NCL - 1) / G::NCL;      // pair mode: tiles 2u and 2u+1 (the last may be missing)
-  const int my_tiles = total_units > unit_id ? (total_units - 1 - unit_id) / n_units + 1 : 0;
+  const int my_tiles = (rt.dbg & 256) ? 0 : (total_units > unit_id ? (total_units - 1 - unit_id) / n_units + 1 : 0);
   constexpr uint32_t acc1_col = 0, acc2_col = G::NBUF * C;       // TMEM columns: [acc1 x NBUF][acc2 x NBUF]
 
   // static round-robin schedule; b only grows along a CTA's tile sequence
@@ -229,7 +255,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       tile_seek();
       const int t0 = tile_t0();
       ptx::mbar_wait(slab_empty(sl.idx), sl.phase ^ 1u);
-      if (leader) {
+      trace(0, n, 0);
+      if (leader && (rt.dbg & 64)) {
+        if (rank == 0) ptx::mbar_arrive(slab_full(sl.idx));
+      } else if (leader) {
         if (rank == 0) ptx::mbar_expect_tx(slab_full(sl.idx), slab_tx * G::NCL);      // pair: both CTAs' slabs land on the leader's barrier
 #pragma unroll
         for (int cb = 0; cb < G::nCB1; ++cb) {
@@ -263,8 +292,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           for (int j = 0; j < KT; ++j) {
             ptx::mbar_wait(w_empty(wr.idx), wr.phase ^ 1u);
             if (leader) {
-              if (rank == 0) ptx::mbar_expect_tx(w_full(wr.idx), G::W1_TX * G::NCL);
-              if (G::PAIR) ptx::tma_load_2d_2sm(sW + wr.idx * G::W_SLOT, &tmW1, w_full(wr.idx), j * C + cb * G::BK1, rank * (C / 2));
+              if (rt.dbg & 128) { if (rank == 0) ptx::mbar_arrive(w_full(wr.idx)); }
+              else if (rank == 0) ptx::mbar_expect_tx(w_full(wr.idx), G::W1_TX * G::NCL);
+              if (rt.dbg & 128) {}
+              else if (G::PAIR) ptx::tma_load_2d_2sm(sW + wr.idx * G::W_SLOT, &tmW1, w_full(wr.idx), j * C + cb * G::BK1, rank * (C / 2));
               else ptx::tma_load_2d(sW + wr.idx * G::W_SLOT, &tmW1, w_full(wr.idx), j * C + cb * G::BK1, 0);
             }
             wr.next(nW);
@@ -275,8 +306,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           for (int j = 0; j < KT; ++j) {
             ptx::mbar_wait(w_empty(wr.idx), wr.phase ^ 1u);
             if (leader) {
-              if (rank == 0) ptx::mbar_expect_tx(w_full(wr.idx), G::W2_TX * G::NCL);
-              if (G::PAIR) ptx::tma_load_2d_2sm(sW + wr.idx * G::W_SLOT, &tmW2, w_full(wr.idx), j * G::C2 + cb * G::BK2, rank * (C / 2));
+              if (rt.dbg & 128) { if (rank == 0) ptx::mbar_arrive(w_full(wr.idx)); }
+              else if (rank == 0) ptx::mbar_expect_tx(w_full(wr.idx), G::W2_TX * G::NCL);
+              if (rt.dbg & 128) {}
+              else if (G::PAIR) ptx::tma_load_2d_2sm(sW + wr.idx * G::W_SLOT, &tmW2, w_full(wr.idx), j * G::C2 + cb * G::BK2, rank * (C / 2));
               else ptx::tma_load_2d(sW + wr.idx * G::W_SLOT, &tmW2, w_full(wr.idx), j * G::C2 + cb * G::BK2, 0);
             }
             wr.next(nW);
@@ -299,16 +332,20 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const uint32_t tap16 = ((uint32_t)rt.dil * G::rb1) >> 4;                  // c1 tap stride in 16-byte units
       const uint64_t dhi1 = ptx::umma_smem_desc(0, G::rb1, 0), dhi2 = ptx::umma_smem_desc(0, G::rb2, 0);
       Cursor sl{0, 0}, ab{0, 0}, gb{0, 0}, wr{0, 0};
+      int tr_c1 = 0, tr_c2 = 0;
       if (G::STATIONARY) { ptx::mbar_wait(w_all, 0); ptx::tc_fence_after(); }
       // pair mode: one instruction drives both CTAs' tensor cores; commits arrive on both CTAs' barrier copies
       auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t id, uint32_t acc) {
+        if (rt.dbg & 8) return;
         if (G::PAIR) ptx::umma_f16_2sm(d, ad, bd, id, acc); else ptx::umma_f16(d, ad, bd, id, acc);
       };
       auto commit = [&](uint32_t bar) { if (G::PAIR) ptx::umma_commit_2sm(bar); else ptx::umma_commit(bar); };
       auto do_c1 = [&]() {
         ptx::mbar_wait(slab_full(sl.idx), sl.phase);
+        trace(1, tr_c1, 0);
         ptx::mbar_wait(acc1_empty(ab.idx), ab.phase ^ 1u);
         ptx::tc_fence_after();
+        trace(6, tr_c1, 0);
         const uint32_t d_tmem = tmem_base + acc1_col + ab.idx * C;
         const uint32_t a16 = ((sSlab + sl.idx * slab_set) & 0x3FFFFu) >> 4;
 #pragma unroll
@@ -338,10 +375,12 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           commit(acc1_full(ab.idx));
           commit(slab_empty(sl.idx));                // c1 no longer reads the slab
         }
+        trace(1, tr_c1, 1); ++tr_c1;
         sl.next(nSlab); ab.next(G::NBUF);
       };
       auto do_c2 = [&]() {
         ptx::mbar_wait(g_full(gb.idx), gb.phase);
+        trace(2, tr_c2, 0);
         ptx::mbar_wait(acc2_empty(gb.idx), gb.phase ^ 1u);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc2_col + gb.idx * C;
@@ -372,6 +411,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           commit(acc2_full(gb.idx));
           commit(g_empty(gb.idx));
         }
+        trace(2, tr_c2, 1); ++tr_c2;
         gb.next(G::NBUF);
       };
       if (G::STATIONARY) {
@@ -389,7 +429,8 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     // =================== epilogue 1: gate -> G tile in shared memory ===================
     const int q = warp & 3, r = q * 32 + lane;
     constexpr int NCH = G::C2 / 16;              // 16-gate chunks per row
-    constexpr bool kBiasRegs = G::C2 <= 32;      // whole cond/bias row preloaded before the accumulator wait
+    const uint32_t sb1 = ptx::smem_u32(&s_bias1[grp][0]);
+    int bias_b = -1;                             // batch row whose cond/bias vector is staged in s_bias1[grp]
     for (int n = grp; n < my_tiles; n += G::NGRP, tile_next()) {
       const Cursor gb{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
       tile_seek();
@@ -397,30 +438,26 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
       const int t = t0 - G::P2 + r;
       const bool live = t >= 0 && t < valid;     // G outside the sequence is the conv's zero padding
-      const float* bias = a.bias1 + (long long)b * a.bias1_bstride;
-      float pa[kBiasRegs ? G::C2 : 16], pb[kBiasRegs ? G::C2 : 16];
-      if (kBiasRegs) {
-#pragma unroll
-        for (int c = 0; c < NCH; ++c) {
-          load16(bias + 16 * c, *reinterpret_cast<float(*)[16]>(&pa[kBiasRegs ? 16 * c : 0]));
-          load16(bias + G::C2 + 16 * c, *reinterpret_cast<float(*)[16]>(&pb[kBiasRegs ? 16 * c : 0]));
-        }
+      if (b != bias_b) {                         // uniform over the group's 4 warps (same tile sequence)
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");      // everyone is done with the old vector
+        const float* bias = a.bias1 + (long long)b * a.bias1_bstride;
+        for (int i = r; i < C; i += 128) s_bias1[grp][i] = bias[i];
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
+        bias_b = b;
       }
       const int s = gb.idx;
       ptx::mbar_wait(acc1_full(s), gb.phase);
       ptx::mbar_wait(g_empty(s), gb.phase ^ 1u);
       ptx::tc_fence_after();
+      if ((warp & 3) == 0) trace(3, n, 0);
       const uint32_t trow = tmem_base + acc1_col + s * C + (static_cast<uint32_t>(q * 32) << 16);
       const uint32_t grow = sG + s * G::G_SET + r * G::rb2;
 #pragma unroll
       for (int c = 0; c < NCH; ++c) {
         const int c0 = 16 * c;
-        if (!kBiasRegs) {
-          load16(bias + c0, *reinterpret_cast<float(*)[16]>(&pa[0]));       // issued before the TMEM loads so both latencies overlap
-          load16(bias + G::C2 + c0, *reinterpret_cast<float(*)[16]>(&pb[0]));
-        }
-        const float* ba = &pa[kBiasRegs ? c0 : 0];
-        const float* bb = &pb[kBiasRegs ? c0 : 0];
+        float ba[16], bb[16];
+        lds16(sb1 + 4 * c0, ba);                 // issued before the TMEM loads so both latencies overlap
+        lds16(sb1 + 4 * (G::C2 + c0), bb);
         uint32_t ra[16], rb[16];
         ptx::tmem_ld16(trow + c0, ra);
         ptx::tmem_ld16(trow + G::C2 + c0, rb);
@@ -432,6 +469,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           const float v1 = gate_fast(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1]);
           p[i] = live ? Pack16<OpT>::pack2(v0, v1) : 0u;
         }
+        if (rt.dbg & 4) continue;
         // channel c0..c0+15 of row r -> block cb2, two 16-byte chunks, swizzled like a TMA write would
         const int cb2 = c0 / G::BK2, cin = c0 - cb2 * G::BK2;
         const uint32_t rowaddr = grow + cb2 * G::G_BYTES + cin * 2;
@@ -446,6 +484,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         if (G::PAIR) { ptx::mbar_arrive_leader(g_full(s)); ptx::mbar_arrive_leader(acc1_empty(s)); }
         else { ptx::mbar_arrive(g_full(s)); ptx::mbar_arrive(acc1_empty(s)); }
       }
+      if ((warp & 3) == 0) trace(3, n, 1);
     }
   } else if (warp >= 8) {
     // =================== epilogue 2: bias + residual + leaky_relu -> global ===================
@@ -456,7 +495,8 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     const uint32_t slab_bytes = rt.slab_bytes;
     const int srow = r + G::P2 + rt.p1;          // slab row holding y_in[t]
     constexpr int NCH = C / 16;                  // 16-column chunks per row
-    constexpr int PF = NCH < 4 ? NCH : 4;        // residual chunks kept in flight (2 x uint4 each)
+    const uint32_t sb2 = ptx::smem_u32(&s_bias2[0]);
+    constexpr int PF = G::NGRP == 2 ? (NCH < 4 ? NCH : 4) : 8;   // residual chunks kept in flight (2 x uint4 each; 96-register cap with 20 warps)
     Cursor sl{0, 0};
     if (grp == 1) sl.next(nSlab);
     for (int n = grp; n < my_tiles; n += G::NGRP, tile_next()) {
@@ -476,7 +516,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       auto load_y = [&](int c, uint4 (&dst)[2]) {
         if (G::RES_GLOBAL) {
           dst[0] = dst[1] = make_uint4(0u, 0u, 0u, 0u);
-          if (in_range) { dst[0] = __ldg(yres + 2 * c); dst[1] = __ldg(yres + 2 * c + 1); }
+          if (in_range && !(rt.dbg & 2)) { dst[0] = ldg_nc_v4_pinned(yres + 2 * c); dst[1] = ldg_nc_v4_pinned(yres + 2 * c + 1); }
         } else {
           const int c0 = 16 * c, cb = c0 / G::BK1, cin = c0 - cb * G::BK1;
           const uint32_t yaddr = yrow + cb * slab_bytes + cin * 2;
@@ -488,15 +528,19 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       for (int c = 0; c < PF; ++c) load_y(c, yq[c]);
       ptx::mbar_wait(acc2_full(s), ab.phase);
       ptx::tc_fence_after();
+      if ((warp & 3) == 0) trace(4, n, 0);
       const uint32_t trow = tmem_base + acc2_col + s * C + (static_cast<uint32_t>(q * 32) << 16);
 #pragma unroll
       for (int c = 0; c < NCH; ++c) {
         const int c0 = 16 * c;
         float bv[16];
-        load16(a.bias2 + c0, bv);
+        lds16(sb2 + 4 * c0, bv);
         uint32_t ra[16];
-        ptx::tmem_ld16(trow + c0, ra);
-        ptx::tmem_ld_wait();
+        if (!(rt.dbg & 32)) { ptx::tmem_ld16(trow + c0, ra); ptx::tmem_ld_wait(); }
+        else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) ra[i] = 0u;
+        }
         const uint4 y0 = yq[c % PF][0], y1 = yq[c % PF][1];
         if (c + PF < NCH) load_y(c + PF, yq[c % PF]);
         const uint32_t yw[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
@@ -509,7 +553,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           v[2 * i + 1] = (__uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1]) + fminf(y.y, 10.f * y.y);
         }
         if (!LAST) {
-          if (in_range) {
+          if (in_range && !(rt.dbg & 1)) {
             uint32_t pk[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -521,10 +565,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
             d[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
             d[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
           }
-        } else if (in_range) {
+        } else if (in_range && !(rt.dbg & 1)) {
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] *= a.scale;
-          if (a.acc_mode & RB_ACC_READ) {
+          if ((a.acc_mode & RB_ACC_READ) && !(rt.dbg & 2)) {
             float x[16];
             load16(a.acc + orow + c0, x);
 #pragma unroll
@@ -549,6 +593,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         if (G::PAIR) ptx::mbar_arrive_leader(acc2_empty(s)); else ptx::mbar_arrive(acc2_empty(s));
         if (!G::RES_GLOBAL) ptx::mbar_arrive(slab_empty(ss));
       }
+      if ((warp & 3) == 0) trace(4, n, 1);
 #pragma unroll
       for (int i = 0; i < G::NGRP; ++i) sl.next(nSlab);
     }
@@ -598,6 +643,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
     if (rt.nW > 8) rt.nW = 8;
   }
   rt.idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM * G::NCL, C);
+  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("VITSB_RB_DBG"); dbg = e ? atoi(e) : 0; } rt.dbg = dbg; }
 
   TmaEncodeFn enc = tma_encode_fn();
   if (!enc) return cudaErrorNotSupported;
@@ -635,7 +681,11 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
     // opt-in limit is 227 KB per CTA INCLUDING the kernel's static shared memory (tile table)
-    attr_err = cudaFuncSetAttribute(rb_fused_kernel<OpT, C, KT, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize, 224 * 1024);
+    cudaFuncAttributes fa{};
+    attr_err = cudaFuncGetAttributes(&fa, rb_fused_kernel<OpT, C, KT, LAST>);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(rb_fused_kernel<OpT, C, KT, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      232448 - (int)fa.sharedSizeBytes);
     int dev = 0; cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
   });
@@ -649,6 +699,15 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   const int grid = units * G::NCL;
   RbArgs args = L.a;
   args.y_res = L.y_in;
+  static long long* d_trace = nullptr;
+  static int trace_C = -1, trace_K = 0, trace_left = 0;
+  if (trace_C < 0) {
+    const char* e = getenv("VITSB_RB_TRACE");      // "C,k,count": dump the CTA-0 timeline of the first `count` launches of that shape
+    trace_C = 0;
+    if (e && sscanf(e, "%d,%d,%d", &trace_C, &trace_K, &trace_left) == 3) cudaMalloc(&d_trace, 7 * 16 * 2 * sizeof(long long));
+  }
+  const bool tracing = d_trace && trace_C == C && trace_K == KT && trace_left > 0 && !LAST;
+  if (tracing) { cudaMemsetAsync(d_trace, 0, 7 * 16 * 2 * sizeof(long long), stream); args.trace = d_trace; }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid, 1, 1);
   cfg.blockDim = dim3(G::THREADS, 1, 1);
@@ -660,6 +719,26 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   cfg.attrs = at; cfg.numAttrs = 1;
   cudaError_t le = cudaLaunchKernelEx(&cfg, rb_fused_kernel<OpT, C, KT, LAST>, tmY, tmW1, tmW2, args, rt);
   if (le == cudaSuccess) le = cudaGetLastError();
+  if (tracing && le == cudaSuccess) {
+    --trace_left;
+    long long h[7 * 16 * 2];
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(h, d_trace, sizeof(h), cudaMemcpyDeviceToHost);
+    long long t0 = 0;
+    for (long long v : h) if (v && (!t0 || v < t0)) t0 = v;
+    const char* names[7] = {"slab.issue", "c1(slab_ok,done)", "c2(g_ok,done)", "gate(start,end)", "store(start,end)", "-", "c1.acc_ok"};
+    fprintf(stderr, "rb_fused trace C=%d k=%d dil=%d nSlab=%d nW=%d (cycles since first event, CTA 0)\n", C, KT, L.dil, rt.nSlab, rt.nW);
+    for (int r = 0; r < 7; ++r) {
+      if (r == 5) continue;
+      fprintf(stderr, "  %-18s", names[r]);
+      for (int t = 0; t < 8; ++t) {
+        const long long x = h[(r * 16 + t) * 2], y = h[(r * 16 + t) * 2 + 1];
+        if (!x && !y) break;
+        fprintf(stderr, " [%lld,%lld]", x ? x - t0 : -1, y ? y - t0 : -1);
+      }
+      fprintf(stderr, "\n");
+    }
+  }
   if (le != cudaSuccess)
     fprintf(stderr, "rb_fused launch failed (%s): C=%d k=%d dil=%d grid=%d smem=%zu nSlab=%d nW=%d\n", cudaGetErrorString(le),
             C, KT, L.dil, grid, smem, rt.nSlab, rt.nW);
