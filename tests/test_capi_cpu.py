@@ -42,7 +42,9 @@ def test_sass_has_tcgen05_and_tma():
     assert "UTCHMMA" in sass or "UTCMMA" in sass      # tcgen05.mma
     assert "UTMALDG" in sass                           # TMA tensor load
     assert "LDTM" in sass                              # tcgen05.ld
-    assert "HMMA." not in sass                         # no legacy mma.sync path
+    import re
+    assert "UTCHMMA.2CTA" in sass                      # CTA-pair (cta_group::2) MMAs
+    assert not re.search(r"(?<![A-Z])HMMA\.", sass)    # no legacy mma.sync path (UTCHMMA.2CTA contains the substring)
 
 
 def test_config_validation_without_device(lib, base_cfg):

@@ -92,6 +92,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   ptx::tc_fence_before();
   if (TWO) ptx::cluster_sync_all(); else __syncthreads();    // barrier inits visible to the peer before any remote signal
   ptx::tc_fence_after();
+  ptx::pdl_launch_dependents();
+  ptx::pdl_wait();                   // prologue above overlapped the previous kernel's tail
   const uint32_t tmem_base = s_tmem;
 
   const int nNT = g.nNT;
@@ -228,6 +230,12 @@ TmaEncodeFn tma_encode_fn() {
   return fn;
 }
 
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("VITSB_PDL"); v = (e && e[0] == '1') ? 1 : 0; }   // measured neutral-to-slightly-negative: off unless VITSB_PDL=1
+  return v == 1;
+}
+
 bool conv_tc_supported(int Cin, int in_ld, int N, int NT, int k) {
   // (in_cols, when different from Cin, must be a multiple of the K block; checked in make_geom)
   if (!(Cin == 16 || Cin == 32 || (Cin % 64 == 0 && Cin > 0))) return false;
@@ -351,10 +359,12 @@ cudaError_t launch_conv_tc(const ConvArgs& a_in, int op, cudaStream_t stream) {
   cfg.blockDim = dim3(kTcThreads, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute at[1];
+  cudaLaunchAttribute at[2];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = ncl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-  cfg.attrs = at; cfg.numAttrs = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
   cudaError_t le;
   if (ncl == 2) {
     le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, conv_tc_kernel<__nv_bfloat16, true>, tmA, tmB, a, g)

@@ -47,6 +47,8 @@ typedef CUresult (*TmaEncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, v
                                 const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
                                 CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 TmaEncodeFn tma_encode_fn();
+// programmatic dependent launch between consecutive tensor-core kernels (VITSB_PDL=0 disables)
+bool pdl_enabled();
 
 // aux_kernels.cu
 // [B][C][T] fp32 channel-major -> time-major fp32 (+ operand copy), rows >= len[b] zeroed

@@ -104,6 +104,13 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
+// ---------------- programmatic dependent launch ----------------
+// Kernels launched with cudaLaunchAttributeProgrammaticStreamSerialization may start (barrier init, TMEM
+// allocation, tensor-map prefetch) while the previous kernel of the stream is still draining; pdl_wait()
+// blocks until that kernel has completed and its writes are visible, pdl_launch_dependents() lets the next one in.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 // ---------------- CTA pair (cta_group::2) ----------------
 // Two CTAs of a (2,1,1) cluster share one UMMA: M = 256 (128 rows from each CTA's smem A tile),
 // each CTA supplies half of the N rows of B and receives its own 128 x N accumulator in TMEM.

@@ -47,6 +47,16 @@
 
 namespace vitsb {
 
+// Timing-experiment hooks (scripts/gpu_ablate.sh, VITSB_RB_TRACE): compiled in only with -DVITSB_RB_DEBUG,
+// because even uniform run-time branches in the epilogue loops cost ~5 % of the kernel.
+#ifdef VITSB_RB_DEBUG
+#define RB_DBG(mask) ((rt.dbg & (mask)) != 0)
+#define RB_TRACE_ON 1
+#else
+#define RB_DBG(mask) (false)
+#define RB_TRACE_ON 0
+#endif
+
 constexpr int kRbMaxB = 512;
 constexpr uint32_t kRbSmemBudget = 220 * 1024;
 
@@ -108,7 +118,7 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
 // free to move across the memory-clobbering tcgen05 asm statements, which silently undoes a software prefetch).
 __device__ __forceinline__ uint4 ldg_nc_v4_pinned(const void* p) {
   uint4 v;
-  asm volatile("ld.global.nc.L1::no_allocate.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  asm volatile("ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
   return v;
 }
 // 16 consecutive floats from shared memory (all lanes read the same address: broadcast, conflict-free)
@@ -163,8 +173,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   __shared__ uint32_t s_tmem;
   // Bias vectors staged in shared memory: with ~220 KB of the SM's 256 KB carved out as smem the L1 is a few KB
   // and the residual stream flushes it, so per-chunk bias loads from global paid an L2 round trip each.
-  __shared__ __align__(16) float s_bias2[C];            // conv2 bias
-  __shared__ __align__(16) float s_bias1[2][C];         // per epilogue group: conv1 bias + conditioning of the current batch row
+  constexpr int kSB = C >= 128 ? C : 4;                   // small C reads its biases from global / L1 (measured faster there)
+  __shared__ __align__(16) float s_bias2[kSB];            // conv2 bias
+  __shared__ __align__(16) float s_bias1[2][kSB];         // per epilogue group: conv1 bias + conditioning of the current batch row
 
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t slab_set = G::nCB1 * rt.slab_bytes;
@@ -200,7 +211,8 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     }
     s_tile_prefix[a.B] = acc;
   }
-  for (int i = threadIdx.x; i < C; i += blockDim.x) s_bias2[i] = a.bias2[i];
+  if (C >= 128)
+    for (int i = threadIdx.x; i < C; i += blockDim.x) s_bias2[i] = a.bias2[i];
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmY); ptx::prefetch_tmap(&tmW1); ptx::prefetch_tmap(&tmW2);
     // slab release: c1's MMA commit, plus the 4 store-epilogue warps when they read the residual from the slab
@@ -219,14 +231,16 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   ptx::tc_fence_before();
   if (G::PAIR) ptx::cluster_sync_all(); else __syncthreads();      // barrier inits visible to the peer before any remote signal
   ptx::tc_fence_after();
+  ptx::pdl_launch_dependents();      // the next kernel may begin its own prologue on SMs this grid has left
+  ptx::pdl_wait();                   // everything above overlapped the previous kernel's tail; its outputs are needed from here on
   const uint32_t tmem_base = s_tmem;
   // timeline trace of CTA 0 (VITSB_RB_TRACE): trace[(role * 16 + tile) * 2 + kind] = clock64()
   auto trace = [&](int role, int tile, int kind) {
-    if (a.trace && blockIdx.x == 0 && tile < 16 && lane == 0) a.trace[(role * 16 + tile) * 2 + kind] = clock64();
+    if (RB_TRACE_ON && a.trace && blockIdx.x == 0 && tile < 16 && lane == 0) a.trace[(role * 16 + tile) * 2 + kind] = clock64();
   };
   const int total_tiles = s_tile_prefix[a.B];
   const int total_units = (total_tiles + G::NCL - 1) / G::NCL;      // pair mode: tiles 2u and 2u+1 (the last may be missing)
-  const int my_tiles = (rt.dbg & 256) ? 0 : (total_units > unit_id ? (total_units - 1 - unit_id) / n_units + 1 : 0);
+  const int my_tiles = RB_DBG(256) ? 0 : (total_units > unit_id ? (total_units - 1 - unit_id) / n_units + 1 : 0);
   constexpr uint32_t acc1_col = 0, acc2_col = G::NBUF * C;       // TMEM columns: [acc1 x NBUF][acc2 x NBUF]
 
   // static round-robin schedule; b only grows along a CTA's tile sequence
@@ -256,7 +270,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const int t0 = tile_t0();
       ptx::mbar_wait(slab_empty(sl.idx), sl.phase ^ 1u);
       trace(0, n, 0);
-      if (leader && (rt.dbg & 64)) {
+      if (leader && RB_DBG(64)) {
         if (rank == 0) ptx::mbar_arrive(slab_full(sl.idx));
       } else if (leader) {
         if (rank == 0) ptx::mbar_expect_tx(slab_full(sl.idx), slab_tx * G::NCL);      // pair: both CTAs' slabs land on the leader's barrier
@@ -292,9 +306,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           for (int j = 0; j < KT; ++j) {
             ptx::mbar_wait(w_empty(wr.idx), wr.phase ^ 1u);
             if (leader) {
-              if (rt.dbg & 128) { if (rank == 0) ptx::mbar_arrive(w_full(wr.idx)); }
+              if RB_DBG(128) { if (rank == 0) ptx::mbar_arrive(w_full(wr.idx)); }
               else if (rank == 0) ptx::mbar_expect_tx(w_full(wr.idx), G::W1_TX * G::NCL);
-              if (rt.dbg & 128) {}
+              if RB_DBG(128) {}
               else if (G::PAIR) ptx::tma_load_2d_2sm(sW + wr.idx * G::W_SLOT, &tmW1, w_full(wr.idx), j * C + cb * G::BK1, rank * (C / 2));
               else ptx::tma_load_2d(sW + wr.idx * G::W_SLOT, &tmW1, w_full(wr.idx), j * C + cb * G::BK1, 0);
             }
@@ -306,9 +320,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           for (int j = 0; j < KT; ++j) {
             ptx::mbar_wait(w_empty(wr.idx), wr.phase ^ 1u);
             if (leader) {
-              if (rt.dbg & 128) { if (rank == 0) ptx::mbar_arrive(w_full(wr.idx)); }
+              if RB_DBG(128) { if (rank == 0) ptx::mbar_arrive(w_full(wr.idx)); }
               else if (rank == 0) ptx::mbar_expect_tx(w_full(wr.idx), G::W2_TX * G::NCL);
-              if (rt.dbg & 128) {}
+              if RB_DBG(128) {}
               else if (G::PAIR) ptx::tma_load_2d_2sm(sW + wr.idx * G::W_SLOT, &tmW2, w_full(wr.idx), j * G::C2 + cb * G::BK2, rank * (C / 2));
               else ptx::tma_load_2d(sW + wr.idx * G::W_SLOT, &tmW2, w_full(wr.idx), j * G::C2 + cb * G::BK2, 0);
             }
@@ -336,7 +350,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       if (G::STATIONARY) { ptx::mbar_wait(w_all, 0); ptx::tc_fence_after(); }
       // pair mode: one instruction drives both CTAs' tensor cores; commits arrive on both CTAs' barrier copies
       auto mma = [&](uint32_t d, uint64_t ad, uint64_t bd, uint32_t id, uint32_t acc) {
-        if (rt.dbg & 8) return;
+        if RB_DBG(8) return;
         if (G::PAIR) ptx::umma_f16_2sm(d, ad, bd, id, acc); else ptx::umma_f16(d, ad, bd, id, acc);
       };
       auto commit = [&](uint32_t bar) { if (G::PAIR) ptx::umma_commit_2sm(bar); else ptx::umma_commit(bar); };
@@ -429,6 +443,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     // =================== epilogue 1: gate -> G tile in shared memory ===================
     const int q = warp & 3, r = q * 32 + lane;
     constexpr int NCH = G::C2 / 16;              // 16-gate chunks per row
+    // bias source: shared memory for C >= 128 (the L1 left next to ~220 KB of smem is tiny and the residual stream
+    // flushes it); global / L1 for small C, where the smem bandwidth belongs to the MMA operands (N <= 64 is smem-bound)
+    constexpr bool kBiasSmem = C >= 128;
     const uint32_t sb1 = ptx::smem_u32(&s_bias1[grp][0]);
     int bias_b = -1;                             // batch row whose cond/bias vector is staged in s_bias1[grp]
     for (int n = grp; n < my_tiles; n += G::NGRP, tile_next()) {
@@ -438,12 +455,24 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
       const int t = t0 - G::P2 + r;
       const bool live = t >= 0 && t < valid;     // G outside the sequence is the conv's zero padding
-      if (b != bias_b) {                         // uniform over the group's 4 warps (same tile sequence)
+      const float* gbias = a.bias1 + (long long)b * a.bias1_bstride;
+      if (kBiasSmem && b != bias_b) {            // uniform over the group's 4 warps (same tile sequence)
         asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");      // everyone is done with the old vector
         const float* bias = a.bias1 + (long long)b * a.bias1_bstride;
         for (int i = r; i < C; i += 128) s_bias1[grp][i] = bias[i];
         asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
         bias_b = b;
+      }
+      // small C: the whole cond/bias row is loaded before the accumulator wait (its latency hides behind c1)
+      constexpr bool kBiasRegs = !kBiasSmem && G::C2 <= 32;
+      float pa[kBiasRegs ? G::C2 : 1], pb[kBiasRegs ? G::C2 : 1];
+      if (kBiasRegs) {
+#pragma unroll
+        for (int i = 0; i < G::C2; i += 4) {
+          const float4 x = *reinterpret_cast<const float4*>(gbias + i), y = *reinterpret_cast<const float4*>(gbias + G::C2 + i);
+          pa[kBiasRegs ? i : 0] = x.x; pa[kBiasRegs ? i + 1 : 0] = x.y; pa[kBiasRegs ? i + 2 : 0] = x.z; pa[kBiasRegs ? i + 3 : 0] = x.w;
+          pb[kBiasRegs ? i : 0] = y.x; pb[kBiasRegs ? i + 1 : 0] = y.y; pb[kBiasRegs ? i + 2 : 0] = y.z; pb[kBiasRegs ? i + 3 : 0] = y.w;
+        }
       }
       const int s = gb.idx;
       ptx::mbar_wait(acc1_full(s), gb.phase);
@@ -456,25 +485,45 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       for (int c = 0; c < NCH; ++c) {
         const int c0 = 16 * c;
         float ba[16], bb[16];
-        lds16(sb1 + 4 * c0, ba);                 // issued before the TMEM loads so both latencies overlap
-        lds16(sb1 + 4 * (G::C2 + c0), bb);
+        if (!RB_DBG(2048)) {
+          if (kBiasSmem) {
+            lds16(sb1 + 4 * c0, ba);             // issued before the TMEM loads so both latencies overlap
+            lds16(sb1 + 4 * (G::C2 + c0), bb);
+          } else if (kBiasRegs) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) { ba[i] = pa[kBiasRegs ? c0 + i : 0]; bb[i] = pb[kBiasRegs ? c0 + i : 0]; }
+          } else {
+            load16(gbias + c0, ba);
+            load16(gbias + G::C2 + c0, bb);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) ba[i] = bb[i] = 0.f;
+        }
         uint32_t ra[16], rb[16];
-        ptx::tmem_ld16(trow + c0, ra);
-        ptx::tmem_ld16(trow + G::C2 + c0, rb);
-        ptx::tmem_ld_wait();
+        if (!RB_DBG(1024)) {
+          ptx::tmem_ld16(trow + c0, ra);
+          ptx::tmem_ld16(trow + G::C2 + c0, rb);
+          ptx::tmem_ld_wait();
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) ra[i] = rb[i] = 0u;
+        }
         uint32_t p[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
+          if RB_DBG(4) { p[i] = ra[i] ^ rb[i]; continue; }     // ablation: no gate math
           const float v0 = gate_fast(__uint_as_float(ra[2 * i]) + ba[2 * i], __uint_as_float(rb[2 * i]) + bb[2 * i]);
           const float v1 = gate_fast(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1]);
           p[i] = live ? Pack16<OpT>::pack2(v0, v1) : 0u;
         }
-        if (rt.dbg & 4) continue;
         // channel c0..c0+15 of row r -> block cb2, two 16-byte chunks, swizzled like a TMA write would
         const int cb2 = c0 / G::BK2, cin = c0 - cb2 * G::BK2;
         const uint32_t rowaddr = grow + cb2 * G::G_BYTES + cin * 2;
-        st_shared_v4(swz_addr<G::rb2>(rowaddr), p[0], p[1], p[2], p[3]);
-        st_shared_v4(swz_addr<G::rb2>(rowaddr + 16), p[4], p[5], p[6], p[7]);
+        if (!RB_DBG(4096)) {
+          st_shared_v4(swz_addr<G::rb2>(rowaddr), p[0], p[1], p[2], p[3]);
+          st_shared_v4(swz_addr<G::rb2>(rowaddr + 16), p[4], p[5], p[6], p[7]);
+        }
       }
       if (G::PAIR) asm volatile("fence.proxy.async;" ::: "memory");   // the leader's tensor core reads this CTA's G tile
       else fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the tensor core (async proxy)
@@ -509,14 +558,19 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const bool live = t < valid;
       const int s = ab.idx, ss = sl.idx;
       const long long orow = ((long long)b * a.L + t) * C;
-      const uint4* yres = reinterpret_cast<const uint4*>(reinterpret_cast<const OpT*>(a.y_res) + orow);
+      const long long orow_ld = RB_DBG(16384) ? (long long)r * C : orow;     // ablation: residual reads always hit the same hot rows
+      const uint4* yres = reinterpret_cast<const uint4*>(reinterpret_cast<const OpT*>(a.y_res) + orow_ld);
       const uint32_t yrow = sSlab + ss * slab_set + srow * G::rb1;
       // residual rows: issued before the accumulator wait so their latency hides behind c2
       uint4 yq[PF][2];
       auto load_y = [&](int c, uint4 (&dst)[2]) {
         if (G::RES_GLOBAL) {
           dst[0] = dst[1] = make_uint4(0u, 0u, 0u, 0u);
-          if (in_range && !(rt.dbg & 2)) { dst[0] = ldg_nc_v4_pinned(yres + 2 * c); dst[1] = ldg_nc_v4_pinned(yres + 2 * c + 1); }
+          if (in_range && !RB_DBG(2)) {
+            // C >= 128: pinned loads = a real software prefetch; C = 64 measured faster when ptxas places the loads itself
+            if (C >= 128) { dst[0] = ldg_nc_v4_pinned(yres + 2 * c); dst[1] = ldg_nc_v4_pinned(yres + 2 * c + 1); }
+            else { dst[0] = __ldg(yres + 2 * c); dst[1] = __ldg(yres + 2 * c + 1); }
+          }
         } else {
           const int c0 = 16 * c, cb = c0 / G::BK1, cin = c0 - cb * G::BK1;
           const uint32_t yaddr = yrow + cb * slab_bytes + cin * 2;
@@ -534,9 +588,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       for (int c = 0; c < NCH; ++c) {
         const int c0 = 16 * c;
         float bv[16];
-        lds16(sb2 + 4 * c0, bv);
+        if (C >= 128) lds16(sb2 + 4 * c0, bv); else load16(a.bias2 + c0, bv);
         uint32_t ra[16];
-        if (!(rt.dbg & 32)) { ptx::tmem_ld16(trow + c0, ra); ptx::tmem_ld_wait(); }
+        if (!RB_DBG(32)) { ptx::tmem_ld16(trow + c0, ra); ptx::tmem_ld_wait(); }
         else {
 #pragma unroll
           for (int i = 0; i < 16; ++i) ra[i] = 0u;
@@ -553,7 +607,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           v[2 * i + 1] = (__uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1]) + fminf(y.y, 10.f * y.y);
         }
         if (!LAST) {
-          if (in_range && !(rt.dbg & 1)) {
+          if (in_range && !RB_DBG(1)) {
             uint32_t pk[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
@@ -561,14 +615,15 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
               const uint32_t w = Pack16<OpT>::pack2(fmaxf(v[2 * i], 0.1f * v[2 * i]), fmaxf(v[2 * i + 1], 0.1f * v[2 * i + 1]));
               pk[i] = live ? w : 0u;
             }
-            uint4* d = reinterpret_cast<uint4*>(reinterpret_cast<OpT*>(a.y_out) + orow + c0);
+            const long long orow_st = RB_DBG(8192) ? (long long)r * C : orow;   // ablation: every tile stores to the same rows (no HBM write stream)
+            uint4* d = reinterpret_cast<uint4*>(reinterpret_cast<OpT*>(a.y_out) + orow_st + c0);
             d[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
             d[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
           }
-        } else if (in_range && !(rt.dbg & 1)) {
+        } else if (in_range && !RB_DBG(1)) {
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] *= a.scale;
-          if ((a.acc_mode & RB_ACC_READ) && !(rt.dbg & 2)) {
+          if ((a.acc_mode & RB_ACC_READ) && !RB_DBG(2)) {
             float x[16];
             load16(a.acc + orow + c0, x);
 #pragma unroll
@@ -713,10 +768,12 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   cfg.blockDim = dim3(G::THREADS, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute at[1];
+  cudaLaunchAttribute at[2];
   at[0].id = cudaLaunchAttributeClusterDimension;
   at[0].val.clusterDim.x = G::NCL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
-  cfg.attrs = at; cfg.numAttrs = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
   cudaError_t le = cudaLaunchKernelEx(&cfg, rb_fused_kernel<OpT, C, KT, LAST>, tmY, tmW1, tmW2, args, rt);
   if (le == cudaSuccess) le = cudaGetLastError();
   if (tracing && le == cudaSuccess) {
@@ -726,12 +783,11 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
     cudaMemcpy(h, d_trace, sizeof(h), cudaMemcpyDeviceToHost);
     long long t0 = 0;
     for (long long v : h) if (v && (!t0 || v < t0)) t0 = v;
-    const char* names[7] = {"slab.issue", "c1(slab_ok,done)", "c2(g_ok,done)", "gate(start,end)", "store(start,end)", "-", "c1.acc_ok"};
+    const char* names[7] = {"slab.issue", "c1(slab_ok,done)", "c2(g_ok,done)", "gate(start,end)", "store(start,end)", "gate0 chunk phases", "c1.acc_ok"};
     fprintf(stderr, "rb_fused trace C=%d k=%d dil=%d nSlab=%d nW=%d (cycles since first event, CTA 0)\n", C, KT, L.dil, rt.nSlab, rt.nW);
     for (int r = 0; r < 7; ++r) {
-      if (r == 5) continue;
       fprintf(stderr, "  %-18s", names[r]);
-      for (int t = 0; t < 8; ++t) {
+      for (int t = 0; t < (r == 5 ? 16 : 8); ++t) {
         const long long x = h[(r * 16 + t) * 2], y = h[(r * 16 + t) * 2 + 1];
         if (!x && !y) break;
         fprintf(stderr, " [%lld,%lld]", x ? x - t0 : -1, y ? y - t0 : -1);

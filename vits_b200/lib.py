@@ -6,7 +6,7 @@ import ctypes as C
 import os
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libvitsb200.so")
+LIB_PATH = os.environ.get("VITSB_LIB", os.path.join(HERE, "libvitsb200.so"))   # VITSB_LIB: A/B a differently built library
 MAX_LIST = 8
 
 PREC_FP16, PREC_BF16, PREC_FP32 = 0, 1, 2
