@@ -148,6 +148,33 @@ def test_c2_batch16_properties(base_cfg, base_sd):
     assert (w32[b:b + 1, :, :lens[b] * 192].cpu() - orr).abs().max().item() <= 1e-5
 
 
+@pytest.mark.parametrize("prec", ["fp16", "fp32"])
+def test_graph_replay_is_bit_identical(base_cfg, base_sd, prec):
+    """The engine issues a shape directly on its first call, captures the workspace-only launches into a CUDA
+    graph on the second and replays it afterwards: all three must agree bit for bit, new input values and
+    fresh input / output buffers must flow through the replay, and a change of lengths must not reuse it."""
+    from vits_b200 import FlowDecoder
+    eng = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision=prec)      # fresh engine: empty graph cache
+    lens = [40, 97, 64]
+    lat = FX.make_latents(base_cfg, lens, seed=77)
+    zp, g = lat["z_p"].cuda(), lat["g"].cuda()
+    w = [eng.synthesize(zp, g, lens).clone() for _ in range(4)]                 # direct, capture, replay, replay
+    for x in w[1:]:
+        assert torch.equal(w[0], x)
+    lat2 = FX.make_latents(base_cfg, lens, seed=78)
+    zp2, g2 = lat2["z_p"].cuda(), lat2["g"].cuda()
+    keep = torch.empty(1 << 20, device="cuda")                                  # perturb the allocator: new buffer addresses
+    w_replay = eng.synthesize(zp2, g2, lens)
+    ref = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision=prec).synthesize(zp2, g2, lens)   # first call: direct
+    assert torch.equal(w_replay, ref) and not torch.equal(w_replay, w[0])
+    lens3 = [40, 90, 64]
+    w3 = eng.synthesize(zp, g, lens3)
+    ref3 = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision=prec).synthesize(zp, g, lens3)
+    assert torch.equal(w3, ref3)
+    assert w3[1, 0, 90 * 192:].abs().sum().item() == 0
+    del keep
+
+
 def test_c3_long_form(base_cfg, base_sd):
     """BASELINE config 3: 60 s single utterance (T=5000)."""
     lat = FX.make_latents(base_cfg, [5000], seed=3)

@@ -40,9 +40,17 @@ struct TcGeom {
   uint32_t b_stride; // smem bytes per B stage (b_bytes rounded to 1024)
   uint32_t tmem_cols;
   uint32_t idesc;
+  int dbg;           // VITSB_TC_DBG timing-experiment mask (only with -DVITSB_RB_DEBUG; results are wrong when set)
 };
 
-constexpr int kTcThreads = 320;
+#ifdef VITSB_RB_DEBUG
+#define TC_DBG(mask) ((g.dbg & (mask)) != 0)
+#else
+#define TC_DBG(mask) (false)
+#endif
+
+constexpr int kTcEpiGroups = 2;                         // 4-warp epilogue groups; every group works on every tile (column units dealt round-robin)
+constexpr int kTcThreads = 64 + 128 * kTcEpiGroups;
 constexpr int kTcMaxB = 512;
 
 // TWO = true: CTA-pair mode (cluster of 2, tcgen05 cta_group::2).  A work item is a PAIR of time tiles
@@ -71,21 +79,12 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const int ncl = TWO ? 2 : 1;                                                                // CTAs per work item
   const int cl_id = blockIdx.x / ncl, n_cl = gridDim.x / ncl;
 
-  if (threadIdx.x == 0) {
-    int acc = 0;
-    for (int b = 0; b < a.B; ++b) {
-      s_prefix[b] = acc;
-      const int valid = a.len ? a.len[b] * a.len_mul : a.L;
-      const int rows = valid + kHaloRows < a.L ? valid + kHaloRows : a.L;   // rows nobody reads are skipped
-      acc += (rows + kTileM - 1) / kTileM;
-    }
-    s_prefix[a.B] = acc;
-  }
+  if (warp == 2) build_tile_prefix(s_prefix, a.B, a.len, a.len_mul, a.L, kTileM, lane);
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
     for (int s = 0; s < 8; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full(i), 1); ptx::mbar_init(acc_empty(i), 4 * ncl); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full(i), 1); ptx::mbar_init(acc_empty(i), 4 * kTcEpiGroups * ncl); }
     ptx::mbar_fence_init();
   }
   if (warp == 1) { if (TWO) ptx::tmem_alloc_2sm(ptx::smem_u32(&s_tmem), g.tmem_cols); else ptx::tmem_alloc(ptx::smem_u32(&s_tmem), g.tmem_cols); }
@@ -135,7 +134,20 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         int col = 0;                                  // (kc * BK) % in_cols without the division
         for (int kc = 0; kc < kchunks; ++kc) {
           ptx::mbar_wait(empty_bar(s), ph ^ 1u);
-          if (leader) {
+          if (leader && (TC_DBG(1) || TC_DBG(2))) {
+            // ablation: 1 = A loaded only where a slab would load it (tap 0, first pass over the columns); 2 = no B loads
+            const bool ldA = !TC_DBG(1) || (j == 0 && kc * BK < in_cols), ldB = !TC_DBG(2);
+            const uint32_t tx = ((ldA ? g.a_bytes : 0u) + (ldB ? g.b_bytes : 0u)) * ncl;
+            if (tx == 0) { if (rank == 0) ptx::mbar_arrive(full_bar(s)); }
+            else if (!TWO || rank == 0) ptx::mbar_expect_tx(full_bar(s), tx);
+            if (TWO) {
+              if (ldA) ptx::tma_load_3d_2sm(sA + s * a_bytes, &tmA, full_bar(s), col, row0 + j * dil, b);
+              if (ldB) ptx::tma_load_2d_2sm(sB + s * b_stride, &tmB, full_bar(s), j * Cin + kc * BK, n0);
+            } else {
+              if (ldA) ptx::tma_load_3d(sA + s * a_bytes, &tmA, full_bar(s), col, row0 + j * dil, b);
+              if (ldB) ptx::tma_load_2d(sB + s * b_stride, &tmB, full_bar(s), j * Cin + kc * BK, n0);
+            }
+          } else if (leader) {
             if (TWO) {
               if (rank == 0) ptx::mbar_expect_tx(full_bar(s), tx_bytes);
               ptx::tma_load_3d_2sm(sA + s * a_bytes, &tmA, full_bar(s), col, row0 + j * dil, b);
@@ -187,21 +199,24 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncwarp();
   } else {
     // ===== epilogue groups: TMEM -> registers -> fused math -> global =====
-    const int grp = warp >= 6 ? 1 : 0;
-    for (int n = grp; n < my_items; n += 2) {
+    // All groups work on every tile (tc_epilogue deals the column units out); accumulators alternate per item.
+    const int grp = (warp - 2) >> 2;
+    for (int n = 0; n < my_items; ++n) {
       int b, t0, ntile; bool live;
       coords(cl_id + n * n_cl, b, t0, ntile, live);
       const int valid = a.len ? a.len[b] * a.len_mul : a.L;
-      ptx::mbar_wait(acc_full(grp), (n >> 1) & 1);
-      ptx::tc_fence_after();
-      if (live) {
+      const int buf = n & 1;
+      auto wait_acc = [&]() { ptx::mbar_wait(acc_full(buf), (n >> 1) & 1); ptx::tc_fence_after(); };
+      if (live && !TC_DBG(4)) {
         const int nsplit_tile = a.n_split > 0 ? a.n_split / a.NT : nNT;
-        if (ntile < nsplit_tile) tc_epilogue<OpT>(a, a.epi, b, t0, ntile, valid, tmem_base + grp * a.NT, warp & 3, lane);
-        else tc_epilogue<OpT>(a, a.epi_b, b, t0, ntile - nsplit_tile, valid, tmem_base + grp * a.NT, warp & 3, lane);
+        if (ntile < nsplit_tile) tc_epilogue<OpT>(a, a.epi, b, t0, ntile, valid, tmem_base + buf * a.NT, warp & 3, lane, grp, kTcEpiGroups, wait_acc);
+        else tc_epilogue<OpT>(a, a.epi_b, b, t0, ntile - nsplit_tile, valid, tmem_base + buf * a.NT, warp & 3, lane, grp, kTcEpiGroups, wait_acc);
+      } else {
+        wait_acc();
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) { if (TWO) ptx::mbar_arrive_leader(acc_empty(grp)); else ptx::mbar_arrive(acc_empty(grp)); }
+      if (lane == 0) { if (TWO) ptx::mbar_arrive_leader(acc_empty(buf)); else ptx::mbar_arrive(acc_empty(buf)); }
     }
   }
 
@@ -313,6 +328,7 @@ cudaError_t launch_conv_tc(const ConvArgs& a_in, int op, cudaStream_t stream) {
   const int ncl = (pair_mode_enabled() && a.NT % 32 == 0 && a.NT >= 32) ? 2 : 1;
   TcGeom g;
   if (!make_geom(a, op, ncl, &g)) return cudaErrorNotSupported;
+  { static int dbg = -1; if (dbg < 0) { const char* e = getenv("VITSB_TC_DBG"); dbg = e ? atoi(e) : 0; } g.dbg = dbg; }
   TmaEncodeFn enc = tma_encode_fn();
   if (!enc) return cudaErrorNotSupported;
 

@@ -83,8 +83,21 @@ struct Engine {
   int load(const vitsb_tensor_desc* t, int n);
   WsLayout layout(int B, int T) const;
 
+  // CUDA-graph replay of the launch plan (engine_run.cu): the ~110 kernels between the two seams of a call are
+  // launch-latency bound for short batches; a call repeated with the same (workspace, B, T, lengths) replays an
+  // instantiated graph instead of re-issuing them.  VITSB_GRAPH=0 disables.
+  struct GraphEntry { std::vector<long long> key; int seen = 0; int launches = 0; cudaGraphExec_t exec = nullptr; unsigned long long stamp = 0; };
+  std::vector<GraphEntry> graphs;
+  cudaStream_t cap_stream = nullptr;
+  unsigned long long graph_clock = 0;
+
   // mode bits for run()
   enum { RUN_FLOW = 1, RUN_DEC = 2 };
+  // phases of one call: FRONT = length upload + seam pack + conditioning GEMV (read caller pointers),
+  // MID = every conv of the flow and the decoder (workspace only), BACK = conv_post (writes the caller's waveform)
+  enum { PH_FRONT = 1, PH_MID = 2, PH_BACK = 4, PH_ALL = 7 };
+  int issue(int phases, int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
+            float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches);
   int run(int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
           float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches);
 };

@@ -58,6 +58,7 @@ struct Ctx {
   Engine* e;
   cudaStream_t stream;
   bool dry;
+  bool skip = false;     // current phase is not part of this issue() pass: launches are neither made nor counted
   int launches = 0;
   std::vector<ProfEv> evs;
   double valid_frames = 0;   // sum_b min(len[b], T) (host-side, for algorithmic FLOP attribution)
@@ -101,6 +102,7 @@ struct Ctx {
   }
   void conv(int tag, const PackedConv& p, const void* in, int L, int len_mul, const int* len, const Epilogue& ep_in,
             const PackedConv* p2 = nullptr, const Epilogue* ep2 = nullptr) {
+    if (skip) return;
     ++launches;
     if (dry || !ok()) return;
     ev_begin(tag, (p.flop_per_pos + (p2 ? p2->flop_per_pos : 0.0)) * (len ? valid_frames : (double)B * T) * len_mul);
@@ -144,8 +146,8 @@ void set_out_op_split(Epilogue& ep, void* p, int C, long long L, float slope, bo
 
 }  // namespace
 
-int Engine::run(int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
-                float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches) {
+int Engine::issue(int phases, int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
+                  float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches) {
   if (!dry) {
     if (!loaded) return fail(VITSB_ERR_WEIGHTS, "weights not loaded");
     if (!z_in || !g || !ws) return fail(VITSB_ERR_BAD_ARG, "null pointer");
@@ -172,7 +174,7 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
   cx.len_flow = len ? d_len : nullptr;
   cx.len_dec = (len && ragged) ? d_len : nullptr;
 
-#define AUX_LAUNCH(tag, expr) do { ++cx.launches; if (!dry && cx.ok()) { cx.ev_begin(tag, 0.0); cx.err = (expr); cx.ev_end(); } } while (0)
+#define AUX_LAUNCH(tag, expr) do { if (cx.skip) break; ++cx.launches; if (!dry && cx.ok()) { cx.ev_begin(tag, 0.0); cx.err = (expr); cx.ev_end(); } } while (0)
   if (!dry) {
     if (len) for (int b = 0; b < B; ++b) cx.valid_frames += len[b];
     else cx.valid_frames = (double)B * T;
@@ -181,13 +183,15 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
   if (!dry) {
     cudaError_t e0 = cudaSetDevice(device);
     if (e0 != cudaSuccess) return fail(VITSB_ERR_CUDA, cudaGetErrorString(e0));
-    if (len) cx.err = cudaMemcpyAsync(d_len, len, sizeof(int) * B, cudaMemcpyHostToDevice, stream);
+    if (len && (phases & PH_FRONT)) cx.err = cudaMemcpyAsync(d_len, len, sizeof(int) * B, cudaMemcpyHostToDevice, stream);
   }
+  cx.skip = !(phases & PH_FRONT);
   // seam: channel-major fp32 -> time-major (masked beyond len)
   AUX_LAUNCH(T_PACK, launch_pack_time_major(z_in, B, IC, T, cx.len_flow, (what & RUN_FLOW) ? F(W.zf) : nullptr, P(W.zop), op, split16 ? 1 : 0, stream));
   // all conditioning Linears of the call: flow cond_layers (modules.py:161) + ResBlock conds (modules.py:254)
   AUX_LAUNCH(T_COND, launch_cond_gemv(d_condW, d_condB, g, B, Ncond, cfg.gin_channels, F(W.cond), stream));
 
+  cx.skip = !(phases & PH_MID);
   if (what & RUN_FLOW) {
     for (const Coupling& cp : couplings) {
       // h = pre(x0)                                                   modules.py:364
@@ -248,6 +252,7 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
           const ResIter& it = st.rb[j][d];
           if (rb_fused) {
             // whole iteration in one kernel; the residual stream is y = op(leaky_relu(x)) only (rb_fused.cu)
+            if (cx.skip) continue;
             ++cx.launches;
             if (dry || !cx.ok()) continue;
             RbLaunch rl{};
@@ -300,6 +305,7 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
       }
     }
     // tanh(conv_post(leaky_relu(x, 0.01)))                                 models.py:315-317
+    cx.skip = !(phases & PH_BACK);
     AUX_LAUNCH(T_POST, launch_conv_post(F(W.acc_f), B, L, post_C, post_k, 0.01f, d_post, cx.len_dec, mul, wav, stream));
   }
 #undef AUX_LAUNCH
@@ -317,6 +323,72 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
   }
   if (!cx.ok()) return fail(VITSB_ERR_CUDA, std::string("launch failed: ") + cudaGetErrorString(cx.err));
   return VITSB_OK;
+}
+
+static bool graphs_enabled() {
+  static int v = -1;
+  if (v < 0) { const char* e = getenv("VITSB_GRAPH"); v = (e && e[0] == '0') ? 0 : 1; }
+  return v == 1;
+}
+
+// Public entry: issue the plan directly, or - from the second identical call on - replay its middle part
+// (every launch that touches only the workspace) as an instantiated CUDA graph.  The seam kernels that read or
+// write caller pointers stay outside the graph, so fresh input / output buffers do not invalidate it.
+int Engine::run(int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
+                float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches) {
+  if (dry || profile || z_out || !graphs_enabled() || B < 1 || B > 4096)
+    return issue(PH_ALL, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, stream, dry, launches);
+
+  std::vector<long long> key = {what, (long long)(uintptr_t)ws, (long long)ws_bytes, B, T, ragged, len ? 1 : 0};
+  if (len) key.insert(key.end(), len, len + B);
+  GraphEntry* ge = nullptr;
+  for (GraphEntry& x : graphs) if (x.key == key) { ge = &x; break; }
+  if (!ge) {                                     // first sighting: run directly, remember the shape
+    constexpr size_t kMaxGraphs = 16;
+    if (graphs.size() >= kMaxGraphs) {
+      size_t old = 0;
+      for (size_t i = 1; i < graphs.size(); ++i) if (graphs[i].stamp < graphs[old].stamp) old = i;
+      if (graphs[old].exec) cudaGraphExecDestroy(graphs[old].exec);
+      graphs.erase(graphs.begin() + old);
+    }
+    GraphEntry n; n.key = std::move(key); n.seen = 1; n.stamp = ++graph_clock;
+    graphs.push_back(std::move(n));
+    return issue(PH_ALL, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, stream, dry, launches);
+  }
+  ge->stamp = ++graph_clock;
+  int n_front = 0, n_back = 0;
+  int rc = issue(PH_FRONT, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, stream, false, &n_front);
+  if (rc != VITSB_OK) return rc;
+  if (!ge->exec && ge->seen >= 0) {              // second sighting: capture the middle on a private stream
+    if (!cap_stream && cudaStreamCreateWithFlags(&cap_stream, cudaStreamNonBlocking) != cudaSuccess) cap_stream = nullptr;
+    cudaGraph_t graph = nullptr;
+    bool ok = cap_stream && cudaStreamBeginCapture(cap_stream, cudaStreamCaptureModeRelaxed) == cudaSuccess;
+    if (ok) {
+      int n_mid = 0;
+      const int rc_mid = issue(PH_MID, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, cap_stream, false, &n_mid);
+      const cudaError_t ee = cudaStreamEndCapture(cap_stream, &graph);
+      ok = rc_mid == VITSB_OK && ee == cudaSuccess && graph != nullptr;
+      if (ok) ok = cudaGraphInstantiate(&ge->exec, graph, 0) == cudaSuccess;
+      if (graph) cudaGraphDestroy(graph);
+      ge->launches = n_mid;
+    }
+    if (!ok) {                                   // capture unavailable: never retry this shape, issue directly
+      cudaGetLastError();
+      ge->exec = nullptr; ge->seen = -1;
+    }
+  }
+  if (ge->exec) {
+    const cudaError_t le = cudaGraphLaunch(ge->exec, stream);
+    if (le != cudaSuccess) return fail(VITSB_ERR_CUDA, std::string("graph launch failed: ") + cudaGetErrorString(le));
+  } else {
+    int n_mid = 0;
+    rc = issue(PH_MID, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, stream, false, &n_mid);
+    if (rc != VITSB_OK) return rc;
+    ge->launches = n_mid;
+  }
+  rc = issue(PH_BACK, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, stream, false, &n_back);
+  if (launches) *launches = n_front + ge->launches + n_back;
+  return rc;
 }
 
 }  // namespace vitsb

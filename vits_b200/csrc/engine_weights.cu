@@ -23,6 +23,8 @@
 namespace vitsb {
 
 Engine::~Engine() {
+  for (GraphEntry& x : graphs) if (x.exec) cudaGraphExecDestroy(x.exec);
+  if (cap_stream) cudaStreamDestroy(cap_stream);
   if (d_w) cudaFree(d_w);
   if (d_bias) cudaFree(d_bias);
   if (d_condW) cudaFree(d_condW);

@@ -201,16 +201,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   const int unit_id = blockIdx.x / G::NCL, n_units = gridDim.x / G::NCL;     // a unit = one CTA, or one CTA pair
 
   // ---- tile table: tiles of batch row b cover output rows [0, min(L, valid_b + halo)) ----
-  if (threadIdx.x == 0) {
-    int acc = 0;
-    for (int b = 0; b < a.B; ++b) {
-      s_tile_prefix[b] = acc;
-      int valid = a.len ? a.len[b] * a.len_mul : a.L;
-      int rows = valid + kHaloRows < a.L ? valid + kHaloRows : a.L;
-      acc += (rows + G::T_OUT - 1) / G::T_OUT;
-    }
-    s_tile_prefix[a.B] = acc;
-  }
+  if (warp == 2) build_tile_prefix(s_tile_prefix, a.B, a.len, a.len_mul, a.L, G::T_OUT, lane);
   if (C >= 128)
     for (int i = threadIdx.x; i < C; i += blockDim.x) s_bias2[i] = a.bias2[i];
   if (warp == 0 && lane == 0) {

@@ -59,72 +59,115 @@ __device__ __forceinline__ void store16(float* dst, const float (&v)[16]) {
   for (int i = 0; i < 4; ++i) d[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
 }
 
+// Tile table of a ragged batch, built by ONE full warp: prefix[b] = number of `tile_rows`-row tiles before batch
+// row b, prefix[B] = total.  Tiles of row b cover rows [0, min(L, valid_b + kHaloRows)).  Lane-parallel length
+// loads + a shuffle scan: a single thread walking len[] paid one dependent global-load latency per few rows in
+// the prologue of every launch.
+__device__ __forceinline__ void build_tile_prefix(int* prefix, int B, const int* len, int len_mul, int L, int tile_rows, int lane) {
+  int carry = 0;
+  for (int b0 = 0; b0 < B; b0 += 32) {
+    const int b = b0 + lane;
+    int n = 0;
+    if (b < B) {
+      const int valid = len ? len[b] * len_mul : L;
+      const int rows = valid + kHaloRows < L ? valid + kHaloRows : L;   // rows nobody reads are skipped
+      n = (rows + tile_rows - 1) / tile_rows;
+    }
+    int inc = n;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) {
+      const int y = __shfl_up_sync(0xffffffffu, inc, o);
+      if (lane >= o) inc += y;
+    }
+    if (b < B) prefix[b] = carry + inc - n;
+    carry += __shfl_sync(0xffffffffu, inc, 31);
+  }
+  if (lane == 0) prefix[B] = carry;
+}
+
 // One epilogue warp: q = TMEM lane quarter (warp_id % 4), thread = one time row.
-// Must be called by all 32 lanes (tcgen05.ld is .sync.aligned) after the
-// accumulator-ready barrier and a tcgen05.fence::after_thread_sync.
-template <typename OpT>
+// The tile's columns are cut into 16-output units dealt round-robin to the `ngrp` epilogue groups
+// (unit u -> group u % ngrp), so one tile's epilogue runs on 4 * ngrp warps at once: these launches have
+// one or two tiles per CTA and the last tile's epilogue is exposed, so its latency is what matters.
+// Each unit issues its global loads (bias / conditioning, residual, accumulator) next to the TMEM load so
+// the latencies overlap.  (Prefetching them ahead of `wait_acc()` - the accumulator-ready wait - needs
+// ~170 registers per thread, more than 18 warps leave; more warps won.)
+// Must be called by all 32 lanes (tcgen05.ld is .sync.aligned); wait_acc() must end with a
+// tcgen05.fence::after_thread_sync.
+template <typename OpT, typename WaitFn>
 __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& ep, int b, int t0, int ntile, int valid,
-                                            uint32_t tmem_acc, int q, int lane) {
+                                            uint32_t tmem_acc, int q, int lane, int ugrp, int ngrp, WaitFn wait_acc) {
     const int row = q * 32 + lane;
     const int t = t0 + row;
     const bool in_range = t < a.L;
     const bool live = t < valid;
     const uint32_t trow = tmem_acc + (static_cast<uint32_t>(q * 32) << 16);
     const float* bias = ep.bias + (long long)b * ep.bias_bstride + (long long)ntile * a.NT;
+    wait_acc();
     if (ep.gate) {
-      // packed columns: groups of GG = [tanh GG/2 | sigmoid GG/2]; output channel = packed gate index
+      // packed columns: groups of GG = [tanh GG/2 | sigmoid GG/2]; output channel = packed gate index.
+      // unit u = 16 gates: gate group gi = u / upg, slice ci = u % upg (advanced without integer division)
       const int GG = a.gate_group > 0 ? a.gate_group : a.NT, gh = GG >> 1;
+      const int upg = gh >> 4, nu = a.NT >> 5;
       const long long orow_op = (long long)b * ep.out_op_bstride + (long long)t * ep.out_op_ld + (long long)ntile * (a.NT >> 1);
-      for (int g0 = 0; g0 < a.NT; g0 += GG) {
-        for (int c0 = 0; c0 < gh; c0 += 16) {
-          uint32_t ra[16], rb[16];
-          ptx::tmem_ld16(trow + g0 + c0, ra);
-          ptx::tmem_ld16(trow + g0 + gh + c0, rb);
-          ptx::tmem_ld_wait();
-          float ba[16], bb[16], v[16];
-          load16(bias + g0 + c0, ba);
-          load16(bias + g0 + gh + c0, bb);
+      int gi = 0, ci = ugrp;
+      while (ci >= upg) { ci -= upg; ++gi; }
+#pragma unroll 1
+      for (int u = ugrp; u < nu; u += ngrp) {
+        const int g0 = gi * GG, c0 = ci << 4;
+        uint32_t ra[16], rb[16];
+        ptx::tmem_ld16(trow + g0 + c0, ra);
+        ptx::tmem_ld16(trow + g0 + gh + c0, rb);
+        float ba[16], bb[16], v[16];
+        load16(bias + g0 + c0, ba);
+        load16(bias + g0 + gh + c0, bb);
+        ptx::tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 16; ++i) {
-            float xa = ep.alpha * (__uint_as_float(ra[i]) + ba[i]);
-            float xb = ep.alpha * (__uint_as_float(rb[i]) + bb[i]);
-            v[i] = live ? gate_fn<false>(xa, xb) : 0.f;
-          }
-          const int oc = (g0 >> 1) + c0;       // output column inside this tile's NT/2 gate channels
-          if (in_range) {
-            if (ep.out_f32)
-              store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + (long long)ntile * (a.NT >> 1) + oc, v);
-            if (ep.out_op) store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + orow_op + oc, v, ep.out_slope, ep.out_op_split);
-          }
+        for (int i = 0; i < 16; ++i) {
+          float xa = ep.alpha * (__uint_as_float(ra[i]) + ba[i]);
+          float xb = ep.alpha * (__uint_as_float(rb[i]) + bb[i]);
+          v[i] = live ? gate_fn<false>(xa, xb) : 0.f;
         }
+        const int oc = (g0 >> 1) + c0;       // output column inside this tile's NT/2 gate channels
+        if (in_range) {
+          if (ep.out_f32)
+            store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + (long long)ntile * (a.NT >> 1) + oc, v);
+          if (ep.out_op) store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + orow_op + oc, v, ep.out_slope, ep.out_op_split);
+        }
+        ci += ngrp;
+        while (ci >= upg) { ci -= upg; ++gi; }
       }
     } else {
       const long long n0 = (long long)ntile * a.NT;
-      for (int c0 = 0; c0 < a.NT; c0 += 16) {
+      const int nu = a.NT >> 4;
+      const bool has_res = in_range && ep.res != nullptr, has_acc = in_range && ep.accum != nullptr;
+      const float* res = ep.res + (long long)b * ep.res_bstride + (long long)t * ep.res_ld + n0;
+      const float* accum = ep.accum + (long long)b * ep.accum_bstride + (long long)t * ep.accum_ld + n0;
+#pragma unroll 1
+      for (int u = ugrp; u < nu; u += ngrp) {
+        const int c0 = u << 4;
         uint32_t r[16];
         ptx::tmem_ld16(trow + c0, r);
-        ptx::tmem_ld_wait();
-        float bv[16], v[16];
+        float bv[16], v[16], rx[16], ax[16];
+        if (has_res) load16(res + c0, rx);
+        if (has_acc) load16(accum + c0, ax);
         load16(bias + c0, bv);
+        ptx::tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = ep.alpha * (__uint_as_float(r[i]) + bv[i]);
+        if (has_res) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = fmaf(ep.beta, rx[i], v[i]);
+        }
+        if (has_acc) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] += ax[i];
+        }
+        if (!live) {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) v[i] = 0.f;
+        }
         if (in_range) {
-          if (ep.res) {
-            float x[16];
-            load16(ep.res + (long long)b * ep.res_bstride + (long long)t * ep.res_ld + n0 + c0, x);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = fmaf(ep.beta, x[i], v[i]);
-          }
-          if (ep.accum) {
-            float x[16];
-            load16(ep.accum + (long long)b * ep.accum_bstride + (long long)t * ep.accum_ld + n0 + c0, x);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] += x[i];
-          }
-          if (!live) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = 0.f;
-          }
           if (ep.out_f32)
             store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + n0 + c0, v);
           if (ep.out_op)
