@@ -84,8 +84,20 @@ struct RbT {
   static constexpr uint32_t TMEM_COLS = 2 * NBUF * C <= 256 ? 256 : 512;
   // epilogue warp groups: with >= 2 accumulator sets, two groups of (4 gate + 4 store) warps take alternate
   // tiles - the epilogues are latency / issue bound (one warp per scheduler reaches IPC ~0.3), not MUFU bound
-  static constexpr int NGRP = NBUF >= 2 ? 2 : 1;
+  // C >= 128 (COOP): the pipeline is bound by the LATENCY of one tile's epilogues (few accumulator sets), so both
+  // groups work on EVERY tile and split its columns; C <= 64 (MMA-bound, 4 sets): groups take alternate tiles.
+  static constexpr bool COOP = C >= 128;
+  static constexpr int NGRP = 2;
+  static constexpr int TSTEP = COOP ? 1 : NGRP;                                   // tile stride of one epilogue group
+  static constexpr int NARR = 4 * NCL * (COOP ? NGRP : 1);                        // epilogue-warp arrivals per barrier phase
   static constexpr int THREADS = 128 + NGRP * 256;
+  // mid-iteration output rows are staged in shared memory (one swizzled [128][CB_O] block per store group)
+  // and written by TMA stores: a thread owns a ROW, so direct global stores touch 32 different lines per
+  // instruction.  C = 64 / k = 11 has no smem left next to its 135 KB of resident weights and stores directly.
+  static constexpr bool STAGE_OUT = !(C == 64 && KT == 11);
+  static constexpr int CB_O = C >= 64 ? 64 : C, RB_O = CB_O * 2, NBLK_O = C / CB_O;
+  static constexpr uint32_t STG_BYTES = (uint32_t)kTileM * RB_O;                   // per store group
+  static constexpr uint32_t STG_ALL = STAGE_OUT ? NGRP * STG_BYTES : 0u;
   static_assert(2 * NBUF * C <= 512, "TMEM columns");
 };
 
@@ -165,7 +177,7 @@ __device__ __forceinline__ float gate_fast(float a, float b) {
 
 template <typename OpT, int C, int KT, bool LAST>
 __global__ void __launch_bounds__((RbT<C, KT>::THREADS), 1)
-rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmW1,
+rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmW1,
                 const __grid_constant__ CUtensorMap tmW2, const RbArgs a, const RbRt rt) {
   using G = RbT<C, KT>;
   extern __shared__ uint8_t smem_raw[];
@@ -183,7 +195,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   const uint32_t sG = sSlab + rt.nSlab * slab_set;                             // [NBUF][nCB2][G_BYTES]
   const uint32_t sW = sG + G::NBUF * G::G_SET;                                 // all boxes (c1 then c2), or the ring
   const uint32_t sW2 = sW + G::NBOX1 * G::W1_TX;                               // resident mode: c2 boxes
-  const uint32_t bars = sW + (G::STATIONARY ? G::W_ALL : rt.nW * G::W_SLOT);
+  constexpr bool kStage = !LAST && G::STAGE_OUT;                               // TMA-stored output rows (mid iterations)
+  const uint32_t sStage = sW + (G::STATIONARY ? G::W_ALL : rt.nW * G::W_SLOT); // [NGRP][128][CB_O] output staging
+  const uint32_t bars = sStage + (kStage ? G::STG_ALL : 0u);
   auto slab_full = [&](int i) { return bars + 8u * i; };
   auto slab_empty = [&](int i) { return bars + 8u * (8 + i); };
   auto acc1_full = [&](int i) { return bars + 8u * (16 + i); };
@@ -206,14 +220,15 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     for (int i = threadIdx.x; i < C; i += blockDim.x) s_bias2[i] = a.bias2[i];
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmY); ptx::prefetch_tmap(&tmW1); ptx::prefetch_tmap(&tmW2);
+    if (kStage) ptx::prefetch_tmap(&tmO);
     // slab release: c1's MMA commit, plus the 4 store-epilogue warps when they read the residual from the slab
     for (int i = 0; i < 8; ++i) { ptx::mbar_init(slab_full(i), 1); ptx::mbar_init(slab_empty(i), G::RES_GLOBAL ? 1 : 5); }
     ptx::mbar_init(w_all, 1);
     for (int i = 0; i < 4; ++i) {
       // pair mode: the leader's copies collect the arrivals of both CTAs' epilogue warps
-      ptx::mbar_init(acc1_full(i), 1);  ptx::mbar_init(acc1_empty(i), 4 * G::NCL);
-      ptx::mbar_init(acc2_full(i), 1);  ptx::mbar_init(acc2_empty(i), 4 * G::NCL);
-      ptx::mbar_init(g_full(i), 4 * G::NCL);     ptx::mbar_init(g_empty(i), 1);
+      ptx::mbar_init(acc1_full(i), 1);  ptx::mbar_init(acc1_empty(i), G::NARR);
+      ptx::mbar_init(acc2_full(i), 1);  ptx::mbar_init(acc2_empty(i), G::NARR);
+      ptx::mbar_init(g_full(i), G::NARR);        ptx::mbar_init(g_empty(i), 1);
     }
     for (int i = 0; i < 8; ++i) { ptx::mbar_init(w_full(i), 1); ptx::mbar_init(w_empty(i), 1); }
     ptx::mbar_fence_init();
@@ -238,8 +253,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   // epilogue group of this warp (warps 4-11: group 0, warps 12-19: group 1) and its tile stride
   const int grp = warp >= 12 ? 1 : 0;
   const bool is_epi = warp >= 4;
-  const int tstep = is_epi ? G::NGRP : 1;
-  int cur_unit = unit_id + (is_epi ? grp : 0) * n_units, cur_b = 0, cur_tile = 0;
+  const int tstep = is_epi ? G::TSTEP : 1;
+  const int n_first = is_epi && !G::COOP ? grp : 0;          // first tile (of this CTA's sequence) the warp works on
+  int cur_unit = unit_id + n_first * n_units, cur_b = 0, cur_tile = 0;
   bool cur_dead = false;                          // pair mode, odd tile count: rank 1 of the last pair runs the protocol on zeros
   auto tile_seek = [&]() {
     const int t = G::PAIR ? cur_unit * 2 + rank : cur_unit;
@@ -439,7 +455,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     constexpr bool kBiasSmem = C >= 128;
     const uint32_t sb1 = ptx::smem_u32(&s_bias1[grp][0]);
     int bias_b = -1;                             // batch row whose cond/bias vector is staged in s_bias1[grp]
-    for (int n = grp; n < my_tiles; n += G::NGRP, tile_next()) {
+    constexpr int NCH_G = G::COOP ? NCH / G::NGRP : NCH;      // chunks of a row this group handles
+    const int ch0 = G::COOP ? grp * NCH_G : 0;
+    static_assert(!G::COOP || NCH % G::NGRP == 0, "column split");
+    for (int n = n_first; n < my_tiles; n += G::TSTEP, tile_next()) {
       const Cursor gb{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
       tile_seek();
       const int b = cur_b, t0 = tile_t0();
@@ -473,8 +492,8 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const uint32_t trow = tmem_base + acc1_col + s * C + (static_cast<uint32_t>(q * 32) << 16);
       const uint32_t grow = sG + s * G::G_SET + r * G::rb2;
 #pragma unroll
-      for (int c = 0; c < NCH; ++c) {
-        const int c0 = 16 * c;
+      for (int cc = 0; cc < NCH_G; ++cc) {
+        const int c0 = 16 * (ch0 + cc);
         float ba[16], bb[16];
         if (!RB_DBG(2048)) {
           if (kBiasSmem) {
@@ -536,10 +555,18 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     const int srow = r + G::P2 + rt.p1;          // slab row holding y_in[t]
     constexpr int NCH = C / 16;                  // 16-column chunks per row
     const uint32_t sb2 = ptx::smem_u32(&s_bias2[0]);
-    constexpr int PF = G::NGRP == 2 ? (NCH < 4 ? NCH : 4) : 8;   // residual chunks kept in flight (2 x uint4 each; 96-register cap with 20 warps)
+    constexpr int NCH_S = G::COOP ? NCH / G::NGRP : NCH;      // chunks of a row this group handles (COOP: column split)
+    const int ch0 = G::COOP ? grp * NCH_S : 0;
+    constexpr int PF = NCH_S < 4 ? NCH_S : 4;    // residual chunks kept in flight (2 x uint4 each; 96-register cap with 20 warps)
     Cursor sl{0, 0};
-    if (grp == 1) sl.next(nSlab);
-    for (int n = grp; n < my_tiles; n += G::NGRP, tile_next()) {
+    if (grp == 1 && !G::COOP) sl.next(nSlab);
+    // output staging (kStage): row r of this group's block, written in place of a TMA-load image; thread 0 of the
+    // group issues the stores and is the one that waits for them (bulk async-groups are per thread)
+    const uint32_t stg = sStage + grp * G::STG_BYTES, stg_row = stg + r * G::RB_O;
+    const bool issuer = r == 0;
+    constexpr int CH_BLK = G::CB_O / 16;         // 16-column chunks per staged block
+    static_assert(!G::COOP || (NCH_S % CH_BLK == 0 && NCH_S % PF == 0), "column split must be block aligned");
+    for (int n = n_first; n < my_tiles; n += G::TSTEP, tile_next()) {
       const Cursor ab{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
       tile_seek();
       const int b = cur_b, t0 = tile_t0();
@@ -570,14 +597,14 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       };
       if (!G::RES_GLOBAL) ptx::mbar_wait(slab_full(ss), sl.phase);      // acquire the TMA-written slab for the residual reads
 #pragma unroll
-      for (int c = 0; c < PF; ++c) load_y(c, yq[c]);
+      for (int c = 0; c < PF; ++c) load_y(ch0 + c, yq[c]);
       ptx::mbar_wait(acc2_full(s), ab.phase);
       ptx::tc_fence_after();
       if ((warp & 3) == 0) trace(4, n, 0);
       const uint32_t trow = tmem_base + acc2_col + s * C + (static_cast<uint32_t>(q * 32) << 16);
 #pragma unroll
-      for (int c = 0; c < NCH; ++c) {
-        const int c0 = 16 * c;
+      for (int cc = 0; cc < NCH_S; ++cc) {
+        const int c = ch0 + cc, c0 = 16 * c;
         float bv[16];
         if (C >= 128) lds16(sb2 + 4 * c0, bv); else load16(a.bias2 + c0, bv);
         uint32_t ra[16];
@@ -586,8 +613,8 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 #pragma unroll
           for (int i = 0; i < 16; ++i) ra[i] = 0u;
         }
-        const uint4 y0 = yq[c % PF][0], y1 = yq[c % PF][1];
-        if (c + PF < NCH) load_y(c + PF, yq[c % PF]);
+        const uint4 y0 = yq[cc % PF][0], y1 = yq[cc % PF][1];
+        if (cc + PF < NCH_S) load_y(c + PF, yq[cc % PF]);
         const uint32_t yw[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
         float v[16];
 #pragma unroll
@@ -597,7 +624,30 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           v[2 * i] = (__uint_as_float(ra[2 * i]) + bv[2 * i]) + fminf(y.x, 10.f * y.x);
           v[2 * i + 1] = (__uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1]) + fminf(y.y, 10.f * y.y);
         }
-        if (!LAST) {
+        if (kStage) {
+          if (cc % CH_BLK == 0) {                // block buffer reuse: the previous store must have read it
+            if (issuer) ptx::bulk_wait_read0();
+            asm volatile("bar.sync %0, 128;" ::"r"(3 + grp) : "memory");
+          }
+          uint32_t pk[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            // leaky_relu(v, 0.1) = max(v, 0.1 v); rows beyond len[b] are stored as zeros
+            const uint32_t w = Pack16<OpT>::pack2(fmaxf(v[2 * i], 0.1f * v[2 * i]), fmaxf(v[2 * i + 1], 0.1f * v[2 * i + 1]));
+            pk[i] = live ? w : 0u;
+          }
+          const uint32_t saddr = stg_row + (cc % CH_BLK) * 32;
+          st_shared_v4(swz_addr<G::RB_O>(saddr), pk[0], pk[1], pk[2], pk[3]);
+          st_shared_v4(swz_addr<G::RB_O>(saddr + 16), pk[4], pk[5], pk[6], pk[7]);
+          if (cc % CH_BLK == CH_BLK - 1) {       // block complete: rows [t0, t0 + T_OUT) x 64 channels, clipped at L by the map
+            fence_proxy_async_smem();
+            asm volatile("bar.sync %0, 128;" ::"r"(3 + grp) : "memory");
+            if (issuer && t0 < a.L && !RB_DBG(1)) {
+              ptx::tma_store_3d(&tmO, stg, (c / CH_BLK) * G::CB_O, t0, b);
+              ptx::bulk_commit();
+            }
+          }
+        } else if (!LAST) {
           if (in_range && !RB_DBG(1)) {
             uint32_t pk[8];
 #pragma unroll
@@ -641,8 +691,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       }
       if ((warp & 3) == 0) trace(4, n, 1);
 #pragma unroll
-      for (int i = 0; i < G::NGRP; ++i) sl.next(nSlab);
+      for (int i = 0; i < G::TSTEP; ++i) sl.next(nSlab);
     }
+    if (kStage && issuer) ptx::bulk_wait0();     // staged rows are in global memory before the CTA retires
   }
 
   ptx::tc_fence_before();
@@ -674,7 +725,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   rt.R1 = (kTileM + (KT - 1) * L.dil + 7) & ~7;
   rt.slab_bytes = ((uint32_t)rt.R1 * G::rb1 + 1023u) & ~1023u;
   const uint32_t slab_set = G::nCB1 * rt.slab_bytes;
-  const uint32_t fixed = 1024 + 512 + G::NBUF * G::G_SET;
+  const uint32_t fixed = 1024 + 512 + G::NBUF * G::G_SET + (LAST ? 0u : G::STG_ALL);
   if (G::STATIONARY) {
     if (fixed + G::W_ALL + 2 * slab_set > kRbSmemBudget) return cudaErrorNotSupported;
     rt.nSlab = (int)((kRbSmemBudget - fixed - G::W_ALL) / slab_set);
@@ -695,7 +746,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   if (!enc) return cudaErrorNotSupported;
   const CUtensorMapDataType dt = op == OP_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   auto swz = [](int rb) { return rb == 128 ? CU_TENSOR_MAP_SWIZZLE_128B : (rb == 64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_32B); };
-  CUtensorMap tmY, tmW1, tmW2;
+  CUtensorMap tmY, tmO, tmW1, tmW2;
   cuuint32_t estr[3] = {1, 1, 1};
   bool ok = true;
   {
@@ -703,6 +754,15 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
     cuuint64_t strides[2] = {(cuuint64_t)C * 2, (cuuint64_t)L.a.L * C * 2};
     cuuint32_t box[3] = {(cuuint32_t)G::BK1, (cuuint32_t)rt.R1, 1};
     ok &= enc(&tmY, dt, 3, const_cast<void*>(L.y_in), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(G::rb1),
+              CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+  }
+  {
+    // output rows of a tile: [T_OUT][CB_O] boxes of y_out (only dereferenced by the staged mid-iteration kernels)
+    cuuint64_t dims[3] = {(cuuint64_t)C, (cuuint64_t)L.a.L, (cuuint64_t)L.B};
+    cuuint64_t strides[2] = {(cuuint64_t)C * 2, (cuuint64_t)L.a.L * C * 2};
+    cuuint32_t box[3] = {(cuuint32_t)G::CB_O, (cuuint32_t)G::T_OUT, 1};
+    void* base = L.a.y_out ? L.a.y_out : const_cast<void*>(L.y_in);
+    ok &= enc(&tmO, dt, 3, base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swz(G::RB_O),
               CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
   }
   {
@@ -721,7 +781,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   }
   if (!ok) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", C, KT); return cudaErrorInvalidValue; }
   const size_t wbytes = G::STATIONARY ? (size_t)G::W_ALL : (size_t)rt.nW * G::W_SLOT;
-  const size_t smem = 1024 + (size_t)rt.nSlab * slab_set + (size_t)G::NBUF * G::G_SET + wbytes + 8 * 57 + 64;
+  const size_t smem = 1024 + (size_t)rt.nSlab * slab_set + (size_t)G::NBUF * G::G_SET + wbytes + (LAST ? 0u : G::STG_ALL) + 8 * 57 + 64;
   static int num_sms = 0;
   static std::once_flag once;     // one flag per template instantiation
   static cudaError_t attr_err = cudaSuccess;
@@ -765,7 +825,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[1].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  cudaError_t le = cudaLaunchKernelEx(&cfg, rb_fused_kernel<OpT, C, KT, LAST>, tmY, tmW1, tmW2, args, rt);
+  cudaError_t le = cudaLaunchKernelEx(&cfg, rb_fused_kernel<OpT, C, KT, LAST>, tmY, tmO, tmW1, tmW2, args, rt);
   if (le == cudaSuccess) le = cudaGetLastError();
   if (tracing && le == cudaSuccess) {
     --trace_left;
