@@ -136,11 +136,15 @@ __device__ __forceinline__ void cluster_sync_all() {
   asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
 }
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;
+// Default semantics (.release at CTA scope), as CUTLASS's ClusterBarrier::arrive(cta_id) does: spelling out
+// .release.cluster makes ptxas emit MEMBAR.ALL.GPU in front of every arrive (1-2k cycles each, measured on the
+// epilogue -> MMA critical path).  What the leader's tensor core needs from this CTA - smem written through the
+// generic proxy, TMEM reads retired - is ordered by fence.proxy.async.shared::cta / tcgen05.fence before the arrive.
 __device__ __forceinline__ void mbar_arrive_leader(uint32_t bar) {     // arrive on the leader CTA's copy of `bar`
   asm volatile(
       "{\n.reg .b32 ra;\n"
       "mapa.shared::cluster.u32 ra, %0, 0;\n"
-      "mbarrier.arrive.release.cluster.shared::cluster.b64 _, [ra];\n}\n"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n}\n"
       ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void tma_load_2d_2sm(uint32_t dst, const CUtensorMap* m, uint32_t bar, int c0, int c1) {

@@ -489,6 +489,12 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       ptx::mbar_wait(g_empty(s), gb.phase ^ 1u);
       ptx::tc_fence_after();
       if ((warp & 3) == 0) trace(3, n, 0);
+      // per-phase timestamps of warps 4 and 12 (quarter 0 of each gate group) on tile 4 (role 5: slot = phase, kind = group)
+      auto ptrace = [&](int phase) {
+        if (RB_TRACE_ON && (warp & 7) == 4 && n == 4 + n_first && a.trace && blockIdx.x == 0 && lane == 0 && phase < 16)
+          a.trace[(5 * 16 + phase) * 2 + grp] = clock64();
+      };
+      ptrace(0);
       const uint32_t trow = tmem_base + acc1_col + s * C + (static_cast<uint32_t>(q * 32) << 16);
       const uint32_t grow = sG + s * G::G_SET + r * G::rb2;
 #pragma unroll
@@ -519,6 +525,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 #pragma unroll
           for (int i = 0; i < 16; ++i) ra[i] = rb[i] = 0u;
         }
+        ptrace(1 + 3 * cc);                    // bias + TMEM loads done
         uint32_t p[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
@@ -530,19 +537,23 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         // channel c0..c0+15 of row r -> block cb2, two 16-byte chunks, swizzled like a TMA write would
         const int cb2 = c0 / G::BK2, cin = c0 - cb2 * G::BK2;
         const uint32_t rowaddr = grow + cb2 * G::G_BYTES + cin * 2;
+        ptrace(2 + 3 * cc);                    // gate math done
         if (!RB_DBG(4096)) {
           st_shared_v4(swz_addr<G::rb2>(rowaddr), p[0], p[1], p[2], p[3]);
           st_shared_v4(swz_addr<G::rb2>(rowaddr + 16), p[4], p[5], p[6], p[7]);
         }
+        ptrace(3 + 3 * cc);                    // G stores issued
       }
-      if (G::PAIR) asm volatile("fence.proxy.async;" ::: "memory");   // the leader's tensor core reads this CTA's G tile
-      else fence_proxy_async_smem();             // generic-proxy smem writes -> visible to the tensor core (async proxy)
+      ptrace(13);
+      fence_proxy_async_smem();                  // generic-proxy smem writes -> visible to this SM's tensor core (async proxy)
+      ptrace(15);
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) {
         if (G::PAIR) { ptx::mbar_arrive_leader(g_full(s)); ptx::mbar_arrive_leader(acc1_empty(s)); }
         else { ptx::mbar_arrive(g_full(s)); ptx::mbar_arrive(acc1_empty(s)); }
       }
+      ptrace(14);
       if ((warp & 3) == 0) trace(3, n, 1);
     }
   } else if (warp >= 8) {
@@ -840,7 +851,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
       fprintf(stderr, "  %-18s", names[r]);
       for (int t = 0; t < (r == 5 ? 16 : 8); ++t) {
         const long long x = h[(r * 16 + t) * 2], y = h[(r * 16 + t) * 2 + 1];
-        if (!x && !y) break;
+        if (!x && !y) { if (r == 5) continue; break; }
         fprintf(stderr, " [%lld,%lld]", x ? x - t0 : -1, y ? y - t0 : -1);
       }
       fprintf(stderr, "\n");
