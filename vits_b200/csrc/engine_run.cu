@@ -267,9 +267,24 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
             ra.bias1 = cx.cond + it.c1.cond_off; ra.bias1_bstride = Ncond;
             ra.bias2 = d_bias + it.c2.bias_off;
             ra.scale = 1.f;
+            // MRF (models.py:311-314).  With <= 3 branches the first branches' results stay 16-bit y streams (their
+            // last iteration is an ordinary mid-type launch into br[j]) and the final branch sums them in its epilogue:
+            // 12 B of traffic per element instead of 20 B through an fp32 accumulator.  br[] reuses the fp32
+            // buffers of the layer-at-a-time plan, which the fused plan does not touch.
+            void* br[2] = {P(W.xin_f), P(W.xb_f)};
+            const bool stream_mrf = nk <= 3;
             if (d < ni - 1) {
               ra.y_out = ping;
-            } else {                                                 // MRF (models.py:311-314)
+            } else if (stream_mrf && j < nk - 1) {
+              ra.y_out = br[j];
+            } else if (stream_mrf) {
+              ra.scale = inv;
+              ra.acc_mode = RB_EMIT_NEXT;
+              ra.add0 = nk > 1 ? br[0] : nullptr;
+              ra.add1 = nk > 2 ? br[1] : nullptr;
+              if (s == ns - 1) ra.nxt_f32 = F(W.acc_f);              // conv_post reads fp32
+              else { ra.nxt_op = P(W.nxt_op); ra.nxt_split = split16 ? 1 : 0; }
+            } else {
               ra.scale = inv;
               ra.acc = F(W.acc_f);
               ra.acc_mode = (j > 0 ? RB_ACC_READ : 0) | (j < nk - 1 ? RB_ACC_STORE : RB_EMIT_NEXT);

@@ -25,7 +25,9 @@ struct RbArgs {
   void* nxt_op;            // op_t leaky_relu(v, 0.1): [B][L][2C] hi|lo if nxt_split else [B][L][C]
   int nxt_split;
   float* nxt_f32;          // fp32 [B][L][C] = v (conv_post input)
-  float scale;             // v = scale * (c2 + bias2 + x)
+  float scale;             // v = scale * (c2 + bias2 + x + x_add0 + x_add1)
+  const void* add0;        // op_t [B][L][C] or null: y = leaky_relu(x_j, 0.1) streams of the other MRF branches, summed in
+  const void* add1;        //   (x_j = min(y, 10 y)): 2 B per element instead of a 4 B fp32 accumulator read-modify-write
   const float* bias1; long long bias1_bstride;   // per-batch conditioning + conv bias, gate-packed order
   const float* bias2;
   int L, B;

@@ -57,6 +57,10 @@ namespace vitsb {
 #define RB_TRACE_ON 0
 #endif
 
+#ifndef VITSB_BIAS_SMEM_MINC
+#define VITSB_BIAS_SMEM_MINC 64
+#endif
+constexpr int kBiasSmemMinC = VITSB_BIAS_SMEM_MINC;      // channel count from which the epilogues read biases from shared memory
 constexpr int kRbMaxB = 512;
 constexpr uint32_t kRbSmemBudget = 220 * 1024;
 
@@ -109,6 +113,7 @@ struct RbRt {
   int nSlab;                 // activation slab buffers (1..8)
   int nW;                    // weight ring slots (streamed mode, 2..8)
   uint32_t idesc;
+  int trace_t0;              // first tile recorded by the timeline trace
   int dbg;                   // VITSB_RB_DBG ablation mask (timing experiments only; results are wrong when set)
 };
 
@@ -185,7 +190,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   __shared__ uint32_t s_tmem;
   // Bias vectors staged in shared memory: with ~220 KB of the SM's 256 KB carved out as smem the L1 is a few KB
   // and the residual stream flushes it, so per-chunk bias loads from global paid an L2 round trip each.
-  constexpr int kSB = C >= 128 ? C : 4;                   // small C reads its biases from global / L1 (measured faster there)
+  constexpr int kSB = C >= kBiasSmemMinC ? C : 4;                   // small C reads its biases from global / L1 (measured faster there)
   __shared__ __align__(16) float s_bias2[kSB];            // conv2 bias
   __shared__ __align__(16) float s_bias1[2][kSB];         // per epilogue group: conv1 bias + conditioning of the current batch row
 
@@ -216,7 +221,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 
   // ---- tile table: tiles of batch row b cover output rows [0, min(L, valid_b + halo)) ----
   if (warp == 2) build_tile_prefix(s_tile_prefix, a.B, a.len, a.len_mul, a.L, G::T_OUT, lane);
-  if (C >= 128)
+  if (C >= kBiasSmemMinC)
     for (int i = threadIdx.x; i < C; i += blockDim.x) s_bias2[i] = a.bias2[i];
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmY); ptx::prefetch_tmap(&tmW1); ptx::prefetch_tmap(&tmW2);
@@ -241,8 +246,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   ptx::pdl_wait();                   // everything above overlapped the previous kernel's tail; its outputs are needed from here on
   const uint32_t tmem_base = s_tmem;
   // timeline trace of CTA 0 (VITSB_RB_TRACE): trace[(role * 16 + tile) * 2 + kind] = clock64()
-  auto trace = [&](int role, int tile, int kind) {
-    if (RB_TRACE_ON && a.trace && blockIdx.x == 0 && tile < 16 && lane == 0) a.trace[(role * 16 + tile) * 2 + kind] = clock64();
+  auto trace = [&](int role, int tile, int kind) {      // rt.trace_t0: first traced tile of the CTA's sequence (VITSB_RB_TRACE "C,k,count,first")
+    tile -= rt.trace_t0;
+    if (RB_TRACE_ON && a.trace && blockIdx.x == 0 && tile >= 0 && tile < 16 && lane == 0) a.trace[(role * 16 + tile) * 2 + kind] = clock64();
   };
   const int total_tiles = s_tile_prefix[a.B];
   const int total_units = (total_tiles + G::NCL - 1) / G::NCL;      // pair mode: tiles 2u and 2u+1 (the last may be missing)
@@ -452,7 +458,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     constexpr int NCH = G::C2 / 16;              // 16-gate chunks per row
     // bias source: shared memory for C >= 128 (the L1 left next to ~220 KB of smem is tiny and the residual stream
     // flushes it); global / L1 for small C, where the smem bandwidth belongs to the MMA operands (N <= 64 is smem-bound)
-    constexpr bool kBiasSmem = C >= 128;
+    constexpr bool kBiasSmem = C >= kBiasSmemMinC;
     const uint32_t sb1 = ptx::smem_u32(&s_bias1[grp][0]);
     int bias_b = -1;                             // batch row whose cond/bias vector is staged in s_bias1[grp]
     constexpr int NCH_G = G::COOP ? NCH / G::NGRP : NCH;      // chunks of a row this group handles
@@ -491,7 +497,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       if ((warp & 3) == 0) trace(3, n, 0);
       // per-phase timestamps of warps 4 and 12 (quarter 0 of each gate group) on tile 4 (role 5: slot = phase, kind = group)
       auto ptrace = [&](int phase) {
-        if (RB_TRACE_ON && (warp & 7) == 4 && n == 4 + n_first && a.trace && blockIdx.x == 0 && lane == 0 && phase < 16)
+        if (RB_TRACE_ON && (warp & 7) == 4 && n == rt.trace_t0 + 4 + n_first && a.trace && blockIdx.x == 0 && lane == 0 && phase < 16)
           a.trace[(5 * 16 + phase) * 2 + grp] = clock64();
       };
       ptrace(0);
@@ -617,7 +623,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       for (int cc = 0; cc < NCH_S; ++cc) {
         const int c = ch0 + cc, c0 = 16 * c;
         float bv[16];
-        if (C >= 128) lds16(sb2 + 4 * c0, bv); else load16(a.bias2 + c0, bv);
+        if (C >= kBiasSmemMinC) lds16(sb2 + 4 * c0, bv); else load16(a.bias2 + c0, bv);
         uint32_t ra[16];
         if (!RB_DBG(32)) { ptx::tmem_ld16(trow + c0, ra); ptx::tmem_ld_wait(); }
         else {
@@ -673,6 +679,22 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
             d[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
           }
         } else if (in_range && !RB_DBG(1)) {
+          // MRF: the other branches' final x_j arrive as 16-bit y streams (models.py:311-314: xs += resblock(x))
+#pragma unroll
+          for (int s2 = 0; s2 < 2; ++s2) {
+            const void* ap = s2 == 0 ? a.add0 : a.add1;
+            if (ap && !RB_DBG(2)) {
+              const uint4* yp = reinterpret_cast<const uint4*>(reinterpret_cast<const OpT*>(ap) + orow + c0);
+              const uint4 z0 = __ldg(yp), z1 = __ldg(yp + 1);
+              const uint32_t zw[8] = {z0.x, z0.y, z0.z, z0.w, z1.x, z1.y, z1.z, z1.w};
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const float2 y = Pack16<OpT>::unpack2(zw[i]);
+                v[2 * i] += fminf(y.x, 10.f * y.x);
+                v[2 * i + 1] += fminf(y.y, 10.f * y.y);
+              }
+            }
+          }
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] *= a.scale;
           if ((a.acc_mode & RB_ACC_READ) && !RB_DBG(2)) {
@@ -817,14 +839,14 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   RbArgs args = L.a;
   args.y_res = L.y_in;
   static long long* d_trace = nullptr;
-  static int trace_C = -1, trace_K = 0, trace_left = 0;
+  static int trace_C = -1, trace_K = 0, trace_left = 0, trace_first = 0;
   if (trace_C < 0) {
     const char* e = getenv("VITSB_RB_TRACE");      // "C,k,count": dump the CTA-0 timeline of the first `count` launches of that shape
     trace_C = 0;
-    if (e && sscanf(e, "%d,%d,%d", &trace_C, &trace_K, &trace_left) == 3) cudaMalloc(&d_trace, 7 * 16 * 2 * sizeof(long long));
+    if (e && sscanf(e, "%d,%d,%d,%d", &trace_C, &trace_K, &trace_left, &trace_first) >= 3) cudaMalloc(&d_trace, 7 * 16 * 2 * sizeof(long long));
   }
   const bool tracing = d_trace && trace_C == C && trace_K == KT && trace_left > 0 && !LAST;
-  if (tracing) { cudaMemsetAsync(d_trace, 0, 7 * 16 * 2 * sizeof(long long), stream); args.trace = d_trace; }
+  if (tracing) { cudaMemsetAsync(d_trace, 0, 7 * 16 * 2 * sizeof(long long), stream); args.trace = d_trace; rt.trace_t0 = trace_first; }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid, 1, 1);
   cfg.blockDim = dim3(G::THREADS, 1, 1);
