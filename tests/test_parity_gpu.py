@@ -215,3 +215,23 @@ def test_error_paths(base_cfg, base_sd):
     from vits_b200 import FlowDecoder
     with pytest.raises(L.VitsbError):
         FlowDecoder(base_cfg, bad, device="cuda:0")
+
+
+def test_host_pipeline_matches_blocking_calls(base_cfg, base_sd):
+    """Serving loop (H2D / synthesis / D2H on three streams, depth 2) returns exactly what the blocking
+    host call returns, request by request, including when a slot is reused."""
+    eng = engine(base_cfg, base_sd, "fp16")
+    lens = [50, 33, 64, 20]
+    B, T = len(lens), max(lens)
+    pipe = eng.host_pipeline(B, T)
+    reqs = []
+    for i in range(5):
+        lat = FX.make_latents(base_cfg, lens, seed=500 + i)
+        reqs.append((lat["z_p"].pin_memory(), lat["g"].pin_memory(),
+                     torch.empty(B, 1, T * 192, dtype=torch.float32).pin_memory()))
+    tickets = [pipe.submit(z, g, lens, out) for z, g, out in reqs]
+    for t in tickets:
+        pipe.wait(t)
+    for z, g, out in reqs:
+        ref = eng.synthesize_host(z, g, lens)
+        assert torch.equal(out, ref)
