@@ -155,8 +155,72 @@ conv_post_kernel(const float* __restrict__ in, int L, int C, int k, float slope,
   wav[(long long)b * L + t] = t < valid ? tanhf(acc) : 0.f;
 }
 
+// Fast path for the base shape (C = 32, k = 7, L % 4 == 0): 64 threads x 4 consecutive outputs.  The generic
+// kernel above issues two LDS.32 per FMA and is shared-memory-issue bound (~2.4x the HBM time of its input);
+// here a thread keeps the 10 input rows of its 4 outputs in registers per 4-channel group, so one LDS.128 feeds
+// up to 16 FMAs.  Tile rows are stored as 8 float4 with the float4 index XOR-swizzled by (row / 4), which makes
+// the row loads of threads that sit 4 rows apart conflict-free.
+constexpr int kPost4Out = 4, kPost4Threads = 64, kPost4Tile = kPost4Out * kPost4Threads;
+template <int C, int K>
+__global__ void __launch_bounds__(kPost4Threads)
+conv_post4_kernel(const float* __restrict__ in, int L, float slope, const float* __restrict__ w,
+                  const int* __restrict__ len, int len_mul, float* __restrict__ wav) {
+  constexpr int C4 = C / 4, ROWS = kPost4Tile + K - 1, PAD = (K - 1) / 2;
+  static_assert(C4 == 8, "swizzle assumes 8 float4 per row");
+  __shared__ float4 tile[ROWS * C4];
+  __shared__ float4 ws[K * C4];
+  const int b = blockIdx.y, t0 = blockIdx.x * kPost4Tile;
+  const int valid = len ? len[b] * len_mul : L;
+  const int t = t0 + threadIdx.x * kPost4Out;
+  if (t0 >= valid) {                           // fully masked tile: write zeros
+    if (t < L) *reinterpret_cast<float4*>(wav + (long long)b * L + t) = make_float4(0.f, 0.f, 0.f, 0.f);
+    return;
+  }
+  const float4* src = reinterpret_cast<const float4*>(in + (long long)b * L * C);
+  for (int i = threadIdx.x; i < ROWS * C4; i += kPost4Threads) {
+    const int r = i / C4, c4 = i - r * C4, tt = t0 + r - PAD;
+    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (tt >= 0 && tt < L) x = __ldg(src + (long long)tt * C4 + c4);
+    x.x = x.x >= 0.f ? x.x : slope * x.x; x.y = x.y >= 0.f ? x.y : slope * x.y;
+    x.z = x.z >= 0.f ? x.z : slope * x.z; x.w = x.w >= 0.f ? x.w : slope * x.w;
+    tile[r * C4 + ((c4 ^ (r >> 2)) & 7)] = x;
+  }
+  for (int i = threadIdx.x; i < K * C4; i += kPost4Threads) ws[i] = __ldg(reinterpret_cast<const float4*>(w) + i);
+  __syncthreads();
+  if (t >= L) return;
+  float acc[kPost4Out] = {0.f, 0.f, 0.f, 0.f};
+  const int r0 = threadIdx.x * kPost4Out;
+#pragma unroll 2
+  for (int c4 = 0; c4 < C4; ++c4) {
+    float4 x[kPost4Out + K - 1];
+#pragma unroll
+    for (int jj = 0; jj < kPost4Out + K - 1; ++jj) {
+      const int r = r0 + jj;
+      x[jj] = tile[r * C4 + ((c4 ^ (r >> 2)) & 7)];
+    }
+#pragma unroll
+    for (int j = 0; j < K; ++j) {
+      const float4 wj = ws[j * C4 + c4];
+#pragma unroll
+      for (int o = 0; o < kPost4Out; ++o) {
+        acc[o] = fmaf(x[o + j].x, wj.x, acc[o]); acc[o] = fmaf(x[o + j].y, wj.y, acc[o]);
+        acc[o] = fmaf(x[o + j].z, wj.z, acc[o]); acc[o] = fmaf(x[o + j].w, wj.w, acc[o]);
+      }
+    }
+  }
+  float4 o4;
+  o4.x = t < valid ? tanhf(acc[0]) : 0.f;     o4.y = t + 1 < valid ? tanhf(acc[1]) : 0.f;
+  o4.z = t + 2 < valid ? tanhf(acc[2]) : 0.f; o4.w = t + 3 < valid ? tanhf(acc[3]) : 0.f;
+  *reinterpret_cast<float4*>(wav + (long long)b * L + t) = o4;
+}
+
 cudaError_t launch_conv_post(const float* in, int B, int L, int C, int k, float slope, const float* w,
                              const int* len, int len_mul, float* wav, cudaStream_t stream) {
+  if (C == 32 && k == 7 && L % 4 == 0) {
+    dim3 grid4(ceil_div(L, kPost4Tile), B);
+    conv_post4_kernel<32, 7><<<grid4, kPost4Threads, 0, stream>>>(in, L, slope, w, len, len_mul, wav);
+    return cudaGetLastError();
+  }
   dim3 grid(ceil_div(L, kPostTile), B);
   size_t smem = (size_t)((kPostTile + k - 1) * (C + 1) + k * C) * sizeof(float);
   conv_post_kernel<<<grid, kPostTile, smem, stream>>>(in, L, C, k, slope, w, len, len_mul, wav);
