@@ -18,7 +18,7 @@ inp = FX.make_p2_inputs(cfg, 33, seed=1234)
 o = e16.infer_p2(*(inp[k].cuda() for k in ("attn", "m_p", "s_p", "g", "noise"))).cpu()
 ref = torch.from_numpy(gold["o"])
 print("golden T=33 : max-abs %.3e  log-mel L1 %.3e" % ((o - ref).abs().max().item(), log_mel_l1(o[:, 0], ref[:, 0])))
-for T in (417, 834):
+for T in (417, 834, 5000):
     lat = FX.make_latents(cfg, [T], seed=5)
     zp, g = lat["z_p"].cuda(), lat["g"].cuda()
     w16, w32 = e16.synthesize(zp, g).cpu(), e32.synthesize(zp, g).cpu()

@@ -13,6 +13,7 @@ namespace vitsb {
 struct PackedConv {
   int Cin = 0, N = 0, NT = 0, k = 1, dil = 1, pad = 0;   // Cin = K per tap in the packed weights
   int in_cols = 0;         // physical columns of an input row (2*C for split-precision convs, else Cin)
+  int in_ld = 0;           // row pitch of the input buffer in elements (0 -> in_cols); an unsplit conv over a [hi|lo] buffer reads hi only
   bool gate = false;
   int gate_group = 0;      // gated: packed columns in groups of gate_group = [tanh | sigmoid] halves (0 -> NT)
   bool split = false;      // 3-term split precision: rows [hi|lo], weights [Wh|Wh|Wl] per tap (common.h)
@@ -49,6 +50,7 @@ struct Engine {
   int op = OP_F16;
   std::string err;
   bool split16 = false;
+  bool flow_in_split = false;   // WN in_layers run 3-term split precision too (VITSB_FLOW_IN_SPLIT=1); default: single fp16 term
   bool rb_fused = false;   // 16-bit paths: ResBlock iterations run as the fused persistent kernel (rb_fused.cu)    // 16-bit paths: flow + conv_pre + upsamplers run split-precision
 
   // packed model

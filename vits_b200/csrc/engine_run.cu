@@ -107,7 +107,8 @@ struct Ctx {
     if (dry || !ok()) return;
     ev_begin(tag, (p.flop_per_pos + (p2 ? p2->flop_per_pos : 0.0)) * (len ? valid_frames : (double)B * T) * len_mul);
     ConvArgs a{};
-    a.in = in; a.in_ld = p.in_cols; a.in_cols = p.in_cols; a.in_bstride = (long long)L * p.in_cols; a.Cin = p.Cin;
+    const int in_ld = p.in_ld > 0 ? p.in_ld : p.in_cols;
+    a.in = in; a.in_ld = in_ld; a.in_cols = p.in_cols; a.in_bstride = (long long)L * in_ld; a.Cin = p.Cin;
     a.w = reinterpret_cast<const char*>(e->d_w) + p.w_off * op_bytes(e->op);
     a.N = p.N; a.NT = p.NT; a.k = p.k; a.dil = p.dil; a.pad = p.pad; a.L = L; a.B = B;
     a.gate_group = p.gate_group; a.m_tiles = m_tiles(L, len_mul, len != nullptr);
@@ -142,6 +143,11 @@ void set_out_op(Epilogue& ep, void* p, int ld, long long L, float slope) {
 void set_out_op_split(Epilogue& ep, void* p, int C, long long L, float slope, bool split) {
   const int ld = split ? 2 * C : C;
   ep.out_op = p; ep.out_op_ld = ld; ep.out_op_bstride = L * ld; ep.out_slope = slope; ep.out_op_split = split ? C : 0;
+}
+// same row pitch as the split layout, lo half written only when a split conv will read it
+void set_out_op_hi(Epilogue& ep, void* p, int C, long long L, bool split_pitch, bool write_lo) {
+  set_out_op_split(ep, p, C, L, 1.f, split_pitch);
+  if (!write_lo) ep.out_op_split = 0;
 }
 
 }  // namespace
@@ -195,7 +201,7 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
   if (what & RUN_FLOW) {
     for (const Coupling& cp : couplings) {
       // h = pre(x0)                                                   modules.py:364
-      { Epilogue ep = epi_base(); set_out_f32(ep, F(W.hf), H, T); set_out_op_split(ep, P(W.hop), H, T, 1.f, split16);
+      { Epilogue ep = epi_base(); set_out_f32(ep, F(W.hf), H, T); set_out_op_hi(ep, P(W.hop), H, T, split16, flow_in_split);
         cx.conv(T_FLOW_PRE, cp.pre, P(W.zop), T, 1, cx.len_flow, ep); }
       const int nl = (int)cp.in_layers.size();
       for (int l = 0; l < nl; ++l) {
@@ -203,7 +209,7 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
         { Epilogue ep = epi_base(); set_out_op_split(ep, P(W.acts), H, T, 1.f, split16);
           cx.conv(T_FLOW_IN, cp.in_layers[l], P(W.hop), T, 1, cx.len_flow, ep); }
         // h += res_skip[:H]                                             modules.py:176-178
-        Epilogue epr = epi_base(); set_res(epr, F(W.hf), H, T); set_out_f32(epr, F(W.hf), H, T); set_out_op_split(epr, P(W.hop), H, T, 1.f, split16);
+        Epilogue epr = epi_base(); set_res(epr, F(W.hf), H, T); set_out_f32(epr, F(W.hf), H, T); set_out_op_hi(epr, P(W.hop), H, T, split16, flow_in_split);
         // output += res_skip[H:] (all of it on the last layer)          modules.py:179-181
         Epilogue eps = epi_base();
         if (l > 0) set_accum(eps, F(W.skipf), H, T);

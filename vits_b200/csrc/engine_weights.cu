@@ -70,6 +70,7 @@ int Engine::validate_config() {
   }
   op = c.precision == VITSB_PREC_FP32 ? OP_F32 : (c.precision == VITSB_PREC_BF16 ? OP_BF16 : OP_F16);
   split16 = op != OP_F32;
+  { const char* ev = getenv("VITSB_FLOW_IN_SPLIT"); flow_in_split = split16 && ev && ev[0] == '1'; }
   {
     const char* ev = getenv("VITSB_RB_FUSED");
     rb_fused = op != OP_F32 && !(ev && ev[0] == '0');
@@ -246,8 +247,9 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
       const int GG = (NT % 64 == 0) ? 64 : NT;   // gate pairs packed in 64-column groups: the launcher may run any NT that is a multiple of it
       std::vector<int> cols = iota_rows(0, H);
       cp.in_layers.push_back(pack_conv(L.weight(p + "enc.in_layers." + li, {2 * H, H, fk}), L.bias(p + "enc.in_layers." + li, 2 * H),
-                                       gate_rows(2 * H, GG), cols, fk, dil, true, NT, cw, cb, l * 2 * H, H, true));
+                                       gate_rows(2 * H, GG), cols, fk, dil, true, NT, cw, cb, l * 2 * H, H, flow_in_split));
       cp.in_layers.back().gate_group = GG;
+      if (split16 && !flow_in_split) cp.in_layers.back().in_ld = 2 * H;     // h operand rows stay [hi | lo] (pitch 2H); hi alone is read
       const int rs = l < nl - 1 ? 2 * H : H;
       const HostTensor* rw = L.weight(p + "enc.res_skip_layers." + li, {rs, H, 1});
       const HostTensor* rb = L.bias(p + "enc.res_skip_layers." + li, rs);
