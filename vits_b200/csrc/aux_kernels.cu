@@ -2,6 +2,7 @@
 // the seam, the per-call conditioning GEMV, and conv_post+tanh (N=1, CUDA cores).
 #include "common.h"
 #include "kernels.h"
+#include "tc_common.cuh"
 
 namespace vitsb {
 
@@ -113,6 +114,70 @@ cudaError_t launch_cond_gemv(const float* W, const float* bias, const float* g, 
 }
 
 // ---------------------------------------------------------------------------
+// MRF average (models.py:311-314) over the branches' final 16-bit y streams (y = leaky_relu(x_j, 0.1), so
+// x_j = min(y, 10 y)): next = op(leaky_relu(scale * sum_j x_j, 0.1)), written as the next upsampler's operand
+// rows ([hi | lo] when split).  HBM-bound and fully coalesced: 8 channels (one 16-byte vector per stream) per
+// thread; 2 B x n_streams in + 2-4 B out per element.  Inside the fused ResBlock kernel the same sum cost more
+// than this whole pass: its row-per-thread epilogue paid one exposed DRAM round trip per 16-column chunk.
+// ---------------------------------------------------------------------------
+template <typename OpT>
+__device__ __forceinline__ void y_accum8(const uint4& y, float (&x)[8]) {
+  const uint32_t w[4] = {y.x, y.y, y.z, y.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const float2 f = Pack16<OpT>::unpack2(w[i]);
+    x[2 * i] += fminf(f.x, 10.f * f.x);
+    x[2 * i + 1] += fminf(f.y, 10.f * f.y);
+  }
+}
+
+template <typename OpT>
+__global__ void __launch_bounds__(256)
+mrf_sum_kernel(const OpT* __restrict__ y0, const OpT* __restrict__ y1, const OpT* __restrict__ y2, int C, int L,
+               const int* __restrict__ len, int len_mul, float scale, float slope, OpT* __restrict__ out, int split) {
+  const int b = blockIdx.y;
+  const int valid = len ? len[b] * len_mul : L;
+  const int rows = valid + kHaloRows < L ? valid + kHaloRows : L;      // rows nobody reads are skipped (as every producer does)
+  const int C8 = C >> 3;
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int t = (int)(i / C8), c = (int)(i - (long long)t * C8) * 8;
+  if (t >= rows) return;
+  const long long e = ((long long)b * L + t) * C + c;
+  float x[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+  if (t < valid) {
+    const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(y0 + e));
+    uint4 a1 = make_uint4(0u, 0u, 0u, 0u), a2 = a1;
+    if (y1) a1 = __ldg(reinterpret_cast<const uint4*>(y1 + e));
+    if (y2) a2 = __ldg(reinterpret_cast<const uint4*>(y2 + e));
+    y_accum8<OpT>(a0, x); y_accum8<OpT>(a1, x); y_accum8<OpT>(a2, x);
+  }
+  uint32_t p[4], q[4];
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    float u = x[2 * k] * scale, v = x[2 * k + 1] * scale;
+    u = u >= 0.f ? u : slope * u; v = v >= 0.f ? v : slope * v;
+    p[k] = Pack16<OpT>::pack2(u, v);
+    const float2 hi = Pack16<OpT>::unpack2(p[k]);
+    q[k] = Pack16<OpT>::pack2(u - hi.x, v - hi.y);
+  }
+  OpT* o = out + ((long long)b * L + t) * (split ? 2 * C : C) + c;
+  *reinterpret_cast<uint4*>(o) = make_uint4(p[0], p[1], p[2], p[3]);
+  if (split) *reinterpret_cast<uint4*>(o + C) = make_uint4(q[0], q[1], q[2], q[3]);
+}
+
+cudaError_t launch_mrf_sum(const void* y0, const void* y1, const void* y2, int B, int L, int C, const int* len, int len_mul,
+                           float scale, float slope, void* out, int split, int op, cudaStream_t stream) {
+  if (op == OP_F32 || C % 8 != 0 || !y0) return cudaErrorNotSupported;
+  const long long per_b = (long long)L * (C / 8);
+  dim3 grid((unsigned)((per_b + 255) / 256), B);
+  if (op == OP_F16) mrf_sum_kernel<__half><<<grid, 256, 0, stream>>>((const __half*)y0, (const __half*)y1, (const __half*)y2, C, L, len, len_mul,
+                                                                     scale, slope, (__half*)out, split);
+  else mrf_sum_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>((const __nv_bfloat16*)y0, (const __nv_bfloat16*)y1, (const __nv_bfloat16*)y2, C, L,
+                                                               len, len_mul, scale, slope, (__nv_bfloat16*)out, split);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
 // leaky_relu(slope) + conv_post (Conv1d C->1, k taps, no bias) + tanh.  HBM-bound:
 // reads C fp32 values (the MRF accumulator of the last stage, never rounded to
 // 16 bits: conv_post sits right before the output and its input rounding would
@@ -161,10 +226,13 @@ conv_post_kernel(const float* __restrict__ in, int L, int C, int k, float slope,
 // up to 16 FMAs.  Tile rows are stored as 8 float4 with the float4 index XOR-swizzled by (row / 4), which makes
 // the row loads of threads that sit 4 rows apart conflict-free.
 constexpr int kPost4Out = 4, kPost4Threads = 64, kPost4Tile = kPost4Out * kPost4Threads;
-template <int C, int K>
+// YT = float: `in` is the fp32 MRF average.  YT = 16-bit operand type: the MRF average is formed here from the
+// branches' final y streams (in, in1, in2; x_j = min(y, 10 y)) times `scale` - the last stage then needs neither
+// an fp32 accumulator pass nor a summing ResBlock epilogue.
+template <int C, int K, typename YT>
 __global__ void __launch_bounds__(kPost4Threads)
-conv_post4_kernel(const float* __restrict__ in, int L, float slope, const float* __restrict__ w,
-                  const int* __restrict__ len, int len_mul, float* __restrict__ wav) {
+conv_post4_kernel(const YT* __restrict__ in, const YT* __restrict__ in1, const YT* __restrict__ in2, float scale, int L, float slope,
+                  const float* __restrict__ w, const int* __restrict__ len, int len_mul, float* __restrict__ wav) {
   constexpr int C4 = C / 4, ROWS = kPost4Tile + K - 1, PAD = (K - 1) / 2;
   static_assert(C4 == 8, "swizzle assumes 8 float4 per row");
   __shared__ float4 tile[ROWS * C4];
@@ -176,14 +244,35 @@ conv_post4_kernel(const float* __restrict__ in, int L, float slope, const float*
     if (t < L) *reinterpret_cast<float4*>(wav + (long long)b * L + t) = make_float4(0.f, 0.f, 0.f, 0.f);
     return;
   }
-  const float4* src = reinterpret_cast<const float4*>(in + (long long)b * L * C);
-  for (int i = threadIdx.x; i < ROWS * C4; i += kPost4Threads) {
-    const int r = i / C4, c4 = i - r * C4, tt = t0 + r - PAD;
-    float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
-    if (tt >= 0 && tt < L) x = __ldg(src + (long long)tt * C4 + c4);
-    x.x = x.x >= 0.f ? x.x : slope * x.x; x.y = x.y >= 0.f ? x.y : slope * x.y;
-    x.z = x.z >= 0.f ? x.z : slope * x.z; x.w = x.w >= 0.f ? x.w : slope * x.w;
-    tile[r * C4 + ((c4 ^ (r >> 2)) & 7)] = x;
+  if constexpr (sizeof(YT) == 4) {
+    const float4* src = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(in) + (long long)b * L * C);
+    for (int i = threadIdx.x; i < ROWS * C4; i += kPost4Threads) {
+      const int r = i / C4, c4 = i - r * C4, tt = t0 + r - PAD;
+      float4 x = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (tt >= 0 && tt < L) x = __ldg(src + (long long)tt * C4 + c4);
+      x.x = x.x >= 0.f ? x.x : slope * x.x; x.y = x.y >= 0.f ? x.y : slope * x.y;
+      x.z = x.z >= 0.f ? x.z : slope * x.z; x.w = x.w >= 0.f ? x.w : slope * x.w;
+      tile[r * C4 + ((c4 ^ (r >> 2)) & 7)] = x;
+    }
+  } else {
+    constexpr int C8 = C / 8;
+    const long long boff = (long long)b * L * C;
+    for (int i = threadIdx.x; i < ROWS * C8; i += kPost4Threads) {
+      const int r = i / C8, c8 = i - r * C8, tt = t0 + r - PAD;
+      float x[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (tt >= 0 && tt < valid) {               // rows beyond len[b] are zero in every stream
+        const long long e = boff + (long long)tt * C + c8 * 8;
+        const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(in + e));
+        uint4 a1 = make_uint4(0u, 0u, 0u, 0u), a2 = a1;
+        if (in1) a1 = __ldg(reinterpret_cast<const uint4*>(in1 + e));
+        if (in2) a2 = __ldg(reinterpret_cast<const uint4*>(in2 + e));
+        y_accum8<YT>(a0, x); y_accum8<YT>(a1, x); y_accum8<YT>(a2, x);
+      }
+#pragma unroll
+      for (int q = 0; q < 8; ++q) { const float v = x[q] * scale; x[q] = v >= 0.f ? v : slope * v; }
+      tile[r * C4 + (((2 * c8) ^ (r >> 2)) & 7)] = make_float4(x[0], x[1], x[2], x[3]);
+      tile[r * C4 + (((2 * c8 + 1) ^ (r >> 2)) & 7)] = make_float4(x[4], x[5], x[6], x[7]);
+    }
   }
   for (int i = threadIdx.x; i < K * C4; i += kPost4Threads) ws[i] = __ldg(reinterpret_cast<const float4*>(w) + i);
   __syncthreads();
@@ -218,12 +307,27 @@ cudaError_t launch_conv_post(const float* in, int B, int L, int C, int k, float 
                              const int* len, int len_mul, float* wav, cudaStream_t stream) {
   if (C == 32 && k == 7 && L % 4 == 0) {
     dim3 grid4(ceil_div(L, kPost4Tile), B);
-    conv_post4_kernel<32, 7><<<grid4, kPost4Threads, 0, stream>>>(in, L, slope, w, len, len_mul, wav);
+    conv_post4_kernel<32, 7, float><<<grid4, kPost4Threads, 0, stream>>>(in, nullptr, nullptr, 1.f, L, slope, w, len, len_mul, wav);
     return cudaGetLastError();
   }
   dim3 grid(ceil_div(L, kPostTile), B);
   size_t smem = (size_t)((kPostTile + k - 1) * (C + 1) + k * C) * sizeof(float);
   conv_post_kernel<<<grid, kPostTile, smem, stream>>>(in, L, C, k, slope, w, len, len_mul, wav);
+  return cudaGetLastError();
+}
+
+bool conv_post_y_supported(int C, int k, int L) { return C == 32 && k == 7 && L % 4 == 0; }
+
+cudaError_t launch_conv_post_y(const void* y0, const void* y1, const void* y2, float scale, int B, int L, int C, int k, float slope,
+                               const float* w, const int* len, int len_mul, float* wav, int op, cudaStream_t stream) {
+  if (op == OP_F32 || !conv_post_y_supported(C, k, L) || !y0) return cudaErrorNotSupported;
+  dim3 grid4(ceil_div(L, kPost4Tile), B);
+  if (op == OP_F16)
+    conv_post4_kernel<32, 7, __half><<<grid4, kPost4Threads, 0, stream>>>((const __half*)y0, (const __half*)y1, (const __half*)y2, scale, L, slope,
+                                                                          w, len, len_mul, wav);
+  else
+    conv_post4_kernel<32, 7, __nv_bfloat16><<<grid4, kPost4Threads, 0, stream>>>((const __nv_bfloat16*)y0, (const __nv_bfloat16*)y1,
+                                                                                 (const __nv_bfloat16*)y2, scale, L, slope, w, len, len_mul, wav);
   return cudaGetLastError();
 }
 

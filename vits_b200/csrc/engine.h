@@ -50,7 +50,8 @@ struct Engine {
   int op = OP_F16;
   std::string err;
   bool split16 = false;
-  bool flow_in_split = false;   // WN in_layers run 3-term split precision too (VITSB_FLOW_IN_SPLIT=1); default: single fp16 term
+  bool mrf_separate = true;     // MRF average as its own coalesced pass over the branches' y streams (VITSB_MRF_SEP=0: summing ResBlock epilogue)
+  bool flow_in_split = false;   // WN in_layers run 3-term split precision too (VITSB_FLOW_IN_SPLIT=1/0); default: fp16 single term, bf16 split
   bool rb_fused = false;   // 16-bit paths: ResBlock iterations run as the fused persistent kernel (rb_fused.cu)    // 16-bit paths: flow + conv_pre + upsamplers run split-precision
 
   // packed model

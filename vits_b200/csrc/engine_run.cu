@@ -49,7 +49,7 @@ WsLayout Engine::layout(int B, int T) const {
 namespace {
 
 // launch tags for the profile table
-enum Tag { T_PACK = 0, T_COND = 1, T_UNPACK = 2, T_POST = 3, T_FLOW_PRE = 10, T_FLOW_IN = 11, T_FLOW_RES = 12,
+enum Tag { T_PACK = 0, T_COND = 1, T_UNPACK = 2, T_POST = 3, T_MRF = 4, T_FLOW_PRE = 10, T_FLOW_IN = 11, T_FLOW_RES = 12,
            T_FLOW_SKIP = 13, T_FLOW_POST = 14, T_CONV_PRE = 20, T_UPS = 30, T_RB_C1 = 40, T_RB_C2 = 50, T_RB_FUSED = 60 };
 
 struct ProfEv { int tag; double flops; cudaEvent_t a, b; };
@@ -240,6 +240,10 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
     int L = T;              // rows per batch item at the current rate
     int mul = 1;            // valid rows = len * mul
     const int ns = (int)stages.size();
+    // conv_post forms the last stage's MRF average from the branches' y streams itself (decided up front: the
+    // decoder loop below is skipped in the PH_BACK pass of a graph replay)
+    const bool post_from_y = rb_fused && mrf_separate && ns > 0 && stages.back().rb.size() <= 3 &&
+                             conv_post_y_supported(post_C, post_k, T * up_total);
     for (int s = 0; s < ns; ++s) {
       const Stage& st = stages[s];
       const int C = st.C, Lo = L * st.u;
@@ -277,10 +281,17 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
             // last iteration is an ordinary mid-type launch into br[j]) and the final branch sums them in its epilogue:
             // 12 B of traffic per element instead of 20 B through an fp32 accumulator.  br[] reuses the fp32
             // buffers of the layer-at-a-time plan, which the fused plan does not touch.
-            void* br[2] = {P(W.xin_f), P(W.xb_f)};
+            void* br[3] = {P(W.xin_f), P(W.xb_f), P(W.acc_f)};
             const bool stream_mrf = nk <= 3;
+            // Separate MRF pass (default): EVERY branch ends in an ordinary mid-type launch into br[j] and one coalesced
+            // pass (mrf_sum_kernel, or conv_post's tile load on the last stage) averages the streams.  The summing
+            // epilogue variant costs 40-100 us more per stage than a mid launch (one exposed DRAM round trip per
+            // 16-column chunk in a row-per-thread epilogue); the separate pass is HBM-bound at 10 B per element.
+            const bool sep_mrf = stream_mrf && mrf_separate && (s < ns - 1 || post_from_y);
             if (d < ni - 1) {
               ra.y_out = ping;
+            } else if (sep_mrf) {
+              ra.y_out = br[j];
             } else if (stream_mrf && j < nk - 1) {
               ra.y_out = br[j];
             } else if (stream_mrf) {
@@ -324,10 +335,21 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
           cx.conv(T_RB_C2 + s, it.c2, P(W.g_op), L, mul, cx.len_dec, ep);
         }
       }
+      if (rb_fused && mrf_separate && nk <= 3 && s < ns - 1) {
+        // x = sum_j resblock_j(x) / num_kernels; next operand = leaky_relu(x, 0.1)      models.py:309-314
+        AUX_LAUNCH(T_MRF, launch_mrf_sum(P(W.xin_f), nk > 1 ? P(W.xb_f) : nullptr, nk > 2 ? P(W.acc_f) : nullptr, B, L, C, cx.len_dec, mul,
+                                         inv, next_slope, P(W.nxt_op), split16 ? 1 : 0, op, stream));
+      }
     }
     // tanh(conv_post(leaky_relu(x, 0.01)))                                 models.py:315-317
     cx.skip = !(phases & PH_BACK);
-    AUX_LAUNCH(T_POST, launch_conv_post(F(W.acc_f), B, L, post_C, post_k, 0.01f, d_post, cx.len_dec, mul, wav, stream));
+    if (post_from_y) {
+      const int nk = (int)stages.back().rb.size();
+      AUX_LAUNCH(T_POST, launch_conv_post_y(P(W.xin_f), nk > 1 ? P(W.xb_f) : nullptr, nk > 2 ? P(W.acc_f) : nullptr, 1.0f / nk, B, L, post_C,
+                                            post_k, 0.01f, d_post, cx.len_dec, mul, wav, op, stream));
+    } else {
+      AUX_LAUNCH(T_POST, launch_conv_post(F(W.acc_f), B, L, post_C, post_k, 0.01f, d_post, cx.len_dec, mul, wav, stream));
+    }
   }
 #undef AUX_LAUNCH
   if (launches) *launches = cx.launches;

@@ -70,7 +70,8 @@ int Engine::validate_config() {
   }
   op = c.precision == VITSB_PREC_FP32 ? OP_F32 : (c.precision == VITSB_PREC_BF16 ? OP_BF16 : OP_F16);
   split16 = op != OP_F32;
-  { const char* ev = getenv("VITSB_FLOW_IN_SPLIT"); flow_in_split = split16 && ev && ev[0] == '1'; }
+  { const char* ev = getenv("VITSB_MRF_SEP"); mrf_separate = !(ev && ev[0] == '0'); }
+  { const char* ev = getenv("VITSB_FLOW_IN_SPLIT"); flow_in_split = split16 && (ev ? ev[0] == '1' : op == OP_BF16); }   // bf16 operands (8x the rounding) keep the split
   {
     const char* ev = getenv("VITSB_RB_FUSED");
     rb_fused = op != OP_F32 && !(ev && ev[0] == '0');

@@ -65,4 +65,12 @@ cudaError_t launch_cond_gemv(const float* W, const float* bias, const float* g, 
 cudaError_t launch_conv_post(const float* in, int B, int L, int C, int k, float slope, const float* w,
                              const int* len, int len_mul, float* wav, cudaStream_t stream);
 
+// MRF average over the branches' final 16-bit y streams -> next upsampler operand rows (16-bit paths)
+cudaError_t launch_mrf_sum(const void* y0, const void* y1, const void* y2, int B, int L, int C, const int* len, int len_mul,
+                           float scale, float slope, void* out, int split, int op, cudaStream_t stream);
+// conv_post whose input is the MRF average of up to three y streams, formed in the tile load (base shape only)
+bool conv_post_y_supported(int C, int k, int L);
+cudaError_t launch_conv_post_y(const void* y0, const void* y1, const void* y2, float scale, int B, int L, int C, int k, float slope,
+                               const float* w, const int* len, int len_mul, float* wav, int op, cudaStream_t stream);
+
 }  // namespace vitsb

@@ -762,7 +762,12 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   if (G::STATIONARY) {
     if (fixed + G::W_ALL + 2 * slab_set > kRbSmemBudget) return cudaErrorNotSupported;
     rt.nSlab = (int)((kRbSmemBudget - fixed - G::W_ALL) / slab_set);
-    const int want = G::RES_GLOBAL ? 4 : G::NBUF + 2;   // slab lifetime: load + c1 only, or the whole 4-stage pipeline
+    // slab lifetime: load + c1 only (RES_GLOBAL), or the whole 4-stage pipeline (C = 32 reads the residual from the slab:
+    // ~6.7 k cycles from TMA issue to the store epilogue's release, so the tile period is that latency / nSlab - measured
+    // 1.1 k cycles per tile with 6 slabs against ~0.4 k of tensor work; use all 8 barrier slots)
+    static int want_env = -1;
+    if (want_env < 0) { const char* e = getenv("VITSB_RB_NSLAB"); want_env = e ? atoi(e) : 0; }
+    const int want = want_env > 0 ? (want_env > 8 ? 8 : want_env) : (G::RES_GLOBAL ? 4 : 8);
     if (rt.nSlab > want) rt.nSlab = want;
   } else {
     // streamed weights: slabs first (2 when the accumulators are double-buffered), the rest to the ring

@@ -93,7 +93,7 @@ class FlowDecoder:
     def launches_per_call(self, B: int, T: int) -> int:
         return int(self.lib.vitsb_launches_per_call(self._h, B, T))
 
-    TAG_NAMES = {0: "pack", 1: "cond_gemv", 2: "unpack", 3: "conv_post", 10: "flow.pre", 11: "flow.in_layers",
+    TAG_NAMES = {0: "pack", 1: "cond_gemv", 2: "unpack", 3: "conv_post", 4: "mrf_sum", 10: "flow.pre", 11: "flow.in_layers",
                  12: "flow.res", 13: "flow.skip", 14: "flow.post", 20: "conv_pre"}
 
     def profile(self, enable: bool):
