@@ -74,34 +74,62 @@ cudaError_t launch_unpack_channel_major(const float* src, int B, int C, int T, f
 // conditioning GEMV: one warp per output row n, all batch rows per pass of W
 // (W is read once per call: 12.5k x 1024 fp32 at base config)
 // ---------------------------------------------------------------------------
-constexpr int kCondBChunk = 8;
+// Two output rows per warp: their W rows (2 x 1024 floats per pass) are loaded into registers with all loads in
+// flight at once (the matrix is read from HBM exactly once), then every batch row's g is streamed through L1
+// against both.  The previous one-row version re-read W per 8 batch rows and kept a single load in flight per
+// lane (70 us for a 51 MB read); this one is bound by the L1 reads of g.
+constexpr int kCondRows = 2, kCondK = 1024;      // rows per warp, k values per register pass (8 float4 per lane)
 __global__ void __launch_bounds__(256)
 cond_gemv_kernel(const float* __restrict__ W, const float* __restrict__ bias, const float* __restrict__ g,
                  int B, int Ncond, int gin, float* __restrict__ out) {
   const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
-  if (warp >= Ncond) return;
-  const float* wr = W + (long long)warp * gin;
-  for (int b0 = 0; b0 < B; b0 += kCondBChunk) {
-    float acc[kCondBChunk];
+  const int n0 = warp * kCondRows;
+  if (n0 >= Ncond) return;
+  for (int b0 = 0; b0 < B; b0 += 32) {             // lane (b - b0) keeps the running sums of batch row b
+    float acc[kCondRows];
 #pragma unroll
-    for (int i = 0; i < kCondBChunk; ++i) acc[i] = 0.f;
-    for (int k = lane * 4; k < gin; k += 128) {
-      float4 wv = *reinterpret_cast<const float4*>(wr + k);
+    for (int r = 0; r < kCondRows; ++r) acc[r] = 0.f;
+    for (int k0 = 0; k0 < gin; k0 += kCondK) {
+      float4 wv[kCondRows][kCondK / 128];
 #pragma unroll
-      for (int i = 0; i < kCondBChunk; ++i) {
-        if (b0 + i < B) {
-          float4 gv = *reinterpret_cast<const float4*>(g + (long long)(b0 + i) * gin + k);
-          acc[i] = fmaf(wv.x, gv.x, acc[i]); acc[i] = fmaf(wv.y, gv.y, acc[i]);
-          acc[i] = fmaf(wv.z, gv.z, acc[i]); acc[i] = fmaf(wv.w, gv.w, acc[i]);
+      for (int r = 0; r < kCondRows; ++r)
+#pragma unroll
+        for (int i = 0; i < kCondK / 128; ++i) {
+          const int k = k0 + i * 128 + lane * 4;
+          wv[r][i] = (n0 + r < Ncond && k < gin) ? __ldg(reinterpret_cast<const float4*>(W + (long long)(n0 + r) * gin + k))
+                                                 : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      const int bend = b0 + 32 < B ? b0 + 32 : B;
+      for (int b = b0; b < bend; ++b) {
+        float p[kCondRows];
+#pragma unroll
+        for (int r = 0; r < kCondRows; ++r) p[r] = 0.f;
+#pragma unroll
+        for (int i = 0; i < kCondK / 128; ++i) {
+          const int k = k0 + i * 128 + lane * 4;
+          if (k < gin) {
+            const float4 gv = __ldg(reinterpret_cast<const float4*>(g + (long long)b * gin + k));
+#pragma unroll
+            for (int r = 0; r < kCondRows; ++r) {
+              p[r] = fmaf(wv[r][i].x, gv.x, p[r]); p[r] = fmaf(wv[r][i].y, gv.y, p[r]);
+              p[r] = fmaf(wv[r][i].z, gv.z, p[r]); p[r] = fmaf(wv[r][i].w, gv.w, p[r]);
+            }
+          }
+        }
+#pragma unroll
+        for (int r = 0; r < kCondRows; ++r) {
+          float v = p[r];
+#pragma unroll
+          for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+          if (lane == b - b0) acc[r] += v;
         }
       }
     }
+    const int b = b0 + lane;
+    if (b < B) {
 #pragma unroll
-    for (int i = 0; i < kCondBChunk; ++i) {
-      float v = acc[i];
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-      if (lane == 0 && b0 + i < B) out[(long long)(b0 + i) * Ncond + warp] = v + bias[warp];
+      for (int r = 0; r < kCondRows; ++r)
+        if (n0 + r < Ncond) out[(long long)b * Ncond + n0 + r] = acc[r] + bias[n0 + r];
     }
   }
 }
@@ -109,7 +137,7 @@ cond_gemv_kernel(const float* __restrict__ W, const float* __restrict__ bias, co
 cudaError_t launch_cond_gemv(const float* W, const float* bias, const float* g, int B, int Ncond, int gin,
                              float* out, cudaStream_t stream) {
   const int warps_per_block = 8;
-  cond_gemv_kernel<<<ceil_div(Ncond, warps_per_block), warps_per_block * 32, 0, stream>>>(W, bias, g, B, Ncond, gin, out);
+  cond_gemv_kernel<<<ceil_div(ceil_div(Ncond, kCondRows), warps_per_block), warps_per_block * 32, 0, stream>>>(W, bias, g, B, Ncond, gin, out);
   return cudaGetLastError();
 }
 
@@ -255,23 +283,32 @@ conv_post4_kernel(const YT* __restrict__ in, const YT* __restrict__ in1, const Y
       tile[r * C4 + ((c4 ^ (r >> 2)) & 7)] = x;
     }
   } else {
-    constexpr int C8 = C / 8;
+    constexpr int C8 = C / 8, U = 4;              // U items per thread per pass: 3 U independent 16-byte loads in flight
     const long long boff = (long long)b * L * C;
-    for (int i = threadIdx.x; i < ROWS * C8; i += kPost4Threads) {
-      const int r = i / C8, c8 = i - r * C8, tt = t0 + r - PAD;
-      float x[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-      if (tt >= 0 && tt < valid) {               // rows beyond len[b] are zero in every stream
-        const long long e = boff + (long long)tt * C + c8 * 8;
-        const uint4 a0 = __ldg(reinterpret_cast<const uint4*>(in + e));
-        uint4 a1 = make_uint4(0u, 0u, 0u, 0u), a2 = a1;
-        if (in1) a1 = __ldg(reinterpret_cast<const uint4*>(in1 + e));
-        if (in2) a2 = __ldg(reinterpret_cast<const uint4*>(in2 + e));
-        y_accum8<YT>(a0, x); y_accum8<YT>(a1, x); y_accum8<YT>(a2, x);
+    for (int i0 = threadIdx.x; i0 < ROWS * C8; i0 += U * kPost4Threads) {
+      uint4 a[U][3];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int i = i0 + u * kPost4Threads, r = i / C8, c8 = i - r * C8, tt = t0 + r - PAD;
+        a[u][0] = a[u][1] = a[u][2] = make_uint4(0u, 0u, 0u, 0u);
+        if (i < ROWS * C8 && tt >= 0 && tt < valid) {          // rows beyond len[b] are zero in every stream
+          const long long e = boff + (long long)tt * C + c8 * 8;
+          a[u][0] = __ldg(reinterpret_cast<const uint4*>(in + e));
+          if (in1) a[u][1] = __ldg(reinterpret_cast<const uint4*>(in1 + e));
+          if (in2) a[u][2] = __ldg(reinterpret_cast<const uint4*>(in2 + e));
+        }
       }
 #pragma unroll
-      for (int q = 0; q < 8; ++q) { const float v = x[q] * scale; x[q] = v >= 0.f ? v : slope * v; }
-      tile[r * C4 + (((2 * c8) ^ (r >> 2)) & 7)] = make_float4(x[0], x[1], x[2], x[3]);
-      tile[r * C4 + (((2 * c8 + 1) ^ (r >> 2)) & 7)] = make_float4(x[4], x[5], x[6], x[7]);
+      for (int u = 0; u < U; ++u) {
+        const int i = i0 + u * kPost4Threads, r = i / C8, c8 = i - r * C8;
+        if (i >= ROWS * C8) break;
+        float x[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        y_accum8<YT>(a[u][0], x); y_accum8<YT>(a[u][1], x); y_accum8<YT>(a[u][2], x);
+#pragma unroll
+        for (int q = 0; q < 8; ++q) { const float v = x[q] * scale; x[q] = v >= 0.f ? v : slope * v; }
+        tile[r * C4 + (((2 * c8) ^ (r >> 2)) & 7)] = make_float4(x[0], x[1], x[2], x[3]);
+        tile[r * C4 + (((2 * c8 + 1) ^ (r >> 2)) & 7)] = make_float4(x[4], x[5], x[6], x[7]);
+      }
     }
   }
   for (int i = threadIdx.x; i < K * C4; i += kPost4Threads) ws[i] = __ldg(reinterpret_cast<const float4*>(w) + i);

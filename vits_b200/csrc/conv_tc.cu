@@ -49,7 +49,10 @@ struct TcGeom {
 #define TC_DBG(mask) (false)
 #endif
 
-constexpr int kTcEpiGroups = 2;                         // 4-warp epilogue groups; every group works on every tile (column units dealt round-robin)
+#ifndef VITSB_TC_EPI_GROUPS
+#define VITSB_TC_EPI_GROUPS 2
+#endif
+constexpr int kTcEpiGroups = VITSB_TC_EPI_GROUPS;                         // 4-warp epilogue groups; every group works on every tile (column units dealt round-robin)
 constexpr int kTcThreads = 64 + 128 * kTcEpiGroups;
 constexpr int kTcMaxB = 512;
 
