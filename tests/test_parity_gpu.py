@@ -237,3 +237,32 @@ def test_host_pipeline_matches_blocking_calls(base_cfg, base_sd):
     for z, g, out in reqs:
         ref = eng.synthesize_host(z, g, lens)
         assert torch.equal(out, ref)
+
+
+@pytest.mark.parametrize("env", [{"VITSB_MRF_SEP": "0"}, {"VITSB_FLOW_IN_SPLIT": "1"}, {"VITSB_RB_FUSED": "0"}])
+def test_alternative_launch_plans_agree(base_cfg, base_sd, env):
+    """The launch-plan switches read at load time (summing ResBlock epilogue instead of the separate MRF pass,
+    3-term split in_layers, layer-at-a-time ResBlocks) stay within the same tolerance of the CPU oracle and of
+    the default plan on a ragged batch."""
+    from vits_b200 import FlowDecoder
+    lens = [97, 40, 64]
+    lat = FX.make_latents(base_cfg, lens, seed=321)
+    with torch.no_grad():
+        _, o_ref = O.synthesize_ragged(base_sd, lat["z_p"], lat["g"], torch.tensor(lens), base_cfg)
+    old = {k: os.environ.get(k) for k in env}
+    os.environ.update(env)
+    try:
+        alt = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision="fp16")
+    finally:
+        for k, v in old.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+    w_alt = alt.synthesize(lat["z_p"].cuda(), lat["g"].cuda(), lens, ragged=True).cpu()
+    w_def = engine(base_cfg, base_sd, "fp16").synthesize(lat["z_p"].cuda(), lat["g"].cuda(), lens, ragged=True).cpu()
+    assert (w_alt - o_ref).abs().max().item() <= TOL_WAV["fp16"]
+    assert (w_def - o_ref).abs().max().item() <= TOL_WAV["fp16"]
+    assert (w_alt - w_def).abs().max().item() <= TOL_WAV["fp16"]
+    for b, L in enumerate(lens):
+        assert w_alt[b, 0, L * 192:].abs().sum().item() == 0

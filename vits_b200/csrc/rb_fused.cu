@@ -63,6 +63,7 @@ namespace vitsb {
 constexpr int kBiasSmemMinC = VITSB_BIAS_SMEM_MINC;      // channel count from which the epilogues read biases from shared memory
 constexpr int kRbMaxB = 512;
 constexpr uint32_t kRbSmemBudget = 220 * 1024;
+constexpr int kRbMaxSlab = 16, kRbBars = 97;
 
 template <int C, int KT>
 struct RbT {
@@ -81,7 +82,10 @@ struct RbT {
   static constexpr uint32_t W_SLOT = W1_TX > W2_TX ? W1_TX : W2_TX;               // ring slot (streamed mode)
   static constexpr int NBOX1 = KT * nCB1, NBOX2 = KT * nCB2;
   static constexpr uint32_t W_ALL = NBOX1 * W1_TX + NBOX2 * W2_TX;
-  static constexpr int NBUF = C <= 64 ? 4 : (C <= 128 ? 2 : 1);                   // G tiles / TMEM accumulator sets
+#ifndef VITSB_RB_NBUF32
+#define VITSB_RB_NBUF32 8
+#endif
+  static constexpr int NBUF = C <= 32 ? VITSB_RB_NBUF32 : (C <= 64 ? 4 : (C <= 128 ? 2 : 1));   // G tiles / TMEM accumulator sets
   static constexpr uint32_t G_SET = nCB2 * G_BYTES;
   static constexpr bool STATIONARY = C <= 64;                                     // W_ALL <= 135 KB: resident weights, two issuers
   static constexpr bool RES_GLOBAL = C >= 64;                                     // residual rows re-read from global (L2)
@@ -203,17 +207,18 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   constexpr bool kStage = !LAST && G::STAGE_OUT;                               // TMA-stored output rows (mid iterations)
   const uint32_t sStage = sW + (G::STATIONARY ? G::W_ALL : rt.nW * G::W_SLOT); // [NGRP][128][CB_O] output staging
   const uint32_t bars = sStage + (kStage ? G::STG_ALL : 0u);
+  // mbarriers: up to kRbMaxSlab slabs, 8 accumulator / G-tile sets, 8 weight-ring slots (kRbBars in total)
   auto slab_full = [&](int i) { return bars + 8u * i; };
-  auto slab_empty = [&](int i) { return bars + 8u * (8 + i); };
-  auto acc1_full = [&](int i) { return bars + 8u * (16 + i); };
-  auto acc1_empty = [&](int i) { return bars + 8u * (20 + i); };
-  auto acc2_full = [&](int i) { return bars + 8u * (24 + i); };
-  auto acc2_empty = [&](int i) { return bars + 8u * (28 + i); };
-  auto g_full = [&](int i) { return bars + 8u * (32 + i); };
-  auto g_empty = [&](int i) { return bars + 8u * (36 + i); };
-  const uint32_t w_all = bars + 8u * 40;
-  auto w_full = [&](int i) { return bars + 8u * (41 + i); };
-  auto w_empty = [&](int i) { return bars + 8u * (49 + i); };
+  auto slab_empty = [&](int i) { return bars + 8u * (16 + i); };
+  auto acc1_full = [&](int i) { return bars + 8u * (32 + i); };
+  auto acc1_empty = [&](int i) { return bars + 8u * (40 + i); };
+  auto acc2_full = [&](int i) { return bars + 8u * (48 + i); };
+  auto acc2_empty = [&](int i) { return bars + 8u * (56 + i); };
+  auto g_full = [&](int i) { return bars + 8u * (64 + i); };
+  auto g_empty = [&](int i) { return bars + 8u * (72 + i); };
+  const uint32_t w_all = bars + 8u * 80;
+  auto w_full = [&](int i) { return bars + 8u * (81 + i); };
+  auto w_empty = [&](int i) { return bars + 8u * (89 + i); };
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;   // provably warp-uniform role id
   const int rank = G::PAIR ? (int)ptx::cluster_ctarank() : 0;
@@ -227,9 +232,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     ptx::prefetch_tmap(&tmY); ptx::prefetch_tmap(&tmW1); ptx::prefetch_tmap(&tmW2);
     if (kStage) ptx::prefetch_tmap(&tmO);
     // slab release: c1's MMA commit, plus the 4 store-epilogue warps when they read the residual from the slab
-    for (int i = 0; i < 8; ++i) { ptx::mbar_init(slab_full(i), 1); ptx::mbar_init(slab_empty(i), G::RES_GLOBAL ? 1 : 5); }
+    for (int i = 0; i < kRbMaxSlab; ++i) { ptx::mbar_init(slab_full(i), 1); ptx::mbar_init(slab_empty(i), G::RES_GLOBAL ? 1 : 5); }
     ptx::mbar_init(w_all, 1);
-    for (int i = 0; i < 4; ++i) {
+    for (int i = 0; i < 8; ++i) {
       // pair mode: the leader's copies collect the arrivals of both CTAs' epilogue warps
       ptx::mbar_init(acc1_full(i), 1);  ptx::mbar_init(acc1_empty(i), G::NARR);
       ptx::mbar_init(acc2_full(i), 1);  ptx::mbar_init(acc2_empty(i), G::NARR);
@@ -758,7 +763,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   rt.R1 = (kTileM + (KT - 1) * L.dil + 7) & ~7;
   rt.slab_bytes = ((uint32_t)rt.R1 * G::rb1 + 1023u) & ~1023u;
   const uint32_t slab_set = G::nCB1 * rt.slab_bytes;
-  const uint32_t fixed = 1024 + 512 + G::NBUF * G::G_SET + (LAST ? 0u : G::STG_ALL);
+  const uint32_t fixed = 1024 + 8 * kRbBars + 64 + G::NBUF * G::G_SET + (LAST ? 0u : G::STG_ALL);
   if (G::STATIONARY) {
     if (fixed + G::W_ALL + 2 * slab_set > kRbSmemBudget) return cudaErrorNotSupported;
     rt.nSlab = (int)((kRbSmemBudget - fixed - G::W_ALL) / slab_set);
@@ -767,7 +772,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
     // 1.1 k cycles per tile with 6 slabs against ~0.4 k of tensor work; use all 8 barrier slots)
     static int want_env = -1;
     if (want_env < 0) { const char* e = getenv("VITSB_RB_NSLAB"); want_env = e ? atoi(e) : 0; }
-    const int want = want_env > 0 ? (want_env > 8 ? 8 : want_env) : (G::RES_GLOBAL ? 4 : 8);
+    const int want = want_env > 0 ? (want_env > kRbMaxSlab ? kRbMaxSlab : want_env) : (G::RES_GLOBAL ? 4 : G::NBUF + 4);
     if (rt.nSlab > want) rt.nSlab = want;
   } else {
     // streamed weights: slabs first (2 when the accumulators are double-buffered), the rest to the ring
@@ -819,7 +824,7 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   }
   if (!ok) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", C, KT); return cudaErrorInvalidValue; }
   const size_t wbytes = G::STATIONARY ? (size_t)G::W_ALL : (size_t)rt.nW * G::W_SLOT;
-  const size_t smem = 1024 + (size_t)rt.nSlab * slab_set + (size_t)G::NBUF * G::G_SET + wbytes + (LAST ? 0u : G::STG_ALL) + 8 * 57 + 64;
+  const size_t smem = 1024 + (size_t)rt.nSlab * slab_set + (size_t)G::NBUF * G::G_SET + wbytes + (LAST ? 0u : G::STG_ALL) + 8 * kRbBars + 64;
   static int num_sms = 0;
   static std::once_flag once;     // one flag per template instantiation
   static cudaError_t attr_err = cudaSuccess;
