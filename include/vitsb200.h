@@ -120,6 +120,13 @@ int vitsb_synthesize(vitsb_handle* h, const float* z_p, const float* g, const in
                      int B, int T_max, int ragged, float* z_out, float* wav,
                      void* ws, size_t ws_bytes, vitsb_stream stream);
 
+/* Replaces: the head of SynthesizerTrn.infer_p2 (models.py:570-572) - the two length-regulation matmuls and the
+ * noise FMA - as one gather/FMA kernel.  attn is the duration path of commons.generate_path
+ * (commons.py:143-155); zero weights are skipped, any other weights are summed like the matmul.
+ *   attn : device fp32 [B, T, Tx];  m_p, s_p : device fp32 [B, inter, Tx];  noise, z_p : device fp32 [B, inter, T]. */
+int vitsb_length_regulate(vitsb_handle* h, const float* attn, const float* m_p, const float* s_p, const float* noise,
+                          int B, int T, int Tx, float* z_p, vitsb_stream stream);
+
 /* Introspection for tests and bench.py. */
 int vitsb_total_upsample(const vitsb_handle* h);
 /* Number of kernels one vitsb_synthesize call launches for (B, T_max). */

@@ -266,3 +266,23 @@ def test_alternative_launch_plans_agree(base_cfg, base_sd, env):
     assert (w_alt - w_def).abs().max().item() <= TOL_WAV["fp16"]
     for b, L in enumerate(lens):
         assert w_alt[b, 0, L * 192:].abs().sum().item() == 0
+
+
+def test_length_regulate_matches_reference_matmuls(base_cfg, base_sd):
+    """the head of infer_p2 (models.py:570-572).  On a 0/1 duration path the gather kernel is
+    bit-identical to the reference's two fp32 matmuls + noise FMA; on an arbitrary attn it is the same weighted sum."""
+    eng = engine(base_cfg, base_sd, "fp32")
+    for T, seed in ((33, 1234), (417, 7), (1, 3)):
+        inp = FX.make_p2_inputs(base_cfg, T, seed=seed)
+        ref = O.length_regulate(inp["attn"], inp["m_p"], inp["s_p"], inp["noise"])
+        z = eng.length_regulate(inp["attn"].cuda(), inp["m_p"].cuda(), inp["s_p"].cuda(), inp["noise"].cuda()).cpu()
+        assert torch.equal(z, ref)
+    g = torch.Generator().manual_seed(5)
+    B, Ty, Tx, C = 3, 70, 45, base_cfg.inter_channels
+    attn = torch.rand(B, Ty, Tx, generator=g) * (torch.rand(B, Ty, Tx, generator=g) < 0.2)
+    m_p, s_p, noise = (torch.randn(B, C, n, generator=g) for n in (Tx, Tx, Ty))
+    ref = O.length_regulate(attn, m_p, s_p, noise)
+    z = eng.length_regulate(attn.cuda(), m_p.cuda(), s_p.cuda(), noise.cuda()).cpu()
+    assert (z - ref).abs().max().item() <= 1e-5
+    with pytest.raises(ValueError):
+        eng.length_regulate(attn.cuda(), m_p[:, :10].cuda(), s_p[:, :10].cuda(), noise.cuda())

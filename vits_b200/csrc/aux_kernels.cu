@@ -71,6 +71,74 @@ cudaError_t launch_unpack_channel_major(const float* src, int B, int C, int T, f
 }
 
 // ---------------------------------------------------------------------------
+// Head of infer_p2 (models.py:570-572): z_p = attn @ m_p^T + noise * (attn @ s_p^T).
+// attn is the duration path (0/1, one source position per frame, commons.py:143-155), so the two matmuls are a
+// gather; the kernel keeps the general weighted sum but skips zero weights, which makes a 0/1 path exact
+// (1.0 * x plus exact zeros) and bit-identical to the reference's fp32 matmuls.  Tile: 32 frames x 64 channels per
+// block, source positions in chunks of 32 staged through shared memory (all global accesses coalesced).
+//   attn [B][T][Tx], m_p / s_p [B][C][Tx], noise / z_p [B][C][T]   (reference layouts)
+// ---------------------------------------------------------------------------
+constexpr int kLrT = 32, kLrC = 64, kLrX = 32;
+__global__ void __launch_bounds__(256)
+length_regulate_kernel(const float* __restrict__ attn, const float* __restrict__ m_p, const float* __restrict__ s_p,
+                       const float* __restrict__ noise, int C, int T, int Tx, float* __restrict__ z_p) {
+  __shared__ float sa[kLrT][kLrX + 1];
+  __shared__ float sm[kLrX][kLrC + 1];
+  __shared__ float ss[kLrX][kLrC + 1];
+  const int b = blockIdx.z, t0 = blockIdx.x * kLrT, c0 = blockIdx.y * kLrC;
+  const int tl = threadIdx.x & 31, cg = threadIdx.x >> 5;          // frame of this thread, group of 8 channels
+  float m[8], sv[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) m[i] = sv[i] = 0.f;
+  const float* A = attn + (long long)b * T * Tx;
+  const float* M = m_p + (long long)b * C * Tx;
+  const float* S = s_p + (long long)b * C * Tx;
+  for (int x0 = 0; x0 < Tx; x0 += kLrX) {
+    for (int i = threadIdx.x; i < kLrT * kLrX; i += 256) {
+      const int r = i / kLrX, x = i - r * kLrX;
+      sa[r][x] = (t0 + r < T && x0 + x < Tx) ? A[(long long)(t0 + r) * Tx + x0 + x] : 0.f;
+    }
+    for (int i = threadIdx.x; i < kLrC * kLrX; i += 256) {
+      const int c = i / kLrX, x = i - c * kLrX;
+      const bool ok = c0 + c < C && x0 + x < Tx;
+      sm[x][c] = ok ? M[(long long)(c0 + c) * Tx + x0 + x] : 0.f;
+      ss[x][c] = ok ? S[(long long)(c0 + c) * Tx + x0 + x] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll 4
+    for (int x = 0; x < kLrX; ++x) {
+      const float a = sa[tl][x];
+      if (a != 0.f) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          m[i] = fmaf(a, sm[x][cg * 8 + i], m[i]);
+          sv[i] = fmaf(a, ss[x][cg * 8 + i], sv[i]);
+        }
+      }
+    }
+    __syncthreads();
+  }
+  const int t = t0 + tl;
+  if (t < T) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = c0 + cg * 8 + i;
+      if (c < C) {
+        const long long o = ((long long)b * C + c) * T + t;
+        z_p[o] = __fadd_rn(m[i], __fmul_rn(noise[o], sv[i]));     // m + noise * s, two roundings like the reference
+      }
+    }
+  }
+}
+
+cudaError_t launch_length_regulate(const float* attn, const float* m_p, const float* s_p, const float* noise,
+                                   int B, int C, int T, int Tx, float* z_p, cudaStream_t stream) {
+  dim3 grid(ceil_div(T, kLrT), ceil_div(C, kLrC), B);
+  length_regulate_kernel<<<grid, 256, 0, stream>>>(attn, m_p, s_p, noise, C, T, Tx, z_p);
+  return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------------------
 // conditioning GEMV: one warp per output row n, all batch rows per pass of W
 // (W is read once per call: 12.5k x 1024 fp32 at base config)
 // ---------------------------------------------------------------------------

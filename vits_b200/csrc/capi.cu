@@ -67,6 +67,19 @@ int vitsb_synthesize(vitsb_handle* h, const float* z_p, const float* g, const in
                     (cudaStream_t)stream, false, nullptr);
 }
 
+int vitsb_length_regulate(vitsb_handle* h, const float* attn, const float* m_p, const float* s_p, const float* noise,
+                          int B, int T, int Tx, float* z_p, vitsb_stream stream) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  if (!attn || !m_p || !s_p || !noise || !z_p) return h->eng.fail(VITSB_ERR_BAD_ARG, "null pointer");
+  if (B < 1 || T < 1 || Tx < 1) return h->eng.fail(VITSB_ERR_BAD_ARG, "B, T and Tx must be >= 1");
+  if (B > 65535) return h->eng.fail(VITSB_ERR_BAD_ARG, "B too large");
+  cudaError_t e = cudaSetDevice(h->eng.device);
+  if (e == cudaSuccess)
+    e = vitsb::launch_length_regulate(attn, m_p, s_p, noise, B, h->eng.cfg.inter_channels, T, Tx, z_p, (cudaStream_t)stream);
+  if (e != cudaSuccess) return h->eng.fail(VITSB_ERR_CUDA, std::string("length_regulate: ") + cudaGetErrorString(e));
+  return VITSB_OK;
+}
+
 int vitsb_total_upsample(const vitsb_handle* h) { return h ? h->eng.up_total : 0; }
 
 int vitsb_launches_per_call(const vitsb_handle* h, int B, int T_max) {

@@ -65,6 +65,9 @@ cudaError_t launch_cond_gemv(const float* W, const float* bias, const float* g, 
 cudaError_t launch_conv_post(const float* in, int B, int L, int C, int k, float slope, const float* w,
                              const int* len, int len_mul, float* wav, cudaStream_t stream);
 
+// head of infer_p2 (models.py:570-572): z_p[B][C][T] = attn @ m_p^T + noise * (attn @ s_p^T), reference layouts, fp32
+cudaError_t launch_length_regulate(const float* attn, const float* m_p, const float* s_p, const float* noise,
+                                   int B, int C, int T, int Tx, float* z_p, cudaStream_t stream);
 // MRF average over the branches' final 16-bit y streams -> next upsampler operand rows (16-bit paths)
 cudaError_t launch_mrf_sum(const void* y0, const void* y1, const void* y2, int B, int L, int C, const int* len, int len_mul,
                            float scale, float slope, void* out, int split, int op, cudaStream_t stream);

@@ -179,15 +179,26 @@ class FlowDecoder:
         return (wav, z) if return_z else wav
 
     @torch.no_grad()
-    def infer_p2(self, attn, m_p, s_p, g, noise) -> torch.Tensor:
-        """SynthesizerTrn.infer_p2 (models.py:568-575).  The length-regulation
-        matmuls stay in PyTorch (north star: they hand their tensors across)."""
+    def length_regulate(self, attn, m_p, s_p, noise) -> torch.Tensor:
+        """Head of SynthesizerTrn.infer_p2 (models.py:570-572): z_p = attn @ m_p^T + noise * (attn @ s_p^T) as one
+        gather/FMA kernel.  attn [B,Ty,Tx], m_p/s_p [B,inter,Tx], noise [B,inter,Ty] -> z_p [B,inter,Ty]."""
         dev = self.device
-        attn, m_p, s_p, noise = (t.to(dev, torch.float32) for t in (attn, m_p, s_p, noise))
-        m = torch.matmul(attn, m_p.transpose(1, 2)).transpose(1, 2)
-        s = torch.matmul(attn, s_p.transpose(1, 2)).transpose(1, 2)
-        z_p = m + noise * s
-        return self.synthesize(z_p, g)
+        attn, m_p, s_p, noise = (t.to(dev, torch.float32).contiguous() for t in (attn, m_p, s_p, noise))
+        if attn.dim() != 3 or m_p.dim() != 3 or tuple(s_p.shape) != tuple(m_p.shape):
+            raise ValueError("expected attn [B,Ty,Tx] and m_p, s_p [B,inter,Tx]")
+        B, Ty, Tx = attn.shape
+        if tuple(m_p.shape) != (B, self.inter_channels, Tx) or tuple(noise.shape) != (B, self.inter_channels, Ty):
+            raise ValueError(f"shape mismatch: attn {tuple(attn.shape)}, m_p {tuple(m_p.shape)}, noise {tuple(noise.shape)}")
+        with torch.cuda.device(dev):
+            z_p = torch.empty_like(noise)
+            self._check(self.lib.vitsb_length_regulate(self._h, attn.data_ptr(), m_p.data_ptr(), s_p.data_ptr(), noise.data_ptr(),
+                                                       B, Ty, Tx, z_p.data_ptr(), self._stream()))
+        return z_p
+
+    @torch.no_grad()
+    def infer_p2(self, attn, m_p, s_p, g, noise) -> torch.Tensor:
+        """SynthesizerTrn.infer_p2 (models.py:568-575): length regulation, reverse flow, decoder - all on the CUDA path."""
+        return self.synthesize(self.length_regulate(attn, m_p, s_p, noise), g)
 
     @torch.no_grad()
     def synthesize_host(self, z_p_host: torch.Tensor, g_host: torch.Tensor, lengths: Sequence[int],
