@@ -120,6 +120,14 @@ int vitsb_synthesize(vitsb_handle* h, const float* z_p, const float* g, const in
                      int B, int T_max, int ragged, float* z_out, float* wav,
                      void* ws, size_t ws_bytes, vitsb_stream stream);
 
+/* vitsb_synthesize with the serving path's output post-processing fused into the last kernel:
+ * pcm = int16(clip(wav * volume * 32767, -32768, 32767)), float32 products, truncation toward zero, exactly
+ * VITSWrap.speaking's np.clip(...).astype(np.int16) (vits_wrap.py:195) on infer.py:182's float waveform.
+ *   pcm : device int16 [B, 1, T_max*prod(upsample_rates)], zero beyond len[b] when ragged. */
+int vitsb_synthesize_pcm16(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len,
+                           int B, int T_max, int ragged, float volume, int16_t* pcm,
+                           void* ws, size_t ws_bytes, vitsb_stream stream);
+
 /* Replaces: the head of SynthesizerTrn.infer_p2 (models.py:570-572) - the two length-regulation matmuls and the
  * noise FMA - as one gather/FMA kernel.  attn is the duration path of commons.generate_path
  * (commons.py:143-155); zero weights are skipped, any other weights are summed like the matmul.

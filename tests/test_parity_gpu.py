@@ -286,3 +286,38 @@ def test_length_regulate_matches_reference_matmuls(base_cfg, base_sd):
     assert (z - ref).abs().max().item() <= 1e-5
     with pytest.raises(ValueError):
         eng.length_regulate(attn.cuda(), m_p[:, :10].cuda(), s_p[:, :10].cuda(), noise.cuda())
+
+
+def test_c4_batch64_rows_independent(base_cfg, base_sd):
+    """BASELINE config 4 (batch 64-512 utterances, sharded by utterance): a 64-row ragged call (short rows so that
+    the test stays fast) equals the per-row B=1 calls bit for bit, stays within tolerance of the fp32 build and
+    stores zeros beyond every row's length; larger batches are the same launch plan with more tiles."""
+    lens = FX.make_lengths(64, 8, 90, seed=64)
+    lat = FX.make_latents(base_cfg, lens, seed=64)
+    zp, g = lat["z_p"].cuda(), lat["g"].cuda()
+    e16, e32 = engine(base_cfg, base_sd, "fp16"), engine(base_cfg, base_sd, "fp32")
+    w16 = e16.synthesize(zp, g, lens, ragged=True)
+    w32 = e32.synthesize(zp, g, lens, ragged=True)
+    assert (w16 - w32).abs().max().item() <= TOL_WAV["fp16"]
+    for b in (0, 17, 40, 63):
+        L = lens[b]
+        wb = e16.synthesize(zp[b:b + 1, :, :L].contiguous(), g[b:b + 1])
+        assert torch.equal(wb[0, 0], w16[b, 0, :L * 192])
+        assert w16[b, 0, L * 192:].abs().sum().item() == 0
+
+
+@pytest.mark.parametrize("prec", ["fp16", "fp32"])
+def test_pcm16_output_matches_reference_postprocessing(base_cfg, base_sd, prec):
+    """int16 output written by the last kernel == np.clip(wav * volume * 32767, -32768, 32767)
+    .astype(np.int16) (vits_wrap.py:195) applied to the same call's float waveform, bit for bit."""
+    eng = engine(base_cfg, base_sd, prec)
+    lens = [50, 21, 64]
+    lat = FX.make_latents(base_cfg, lens, seed=909)
+    zp, g = lat["z_p"].cuda(), lat["g"].cuda()
+    wav = eng.synthesize(zp, g, lens).cpu().numpy()
+    for volume in (1.0, 0.7, 3.0):                      # 3.0 clips
+        pcm = eng.synthesize_pcm16(zp, g, lens, volume=volume).cpu().numpy()
+        ref = np.clip(wav * volume * 32767, -32768, 32767).astype(np.int16)
+        assert pcm.dtype == np.int16 and pcm.shape == ref.shape
+        assert np.array_equal(pcm, ref)
+    assert np.abs(pcm).max() == 32767

@@ -279,10 +279,18 @@ cudaError_t launch_mrf_sum(const void* y0, const void* y1, const void* y2, int B
 // 16 bits: conv_post sits right before the output and its input rounding would
 // be the single largest error term) and writes one fp32 sample per position.
 // ---------------------------------------------------------------------------
+// Output post-processing of the serving path fused into the last kernel (vits_wrap.py:195:
+// np.clip(wav * volume * 32767, -32768, 32767).astype(np.int16) - float32 products, truncation toward zero)
+__device__ __forceinline__ short to_pcm16(float w, float volume) {
+  float v = __fmul_rn(__fmul_rn(w, volume), 32767.f);
+  v = fminf(fmaxf(v, -32768.f), 32767.f);
+  return (short)__float2int_rz(v);
+}
+
 constexpr int kPostTile = 256;
 __global__ void __launch_bounds__(kPostTile)
 conv_post_kernel(const float* __restrict__ in, int L, int C, int k, float slope, const float* __restrict__ w,
-                 const int* __restrict__ len, int len_mul, float* __restrict__ wav) {
+                 const int* __restrict__ len, int len_mul, float* __restrict__ wav, short* __restrict__ pcm, float volume) {
   extern __shared__ float sm[];
   const int pad = (k - 1) / 2;
   const int rows = kPostTile + k - 1;
@@ -293,7 +301,7 @@ conv_post_kernel(const float* __restrict__ in, int L, int C, int k, float slope,
   const int valid = len ? len[b] * len_mul : L;
   if (t0 >= valid) {                           // fully masked tile: write zeros
     int t = t0 + threadIdx.x;
-    if (t < L) wav[(long long)b * L + t] = 0.f;
+    if (t < L) { if (pcm) pcm[(long long)b * L + t] = 0; else wav[(long long)b * L + t] = 0.f; }
     return;
   }
   const float* src = in + (long long)b * L * C;
@@ -313,7 +321,8 @@ conv_post_kernel(const float* __restrict__ in, int L, int C, int k, float slope,
 #pragma unroll 8
     for (int c = 0; c < C; ++c) acc = fmaf(row[c], wj[c], acc);
   }
-  wav[(long long)b * L + t] = t < valid ? tanhf(acc) : 0.f;
+  const float o = t < valid ? tanhf(acc) : 0.f;
+  if (pcm) pcm[(long long)b * L + t] = to_pcm16(o, volume); else wav[(long long)b * L + t] = o;
 }
 
 // Fast path for the base shape (C = 32, k = 7, L % 4 == 0): 64 threads x 4 consecutive outputs.  The generic
@@ -328,7 +337,8 @@ constexpr int kPost4Out = 4, kPost4Threads = 64, kPost4Tile = kPost4Out * kPost4
 template <int C, int K, typename YT>
 __global__ void __launch_bounds__(kPost4Threads)
 conv_post4_kernel(const YT* __restrict__ in, const YT* __restrict__ in1, const YT* __restrict__ in2, float scale, int L, float slope,
-                  const float* __restrict__ w, const int* __restrict__ len, int len_mul, float* __restrict__ wav) {
+                  const float* __restrict__ w, const int* __restrict__ len, int len_mul, float* __restrict__ wav,
+                  short* __restrict__ pcm, float volume) {
   constexpr int C4 = C / 4, ROWS = kPost4Tile + K - 1, PAD = (K - 1) / 2;
   static_assert(C4 == 8, "swizzle assumes 8 float4 per row");
   __shared__ float4 tile[ROWS * C4];
@@ -337,7 +347,10 @@ conv_post4_kernel(const YT* __restrict__ in, const YT* __restrict__ in1, const Y
   const int valid = len ? len[b] * len_mul : L;
   const int t = t0 + threadIdx.x * kPost4Out;
   if (t0 >= valid) {                           // fully masked tile: write zeros
-    if (t < L) *reinterpret_cast<float4*>(wav + (long long)b * L + t) = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (t < L) {
+      if (pcm) *reinterpret_cast<short4*>(pcm + (long long)b * L + t) = make_short4(0, 0, 0, 0);
+      else *reinterpret_cast<float4*>(wav + (long long)b * L + t) = make_float4(0.f, 0.f, 0.f, 0.f);
+    }
     return;
   }
   if constexpr (sizeof(YT) == 4) {
@@ -405,34 +418,37 @@ conv_post4_kernel(const YT* __restrict__ in, const YT* __restrict__ in1, const Y
   float4 o4;
   o4.x = t < valid ? tanhf(acc[0]) : 0.f;     o4.y = t + 1 < valid ? tanhf(acc[1]) : 0.f;
   o4.z = t + 2 < valid ? tanhf(acc[2]) : 0.f; o4.w = t + 3 < valid ? tanhf(acc[3]) : 0.f;
-  *reinterpret_cast<float4*>(wav + (long long)b * L + t) = o4;
+  if (pcm) *reinterpret_cast<short4*>(pcm + (long long)b * L + t) =
+      make_short4(to_pcm16(o4.x, volume), to_pcm16(o4.y, volume), to_pcm16(o4.z, volume), to_pcm16(o4.w, volume));
+  else *reinterpret_cast<float4*>(wav + (long long)b * L + t) = o4;
 }
 
 cudaError_t launch_conv_post(const float* in, int B, int L, int C, int k, float slope, const float* w,
-                             const int* len, int len_mul, float* wav, cudaStream_t stream) {
+                             const int* len, int len_mul, float* wav, short* pcm, float volume, cudaStream_t stream) {
   if (C == 32 && k == 7 && L % 4 == 0) {
     dim3 grid4(ceil_div(L, kPost4Tile), B);
-    conv_post4_kernel<32, 7, float><<<grid4, kPost4Threads, 0, stream>>>(in, nullptr, nullptr, 1.f, L, slope, w, len, len_mul, wav);
+    conv_post4_kernel<32, 7, float><<<grid4, kPost4Threads, 0, stream>>>(in, nullptr, nullptr, 1.f, L, slope, w, len, len_mul, wav, pcm, volume);
     return cudaGetLastError();
   }
   dim3 grid(ceil_div(L, kPostTile), B);
   size_t smem = (size_t)((kPostTile + k - 1) * (C + 1) + k * C) * sizeof(float);
-  conv_post_kernel<<<grid, kPostTile, smem, stream>>>(in, L, C, k, slope, w, len, len_mul, wav);
+  conv_post_kernel<<<grid, kPostTile, smem, stream>>>(in, L, C, k, slope, w, len, len_mul, wav, pcm, volume);
   return cudaGetLastError();
 }
 
 bool conv_post_y_supported(int C, int k, int L) { return C == 32 && k == 7 && L % 4 == 0; }
 
 cudaError_t launch_conv_post_y(const void* y0, const void* y1, const void* y2, float scale, int B, int L, int C, int k, float slope,
-                               const float* w, const int* len, int len_mul, float* wav, int op, cudaStream_t stream) {
+                               const float* w, const int* len, int len_mul, float* wav, short* pcm, float volume, int op,
+                               cudaStream_t stream) {
   if (op == OP_F32 || !conv_post_y_supported(C, k, L) || !y0) return cudaErrorNotSupported;
   dim3 grid4(ceil_div(L, kPost4Tile), B);
   if (op == OP_F16)
     conv_post4_kernel<32, 7, __half><<<grid4, kPost4Threads, 0, stream>>>((const __half*)y0, (const __half*)y1, (const __half*)y2, scale, L, slope,
-                                                                          w, len, len_mul, wav);
+                                                                          w, len, len_mul, wav, pcm, volume);
   else
     conv_post4_kernel<32, 7, __nv_bfloat16><<<grid4, kPost4Threads, 0, stream>>>((const __nv_bfloat16*)y0, (const __nv_bfloat16*)y1,
-                                                                                 (const __nv_bfloat16*)y2, scale, L, slope, w, len, len_mul, wav);
+                                                                                 (const __nv_bfloat16*)y2, scale, L, slope, w, len, len_mul, wav, pcm, volume);
   return cudaGetLastError();
 }
 

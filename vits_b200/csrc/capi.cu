@@ -67,6 +67,19 @@ int vitsb_synthesize(vitsb_handle* h, const float* z_p, const float* g, const in
                     (cudaStream_t)stream, false, nullptr);
 }
 
+int vitsb_synthesize_pcm16(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len, int B, int T_max, int ragged,
+                           float volume, int16_t* pcm, void* ws, size_t ws_bytes, vitsb_stream stream) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  if (!pcm) return h->eng.fail(VITSB_ERR_BAD_ARG, "null pcm");
+  h->eng.pcm_out = reinterpret_cast<short*>(pcm);
+  h->eng.pcm_volume = volume;
+  const int rc = h->eng.run(Engine::RUN_FLOW | Engine::RUN_DEC, z_p, g, len, B, T_max, ragged, nullptr, nullptr, ws, ws_bytes,
+                            (cudaStream_t)stream, false, nullptr);
+  h->eng.pcm_out = nullptr;
+  h->eng.pcm_volume = 1.f;
+  return rc;
+}
+
 int vitsb_length_regulate(vitsb_handle* h, const float* attn, const float* m_p, const float* s_p, const float* noise,
                           int B, int T, int Tx, float* z_p, vitsb_stream stream) {
   if (!h) return VITSB_ERR_BAD_ARG;

@@ -74,6 +74,11 @@ struct Engine {
   float* d_condB = nullptr;
   float* d_post = nullptr;
 
+  // output form of the current call (set by the C entry point): int16 PCM with the serving path's volume scaling
+  // (vits_wrap.py:195) written by conv_post instead of the fp32 waveform
+  short* pcm_out = nullptr;
+  float pcm_volume = 1.f;
+
   // optional per-launch timing (cudaEvent pairs around every launch, read back after a sync)
   bool profile = false;
   struct ProfRow { double ms = 0; long long launches = 0; double flops = 0; };

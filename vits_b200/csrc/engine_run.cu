@@ -157,7 +157,7 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
   if (!dry) {
     if (!loaded) return fail(VITSB_ERR_WEIGHTS, "weights not loaded");
     if (!z_in || !g || !ws) return fail(VITSB_ERR_BAD_ARG, "null pointer");
-    if ((what & RUN_DEC) && !wav) return fail(VITSB_ERR_BAD_ARG, "null wav");
+    if ((what & RUN_DEC) && !wav && !pcm_out) return fail(VITSB_ERR_BAD_ARG, "null wav");
   }
   if (B < 1 || T < 1) return fail(VITSB_ERR_BAD_ARG, "B and T_max must be >= 1");
   if ((long long)T * up_total > 0x7fffffffLL / 64) return fail(VITSB_ERR_BAD_ARG, "T_max too large");
@@ -346,9 +346,9 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
     if (post_from_y) {
       const int nk = (int)stages.back().rb.size();
       AUX_LAUNCH(T_POST, launch_conv_post_y(P(W.xin_f), nk > 1 ? P(W.xb_f) : nullptr, nk > 2 ? P(W.acc_f) : nullptr, 1.0f / nk, B, L, post_C,
-                                            post_k, 0.01f, d_post, cx.len_dec, mul, wav, op, stream));
+                                            post_k, 0.01f, d_post, cx.len_dec, mul, wav, pcm_out, pcm_volume, op, stream));
     } else {
-      AUX_LAUNCH(T_POST, launch_conv_post(F(W.acc_f), B, L, post_C, post_k, 0.01f, d_post, cx.len_dec, mul, wav, stream));
+      AUX_LAUNCH(T_POST, launch_conv_post(F(W.acc_f), B, L, post_C, post_k, 0.01f, d_post, cx.len_dec, mul, wav, pcm_out, pcm_volume, stream));
     }
   }
 #undef AUX_LAUNCH

@@ -62,8 +62,9 @@ cudaError_t launch_unpack_channel_major(const float* src, int B, int C, int T, f
 cudaError_t launch_cond_gemv(const float* W, const float* bias, const float* g, int B, int Ncond, int gin,
                              float* out, cudaStream_t stream);
 // leaky_relu + conv_post + tanh: in = fp32 [B][L][C], w fp32 [k][C], out fp32 [B][L]
+// pcm != nullptr: write int16 clip(wav * volume * 32767) there instead of the fp32 waveform (vits_wrap.py:195)
 cudaError_t launch_conv_post(const float* in, int B, int L, int C, int k, float slope, const float* w,
-                             const int* len, int len_mul, float* wav, cudaStream_t stream);
+                             const int* len, int len_mul, float* wav, short* pcm, float volume, cudaStream_t stream);
 
 // head of infer_p2 (models.py:570-572): z_p[B][C][T] = attn @ m_p^T + noise * (attn @ s_p^T), reference layouts, fp32
 cudaError_t launch_length_regulate(const float* attn, const float* m_p, const float* s_p, const float* noise,
@@ -74,6 +75,7 @@ cudaError_t launch_mrf_sum(const void* y0, const void* y1, const void* y2, int B
 // conv_post whose input is the MRF average of up to three y streams, formed in the tile load (base shape only)
 bool conv_post_y_supported(int C, int k, int L);
 cudaError_t launch_conv_post_y(const void* y0, const void* y1, const void* y2, float scale, int B, int L, int C, int k, float slope,
-                               const float* w, const int* len, int len_mul, float* wav, int op, cudaStream_t stream);
+                               const float* w, const int* len, int len_mul, float* wav, short* pcm, float volume, int op,
+                               cudaStream_t stream);
 
 }  // namespace vitsb

@@ -179,6 +179,19 @@ class FlowDecoder:
         return (wav, z) if return_z else wav
 
     @torch.no_grad()
+    def synthesize_pcm16(self, z_p: torch.Tensor, g: torch.Tensor, lengths: Optional[Sequence[int]] = None,
+                         ragged: bool = True, volume: float = 1.0) -> torch.Tensor:
+        """synthesize() + VITSWrap.speaking's output step (vits_wrap.py:195) in the last kernel: int16 [B,1,192*T] =
+        clip(wav * volume * 32767, -32768, 32767) truncated toward zero; half the D2H bytes."""
+        z_p, g, lens, B, T = self._prep(z_p, g, lengths)
+        with torch.cuda.device(self.device):
+            ws = self._workspace(B, T)
+            pcm = torch.empty(B, 1, T * self.total_upsample, dtype=torch.int16, device=self.device)
+            self._check(self.lib.vitsb_synthesize_pcm16(self._h, z_p.data_ptr(), g.data_ptr(), lens, B, T, int(bool(ragged)),
+                                                        float(volume), pcm.data_ptr(), ws.data_ptr(), ws.numel(), self._stream()))
+        return pcm
+
+    @torch.no_grad()
     def length_regulate(self, attn, m_p, s_p, noise) -> torch.Tensor:
         """Head of SynthesizerTrn.infer_p2 (models.py:570-572): z_p = attn @ m_p^T + noise * (attn @ s_p^T) as one
         gather/FMA kernel.  attn [B,Ty,Tx], m_p/s_p [B,inter,Tx], noise [B,inter,Ty] -> z_p [B,inter,Ty]."""

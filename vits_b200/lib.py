@@ -46,6 +46,8 @@ SYMBOLS = {
     "vitsb_decode": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, _P, _P, C.c_size_t, _P]),
     "vitsb_synthesize": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, _P, _P, _P,
                                    C.c_size_t, _P]),
+    "vitsb_synthesize_pcm16": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_float, _P, _P,
+                                         C.c_size_t, _P]),
     "vitsb_length_regulate": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P]),
     "vitsb_total_upsample": (C.c_int, [_P]),
     "vitsb_launches_per_call": (C.c_int, [_P, C.c_int, C.c_int]),
