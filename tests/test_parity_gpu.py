@@ -321,3 +321,22 @@ def test_pcm16_output_matches_reference_postprocessing(base_cfg, base_sd, prec):
         assert pcm.dtype == np.int16 and pcm.shape == ref.shape
         assert np.array_equal(pcm, ref)
     assert np.abs(pcm).max() == 32767
+
+
+def test_synthesize_segments_equals_sequential_calls(base_cfg, base_sd):
+    """the serving loop's sequential per-segment calls (vits_wrap.py:177-183) as ragged batches -
+    same waveforms bit for bit, original order, whatever the batch split."""
+    eng = engine(base_cfg, base_sd, "fp16")
+    lens = [33, 120, 7, 64, 90, 15, 1]
+    segs = []
+    for i, T in enumerate(lens):
+        lat = FX.make_latents(base_cfg, [T], seed=700 + i)
+        segs.append((lat["z_p"].cuda(), lat["g"].cuda()))
+    ref = [eng.synthesize(z, g) for z, g in segs]
+    for kw in ({}, {"max_batch": 3}, {"max_batch_frames": 200}):
+        got = eng.synthesize_segments(segs, **kw)
+        assert len(got) == len(ref)
+        for a, b in zip(got, ref):
+            assert a.shape == b.shape and torch.equal(a, b)
+    with pytest.raises(ValueError):
+        eng.synthesize_segments([(segs[0][0][:, :10], segs[0][1])])

@@ -8,6 +8,7 @@ emotional-vits/):
   decode(z, g, lengths, ragged)   Generator.forward                                          models.py:306-318
   infer_p2(attn, m_p, s_p, g, noise)  SynthesizerTrn.infer_p2                                models.py:568-575
   synthesize(z_p, g, lengths, ragged) tail of infer_p2 / inference                           models.py:533-534,573-574
+  synthesize_segments(segments)   the per-segment loop of VITSWrap.speaking as ragged batches  vits_wrap.py:177-183
 
 PyTorch is plumbing here (device memory, streams); every FLOP of the path runs
 in libvitsb200.so.  There is no CPU fallback: constructing a FlowDecoder
@@ -227,6 +228,42 @@ class FlowDecoder:
             out_host.copy_(wav, non_blocking=True)
             torch.cuda.current_stream(self.device).synchronize()
         return out_host
+
+    @torch.no_grad()
+    def synthesize_segments(self, segments: Sequence[Sequence[torch.Tensor]], max_batch_frames: int = 16384,
+                            max_batch: int = 64) -> list:
+        """Batched form of the serving loop's per-segment calls (`VITSWrap.speaking` runs the segments of a request one
+        after the other, vits_wrap.py:177-183).  `segments` is a list of (z_p [1,inter,T_i] or
+        [inter,T_i], g [1,gin] or [gin]); they are sorted by length, packed into ragged batches of at most `max_batch`
+        rows and `max_batch_frames` padded frames (B * T_max: bounds the workspace), and each batch is ONE synthesize
+        call.  Returns the waveforms [1,1,192*T_i] in the order of `segments`; by row independence of the ragged plan
+        every waveform is bit-identical to the B=1 call on that segment."""
+        items = []
+        for i, (z, g) in enumerate(segments):
+            z = z if z.dim() == 3 else z.unsqueeze(0)
+            g = g if g.dim() == 2 else g.reshape(1, -1)
+            if z.size(0) != 1 or z.size(1) != self.inter_channels or g.size(0) != 1:
+                raise ValueError(f"segment {i}: expected z_p [1,{self.inter_channels},T] and g [1,{self.gin_channels}]")
+            items.append((int(z.size(2)), i, z, g))
+        out = [None] * len(items)
+        order = sorted(items, key=lambda it: -it[0])
+        pos = 0
+        while pos < len(order):
+            T = order[pos][0]                                  # longest of the batch (descending order)
+            n = max(1, min(max_batch, max_batch_frames // max(T, 1), len(order) - pos))
+            batch = order[pos:pos + n]
+            zb = torch.zeros(n, self.inter_channels, T, dtype=torch.float32, device=self.device)
+            gb = torch.empty(n, self.gin_channels, dtype=torch.float32, device=self.device)
+            lens = []
+            for r, (Ti, _, z, g) in enumerate(batch):
+                zb[r, :, :Ti] = z[0].to(self.device, torch.float32)
+                gb[r] = g[0].to(self.device, torch.float32)
+                lens.append(Ti)
+            wav = self.synthesize(zb, gb, lens, ragged=True)
+            for r, (Ti, i, _, _) in enumerate(batch):
+                out[i] = wav[r:r + 1, :, :Ti * self.total_upsample].clone()
+            pos += n
+        return out
 
     def host_pipeline(self, B: int, T_max: int, depth: int = 2) -> "HostPipeline":
         """Serving loop for HOST buffers: see HostPipeline."""
