@@ -45,6 +45,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-sync", action="store_true", help="time e2e as one blocking synthesize_host call per step instead of the depth-2 host pipeline")
     ap.add_argument("--profile-out", default=None, help="write the per-launch-family table to this file")
+    ap.add_argument("--batch-per-gpu", type=int, default=PER_GPU_BATCH,
+                    help="utterances per GPU and step (default 16 = BASELINE config C2; 64-512 are C4 sweep points, not the headline)")
     return ap.parse_args()
 
 
@@ -315,7 +317,7 @@ def run_b200(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": {"fp16": "f16", "bf16": "bf16", "fp32": "f32"}[args.precision] + " operands, f32 accumulate",
             "data": "synthetic",
-            "config": {"workload": f"C2: emotional-vits base config, {PER_GPU_BATCH} mixed-length utterances per GPU "
+            "config": {"workload": f"{'C2' if PER_GPU_BATCH == 16 else 'C4 sweep point'}: emotional-vits base config, {PER_GPU_BATCH} mixed-length utterances per GPU "
                                    f"(1-10 s, ragged/masked), flow-reverse + Generator",
                        "global_batch": PER_GPU_BATCH * world, "valid_audio_s_per_step": audio_all,
                        "parallelism": f"utterance-sharded replicas x{world} (LPT), no collective",
@@ -354,7 +356,9 @@ def run_b200(args):
 
 
 def main():
+    global PER_GPU_BATCH
     args = parse()
+    PER_GPU_BATCH = args.batch_per_gpu
     if args.impl == "reference":
         run_reference(args)
     else:
