@@ -96,7 +96,12 @@ __device__ __forceinline__ void build_tile_prefix(int* prefix, int B, const int*
 // tcgen05.fence::after_thread_sync.
 template <typename OpT, typename WaitFn>
 __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& ep, int b, int t0, int ntile, int valid,
-                                            uint32_t tmem_acc, int q, int lane, int ugrp, int ngrp, WaitFn wait_acc) {
+                                            uint32_t tmem_acc, int q, int lane, int ugrp, int ngrp, WaitFn wait_acc, int dbg = 0) {
+#ifdef VITSB_RB_DEBUG
+#define TCE_DBG(m) ((dbg & (m)) != 0)      // timing ablations: 8 no global stores, 16 no bias / residual / accumulator loads, 32 no gate math
+#else
+#define TCE_DBG(m) (false)
+#endif
     const int row = q * 32 + lane;
     const int t = t0 + row;
     const bool in_range = t < a.L;
@@ -119,17 +124,20 @@ __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& e
         ptx::tmem_ld16(trow + g0 + c0, ra);
         ptx::tmem_ld16(trow + g0 + gh + c0, rb);
         float ba[16], bb[16], v[16];
-        load16(bias + g0 + c0, ba);
-        load16(bias + g0 + gh + c0, bb);
+        if (!TCE_DBG(16)) { load16(bias + g0 + c0, ba); load16(bias + g0 + gh + c0, bb); }
+        else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) ba[i] = bb[i] = 0.f;
+        }
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 16; ++i) {
           float xa = ep.alpha * (__uint_as_float(ra[i]) + ba[i]);
           float xb = ep.alpha * (__uint_as_float(rb[i]) + bb[i]);
-          v[i] = live ? gate_fn<false>(xa, xb) : 0.f;
+          v[i] = TCE_DBG(32) ? xa + xb : (live ? gate_fn<false>(xa, xb) : 0.f);
         }
         const int oc = (g0 >> 1) + c0;       // output column inside this tile's NT/2 gate channels
-        if (in_range) {
+        if (in_range && !TCE_DBG(8)) {
           if (ep.out_f32)
             store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + (long long)ntile * (a.NT >> 1) + oc, v);
           if (ep.out_op) store_op16<OpT>(reinterpret_cast<OpT*>(ep.out_op) + orow_op + oc, v, ep.out_slope, ep.out_op_split);
@@ -149,9 +157,14 @@ __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& e
         uint32_t r[16];
         ptx::tmem_ld16(trow + c0, r);
         float bv[16], v[16], rx[16], ax[16];
-        if (has_res) load16(res + c0, rx);
-        if (has_acc) load16(accum + c0, ax);
-        load16(bias + c0, bv);
+        if (!TCE_DBG(16)) {
+          if (has_res) load16(res + c0, rx);
+          if (has_acc) load16(accum + c0, ax);
+          load16(bias + c0, bv);
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) rx[i] = ax[i] = bv[i] = 0.f;
+        }
         ptx::tmem_ld_wait();
 #pragma unroll
         for (int i = 0; i < 16; ++i) v[i] = ep.alpha * (__uint_as_float(r[i]) + bv[i]);
@@ -167,7 +180,7 @@ __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& e
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] = 0.f;
         }
-        if (in_range) {
+        if (in_range && !TCE_DBG(8)) {
           if (ep.out_f32)
             store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + n0 + c0, v);
           if (ep.out_op)
