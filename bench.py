@@ -133,7 +133,8 @@ def cpu_oracle_run(lengths, budget_s: float, min_utts: int = 1):
     import torch
     from oracle import fixtures as FX
     from oracle import vits_oracle as O
-    cfg = O.HotPathConfig()
+    from vits_b200.config import HotPathConfig
+    cfg = HotPathConfig()
     sd = FX.make_state_dict(cfg, seed=1234)
     torch.set_num_threads(os.cpu_count() or 1)
     lat = FX.make_latents(cfg, lengths, seed=1234)
@@ -189,7 +190,7 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from oracle import fixtures as FX            # input/weight generator only (never on the timed path)
-    from oracle.vits_oracle import HotPathConfig
+    from vits_b200.config import HotPathConfig
     from vits_b200 import FlowDecoder
 
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -10,7 +10,14 @@
  *   - every function returns a vitsb_status (0 = ok); nothing throws across
  *     the ABI; vitsb_last_error(h) gives the message of the last failure.
  *   - the caller owns every input, output and workspace buffer.  The handle
- *     owns only packed weights.  Calls are asynchronous on `stream`.
+ *     owns the packed weights, its options, a small cache of instantiated CUDA
+ *     graphs (replay of the workspace-only launches of a repeated shape) and the
+ *     private stream those are captured on.  Calls are asynchronous on `stream`.
+ *   - threads: every entry point takes the handle's mutex, so a handle may be
+ *     shared between threads; calls on ONE handle are serialised on the host
+ *     (their device work is ordered by the streams passed in) and concurrent
+ *     calls must use distinct workspaces.  Use one handle per thread to issue
+ *     from several threads at once.
  *   - tensors at the seam use the reference's layout: channel-major
  *     [B, C, T] fp32, contiguous.  `len` is a HOST array of B valid frame
  *     counts (the reference has them on the host too: infer.py:171,
@@ -94,7 +101,21 @@ const char* vitsb_last_error(const vitsb_handle* h);   /* h may be NULL: last cr
  * uploads.  May be called again to swap checkpoints. */
 int vitsb_load_weights(vitsb_handle* h, const vitsb_tensor_desc* tensors, int n);
 
-/* Bytes of device workspace needed for a call with B rows of at most T_max frames. */
+/* Options: per handle, never read from the environment.  Keys (int values):
+ *   "cuda_graph" 0/1 (1)   replay the workspace-only launches of a repeated shape as a CUDA graph
+ *   "pdl" 0/1 (0)          programmatic dependent launch between the tensor-core kernels
+ *   "tc_pair" 0/1 (1)      CTA-pair (cta_group::2) mode of the generic conv kernel
+ *   "rb_nslab" 0..16 (0)   fused-ResBlock slab count override, 0 = automatic
+ *   "ws_cap_mb" (24576)    workspace cap; batches whose layout exceeds it run in row chunks
+ *   "rb_fused", "flow_fused", "flow_in_split" -1/0/1 (-1 = automatic): launch-plan / packing choices; they take
+ *       effect at the next vitsb_load_weights.
+ * vitsb_get_option also answers "plan.rb_fused", "plan.flow_fused", "plan.flow_in_split" (the plan in force). */
+int vitsb_set_option(vitsb_handle* h, const char* key, int value);
+int vitsb_get_option(const vitsb_handle* h, const char* key, int* value);
+
+/* Bytes of device workspace for a call with B rows of at most T_max frames (call after vitsb_load_weights).  Rows are
+ * independent, so any workspace of at least vitsb_workspace_bytes(h, 1, T_max) is accepted: a batch whose full layout
+ * does not fit the workspace handed in (or exceeds "ws_cap_mb" / 512 rows) is processed in row chunks. */
 size_t vitsb_workspace_bytes(const vitsb_handle* h, int B, int T_max);
 
 /* Replaces: ResidualCouplingBlock.infer(x, g, reverse=True) (models.py:228-235)
@@ -144,8 +165,8 @@ double vitsb_flop_per_frame(const vitsb_handle* h);
 /* Per-launch device timing for bench.py / profiling: while enabled every kernel
  * launch of a call is bracketed by CUDA events on the call's stream and the call
  * ends with a stream synchronisation.  vitsb_profile_read returns one row per
- * launch family (tag: 0 pack, 1 cond, 2 unpack, 3 conv_post, 10-14 flow
- * pre/in/res/skip/post, 20 conv_pre, 30+s ups, 40+s ResBlock c1, 50+s ResBlock c2
+ * launch family (tag: 0 pack, 1 cond, 2 unpack, 3 conv_post, 4 mrf_sum, 10-14 flow
+ * pre/in/res/skip/post (layer-at-a-time flow), 15 fused coupling layer, 20 conv_pre, 30+s ups, 40+s ResBlock c1, 50+s ResBlock c2
  * of stage s) with summed milliseconds, launch count and algorithmic FLOP. */
 int vitsb_profile(vitsb_handle* h, int enable);
 int vitsb_profile_read(const vitsb_handle* h, int32_t* tags, double* ms, int64_t* launches, double* flops, int cap);

@@ -17,7 +17,7 @@ from typing import Dict, List, Tuple
 
 import torch
 
-from .vits_oracle import HotPathConfig
+from vits_b200.config import HotPathConfig
 
 
 def hot_param_specs(cfg: HotPathConfig) -> List[Tuple[str, Tuple[int, ...], str, int]]:

@@ -45,7 +45,7 @@ def build_reference(cfgj, sd):
 
 def main():
     from oracle import fixtures as FX
-    from oracle.vits_oracle import HotPathConfig
+    from vits_b200.config import HotPathConfig
     os.makedirs(OUT, exist_ok=True)
     torch.manual_seed(0)
     torch.set_grad_enabled(False)

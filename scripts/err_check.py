@@ -5,7 +5,7 @@ import numpy as np
 import torch
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 from oracle import fixtures as FX
-from oracle.vits_oracle import HotPathConfig
+from vits_b200.config import HotPathConfig
 from oracle.logmel import log_mel_l1
 from vits_b200 import FlowDecoder
 

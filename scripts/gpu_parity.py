@@ -9,9 +9,10 @@ from oracle import fixtures as FX  # noqa: E402
 from oracle import vits_oracle as O  # noqa: E402
 from oracle.logmel import log_mel_l1  # noqa: E402
 from vits_b200 import FlowDecoder  # noqa: E402
+from vits_b200.config import HotPathConfig  # noqa: E402
 
 prec = sys.argv[1] if len(sys.argv) > 1 else "fp32"
-cfg = O.HotPathConfig()
+cfg = HotPathConfig()
 sd = FX.make_state_dict(cfg, seed=1234)
 eng = FlowDecoder(cfg, sd, device="cuda:0", precision=prec)
 print(f"[{prec}] flop/frame {eng.flop_per_frame:.0f} launches {eng.launches_per_call(1, 100)}")

@@ -4,7 +4,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 import torch
 from oracle import fixtures as FX
-from oracle.vits_oracle import HotPathConfig
+from vits_b200.config import HotPathConfig
 from vits_b200 import FlowDecoder
 cfg = HotPathConfig()
 sd = FX.make_state_dict(cfg, seed=1234)

@@ -3,7 +3,7 @@ import os, sys
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from oracle import fixtures as FX
-from oracle.vits_oracle import HotPathConfig
+from vits_b200.config import HotPathConfig
 from vits_b200 import FlowDecoder
 cfg = HotPathConfig()
 sd = FX.make_state_dict(cfg, seed=1234)

@@ -20,13 +20,13 @@ def golden_dir():
 
 @pytest.fixture(scope="session")
 def base_cfg():
-    from oracle.vits_oracle import HotPathConfig
+    from vits_b200.config import HotPathConfig
     return HotPathConfig()
 
 
 @pytest.fixture(scope="session")
 def adapt_cfg():
-    from oracle.vits_oracle import HotPathConfig
+    from vits_b200.config import HotPathConfig
     # sat/configs/adapt.json model block (second real shape set)
     return HotPathConfig(gin_channels=256, upsample_rates=(6, 4, 2, 2), upsample_kernel_sizes=(12, 8, 4, 4),
                          sampling_rate=8000, hop_length=96)

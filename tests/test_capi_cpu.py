@@ -58,6 +58,19 @@ def test_config_validation_without_device(lib, base_cfg):
     assert lib.vitsb_create(C.byref(c), 0, C.byref(h)) == 2
     with pytest.raises(L.VitsbError):
         L.make_config({**base_cfg.__dict__, "resblock": "1"}, "fp16")   # ResBlock1: broken in the reference
+    c = L.make_config({**base_cfg.__dict__, "n_flows": 3, "dilation_rate": [1, 1, 1]}, "fp16")
+    assert lib.vitsb_create(C.byref(c), 0, C.byref(h)) == 2          # odd n_flows: the folded Flips would not cancel
+    assert b"n_flows" in lib.vitsb_last_error(None)
+
+
+def test_no_environment_switches_in_the_library():
+    """Launch-plan choices are vitsb_set_option keys; getenv survives only inside the debug-hook build."""
+    import re
+    csrc = os.path.join(ROOT, "vits_b200", "csrc")
+    for f in os.listdir(csrc):
+        src = open(os.path.join(csrc, f)).read()
+        src = re.sub(r"#ifdef VITSB_RB_DEBUG.*?#endif", "", src, flags=re.S)
+        assert "getenv" not in src, f
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU behaviour")

@@ -22,6 +22,9 @@ from oracle.logmel import log_mel_l1
 pytestmark = pytest.mark.gpu
 
 TOL_WAV = {"fp32": 1e-5, "fp16": 2e-3, "bf16": 8e-3}
+# bf16 operands at BASELINE sizes: the emulated floor of bf16 rounding alone is 1.2e-2 at T=417 (DESIGN.md section 3,
+# BASELINE.md "precision deviation"); the bf16 variant is held to twice that, and to the north-star log-mel bound
+TOL_WAV_BF16_LONG = 2.5e-2
 # z is an intermediate, not a north-star quantity: |z| reaches ~5.4 on these fixtures, so 4e-3 is about one fp16 ulp of
 # the largest values (the WN in_layers run a single fp16 term; the 3-term split everywhere gave 6e-5)
 TOL_Z = {"fp32": 2e-5, "fp16": 4e-3, "bf16": 5e-3}
@@ -109,7 +112,7 @@ def test_weight_norm_state_dict_packs_identically(base_cfg, base_sd):
     assert (wa - wb).abs().max().item() <= 1e-5
 
 
-@pytest.mark.parametrize("prec", ["fp32", "fp16"])
+@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16"])
 def test_c1_single_utterance_vs_oracle(base_cfg, base_sd, prec):
     """BASELINE config 1: one ~5 s utterance (T=417)."""
     lat = FX.make_latents(base_cfg, [417], seed=1234)
@@ -118,19 +121,49 @@ def test_c1_single_utterance_vs_oracle(base_cfg, base_sd, prec):
         o_ref = O.generator(base_sd, z_ref, lat["g"], base_cfg)
     eng = engine(base_cfg, base_sd, prec)
     wav = eng.synthesize(lat["z_p"].cuda(), lat["g"].cuda()).cpu()
-    assert (wav - o_ref).abs().max().item() <= TOL_WAV[prec]
+    assert (wav - o_ref).abs().max().item() <= (TOL_WAV_BF16_LONG if prec == "bf16" else TOL_WAV[prec])
     assert log_mel_l1(wav[:, 0], o_ref[:, 0]) <= TOL_MEL[prec]
 
 
+_c2_cache = {}
+
+
+def _c2_oracle(base_cfg, base_sd):
+    """CPU oracle on the full C2 batch, row by row (ragged semantics); ~95 s of audio, a few seconds of CPU."""
+    if not _c2_cache:
+        lens = FX.make_lengths(16, 84, 834, seed=1234)
+        lat = FX.make_latents(base_cfg, lens, seed=1234)
+        with torch.no_grad():
+            z_ref, o_ref = O.synthesize_ragged(base_sd, lat["z_p"], lat["g"], lat["lengths"], base_cfg)
+        _c2_cache.update(lens=lens, lat=lat, z=z_ref, o=o_ref)
+    return _c2_cache
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16", "bf16"])
+def test_c2_batch16_vs_oracle_every_row(base_cfg, base_sd, prec):
+    """BASELINE config 2 at full size (16 mixed-length utterances, 1-10 s), compared DIRECTLY with the CPU oracle:
+    waveform max-abs and log-mel L1 of every row, z of every row."""
+    c = _c2_oracle(base_cfg, base_sd)
+    lens, lat = c["lens"], c["lat"]
+    eng = engine(base_cfg, base_sd, prec)
+    wav, z = eng.synthesize(lat["z_p"].cuda(), lat["g"].cuda(), lens, ragged=True, return_z=True)
+    wav, z = wav.cpu(), z.cpu()
+    tol_w = TOL_WAV_BF16_LONG if prec == "bf16" else TOL_WAV[prec]
+    tol_z = 3e-2 if prec == "bf16" else TOL_Z[prec]
+    for b, L in enumerate(lens):
+        assert (wav[b, :, :L * 192] - c["o"][b, :, :L * 192]).abs().max().item() <= tol_w, b
+        assert log_mel_l1(wav[b, :, :L * 192], c["o"][b, :, :L * 192]) <= TOL_MEL[prec], b
+        assert (z[b, :, :L] - c["z"][b, :, :L]).abs().max().item() <= tol_z, b
+        assert wav[b, :, L * 192:].abs().sum().item() == 0 and z[b, :, L:].abs().sum().item() == 0
+
+
 def test_c2_batch16_properties(base_cfg, base_sd):
-    """BASELINE config 2 at full size (16 mixed-length utterances, 1-10 s) through
-    size-independent properties: determinism, row independence (row b of the
-    ragged batch == the B=1 call on that row, bit for bit), zero beyond len,
-    fp16 within tolerance of the fp32-verification path."""
+    """C2 through size-independent properties: determinism, row independence (row b of the ragged batch == the B=1
+    call on that row, bit for bit), zero beyond len."""
     lens = FX.make_lengths(16, 84, 834, seed=1234)
     lat = FX.make_latents(base_cfg, lens, seed=1234)
     zp, g = lat["z_p"].cuda(), lat["g"].cuda()
-    e16, e32 = engine(base_cfg, base_sd, "fp16"), engine(base_cfg, base_sd, "fp32")
+    e16 = engine(base_cfg, base_sd, "fp16")
     w1 = e16.synthesize(zp, g, lens, ragged=True)
     w2 = e16.synthesize(zp, g, lens, ragged=True)
     assert torch.equal(w1, w2)
@@ -139,15 +172,7 @@ def test_c2_batch16_properties(base_cfg, base_sd):
         wb = e16.synthesize(zp[b:b + 1, :, :L].contiguous(), g[b:b + 1])
         assert torch.equal(wb[0, 0], w1[b, 0, :L * 192])
         assert w1[b, 0, L * 192:].abs().sum().item() == 0
-    w32 = e32.synthesize(zp, g, lens, ragged=True)
-    assert (w1 - w32).abs().max().item() <= 2e-3
     assert not torch.isnan(w1).any()
-    # spot-check one row against the CPU oracle
-    b = int(np.argmin(lens))
-    with torch.no_grad():
-        zr = O.flow_reverse(base_sd, lat["z_p"][b:b + 1, :, :lens[b]], lat["g"][b:b + 1], base_cfg)
-        orr = O.generator(base_sd, zr, lat["g"][b:b + 1], base_cfg)
-    assert (w32[b:b + 1, :, :lens[b] * 192].cpu() - orr).abs().max().item() <= 1e-5
 
 
 @pytest.mark.parametrize("prec", ["fp16", "fp32"])
@@ -169,25 +194,135 @@ def test_graph_replay_is_bit_identical(base_cfg, base_sd, prec):
     w_replay = eng.synthesize(zp2, g2, lens)
     ref = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision=prec).synthesize(zp2, g2, lens)   # first call: direct
     assert torch.equal(w_replay, ref) and not torch.equal(w_replay, w[0])
+    # different lengths with the SAME tile counts replay the same graph (the lengths are read from device memory) ...
     lens3 = [40, 90, 64]
     w3 = eng.synthesize(zp, g, lens3)
     ref3 = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision=prec).synthesize(zp, g, lens3)
     assert torch.equal(w3, ref3)
     assert w3[1, 0, 90 * 192:].abs().sum().item() == 0
+    # ... and lengths that change a tile count take a different one
+    lens4 = [40, 97, 12]
+    w4 = [eng.synthesize(zp, g, lens4).clone() for _ in range(3)]
+    ref4 = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision=prec).synthesize(zp, g, lens4)
+    for x in w4:
+        assert torch.equal(x, ref4)
     del keep
 
 
-def test_c3_long_form(base_cfg, base_sd):
-    """BASELINE config 3: 60 s single utterance (T=5000)."""
-    lat = FX.make_latents(base_cfg, [5000], seed=3)
+def test_reload_invalidates_cached_graphs(base_cfg, base_sd):
+    """A second load_state_dict on the same handle must not replay graphs captured against the old weight pools."""
+    from vits_b200 import FlowDecoder
+    eng = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision="fp16")
+    lens = [40, 97, 64]
+    lat = FX.make_latents(base_cfg, lens, seed=77)
     zp, g = lat["z_p"].cuda(), lat["g"].cuda()
-    w16 = engine(base_cfg, base_sd, "fp16").synthesize(zp, g)
-    w32 = engine(base_cfg, base_sd, "fp32").synthesize(zp, g)
-    assert w16.shape == (1, 1, 960000)
-    assert (w16 - w32).abs().max().item() <= 2e-3
-    # time-locality: the first 2 s do not depend on what follows them (receptive field << 1 s)
-    ws = engine(base_cfg, base_sd, "fp32").synthesize(zp[:, :, :400].contiguous(), g)
-    assert (ws[0, 0, :32000] - w32[0, 0, :32000]).abs().max().item() <= 1e-5
+    w_old = [eng.synthesize(zp, g, lens).clone() for _ in range(3)]          # direct, capture, replay
+    sd2 = FX.make_state_dict(base_cfg, seed=4242)
+    eng.load_state_dict(sd2)
+    w_new = [eng.synthesize(zp, g, lens).clone() for _ in range(3)]
+    ref = FlowDecoder(base_cfg, sd2, device="cuda:0", precision="fp16").synthesize(zp, g, lens)
+    for x in w_new:
+        assert torch.equal(x, ref)
+    assert not torch.equal(w_new[0], w_old[0])
+    bad = dict(sd2)
+    bad.pop("dec.conv_post.weight")
+    from vits_b200 import lib as L
+    with pytest.raises(L.VitsbError):
+        eng.load_state_dict(bad)
+    with pytest.raises(L.VitsbError):                   # a failed reload leaves the handle unloaded, not half-built
+        eng.synthesize(zp, g, lens)
+
+
+def test_two_threads_share_one_handle(base_cfg, base_sd):
+    """include/vitsb200.h: entry points take the handle's mutex; concurrent calls need distinct workspaces."""
+    import ctypes as C
+    import threading
+    eng = engine(base_cfg, base_sd, "fp16")
+    lens = [33, 50]
+    lats = [FX.make_latents(base_cfg, lens, seed=900 + i) for i in range(2)]
+    refs = [eng.synthesize(l["z_p"].cuda(), l["g"].cuda(), lens).clone() for l in lats]
+    outs, errs = [None, None], []
+
+    def work(i):
+        try:
+            with torch.cuda.device(0):
+                st = torch.cuda.Stream()
+                zp, g = lats[i]["z_p"].cuda(), lats[i]["g"].cuda()
+                ws = torch.empty(eng.workspace_bytes(2, max(lens)), dtype=torch.uint8, device="cuda")
+                wav = torch.empty(2, 1, max(lens) * 192, device="cuda")
+                torch.cuda.synchronize()
+                arr = (C.c_int32 * 2)(*lens)
+                for _ in range(20):
+                    rc = eng.lib.vitsb_synthesize(eng._h, zp.data_ptr(), g.data_ptr(), arr, 2, max(lens), 1, None, wav.data_ptr(),
+                                                  ws.data_ptr(), ws.numel(), C.c_void_p(st.cuda_stream))
+                    assert rc == 0
+                st.synchronize()
+                outs[i] = wav
+        except Exception as e:       # noqa
+            errs.append(e)
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    [t.start() for t in th]
+    [t.join() for t in th]
+    assert not errs, errs
+    for i in range(2):
+        assert torch.equal(outs[i], refs[i])
+
+
+def test_row_chunking_small_workspace_and_large_batch(base_cfg, base_sd):
+    """Memory plan (C4): a workspace smaller than the batch's layout, or more rows than the kernels' 512-row tile
+    tables, runs the batch in row chunks - bit-identical to the single-pass result."""
+    import ctypes as C
+    eng = engine(base_cfg, base_sd, "fp16")
+    lens = FX.make_lengths(12, 8, 60, seed=5)
+    lat = FX.make_latents(base_cfg, lens, seed=5)
+    zp, g = lat["z_p"].cuda(), lat["g"].cuda()
+    ref = eng.synthesize(zp, g, lens)
+    T = max(lens)
+    small = eng.workspace_bytes(5, T)
+    assert small < eng.workspace_bytes(12, T)
+    ws = torch.empty(small, dtype=torch.uint8, device="cuda")
+    wav = torch.empty_like(ref)
+    arr = (C.c_int32 * 12)(*lens)
+    rc = eng.lib.vitsb_synthesize(eng._h, zp.data_ptr(), g.data_ptr(), arr, 12, T, 1, None, wav.data_ptr(), ws.data_ptr(),
+                                  ws.numel(), eng._stream())
+    assert rc == 0
+    assert torch.equal(wav, ref)
+    tiny = torch.empty(eng.workspace_bytes(1, T) - 1024, dtype=torch.uint8, device="cuda")
+    rc = eng.lib.vitsb_synthesize(eng._h, zp.data_ptr(), g.data_ptr(), arr, 12, T, 1, None, wav.data_ptr(), tiny.data_ptr(),
+                                  tiny.numel(), eng._stream())
+    assert rc == 5                                                       # VITSB_ERR_WORKSPACE
+    # 520 rows > 512: chunked internally
+    lens_b = [3 + (i % 5) for i in range(520)]
+    latb = FX.make_latents(base_cfg, lens_b, seed=6)
+    wb = eng.synthesize(latb["z_p"].cuda(), latb["g"].cuda(), lens_b)
+    for b in (0, 511, 512, 519):
+        L = lens_b[b]
+        one = eng.synthesize(latb["z_p"][b:b + 1, :, :L].contiguous().cuda(), latb["g"][b:b + 1].cuda())
+        assert torch.equal(one[0, 0], wb[b, 0, :L * 192])
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16"])
+def test_c3_long_form_vs_oracle(base_cfg, base_sd, prec):
+    """BASELINE config 3: 60 s single utterance (T=5000), compared directly with the CPU oracle (waveform max-abs and
+    log-mel L1 over the whole minute), plus time-locality."""
+    lat = FX.make_latents(base_cfg, [5000], seed=3)
+    if "c3" not in _c2_cache:
+        with torch.no_grad():
+            zr = O.flow_reverse(base_sd, lat["z_p"], lat["g"], base_cfg)
+            _c2_cache["c3"] = (zr, O.generator(base_sd, zr, lat["g"], base_cfg))
+    z_ref, o_ref = _c2_cache["c3"]
+    zp, g = lat["z_p"].cuda(), lat["g"].cuda()
+    eng = engine(base_cfg, base_sd, prec)
+    w, z = eng.synthesize(zp, g, return_z=True)
+    assert w.shape == (1, 1, 960000)
+    assert (w.cpu() - o_ref).abs().max().item() <= TOL_WAV[prec]
+    assert log_mel_l1(w.cpu()[:, 0], o_ref[:, 0]) <= TOL_MEL[prec]
+    assert (z.cpu() - z_ref).abs().max().item() <= TOL_Z[prec]
+    if prec == "fp32":
+        # time-locality: the first 2 s do not depend on what follows them (receptive field << 1 s)
+        ws = eng.synthesize(zp[:, :, :400].contiguous(), g)
+        assert (ws[0, 0, :32000] - w[0, 0, :32000]).abs().max().item() <= 1e-5
 
 
 def test_c5_distinct_speakers_per_row(base_cfg, base_sd):
@@ -239,33 +374,37 @@ def test_host_pipeline_matches_blocking_calls(base_cfg, base_sd):
         assert torch.equal(out, ref)
 
 
-@pytest.mark.parametrize("env", [{"VITSB_MRF_SEP": "0"}, {"VITSB_FLOW_IN_SPLIT": "1"}, {"VITSB_RB_FUSED": "0"}])
-def test_alternative_launch_plans_agree(base_cfg, base_sd, env):
-    """The launch-plan switches read at load time (summing ResBlock epilogue instead of the separate MRF pass,
-    3-term split in_layers, layer-at-a-time ResBlocks) stay within the same tolerance of the CPU oracle and of
+@pytest.mark.parametrize("opts", [{"flow_fused": 0}, {"flow_fused": 0, "flow_in_split": 1}, {"rb_fused": 0}, {"tc_pair": 0},
+                                  {"cuda_graph": 0, "pdl": 1}])
+def test_alternative_launch_plans_agree(base_cfg, base_sd, opts):
+    """The launch-plan options (layer-at-a-time flow instead of the fused coupling kernel, 3-term split in_layers,
+    layer-at-a-time ResBlocks, no CTA pairs, no graphs + PDL) stay within the same tolerance of the CPU oracle and of
     the default plan on a ragged batch."""
     from vits_b200 import FlowDecoder
     lens = [97, 40, 64]
     lat = FX.make_latents(base_cfg, lens, seed=321)
     with torch.no_grad():
-        _, o_ref = O.synthesize_ragged(base_sd, lat["z_p"], lat["g"], torch.tensor(lens), base_cfg)
-    old = {k: os.environ.get(k) for k in env}
-    os.environ.update(env)
-    try:
-        alt = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision="fp16")
-    finally:
-        for k, v in old.items():
-            if v is None:
-                os.environ.pop(k, None)
-            else:
-                os.environ[k] = v
-    w_alt = alt.synthesize(lat["z_p"].cuda(), lat["g"].cuda(), lens, ragged=True).cpu()
-    w_def = engine(base_cfg, base_sd, "fp16").synthesize(lat["z_p"].cuda(), lat["g"].cuda(), lens, ragged=True).cpu()
+        z_ref, o_ref = O.synthesize_ragged(base_sd, lat["z_p"], lat["g"], torch.tensor(lens), base_cfg)
+    alt = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision="fp16", options=opts)
+    for k, v in opts.items():
+        assert alt.get_option(k) == v
+    deflt = engine(base_cfg, base_sd, "fp16")
+    assert deflt.get_option("plan.flow_fused") == 1 and deflt.get_option("plan.rb_fused") == 1
+    if "flow_fused" in opts:
+        assert alt.get_option("plan.flow_fused") == 0
+    w_alt, z_alt = alt.synthesize(lat["z_p"].cuda(), lat["g"].cuda(), lens, ragged=True, return_z=True)
+    w_alt2 = alt.synthesize(lat["z_p"].cuda(), lat["g"].cuda(), lens, ragged=True)
+    w_def, z_def = deflt.synthesize(lat["z_p"].cuda(), lat["g"].cuda(), lens, ragged=True, return_z=True)
+    w_alt, w_def = w_alt.cpu(), w_def.cpu()
+    assert torch.equal(w_alt, w_alt2.cpu())
     assert (w_alt - o_ref).abs().max().item() <= TOL_WAV["fp16"]
     assert (w_def - o_ref).abs().max().item() <= TOL_WAV["fp16"]
     assert (w_alt - w_def).abs().max().item() <= TOL_WAV["fp16"]
+    assert (z_alt.cpu() - z_ref).abs().max().item() <= TOL_Z["fp16"] and (z_def.cpu() - z_ref).abs().max().item() <= TOL_Z["fp16"]
     for b, L in enumerate(lens):
         assert w_alt[b, 0, L * 192:].abs().sum().item() == 0
+    with pytest.raises(Exception):
+        alt.set_option("no_such_option", 1)
 
 
 def test_length_regulate_matches_reference_matmuls(base_cfg, base_sd):

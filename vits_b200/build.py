@@ -1,6 +1,12 @@
-"""Build the C-ABI CUDA library in-tree (vits_b200/libvitsb200.so) with nvcc for sm_100a."""
+"""Build the C-ABI CUDA library in-tree (vits_b200/libvitsb200.so) with nvcc for sm_100a.
+
+Each .cu is compiled to an object under vits_b200/build/ (in parallel, re-compiled only when it or a header is
+newer) and the objects are linked into the shared library.
+"""
 from __future__ import annotations
 
+import concurrent.futures
+import hashlib
 import os
 import shutil
 import subprocess
@@ -8,10 +14,12 @@ import sys
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
+OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libvitsb200.so")
-SOURCES = ["conv_f32.cu", "aux_kernels.cu", "conv_tc.cu", "rb_fused.cu", "engine_weights.cu", "engine_run.cu", "capi.cu"]
-NVCC_FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3",
-              "-Xcompiler", "-fPIC", "-shared", "-cudart", "static"]
+SOURCES = ["conv_f32.cu", "aux_kernels.cu", "conv_tc.cu", "rb_fused.cu", "flow_fused.cu", "engine_weights.cu", "engine_run.cu",
+           "capi.cu"]
+NVCC_FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-Xcompiler", "-fPIC"]
+LINK_FLAGS = ["-shared", "-cudart", "static"]
 
 
 def _nvcc() -> str:
@@ -19,6 +27,15 @@ def _nvcc() -> str:
         if cand and os.path.exists(cand):
             return cand
     raise RuntimeError("nvcc not found")
+
+
+def _headers():
+    return [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))] + \
+           [os.path.join(HERE, "..", "include", "vitsb200.h")]
+
+
+def _sources():
+    return [s for s in SOURCES if os.path.exists(os.path.join(CSRC, s))]
 
 
 def needs_build() -> bool:
@@ -33,13 +50,33 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
     extra = os.environ.get("VITSB_EXTRA_NVCC", "").split()          # e.g. -DVITSB_RB_DEBUG for the timing-experiment hooks
-    cmd = [_nvcc()] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB] + \
-          [os.path.join(CSRC, s) for s in SOURCES]
-    r = subprocess.run(cmd, capture_output=True, text=True)
+    tag = hashlib.sha1(" ".join(NVCC_FLAGS + extra).encode()).hexdigest()[:8]
+    os.makedirs(OBJ, exist_ok=True)
+    nvcc = _nvcc()
+    hdr_t = max(os.path.getmtime(h) for h in _headers())
+    jobs = []
+    objs = []
+    for s in _sources():
+        src = os.path.join(CSRC, s)
+        obj = os.path.join(OBJ, f"{os.path.splitext(s)[0]}.{tag}.o")
+        objs.append(obj)
+        if force or not os.path.exists(obj) or os.path.getmtime(obj) < max(os.path.getmtime(src), hdr_t):
+            jobs.append((s, [nvcc] + NVCC_FLAGS + extra + (["-Xptxas", "-v"] if verbose else []) + ["-c", src, "-o", obj]))
+
+    def run(job):
+        name, cmd = job
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        return name, r
+
+    with concurrent.futures.ThreadPoolExecutor(max_workers=max(1, min(len(jobs), os.cpu_count() or 1))) as ex:
+        for name, r in ex.map(run, jobs):
+            if r.returncode != 0:
+                raise RuntimeError(f"nvcc failed on {name}:\n" + r.stdout + r.stderr)
+            if verbose:
+                print(r.stderr)
+    r = subprocess.run([nvcc] + NVCC_FLAGS + LINK_FLAGS + ["-o", LIB] + objs, capture_output=True, text=True)
     if r.returncode != 0:
-        raise RuntimeError("nvcc failed:\n" + r.stdout + r.stderr)
-    if verbose:
-        print(r.stderr)
+        raise RuntimeError("nvcc link failed:\n" + r.stdout + r.stderr)
     return LIB
 
 

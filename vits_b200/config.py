@@ -1,0 +1,53 @@
+"""Shape parameters of the flow + decoder hot path (the `model` block of the reference's configs/base.json).
+
+This dataclass is the product's public config type: `FlowDecoder(cfg, state_dict)` accepts it (or the reference's
+`hps.model`, or a dict with the same names); the test oracle imports it from here.
+"""
+from __future__ import annotations
+
+from dataclasses import dataclass
+from typing import Sequence
+
+
+@dataclass
+class HotPathConfig:
+    """Shape parameters of the hot path (configs/base.json `model` block)."""
+    inter_channels: int = 192
+    hidden_channels: int = 256
+    gin_channels: int = 1024
+    n_flows: int = 4
+    flow_kernel_size: int = 5          # models.py:462 (hard-coded 5)
+    flow_n_layers: int = 4             # models.py:462 (hard-coded 4)
+    dilation_rate: Sequence[int] = (1, 1, 1, 1)
+    resblock_kernel_sizes: Sequence[int] = (3, 7, 11)
+    resblock_dilation_sizes: Sequence[Sequence[int]] = ((1, 3, 5), (1, 3, 5), (1, 3, 5))
+    upsample_rates: Sequence[int] = (8, 6, 2, 2)
+    upsample_initial_channel: int = 512
+    upsample_kernel_sizes: Sequence[int] = (16, 12, 4, 4)
+    sampling_rate: int = 16000
+    hop_length: int = 192
+
+    @staticmethod
+    def from_json(cfg: dict) -> "HotPathConfig":
+        m, d = cfg["model"], cfg.get("data", {})
+        return HotPathConfig(
+            inter_channels=m["inter_channels"],
+            hidden_channels=m["hidden_channels"],
+            gin_channels=m["gin_channels"],
+            n_flows=m.get("n_flows", 4),
+            dilation_rate=tuple(m.get("dilation_rate", [1, 1, 1, 1])),
+            resblock_kernel_sizes=tuple(m["resblock_kernel_sizes"]),
+            resblock_dilation_sizes=tuple(tuple(x) for x in m["resblock_dilation_sizes"]),
+            upsample_rates=tuple(m["upsample_rates"]),
+            upsample_initial_channel=m["upsample_initial_channel"],
+            upsample_kernel_sizes=tuple(m["upsample_kernel_sizes"]),
+            sampling_rate=d.get("sampling_rate", 16000),
+            hop_length=d.get("hop_length", 192),
+        )
+
+    @property
+    def total_upsample(self) -> int:
+        r = 1
+        for u in self.upsample_rates:
+            r *= u
+        return r

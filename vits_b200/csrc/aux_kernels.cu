@@ -230,7 +230,8 @@ __device__ __forceinline__ void y_accum8(const uint4& y, float (&x)[8]) {
 template <typename OpT>
 __global__ void __launch_bounds__(256)
 mrf_sum_kernel(const OpT* __restrict__ y0, const OpT* __restrict__ y1, const OpT* __restrict__ y2, int C, int L,
-               const int* __restrict__ len, int len_mul, float scale, float slope, OpT* __restrict__ out, int split) {
+               const int* __restrict__ len, int len_mul, float scale, float slope, OpT* __restrict__ out, int split,
+               float* __restrict__ out_f32) {
   const int b = blockIdx.y;
   const int valid = len ? len[b] * len_mul : L;
   const int rows = valid + kHaloRows < L ? valid + kHaloRows : L;      // rows nobody reads are skipped (as every producer does)
@@ -247,6 +248,12 @@ mrf_sum_kernel(const OpT* __restrict__ y0, const OpT* __restrict__ y1, const OpT
     if (y2) a2 = __ldg(reinterpret_cast<const uint4*>(y2 + e));
     y_accum8<OpT>(a0, x); y_accum8<OpT>(a1, x); y_accum8<OpT>(a2, x);
   }
+  if (out_f32) {                          // fp32 average itself (input of the generic conv_post)
+    float4* o = reinterpret_cast<float4*>(out_f32 + e);
+    o[0] = make_float4(x[0] * scale, x[1] * scale, x[2] * scale, x[3] * scale);
+    o[1] = make_float4(x[4] * scale, x[5] * scale, x[6] * scale, x[7] * scale);
+    return;
+  }
   uint32_t p[4], q[4];
 #pragma unroll
   for (int k = 0; k < 4; ++k) {
@@ -262,14 +269,14 @@ mrf_sum_kernel(const OpT* __restrict__ y0, const OpT* __restrict__ y1, const OpT
 }
 
 cudaError_t launch_mrf_sum(const void* y0, const void* y1, const void* y2, int B, int L, int C, const int* len, int len_mul,
-                           float scale, float slope, void* out, int split, int op, cudaStream_t stream) {
-  if (op == OP_F32 || C % 8 != 0 || !y0) return cudaErrorNotSupported;
+                           float scale, float slope, void* out, int split, float* out_f32, int op, cudaStream_t stream) {
+  if (op == OP_F32 || C % 8 != 0 || !y0 || (!out && !out_f32)) return cudaErrorNotSupported;
   const long long per_b = (long long)L * (C / 8);
   dim3 grid((unsigned)((per_b + 255) / 256), B);
   if (op == OP_F16) mrf_sum_kernel<__half><<<grid, 256, 0, stream>>>((const __half*)y0, (const __half*)y1, (const __half*)y2, C, L, len, len_mul,
-                                                                     scale, slope, (__half*)out, split);
+                                                                     scale, slope, (__half*)out, split, out_f32);
   else mrf_sum_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>((const __nv_bfloat16*)y0, (const __nv_bfloat16*)y1, (const __nv_bfloat16*)y2, C, L,
-                                                               len, len_mul, scale, slope, (__nv_bfloat16*)out, split);
+                                                               len, len_mul, scale, slope, (__nv_bfloat16*)out, split, out_f32);
   return cudaGetLastError();
 }
 
@@ -430,10 +437,21 @@ cudaError_t launch_conv_post(const float* in, int B, int L, int C, int k, float 
     conv_post4_kernel<32, 7, float><<<grid4, kPost4Threads, 0, stream>>>(in, nullptr, nullptr, 1.f, L, slope, w, len, len_mul, wav, pcm, volume);
     return cudaGetLastError();
   }
+  if (!conv_post_supported(C, k)) return cudaErrorNotSupported;
   dim3 grid(ceil_div(L, kPostTile), B);
   size_t smem = (size_t)((kPostTile + k - 1) * (C + 1) + k * C) * sizeof(float);
+  static PerDeviceOnce smem_optin;
+  const cudaError_t ae = smem_optin.run([] {
+    return cudaFuncSetAttribute(conv_post_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+  });
+  if (ae != cudaSuccess) return ae;
   conv_post_kernel<<<grid, kPostTile, smem, stream>>>(in, L, C, k, slope, w, len, len_mul, wav, pcm, volume);
   return cudaGetLastError();
+}
+
+// generic kernel: the [256 + k - 1][C + 1] fp32 tile and the weights must fit the opted-in shared memory
+bool conv_post_supported(int C, int k) {
+  return C >= 1 && k >= 1 && (size_t)((kPostTile + k - 1) * (C + 1) + k * C) * sizeof(float) <= 200 * 1024;
 }
 
 bool conv_post_y_supported(int C, int k, int L) { return C == 32 && k == 7 && L % 4 == 0; }

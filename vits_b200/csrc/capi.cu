@@ -37,52 +37,78 @@ void vitsb_destroy(vitsb_handle* h) { delete h; }
 
 const char* vitsb_last_error(const vitsb_handle* h) { return h ? h->eng.err.c_str() : g_create_err.c_str(); }
 
+int vitsb_set_option(vitsb_handle* h, const char* key, int value) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  std::lock_guard<std::mutex> lk(h->eng.mu);
+  return h->eng.set_option(key, value);
+}
+
+int vitsb_get_option(const vitsb_handle* h, const char* key, int* value) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  return h->eng.get_option(key, value);
+}
+
 int vitsb_load_weights(vitsb_handle* h, const vitsb_tensor_desc* tensors, int n) {
   if (!h) return VITSB_ERR_BAD_ARG;
+  std::lock_guard<std::mutex> lk(h->eng.mu);
   return h->eng.load(tensors, n);
 }
 
 size_t vitsb_workspace_bytes(const vitsb_handle* h, int B, int T_max) {
   if (!h || B < 1 || T_max < 1) return 0;
-  return h->eng.layout(B, T_max).total;
+  return h->eng.workspace_bytes(B, T_max);
+}
+
+static Call make_call(int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged, void* ws,
+                      size_t ws_bytes, vitsb_stream stream) {
+  Call c;
+  c.what = what; c.z_in = z_in; c.g = g; c.len = len; c.B = B; c.T = T; c.ragged = ragged;
+  c.ws = ws; c.ws_bytes = ws_bytes; c.stream = (cudaStream_t)stream;
+  return c;
 }
 
 int vitsb_flow_reverse(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len, int B, int T_max,
                        float* z, void* ws, size_t ws_bytes, vitsb_stream stream) {
   if (!h) return VITSB_ERR_BAD_ARG;
+  std::lock_guard<std::mutex> lk(h->eng.mu);
   if (!z) return h->eng.fail(VITSB_ERR_BAD_ARG, "null z");
-  return h->eng.run(Engine::RUN_FLOW, z_p, g, len, B, T_max, 1, z, nullptr, ws, ws_bytes, (cudaStream_t)stream, false, nullptr);
+  Call c = make_call(Engine::RUN_FLOW, z_p, g, len, B, T_max, 1, ws, ws_bytes, stream);
+  c.z_out = z;
+  return h->eng.run(c, false, nullptr);
 }
 
 int vitsb_decode(vitsb_handle* h, const float* z, const float* g, const int32_t* len, int B, int T_max, int ragged,
                  float* wav, void* ws, size_t ws_bytes, vitsb_stream stream) {
   if (!h) return VITSB_ERR_BAD_ARG;
-  return h->eng.run(Engine::RUN_DEC, z, g, len, B, T_max, ragged, nullptr, wav, ws, ws_bytes, (cudaStream_t)stream, false, nullptr);
+  std::lock_guard<std::mutex> lk(h->eng.mu);
+  Call c = make_call(Engine::RUN_DEC, z, g, len, B, T_max, ragged, ws, ws_bytes, stream);
+  c.wav = wav;
+  return h->eng.run(c, false, nullptr);
 }
 
 int vitsb_synthesize(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len, int B, int T_max, int ragged,
                      float* z_out, float* wav, void* ws, size_t ws_bytes, vitsb_stream stream) {
   if (!h) return VITSB_ERR_BAD_ARG;
-  return h->eng.run(Engine::RUN_FLOW | Engine::RUN_DEC, z_p, g, len, B, T_max, ragged, z_out, wav, ws, ws_bytes,
-                    (cudaStream_t)stream, false, nullptr);
+  std::lock_guard<std::mutex> lk(h->eng.mu);
+  Call c = make_call(Engine::RUN_FLOW | Engine::RUN_DEC, z_p, g, len, B, T_max, ragged, ws, ws_bytes, stream);
+  c.z_out = z_out; c.wav = wav;
+  return h->eng.run(c, false, nullptr);
 }
 
 int vitsb_synthesize_pcm16(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len, int B, int T_max, int ragged,
                            float volume, int16_t* pcm, void* ws, size_t ws_bytes, vitsb_stream stream) {
   if (!h) return VITSB_ERR_BAD_ARG;
+  std::lock_guard<std::mutex> lk(h->eng.mu);
   if (!pcm) return h->eng.fail(VITSB_ERR_BAD_ARG, "null pcm");
-  h->eng.pcm_out = reinterpret_cast<short*>(pcm);
-  h->eng.pcm_volume = volume;
-  const int rc = h->eng.run(Engine::RUN_FLOW | Engine::RUN_DEC, z_p, g, len, B, T_max, ragged, nullptr, nullptr, ws, ws_bytes,
-                            (cudaStream_t)stream, false, nullptr);
-  h->eng.pcm_out = nullptr;
-  h->eng.pcm_volume = 1.f;
-  return rc;
+  Call c = make_call(Engine::RUN_FLOW | Engine::RUN_DEC, z_p, g, len, B, T_max, ragged, ws, ws_bytes, stream);
+  c.pcm = reinterpret_cast<short*>(pcm); c.volume = volume;      // call-local: nothing about the output form lives in the handle
+  return h->eng.run(c, false, nullptr);
 }
 
 int vitsb_length_regulate(vitsb_handle* h, const float* attn, const float* m_p, const float* s_p, const float* noise,
                           int B, int T, int Tx, float* z_p, vitsb_stream stream) {
   if (!h) return VITSB_ERR_BAD_ARG;
+  std::lock_guard<std::mutex> lk(h->eng.mu);
   if (!attn || !m_p || !s_p || !noise || !z_p) return h->eng.fail(VITSB_ERR_BAD_ARG, "null pointer");
   if (B < 1 || T < 1 || Tx < 1) return h->eng.fail(VITSB_ERR_BAD_ARG, "B, T and Tx must be >= 1");
   if (B > 65535) return h->eng.fail(VITSB_ERR_BAD_ARG, "B too large");
@@ -99,8 +125,10 @@ int vitsb_launches_per_call(const vitsb_handle* h, int B, int T_max) {
   if (!h) return 0;
   int n = 0;
   Engine* e = const_cast<Engine*>(&h->eng);
-  if (e->run(Engine::RUN_FLOW | Engine::RUN_DEC, nullptr, nullptr, nullptr, B, T_max, 1, nullptr, nullptr, nullptr, 0, 0, true, &n) != VITSB_OK)
-    return 0;
+  std::lock_guard<std::mutex> lk(e->mu);
+  Call c;
+  c.what = Engine::RUN_FLOW | Engine::RUN_DEC; c.B = B; c.T = T_max; c.ragged = 1;
+  if (e->run(c, true, &n) != VITSB_OK) return 0;
   return n;
 }
 
@@ -108,6 +136,7 @@ double vitsb_flop_per_frame(const vitsb_handle* h) { return h ? h->eng.flop_per_
 
 int vitsb_profile(vitsb_handle* h, int enable) {
   if (!h) return VITSB_ERR_BAD_ARG;
+  std::lock_guard<std::mutex> lk(h->eng.mu);
   h->eng.profile = enable != 0;
   h->eng.prof.clear();
   return VITSB_OK;
@@ -128,7 +157,7 @@ int vitsb_profile_read(const vitsb_handle* h, int32_t* tags, double* ms, int64_t
 }
 
 const char* vitsb_build_info(void) {
-  return "vitsb200;arch=sm_100a;tensor=tcgen05.mma.kind::f16+TMEM;copy=TMA(cp.async.bulk.tensor);verify=fp32-ffma;cpu_fallback=none";
+  return "vitsb200;arch=sm_100a;tensor=tcgen05.mma.kind::f16+TMEM;copy=TMA(cp.async.bulk.tensor);flow=fused-coupling;resblock=fused;verify=fp32-ffma;cpu_fallback=none";
 }
 
 // ---------------------------------------------------------------------------
@@ -185,7 +214,7 @@ int vitsb_selftest_conv(int device, int precision, int Cin, int N, int k, int di
   r.in = d_in32; r.w = d_w32; r.epi.out_f32 = d_o1; r.epi.out_op = d_op1;
   a.in = d_in16; a.w = d_w16; a.epi.out_f32 = d_o2; a.epi.out_op = d_op2;
   cudaError_t e1 = launch_conv_f32(r, 0);
-  cudaError_t e2 = launch_conv_tc(a, op, 0);
+  cudaError_t e2 = launch_conv_tc(a, op, LaunchOpts{}, 0);
   cudaError_t e3 = cudaDeviceSynchronize();
   int rc = VITSB_OK;
   if (e1 != cudaSuccess || e2 != cudaSuccess || e3 != cudaSuccess) {

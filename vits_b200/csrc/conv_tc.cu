@@ -54,7 +54,7 @@ struct TcGeom {
 #endif
 constexpr int kTcEpiGroups = VITSB_TC_EPI_GROUPS;                         // 4-warp epilogue groups; every group works on every tile (column units dealt round-robin)
 constexpr int kTcThreads = 64 + 128 * kTcEpiGroups;
-constexpr int kTcMaxB = 512;
+constexpr int kTcMaxB = kMaxBatchRows;
 
 // TWO = true: CTA-pair mode (cluster of 2, tcgen05 cta_group::2).  A work item is a PAIR of time tiles
 // (pair p = m-tiles 2p and 2p+1 of the flattened (batch row, time tile) list; rank r of the pair owns
@@ -248,12 +248,6 @@ TmaEncodeFn tma_encode_fn() {
   return fn;
 }
 
-bool pdl_enabled() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("VITSB_PDL"); v = (e && e[0] == '1') ? 1 : 0; }   // measured neutral-to-slightly-negative: off unless VITSB_PDL=1
-  return v == 1;
-}
-
 bool conv_tc_supported(int Cin, int in_ld, int N, int NT, int k) {
   // (in_cols, when different from Cin, must be a multiple of the K block; checked in make_geom)
   if (!(Cin == 16 || Cin == 32 || (Cin % 64 == 0 && Cin > 0))) return false;
@@ -290,12 +284,6 @@ static bool make_geom(const ConvArgs& a, int op, int ncl, TcGeom* g) {
   return true;
 }
 
-static bool pair_mode_enabled() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("VITSB_TC_PAIR"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v == 1;
-}
-
 // Wave balance: one output tile is 128 rows x NT columns and a CTA (pair) runs its tiles back to back,
 // so the kernel lasts ceil(items / groups) tiles.  With ~75 time tiles per call (16 utterances) NT = 256
 // gives 150 tiles on 148 SMs - two waves, the second almost empty.  Pick the N tile that minimises
@@ -317,21 +305,19 @@ static int pick_launch_nt(const ConvArgs& a, int num_sms, bool pair_ok) {
   return best;
 }
 
-cudaError_t launch_conv_tc(const ConvArgs& a_in, int op, cudaStream_t stream) {
+cudaError_t launch_conv_tc(const ConvArgs& a_in, int op, const LaunchOpts& lo, cudaStream_t stream) {
   if (op == OP_F32) return cudaErrorNotSupported;
-  static int num_sms = 0;
-  if (num_sms == 0) {
-    int dev = 0; cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    if (num_sms <= 0) num_sms = 148;
-  }
+  const int num_sms = lo.num_sms > 0 ? lo.num_sms : 148;
   ConvArgs a = a_in;
-  a.NT = pick_launch_nt(a_in, num_sms, pair_mode_enabled());
+  a.NT = pick_launch_nt(a_in, num_sms, lo.pair);
   // CTA-pair mode whenever each CTA's half of the weight box is a whole number of 8-row swizzle atoms
-  const int ncl = (pair_mode_enabled() && a.NT % 32 == 0 && a.NT >= 32) ? 2 : 1;
+  const int ncl = (lo.pair && a.NT % 32 == 0 && a.NT >= 32) ? 2 : 1;
   TcGeom g;
   if (!make_geom(a, op, ncl, &g)) return cudaErrorNotSupported;
+  g.dbg = 0;
+#ifdef VITSB_RB_DEBUG
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("VITSB_TC_DBG"); dbg = e ? atoi(e) : 0; } g.dbg = dbg; }
+#endif
   TmaEncodeFn enc = tma_encode_fn();
   if (!enc) return cudaErrorNotSupported;
 
@@ -358,15 +344,15 @@ cudaError_t launch_conv_tc(const ConvArgs& a_in, int op, cudaStream_t stream) {
     if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
   }
   const size_t smem = 1024 + (size_t)g.stages * (g.a_bytes + g.b_stride) + 8 * 20 + 16;
-  static std::once_flag once;
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
+  static PerDeviceOnce smem_optin;             // the opt-in is per device: a second engine on another GPU needs its own
+  const cudaError_t attr_err = smem_optin.run([] {
     cudaError_t e[4] = {
         cudaFuncSetAttribute(conv_tc_kernel<__nv_bfloat16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024),
         cudaFuncSetAttribute(conv_tc_kernel<__half, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024),
         cudaFuncSetAttribute(conv_tc_kernel<__nv_bfloat16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024),
         cudaFuncSetAttribute(conv_tc_kernel<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024)};
-    for (cudaError_t x : e) if (x != cudaSuccess) attr_err = x;
+    for (cudaError_t x : e) if (x != cudaSuccess) return x;
+    return cudaSuccess;
   });
   if (attr_err != cudaSuccess) return attr_err;
   const long long max_items = (long long)ceil_div(a.m_tiles > 0 ? a.m_tiles : a.B * ceil_div(a.L, kTileM), ncl) * g.nNT;
@@ -383,7 +369,7 @@ cudaError_t launch_conv_tc(const ConvArgs& a_in, int op, cudaStream_t stream) {
   at[0].val.clusterDim.x = ncl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[1].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
+  cfg.attrs = at; cfg.numAttrs = lo.pdl ? 2 : 1;
   cudaError_t le;
   if (ncl == 2) {
     le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, conv_tc_kernel<__nv_bfloat16, true>, tmA, tmB, a, g)

@@ -1,6 +1,7 @@
 // Host-side engine: packed weights + the per-call launch plan.
 #pragma once
 #include <map>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -27,6 +28,8 @@ struct Coupling {          // modules.ResidualCouplingLayer (reverse, mean_only)
   PackedConv pre, post;
   std::vector<PackedConv> in_layers, res, skip;
   int coff = 0;            // physical channel offset of the half updated by `post`
+  FlowFusedWeights ff;     // the same layer in the fused coupling kernel's packing (flow_fused.cu); valid when Engine::flow_fused
+  double flop_per_pos = 0; // algorithmic FLOP of the whole coupling per frame
 };
 
 struct ResIter { PackedConv c1, c2; };
@@ -39,20 +42,46 @@ struct Stage {             // ups[i] + its MRF (num_kernels ResBlock2 x iteratio
 
 struct WsLayout {
   size_t len = 0, cond = 0;
-  size_t zf = 0, zop = 0, hf = 0, hop = 0, acts = 0, skipf = 0, skipop = 0;   // flow
-  size_t xin_f = 0, xb_f = 0, acc_f = 0, xin_op = 0, xb_op = 0, xb2_op = 0, g_op = 0, nxt_op = 0;  // decoder
+  size_t zf = 0, zop = 0, hf = 0, hop = 0, acts = 0, skipf = 0, skipop = 0;   // flow (h / acts / skip: layer-at-a-time flow only)
+  size_t xin_f = 0, xb_f = 0, acc_f = 0, g_op = 0;                            // decoder, layer-at-a-time plan (fp32 build)
+  size_t xin_op = 0, xb_op = 0, xb2_op = 0, br0 = 0, br1 = 0, nxt_op = 0;     // decoder, 16-bit streams
   size_t total = 0;
+};
+
+// One call through the C ABI (all pointers caller-owned; nothing here outlives the call).
+struct Call {
+  int what = 0;                   // Engine::RUN_FLOW | Engine::RUN_DEC
+  const float* z_in = nullptr;    // [B][inter][T] fp32, reference layout
+  const float* g = nullptr;       // [B][gin]
+  const int32_t* len = nullptr;   // host [B] or null
+  int B = 0, T = 0, ragged = 1;
+  float* z_out = nullptr;         // optional [B][inter][T]
+  float* wav = nullptr;           // [B][1][T*up] fp32 ...
+  short* pcm = nullptr;           // ... or int16 PCM with the serving path's volume scaling (vits_wrap.py:195)
+  float volume = 1.f;
+  void* ws = nullptr; size_t ws_bytes = 0;
+  cudaStream_t stream = nullptr;
 };
 
 struct Engine {
   vitsb_config cfg{};
   int device = 0;
+  int num_sms = 148;
   int op = OP_F16;
   std::string err;
-  bool split16 = false;
-  bool mrf_separate = true;     // MRF average as its own coalesced pass over the branches' y streams (VITSB_MRF_SEP=0: summing ResBlock epilogue)
-  bool flow_in_split = false;   // WN in_layers run 3-term split precision too (VITSB_FLOW_IN_SPLIT=1/0); default: fp16 single term, bf16 split
-  bool rb_fused = false;   // 16-bit paths: ResBlock iterations run as the fused persistent kernel (rb_fused.cu)    // 16-bit paths: flow + conv_pre + upsamplers run split-precision
+  std::mutex mu;                // the C entry points serialise on it: one call at a time per handle (host side); the
+                                // enqueued work is stream-ordered as usual
+  bool split16 = false;         // 16-bit paths: flow + conv_pre + upsamplers run split-precision
+  bool flow_in_split = false;   // WN in_layers run 3-term split precision too; default: fp16 single term, bf16 split
+  bool rb_fused = false;        // 16-bit paths: ResBlock iterations run as the fused persistent kernel (rb_fused.cu)
+  bool flow_fused = false;      // 16-bit paths: each coupling layer runs as one cluster kernel (flow_fused.cu)
+
+  // options (vitsb_set_option); -1 = automatic.  Packing / plan options take effect at the next vitsb_load_weights.
+  int opt_graph = 1, opt_pdl = 0, opt_tc_pair = 1, opt_rb_fused = -1, opt_flow_fused = -1, opt_flow_in_split = -1,
+      opt_rb_nslab = 0, opt_ws_cap_mb = 24576;
+  int set_option(const char* key, int value);
+  int get_option(const char* key, int* value) const;
+  LaunchOpts lopts() const { LaunchOpts o; o.pdl = opt_pdl != 0; o.pair = opt_tc_pair != 0; o.num_sms = num_sms; o.rb_nslab = opt_rb_nslab; return o; }
 
   // packed model
   bool loaded = false;
@@ -73,11 +102,7 @@ struct Engine {
   float* d_condW = nullptr;
   float* d_condB = nullptr;
   float* d_post = nullptr;
-
-  // output form of the current call (set by the C entry point): int16 PCM with the serving path's volume scaling
-  // (vits_wrap.py:195) written by conv_post instead of the fp32 waveform
-  short* pcm_out = nullptr;
-  float pcm_volume = 1.f;
+  void free_device();
 
   // optional per-launch timing (cudaEvent pairs around every launch, read back after a sync)
   bool profile = false;
@@ -88,26 +113,32 @@ struct Engine {
   int fail(int code, const std::string& msg) { err = msg; return code; }
 
   int validate_config();
+  int resolve_plan();              // precision + options -> rb_fused / flow_fused / flow_in_split (at create and before every load)
   int load(const vitsb_tensor_desc* t, int n);
   WsLayout layout(int B, int T) const;
+  size_t workspace_bytes(int B, int T) const;     // layout of the largest row chunk under the workspace cap
+  int chunk_rows(int B, int T, size_t ws_bytes) const;
 
-  // CUDA-graph replay of the launch plan (engine_run.cu): the ~110 kernels between the two seams of a call are
-  // launch-latency bound for short batches; a call repeated with the same (workspace, B, T, lengths) replays an
-  // instantiated graph instead of re-issuing them.  VITSB_GRAPH=0 disables.
+  // CUDA-graph replay of the launch plan (engine_run.cu): the ~80 kernels between the two seams of a call are
+  // launch-latency bound for short batches; a call whose launch geometry (workspace, B, T, per-rate tile counts) has
+  // been seen before replays an instantiated graph instead of re-issuing them.  The lengths themselves are read by
+  // the kernels from device memory, so they are not part of the key.  Option "cuda_graph" = 0 disables.
   struct GraphEntry { std::vector<long long> key; int seen = 0; int launches = 0; cudaGraphExec_t exec = nullptr; unsigned long long stamp = 0; };
   std::vector<GraphEntry> graphs;
   cudaStream_t cap_stream = nullptr;
   unsigned long long graph_clock = 0;
+  void drop_graphs();
+  std::vector<long long> graph_key(const Call& c) const;
 
   // mode bits for run()
   enum { RUN_FLOW = 1, RUN_DEC = 2 };
   // phases of one call: FRONT = length upload + seam pack + conditioning GEMV (read caller pointers),
   // MID = every conv of the flow and the decoder (workspace only), BACK = conv_post (writes the caller's waveform)
   enum { PH_FRONT = 1, PH_MID = 2, PH_BACK = 4, PH_ALL = 7 };
-  int issue(int phases, int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
-            float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches);
-  int run(int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
-          float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches);
+  int check_call(const Call& c, bool dry);
+  int issue(int phases, const Call& c, bool dry, int* launches);
+  int run_chunk(const Call& c, bool dry, int* launches);
+  int run(const Call& c, bool dry, int* launches);
 };
 
 }  // namespace vitsb

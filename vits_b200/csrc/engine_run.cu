@@ -5,14 +5,14 @@
 //   dec   : models.py:306-318 -> modules.py:250-260
 // Buffer roles (all time-major [B][L][C]):
 //   zf/zop      flow state, fp32 master + operand copy        [T][inter]
-//   hf/hop      WN residual stream                             [T][H]
-//   acts        gated activations (operand)                    [T][H]
-//   skipf/skipop WN skip accumulator                            [T][H]
-//   xin_f/xin_op  stage input x (after ups) and leaky_relu(x)   [L_s][C_s]
-//   xb_f/xb_op    per-branch ResBlock residual stream
-//   g_op          gated activations                             [L_s][C_s/2]
-//   acc_f         MRF accumulator (sum of branches / num_kernels)
-//   nxt_op        leaky_relu(acc) = next stage's ups / conv_post input
+//   hf/hop      WN residual stream                             [T][H]      (layer-at-a-time flow only)
+//   acts        gated activations (operand)                    [T][H]      (layer-at-a-time flow only)
+//   skipf/skipop WN skip accumulator                            [T][H]      (layer-at-a-time flow only)
+//   xin_op        stage input leaky_relu(x) (after ups)         [L_s][C_s]
+//   xb_op/xb2_op  per-branch ResBlock residual stream (ping / pong; xb_op also holds the last branch's result)
+//   br0/br1       results of the first two MRF branches
+//   nxt_op        leaky_relu(MRF average) = next stage's ups input (conv_pre's output before stage 0)
+//   xin_f/xb_f/acc_f/g_op  fp32 residual copies, MRF accumulator and gate tile of the layer-at-a-time plan (fp32 build)
 #include "engine.h"
 
 namespace vitsb {
@@ -30,9 +30,11 @@ WsLayout Engine::layout(int B, int T) const {
   w.len = take(sizeof(int) * (size_t)B);
   w.cond = take(sizeof(float) * (size_t)B * (Ncond > 0 ? Ncond : 1));
   w.zf = take(4 * BT * IC);  w.zop = take(ob * BT * IC * sm);
-  w.hf = take(4 * BT * H);   w.hop = take(ob * BT * H * sm);
-  w.acts = take(ob * BT * H * sm);
-  w.skipf = take(4 * BT * H); w.skipop = take(ob * BT * H * sm);
+  if (!flow_fused) {                             // the fused coupling kernel keeps h / acts / skip on chip
+    w.hf = take(4 * BT * H);   w.hop = take(ob * BT * H * sm);
+    w.acts = take(ob * BT * H * sm);
+    w.skipf = take(4 * BT * H); w.skipop = take(ob * BT * H * sm);
+  }
   // decoder: elements per frame of the widest stage tensor
   size_t E = cfg.upsample_initial_channel;     // conv_pre output lives in nxt_op
   size_t pos = 1; int C = cfg.upsample_initial_channel;
@@ -40,17 +42,48 @@ WsLayout Engine::layout(int B, int T) const {
     pos *= cfg.upsample_rates[i]; C /= 2;
     if (pos * C > E) E = pos * C;
   }
-  w.xin_f = take(4 * BT * E); w.xb_f = take(4 * BT * E); w.acc_f = take(4 * BT * E);
-  w.xin_op = take(ob * BT * E); w.xb_op = take(ob * BT * E); w.xb2_op = take(rb_fused ? ob * BT * E : 16); w.g_op = take(ob * BT * E / 2 + 16); w.nxt_op = take(ob * BT * E * sm);
+  if (rb_fused) {
+    // 16-bit streams only: stage input, ping / pong, two branch results (the third lands in ping), next operand
+    w.xin_op = take(ob * BT * E); w.xb_op = take(ob * BT * E); w.xb2_op = take(ob * BT * E);
+    w.br0 = take(ob * BT * E); w.br1 = take(ob * BT * E);
+    const bool need_f32_post = !conv_post_y_supported(post_C, post_k, T * up_total);
+    if (need_f32_post) w.acc_f = take(4 * BT * E);
+  } else {
+    w.xin_f = take(4 * BT * E); w.xb_f = take(4 * BT * E); w.acc_f = take(4 * BT * E);
+    w.xin_op = take(ob * BT * E); w.xb_op = take(ob * BT * E); w.g_op = take(ob * BT * E / 2 + 16);
+  }
+  w.nxt_op = take(ob * BT * E * sm);
   w.total = off;
   return w;
+}
+
+// Rows per chunk: the whole batch when its layout fits both the kernels' tile tables and the workspace on offer.
+int Engine::chunk_rows(int B, int T, size_t ws_bytes) const {
+  int n = B < kMaxBatchRows ? B : kMaxBatchRows;
+  if (layout(n, T).total <= ws_bytes) return n;
+  const size_t per_row = layout(2, T).total - layout(1, T).total + 2048;     // layout is affine in B up to the 1 KB alignment
+  const size_t one = layout(1, T).total;
+  if (one > ws_bytes) return 0;
+  n = (int)((ws_bytes - one) / per_row) + 1;
+  while (n > 1 && layout(n, T).total > ws_bytes) --n;
+  return n < 1 ? 0 : n;
+}
+
+size_t Engine::workspace_bytes(int B, int T) const {
+  const size_t cap = (size_t)opt_ws_cap_mb << 20;
+  const int n = B < kMaxBatchRows ? B : kMaxBatchRows;
+  const size_t full = layout(n, T).total;
+  if (full <= cap) return full;
+  const int rows = chunk_rows(B, T, cap);
+  return layout(rows > 0 ? rows : 1, T).total;
 }
 
 namespace {
 
 // launch tags for the profile table
 enum Tag { T_PACK = 0, T_COND = 1, T_UNPACK = 2, T_POST = 3, T_MRF = 4, T_FLOW_PRE = 10, T_FLOW_IN = 11, T_FLOW_RES = 12,
-           T_FLOW_SKIP = 13, T_FLOW_POST = 14, T_CONV_PRE = 20, T_UPS = 30, T_RB_C1 = 40, T_RB_C2 = 50, T_RB_FUSED = 60 };
+           T_FLOW_SKIP = 13, T_FLOW_POST = 14, T_FLOW_FUSED = 15, T_CONV_PRE = 20, T_UPS = 30, T_RB_C1 = 40, T_RB_C2 = 50,
+           T_RB_FUSED = 60 };
 
 struct ProfEv { int tag; double flops; cudaEvent_t a, b; };
 
@@ -78,15 +111,17 @@ struct Ctx {
   const int* len_flow;   // device lens used for masking (nullptr = all rows live)
   const int* len_dec;
   const float* cond;     // device [B][Ncond]
+  LaunchOpts lo;
 
   const int32_t* h_len = nullptr;   // host copy of len (tile counts for the launcher's wave balancing)
-  int m_tiles(int L, int len_mul, bool ragged) const {
-    if (!ragged || !h_len) return B * ((L + kTileM - 1) / kTileM);
+  int m_tiles(int L, int len_mul, bool ragged) const { return count_tiles(h_len, B, L, len_mul, ragged, kTileM, kHaloRows); }
+  static int count_tiles(const int32_t* h_len, int B, int L, int len_mul, bool ragged, int tile_rows, int extra) {
+    if (!ragged || !h_len) return B * ((L + tile_rows - 1) / tile_rows);
     int q = 0;
     for (int b = 0; b < B; ++b) {
-      long long rows = (long long)h_len[b] * len_mul + kHaloRows;
+      long long rows = (long long)h_len[b] * len_mul + extra;
       if (rows > L) rows = L;
-      q += (int)((rows + kTileM - 1) / kTileM);
+      q += (int)((rows + tile_rows - 1) / tile_rows);
     }
     return q;
   }
@@ -122,7 +157,7 @@ struct Ctx {
       a.epi_b = *ep2; a.epi_b.gate = 0;
       a.epi_b.bias = e->d_bias + p2->bias_off; a.epi_b.bias_bstride = 0;
     }
-    err = e->op == OP_F32 ? launch_conv_f32(a, stream) : launch_conv_tc(a, e->op, stream);
+    err = e->op == OP_F32 ? launch_conv_f32(a, stream) : launch_conv_tc(a, e->op, lo, stream);
     ev_end();
   }
 };
@@ -152,21 +187,28 @@ void set_out_op_hi(Epilogue& ep, void* p, int C, long long L, bool split_pitch, 
 
 }  // namespace
 
-int Engine::issue(int phases, int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
-                  float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches) {
+int Engine::check_call(const Call& c, bool dry) {
   if (!dry) {
     if (!loaded) return fail(VITSB_ERR_WEIGHTS, "weights not loaded");
-    if (!z_in || !g || !ws) return fail(VITSB_ERR_BAD_ARG, "null pointer");
-    if ((what & RUN_DEC) && !wav && !pcm_out) return fail(VITSB_ERR_BAD_ARG, "null wav");
+    if (!c.z_in || !c.g || !c.ws) return fail(VITSB_ERR_BAD_ARG, "null pointer");
+    if ((c.what & RUN_DEC) && !c.wav && !c.pcm) return fail(VITSB_ERR_BAD_ARG, "null wav");
   }
-  if (B < 1 || T < 1) return fail(VITSB_ERR_BAD_ARG, "B and T_max must be >= 1");
-  if ((long long)T * up_total > 0x7fffffffLL / 64) return fail(VITSB_ERR_BAD_ARG, "T_max too large");
-  const WsLayout W = layout(B, T);
-  if (!dry && ws_bytes < W.total) return fail(VITSB_ERR_WORKSPACE, "workspace too small");
-  if (!dry && len) for (int b = 0; b < B; ++b)
-    if (len[b] < 0 || len[b] > T) return fail(VITSB_ERR_BAD_ARG, "len[b] out of [0, T_max]");
+  if (c.B < 1 || c.T < 1) return fail(VITSB_ERR_BAD_ARG, "B and T_max must be >= 1");
+  if (c.B > 65535) return fail(VITSB_ERR_BAD_ARG, "B too large (at most 65535 rows per call)");
+  if ((long long)c.T * up_total > 0x7fffffffLL / 64) return fail(VITSB_ERR_BAD_ARG, "T_max too large");
+  if (!dry && c.len) for (int b = 0; b < c.B; ++b)
+    if (c.len[b] < 0 || c.len[b] > c.T) return fail(VITSB_ERR_BAD_ARG, "len[b] out of [0, T_max]");
+  return VITSB_OK;
+}
 
-  char* base = reinterpret_cast<char*>(ws);
+int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
+  const int B = c.B, T = c.T, what = c.what;
+  const int32_t* len = c.len;
+  const WsLayout W = layout(B, T);
+  if (!dry && c.ws_bytes < W.total) return fail(VITSB_ERR_WORKSPACE, "workspace too small");
+  cudaStream_t stream = c.stream;
+
+  char* base = reinterpret_cast<char*>(c.ws);
   auto F = [&](size_t off) { return reinterpret_cast<float*>(base + off); };
   auto P = [&](size_t off) { return reinterpret_cast<void*>(base + off); };
   const size_t ob = op_bytes(op);
@@ -176,9 +218,10 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
   cx.B = B; cx.T = T;
   cx.cond = F(W.cond);
   cx.h_len = len;
+  cx.lo = lopts();
   int* d_len = reinterpret_cast<int*>(base + W.len);
   cx.len_flow = len ? d_len : nullptr;
-  cx.len_dec = (len && ragged) ? d_len : nullptr;
+  cx.len_dec = (len && c.ragged) ? d_len : nullptr;
 
 #define AUX_LAUNCH(tag, expr) do { if (cx.skip) break; ++cx.launches; if (!dry && cx.ok()) { cx.ev_begin(tag, 0.0); cx.err = (expr); cx.ev_end(); } } while (0)
   if (!dry) {
@@ -193,12 +236,30 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
   }
   cx.skip = !(phases & PH_FRONT);
   // seam: channel-major fp32 -> time-major (masked beyond len)
-  AUX_LAUNCH(T_PACK, launch_pack_time_major(z_in, B, IC, T, cx.len_flow, (what & RUN_FLOW) ? F(W.zf) : nullptr, P(W.zop), op, split16 ? 1 : 0, stream));
+  AUX_LAUNCH(T_PACK, launch_pack_time_major(c.z_in, B, IC, T, cx.len_flow, (what & RUN_FLOW) ? F(W.zf) : nullptr, P(W.zop), op, split16 ? 1 : 0, stream));
   // all conditioning Linears of the call: flow cond_layers (modules.py:161) + ResBlock conds (modules.py:254)
-  AUX_LAUNCH(T_COND, launch_cond_gemv(d_condW, d_condB, g, B, Ncond, cfg.gin_channels, F(W.cond), stream));
+  AUX_LAUNCH(T_COND, launch_cond_gemv(d_condW, d_condB, c.g, B, Ncond, cfg.gin_channels, F(W.cond), stream));
 
   cx.skip = !(phases & PH_MID);
-  if (what & RUN_FLOW) {
+  if ((what & RUN_FLOW) && flow_fused) {
+    // one kernel per coupling layer: pre -> WN -> post -> x1 -= m, h / acts / m on chip (flow_fused.cu)
+    const int t_out = flow_fused_tile_rows(cfg.flow_n_layers);
+    for (const Coupling& cp : couplings) {
+      if (cx.skip) continue;
+      ++cx.launches;
+      if (dry || !cx.ok()) continue;
+      FlowFusedArgs fa{};
+      fa.zf = F(W.zf); fa.zop = P(W.zop); fa.w = d_w; fa.bias = d_bias;
+      fa.cond = cx.cond; fa.cond_bstride = Ncond;
+      fa.fw = cp.ff; fa.n_layers = cfg.flow_n_layers;
+      fa.T = T; fa.B = B; fa.len = cx.len_flow;
+      fa.m_tiles = Ctx::count_tiles(len, B, T, 1, len != nullptr, t_out, 0);
+      cx.ev_begin(T_FLOW_FUSED, cp.flop_per_pos * cx.valid_frames);
+      cx.err = launch_flow_fused(fa, op, cx.lo, stream);
+      cx.ev_end();
+    }
+    if (c.z_out) AUX_LAUNCH(T_UNPACK, launch_unpack_channel_major(F(W.zf), B, IC, T, c.z_out, stream));
+  } else if (what & RUN_FLOW) {
     for (const Coupling& cp : couplings) {
       // h = pre(x0)                                                   modules.py:364
       { Epilogue ep = epi_base(); set_out_f32(ep, F(W.hf), H, T); set_out_op_hi(ep, P(W.hop), H, T, split16, flow_in_split);
@@ -230,7 +291,7 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
         ep.out_op_split = split16 ? IC : 0;
         cx.conv(T_FLOW_POST, cp.post, P(W.skipop), T, 1, cx.len_flow, ep); }
     }
-    if (z_out) AUX_LAUNCH(T_UNPACK, launch_unpack_channel_major(F(W.zf), B, IC, T, z_out, stream));
+    if (c.z_out) AUX_LAUNCH(T_UNPACK, launch_unpack_channel_major(F(W.zf), B, IC, T, c.z_out, stream));
   }
 
   if (what & RUN_DEC) {
@@ -240,10 +301,8 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
     int L = T;              // rows per batch item at the current rate
     int mul = 1;            // valid rows = len * mul
     const int ns = (int)stages.size();
-    // conv_post forms the last stage's MRF average from the branches' y streams itself (decided up front: the
-    // decoder loop below is skipped in the PH_BACK pass of a graph replay)
-    const bool post_from_y = rb_fused && mrf_separate && ns > 0 && stages.back().rb.size() <= 3 &&
-                             conv_post_y_supported(post_C, post_k, T * up_total);
+    // 16-bit plan: conv_post forms the last stage's MRF average from the branches' y streams itself when the shape allows
+    const bool post_from_y = rb_fused && conv_post_y_supported(post_C, post_k, T * up_total);
     for (int s = 0; s < ns; ++s) {
       const Stage& st = stages[s];
       const int C = st.C, Lo = L * st.u;
@@ -256,12 +315,16 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
       const int nk = (int)st.rb.size();
       const float inv = 1.0f / nk;
       const float next_slope = 0.1f;                           // models.py:309 (the 0.01 of models.py:315 is in conv_post)
+      // results of the MRF branches (16-bit plan): the third one lands in the ping buffer, free during its last iteration
+      void* br[3] = {P(W.br0), P(W.br1), P(W.xb_op)};
       for (int j = 0; j < nk; ++j) {
         const int ni = (int)st.rb[j].size();
         for (int d = 0; d < ni; ++d) {
           const ResIter& it = st.rb[j][d];
           if (rb_fused) {
-            // whole iteration in one kernel; the residual stream is y = op(leaky_relu(x)) only (rb_fused.cu)
+            // whole iteration in one kernel; the residual stream is y = op(leaky_relu(x)) only (rb_fused.cu).  Every branch
+            // ends in an ordinary launch into br[j]; one coalesced pass (mrf_sum_kernel, or conv_post's tile load on the
+            // last stage) forms the MRF average (models.py:311-314).
             if (cx.skip) continue;
             ++cx.launches;
             if (dry || !cx.ok()) continue;
@@ -276,42 +339,14 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
             ra.L = L; ra.B = B; ra.len = cx.len_dec; ra.len_mul = mul;
             ra.bias1 = cx.cond + it.c1.cond_off; ra.bias1_bstride = Ncond;
             ra.bias2 = d_bias + it.c2.bias_off;
-            ra.scale = 1.f;
-            // MRF (models.py:311-314).  With <= 3 branches the first branches' results stay 16-bit y streams (their
-            // last iteration is an ordinary mid-type launch into br[j]) and the final branch sums them in its epilogue:
-            // 12 B of traffic per element instead of 20 B through an fp32 accumulator.  br[] reuses the fp32
-            // buffers of the layer-at-a-time plan, which the fused plan does not touch.
-            void* br[3] = {P(W.xin_f), P(W.xb_f), P(W.acc_f)};
-            const bool stream_mrf = nk <= 3;
-            // Separate MRF pass (default): EVERY branch ends in an ordinary mid-type launch into br[j] and one coalesced
-            // pass (mrf_sum_kernel, or conv_post's tile load on the last stage) averages the streams.  The summing
-            // epilogue variant costs 40-100 us more per stage than a mid launch (one exposed DRAM round trip per
-            // 16-column chunk in a row-per-thread epilogue); the separate pass is HBM-bound at 10 B per element.
-            const bool sep_mrf = stream_mrf && mrf_separate && (s < ns - 1 || post_from_y);
-            if (d < ni - 1) {
-              ra.y_out = ping;
-            } else if (sep_mrf) {
-              ra.y_out = br[j];
-            } else if (stream_mrf && j < nk - 1) {
-              ra.y_out = br[j];
-            } else if (stream_mrf) {
-              ra.scale = inv;
-              ra.acc_mode = RB_EMIT_NEXT;
-              ra.add0 = nk > 1 ? br[0] : nullptr;
-              ra.add1 = nk > 2 ? br[1] : nullptr;
-              if (s == ns - 1) ra.nxt_f32 = F(W.acc_f);              // conv_post reads fp32
-              else { ra.nxt_op = P(W.nxt_op); ra.nxt_split = split16 ? 1 : 0; }
-            } else {
-              ra.scale = inv;
-              ra.acc = F(W.acc_f);
-              ra.acc_mode = (j > 0 ? RB_ACC_READ : 0) | (j < nk - 1 ? RB_ACC_STORE : RB_EMIT_NEXT);
-              if (j == nk - 1) {
-                if (s == ns - 1) ra.nxt_f32 = F(W.acc_f);            // conv_post reads fp32
-                else { ra.nxt_op = P(W.nxt_op); ra.nxt_split = split16 ? 1 : 0; }
-              }
-            }
+            // the last iteration writes the branch result; br[2] aliases a ping / pong buffer, which must not be the one
+            // this iteration reads
+            void* dst = d < ni - 1 ? ping : br[j];
+            if (dst == rl.y_in) dst = P(W.xb2_op) == rl.y_in ? P(W.xb_op) : P(W.xb2_op);
+            ra.y_out = dst;
+            if (d == ni - 1) br[j] = dst;
             cx.ev_begin(T_RB_FUSED + s, (it.c1.flop_per_pos + it.c2.flop_per_pos) * (cx.len_dec ? cx.valid_frames : (double)B * T) * mul);
-            cx.err = launch_rb_fused(rl, op, stream);
+            cx.err = launch_rb_fused(rl, op, cx.lo, stream);
             cx.ev_end();
             continue;
           }
@@ -335,20 +370,26 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
           cx.conv(T_RB_C2 + s, it.c2, P(W.g_op), L, mul, cx.len_dec, ep);
         }
       }
-      if (rb_fused && mrf_separate && nk <= 3 && s < ns - 1) {
-        // x = sum_j resblock_j(x) / num_kernels; next operand = leaky_relu(x, 0.1)      models.py:309-314
-        AUX_LAUNCH(T_MRF, launch_mrf_sum(P(W.xin_f), nk > 1 ? P(W.xb_f) : nullptr, nk > 2 ? P(W.acc_f) : nullptr, B, L, C, cx.len_dec, mul,
-                                         inv, next_slope, P(W.nxt_op), split16 ? 1 : 0, op, stream));
+      if (rb_fused) {
+        if (s < ns - 1) {
+          // x = sum_j resblock_j(x) / num_kernels; next operand = leaky_relu(x, 0.1)      models.py:309-314
+          AUX_LAUNCH(T_MRF, launch_mrf_sum(br[0], nk > 1 ? br[1] : nullptr, nk > 2 ? br[2] : nullptr, B, L, C, cx.len_dec, mul,
+                                           inv, next_slope, P(W.nxt_op), split16 ? 1 : 0, nullptr, op, stream));
+        } else if (!post_from_y) {
+          AUX_LAUNCH(T_MRF, launch_mrf_sum(br[0], nk > 1 ? br[1] : nullptr, nk > 2 ? br[2] : nullptr, B, L, C, cx.len_dec, mul,
+                                           inv, 1.f, nullptr, 0, F(W.acc_f), op, stream));
+        }
       }
-    }
-    // tanh(conv_post(leaky_relu(x, 0.01)))                                 models.py:315-317
-    cx.skip = !(phases & PH_BACK);
-    if (post_from_y) {
-      const int nk = (int)stages.back().rb.size();
-      AUX_LAUNCH(T_POST, launch_conv_post_y(P(W.xin_f), nk > 1 ? P(W.xb_f) : nullptr, nk > 2 ? P(W.acc_f) : nullptr, 1.0f / nk, B, L, post_C,
-                                            post_k, 0.01f, d_post, cx.len_dec, mul, wav, pcm_out, pcm_volume, op, stream));
-    } else {
-      AUX_LAUNCH(T_POST, launch_conv_post(F(W.acc_f), B, L, post_C, post_k, 0.01f, d_post, cx.len_dec, mul, wav, pcm_out, pcm_volume, stream));
+      if (s == ns - 1) {
+        // tanh(conv_post(leaky_relu(x, 0.01)))                                 models.py:315-317
+        cx.skip = !(phases & PH_BACK);
+        if (post_from_y) {
+          AUX_LAUNCH(T_POST, launch_conv_post_y(br[0], nk > 1 ? br[1] : nullptr, nk > 2 ? br[2] : nullptr, inv, B, L, post_C,
+                                                post_k, 0.01f, d_post, cx.len_dec, mul, c.wav, c.pcm, c.volume, op, stream));
+        } else {
+          AUX_LAUNCH(T_POST, launch_conv_post(F(W.acc_f), B, L, post_C, post_k, 0.01f, d_post, cx.len_dec, mul, c.wav, c.pcm, c.volume, stream));
+        }
+      }
     }
   }
 #undef AUX_LAUNCH
@@ -368,22 +409,31 @@ int Engine::issue(int phases, int what, const float* z_in, const float* g, const
   return VITSB_OK;
 }
 
-static bool graphs_enabled() {
-  static int v = -1;
-  if (v < 0) { const char* e = getenv("VITSB_GRAPH"); v = (e && e[0] == '0') ? 0 : 1; }
-  return v == 1;
+// Everything the captured launches depend on besides device memory contents: the workspace, the shape, and the
+// per-rate tile counts the launchers size their grids with.  The lengths themselves are read from device memory.
+std::vector<long long> Engine::graph_key(const Call& c) const {
+  std::vector<long long> key = {c.what, (long long)(uintptr_t)c.ws, (long long)c.ws_bytes, c.B, c.T, c.ragged, c.len ? 1 : 0,
+                                opt_pdl, opt_tc_pair, opt_rb_nslab};
+  if (c.len) {
+    int mul = 1;
+    key.push_back(Ctx::count_tiles(c.len, c.B, c.T, 1, true, kTileM, kHaloRows));
+    key.push_back(Ctx::count_tiles(c.len, c.B, c.T, 1, true, flow_fused_tile_rows(cfg.flow_n_layers), 0));
+    for (int i = 0; i < cfg.n_upsamples; ++i) {
+      mul *= cfg.upsample_rates[i];
+      key.push_back(Ctx::count_tiles(c.len, c.B, c.T * mul, mul, true, kTileM, kHaloRows));
+    }
+  }
+  return key;
 }
 
-// Public entry: issue the plan directly, or - from the second identical call on - replay its middle part
-// (every launch that touches only the workspace) as an instantiated CUDA graph.  The seam kernels that read or
-// write caller pointers stay outside the graph, so fresh input / output buffers do not invalidate it.
-int Engine::run(int what, const float* z_in, const float* g, const int32_t* len, int B, int T, int ragged,
-                float* z_out, float* wav, void* ws, size_t ws_bytes, cudaStream_t stream, bool dry, int* launches) {
-  if (dry || profile || z_out || !graphs_enabled() || B < 1 || B > 4096)
-    return issue(PH_ALL, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, stream, dry, launches);
+// One chunk of rows: issue the plan directly, or - from the second call with the same launch geometry on - replay its
+// middle part (every launch that touches only the workspace) as an instantiated CUDA graph.  The seam kernels that
+// read or write caller pointers stay outside the graph, so fresh input / output buffers do not invalidate it.
+int Engine::run_chunk(const Call& c, bool dry, int* launches) {
+  if (dry || profile || c.z_out || !opt_graph)
+    return issue(PH_ALL, c, dry, launches);
 
-  std::vector<long long> key = {what, (long long)(uintptr_t)ws, (long long)ws_bytes, B, T, ragged, len ? 1 : 0};
-  if (len) key.insert(key.end(), len, len + B);
+  std::vector<long long> key = graph_key(c);
   GraphEntry* ge = nullptr;
   for (GraphEntry& x : graphs) if (x.key == key) { ge = &x; break; }
   if (!ge) {                                     // first sighting: run directly, remember the shape
@@ -396,11 +446,11 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
     }
     GraphEntry n; n.key = std::move(key); n.seen = 1; n.stamp = ++graph_clock;
     graphs.push_back(std::move(n));
-    return issue(PH_ALL, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, stream, dry, launches);
+    return issue(PH_ALL, c, dry, launches);
   }
   ge->stamp = ++graph_clock;
   int n_front = 0, n_back = 0;
-  int rc = issue(PH_FRONT, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, stream, false, &n_front);
+  int rc = issue(PH_FRONT, c, false, &n_front);
   if (rc != VITSB_OK) return rc;
   if (!ge->exec && ge->seen >= 0) {              // second sighting: capture the middle on a private stream
     if (!cap_stream && cudaStreamCreateWithFlags(&cap_stream, cudaStreamNonBlocking) != cudaSuccess) cap_stream = nullptr;
@@ -408,7 +458,8 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
     bool ok = cap_stream && cudaStreamBeginCapture(cap_stream, cudaStreamCaptureModeRelaxed) == cudaSuccess;
     if (ok) {
       int n_mid = 0;
-      const int rc_mid = issue(PH_MID, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, cap_stream, false, &n_mid);
+      Call cc = c; cc.stream = cap_stream;
+      const int rc_mid = issue(PH_MID, cc, false, &n_mid);
       const cudaError_t ee = cudaStreamEndCapture(cap_stream, &graph);
       ok = rc_mid == VITSB_OK && ee == cudaSuccess && graph != nullptr;
       if (ok) ok = cudaGraphInstantiate(&ge->exec, graph, 0) == cudaSuccess;
@@ -421,17 +472,51 @@ int Engine::run(int what, const float* z_in, const float* g, const int32_t* len,
     }
   }
   if (ge->exec) {
-    const cudaError_t le = cudaGraphLaunch(ge->exec, stream);
+    const cudaError_t le = cudaGraphLaunch(ge->exec, c.stream);
     if (le != cudaSuccess) return fail(VITSB_ERR_CUDA, std::string("graph launch failed: ") + cudaGetErrorString(le));
   } else {
     int n_mid = 0;
-    rc = issue(PH_MID, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, stream, false, &n_mid);
+    rc = issue(PH_MID, c, false, &n_mid);
     if (rc != VITSB_OK) return rc;
     ge->launches = n_mid;
   }
-  rc = issue(PH_BACK, what, z_in, g, len, B, T, ragged, z_out, wav, ws, ws_bytes, stream, false, &n_back);
+  rc = issue(PH_BACK, c, false, &n_back);
   if (launches) *launches = n_front + ge->launches + n_back;
   return rc;
+}
+
+// Public entry.  Rows are independent (every kernel masks by len[b] and no op crosses batch rows), so a batch whose
+// layout exceeds the workspace on offer - or the kernels' 512-row tile tables - is processed in row chunks through the
+// same workspace: that is the memory plan for the C4-sized batches (64-512 utterances).
+int Engine::run(const Call& c, bool dry, int* launches) {
+  int rc = check_call(c, dry);
+  if (rc != VITSB_OK) return rc;
+  if (dry) {
+    Call cc = c;
+    cc.B = c.B < kMaxBatchRows ? c.B : kMaxBatchRows;
+    return run_chunk(cc, true, launches);
+  }
+  const int rows = chunk_rows(c.B, c.T, c.ws_bytes);
+  if (rows < 1) return fail(VITSB_ERR_WORKSPACE, "workspace too small (needs at least the layout of one row: vitsb_workspace_bytes(h, 1, T_max))");
+  if (rows >= c.B) return run_chunk(c, false, launches);
+  const size_t IC = cfg.inter_channels, gin = cfg.gin_channels, LT = (size_t)c.T * up_total;
+  int total = 0;
+  for (int b0 = 0; b0 < c.B; b0 += rows) {
+    Call cc = c;
+    cc.B = c.B - b0 < rows ? c.B - b0 : rows;
+    cc.z_in = c.z_in + (size_t)b0 * IC * c.T;
+    cc.g = c.g + (size_t)b0 * gin;
+    if (c.len) cc.len = c.len + b0;
+    if (c.z_out) cc.z_out = c.z_out + (size_t)b0 * IC * c.T;
+    if (c.wav) cc.wav = c.wav + (size_t)b0 * LT;
+    if (c.pcm) cc.pcm = c.pcm + (size_t)b0 * LT;
+    int n = 0;
+    rc = run_chunk(cc, false, &n);
+    if (rc != VITSB_OK) return rc;
+    total += n;
+  }
+  if (launches) *launches = total;
+  return VITSB_OK;
 }
 
 }  // namespace vitsb

@@ -22,14 +22,60 @@
 
 namespace vitsb {
 
-Engine::~Engine() {
+void Engine::drop_graphs() {
   for (GraphEntry& x : graphs) if (x.exec) cudaGraphExecDestroy(x.exec);
+  graphs.clear();
+}
+
+void Engine::free_device() {
+  if (d_w) { cudaFree(d_w); d_w = nullptr; }
+  if (d_bias) { cudaFree(d_bias); d_bias = nullptr; }
+  if (d_condW) { cudaFree(d_condW); d_condW = nullptr; }
+  if (d_condB) { cudaFree(d_condB); d_condB = nullptr; }
+  if (d_post) { cudaFree(d_post); d_post = nullptr; }
+}
+
+Engine::~Engine() {
+  drop_graphs();
   if (cap_stream) cudaStreamDestroy(cap_stream);
-  if (d_w) cudaFree(d_w);
-  if (d_bias) cudaFree(d_bias);
-  if (d_condW) cudaFree(d_condW);
-  if (d_condB) cudaFree(d_condB);
-  if (d_post) cudaFree(d_post);
+  free_device();
+}
+
+// ---- options (replace the environment switches of round 1; per handle, visible through the C ABI) ----
+namespace {
+struct OptDesc { const char* key; int Engine::*field; int lo, hi; };
+const OptDesc kOpts[] = {
+    {"cuda_graph", &Engine::opt_graph, 0, 1},             // replay the workspace-only launches of a repeated shape as a CUDA graph
+    {"pdl", &Engine::opt_pdl, 0, 1},                      // programmatic dependent launch between tensor-core kernels
+    {"tc_pair", &Engine::opt_tc_pair, 0, 1},              // conv_tc CTA-pair mode
+    {"rb_fused", &Engine::opt_rb_fused, -1, 1},           // fused ResBlock kernel (-1 auto); applies at the next load
+    {"flow_fused", &Engine::opt_flow_fused, -1, 1},       // fused coupling-layer kernel (-1 auto); applies at the next load
+    {"flow_in_split", &Engine::opt_flow_in_split, -1, 1}, // 3-term split WN in_layers (-1: bf16 yes, fp16 no); applies at the next load
+    {"rb_nslab", &Engine::opt_rb_nslab, 0, 16},           // rb_fused slab count override (0 auto)
+    {"ws_cap_mb", &Engine::opt_ws_cap_mb, 64, 1 << 20},   // workspace cap: larger batches are processed in row chunks
+};
+}  // namespace
+
+int Engine::set_option(const char* key, int value) {
+  if (!key) return fail(VITSB_ERR_BAD_ARG, "null option key");
+  for (const OptDesc& o : kOpts)
+    if (std::strcmp(o.key, key) == 0) {
+      if (value < o.lo || value > o.hi) return fail(VITSB_ERR_BAD_ARG, std::string("option value out of range: ") + key);
+      this->*(o.field) = value;
+      return VITSB_OK;
+    }
+  return fail(VITSB_ERR_BAD_ARG, std::string("unknown option: ") + key);
+}
+
+int Engine::get_option(const char* key, int* value) const {
+  if (!key || !value) return VITSB_ERR_BAD_ARG;
+  for (const OptDesc& o : kOpts)
+    if (std::strcmp(o.key, key) == 0) { *value = this->*(o.field); return VITSB_OK; }
+  // read-only: the plan actually in force
+  if (std::strcmp(key, "plan.rb_fused") == 0) { *value = rb_fused; return VITSB_OK; }
+  if (std::strcmp(key, "plan.flow_fused") == 0) { *value = flow_fused; return VITSB_OK; }
+  if (std::strcmp(key, "plan.flow_in_split") == 0) { *value = flow_in_split; return VITSB_OK; }
+  return VITSB_ERR_BAD_ARG;
 }
 
 int Engine::validate_config() {
@@ -41,6 +87,9 @@ int Engine::validate_config() {
   if (c.gin_channels <= 0 || c.gin_channels % 4 != 0) return bad("gin_channels must be a positive multiple of 4 "
                                                                  "(the reference hot path is always speaker-conditioned)");
   if (c.n_flows < 1 || c.n_flows > VITSB_MAX_LIST) return bad("n_flows");
+  // every coupling is preceded by a Flip (models.py:213-217): an odd count leaves the state channel-reversed, which the
+  // packed pre / post column orders do not undo
+  if (c.n_flows % 2 != 0) return bad("n_flows must be even (the Flips are folded into the weight packing)");
   if (c.flow_kernel_size % 2 != 1) return bad("flow kernel size must be odd (modules.py:96)");
   if (c.flow_n_layers < 1 || c.flow_n_layers > VITSB_MAX_LIST) return bad("flow_n_layers");
   if (c.n_upsamples < 1 || c.n_upsamples > VITSB_MAX_LIST) return bad("n_upsamples");
@@ -68,23 +117,35 @@ int Engine::validate_config() {
     for (int l = 1; l < c.flow_n_layers; ++l) pad *= dr > 1 ? dr : 1;
     if (dr < 1 || pad > kHaloRows) return bad("flow dilation");
   }
-  op = c.precision == VITSB_PREC_FP32 ? OP_F32 : (c.precision == VITSB_PREC_BF16 ? OP_BF16 : OP_F16);
-  split16 = op != OP_F32;
-  { const char* ev = getenv("VITSB_MRF_SEP"); mrf_separate = !(ev && ev[0] == '0'); }
-  { const char* ev = getenv("VITSB_FLOW_IN_SPLIT"); flow_in_split = split16 && (ev ? ev[0] == '1' : op == OP_BF16); }   // bf16 operands (8x the rounding) keep the split
   {
-    const char* ev = getenv("VITSB_RB_FUSED");
-    rb_fused = op != OP_F32 && !(ev && ev[0] == '0');
-    int Cs = c.upsample_initial_channel;
-    for (int i = 0; i < c.n_upsamples && rb_fused; ++i) {
-      Cs /= 2;
-      for (int j = 0; j < c.n_resblock_kernels; ++j)
-        for (int d = 0; d < c.n_resblock_dilations; ++d)
-          if (!rb_fused_supported(Cs, c.resblock_kernel_sizes[j], c.resblock_dilation_sizes[j][d], 1)) rb_fused = false;
-    }
+    int Cl = c.upsample_initial_channel;
+    for (int i = 0; i < c.n_upsamples; ++i) Cl /= 2;
+    if (!conv_post_supported(Cl, 7)) return bad("conv_post input channels");
   }
   up_total = 1;
   for (int i = 0; i < c.n_upsamples; ++i) up_total *= c.upsample_rates[i];
+  return resolve_plan();
+}
+
+// precision + options -> the launch plan (which fused kernels run); called at create and at the top of every load
+int Engine::resolve_plan() {
+  const vitsb_config& c = cfg;
+  op = c.precision == VITSB_PREC_FP32 ? OP_F32 : (c.precision == VITSB_PREC_BF16 ? OP_BF16 : OP_F16);
+  split16 = op != OP_F32;
+  flow_in_split = split16 && (opt_flow_in_split >= 0 ? opt_flow_in_split == 1 : op == OP_BF16);   // bf16 operands (8x the rounding) keep the split
+  // fused ResBlock iterations: every (C, k, dilation) must be a compiled shape, and the MRF average is the separate
+  // pass over <= 3 branch streams
+  rb_fused = op != OP_F32 && opt_rb_fused != 0 && c.n_resblock_kernels <= 3;
+  int Cs = c.upsample_initial_channel;
+  for (int i = 0; i < c.n_upsamples && rb_fused; ++i) {
+    Cs /= 2;
+    for (int j = 0; j < c.n_resblock_kernels; ++j)
+      for (int d = 0; d < c.n_resblock_dilations; ++d)
+        if (!rb_fused_supported(Cs, c.resblock_kernel_sizes[j], c.resblock_dilation_sizes[j][d], 1)) rb_fused = false;
+  }
+  flow_fused = op != OP_F32 && opt_flow_fused != 0 && !flow_in_split &&
+               flow_fused_supported(c.inter_channels, c.hidden_channels, c.flow_kernel_size, c.flow_n_layers, c.flow_dilation_rate,
+                                    c.n_flows, op);
   return VITSB_OK;
 }
 
@@ -171,6 +232,11 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
   }
 
   const vitsb_config& c = cfg;
+  // A reload invalidates everything derived from the old pools: cached graph execs hold the old weight pointers and
+  // tensor maps, and a failed reload must not leave a half-built plan marked as loaded.
+  drop_graphs();
+  loaded = false;
+  resolve_plan();
   h_w.clear(); h_bias.clear(); h_condW.clear(); h_condB.clear(); h_post.clear();
   couplings.clear(); stages.clear();
   Ncond = 0; flop_per_frame = 0;
@@ -231,6 +297,102 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
     const bool flipped = ((step + 1) % 2) == 1;          // number of Flips applied before this coupling is step+1
     const std::string p = "flow.flows." + std::to_string(2 * fi) + ".";
     Coupling cp;
+    if (flow_fused) {
+      // ---- packing of the fused coupling kernel (flow_fused.cu) ----
+      const HostTensor* wpre = L.weight(p + "pre", {H, half, 1});
+      const HostTensor* bpre = L.bias(p + "pre", H);
+      const HostTensor* wpost = L.weight(p + "post", {half, H, 1});
+      const HostTensor* bpost = L.bias(p + "post", half);
+      const HostTensor* cw = L.weight(p + "enc.cond_layer", {2 * H * nl, gin});
+      const HostTensor* cb = L.bias(p + "enc.cond_layer", 2 * H * nl);
+      if (!wpre || !bpre || !wpost || !bpost || !cw || !cb) { ok = false; break; }
+      constexpr int XW = 128;                              // x0 window of the z row: [0, 128) or [inter - 128, inter)
+      FlowFusedWeights& fw = cp.ff;
+      fw.xwin = flipped ? IC - XW : 0;
+      fw.coff = cp.coff = flipped ? 0 : half;
+      // pre: [H][Wh(XW) | Wl(XW)], zero on the window columns that belong to x1
+      fw.w_pre = h_w.size();
+      h_w.resize(h_w.size() + (size_t)H * 2 * XW, 0.f);
+      for (int nn = 0; nn < H; ++nn)
+        for (int wc = 0; wc < XW; ++wc) {
+          const int pc = fw.xwin + wc;                     // physical z column
+          const int cl = flipped ? IC - 1 - pc : pc;       // logical channel (Flip folded, modules.py:278-289)
+          if (cl < 0 || cl >= half) continue;
+          const float v = wpre->v[(size_t)nn * half + cl], hi = op_round(v);
+          h_w[fw.w_pre + (size_t)nn * 2 * XW + wc] = hi;
+          h_w[fw.w_pre + (size_t)nn * 2 * XW + XW + wc] = op_round(v - hi);
+        }
+      // in_layers: gate rows in 128-row groups [tanh 64 | sigmoid 64], all layers contiguous (weights and cond columns)
+      std::vector<const HostTensor*> rsw(nl), rsb(nl);
+      for (int l = 0; l < nl && ok; ++l) {
+        const std::string li = std::to_string(l);
+        PackedConv pc = pack_conv(L.weight(p + "enc.in_layers." + li, {2 * H, H, fk}), L.bias(p + "enc.in_layers." + li, 2 * H),
+                                  gate_rows(2 * H, 128), iota_rows(0, H), fk, 1, true, 128, cw, cb, l * 2 * H, H, false);
+        if (l == 0) { fw.w_in = pc.w_off; fw.cond_off = pc.cond_off; }
+        cp.flop_per_pos += pc.flop_per_pos;
+        const int rs = l < nl - 1 ? 2 * H : H;
+        rsw[l] = L.weight(p + "enc.res_skip_layers." + li, {rs, H, 1});
+        rsb[l] = L.bias(p + "enc.res_skip_layers." + li, rs);
+        if (!rsw[l] || !rsb[l]) ok = false;
+        else cp.flop_per_pos += 2.0 * H * rs;
+      }
+      if (!ok) break;
+      cp.flop_per_pos += 2.0 * half * H * 2;               // pre + post
+      // res | (post o skip): rows [res H | m half] per layer, K = [Wh(H) | Wl(H)].  post is a 1x1 conv on the skip sum
+      // (modules.py:366), so post(sum_l skip_l(acts_l) + b) = sum_l (Wpost Wskip_l) acts_l + Wpost sum_l b_l + b_post.
+      const int RS = H + half;
+      fw.w_rs = h_w.size();
+      h_w.resize(h_w.size() + (size_t)nl * RS * 2 * H, 0.f);
+      std::vector<double> bskip(H, 0.0);
+      std::vector<double> comp((size_t)half * H);
+      for (int l = 0; l < nl; ++l) {
+        float* base = h_w.data() + fw.w_rs + (size_t)l * RS * 2 * H;
+        const bool lastl = l == nl - 1;
+        const int skip0 = lastl ? 0 : H;                   // last layer: all H outputs go to the skip sum (modules.py:180-181)
+        if (!lastl)
+          for (int nn = 0; nn < H; ++nn)
+            for (int ci = 0; ci < H; ++ci) {
+              const float v = rsw[l]->v[(size_t)nn * H + ci], hi = op_round(v);
+              base[(size_t)nn * 2 * H + ci] = hi;
+              base[(size_t)nn * 2 * H + H + ci] = op_round(v - hi);
+            }
+        for (int r = 0; r < half; ++r) {
+          const int pr = flipped ? half - 1 - r : r;       // physical x1 offset r <-> logical post row
+          for (int ci = 0; ci < H; ++ci) {
+            double acc = 0;
+            for (int k2 = 0; k2 < H; ++k2) acc += (double)wpost->v[(size_t)pr * H + k2] * (double)rsw[l]->v[(size_t)(skip0 + k2) * H + ci];
+            comp[(size_t)r * H + ci] = acc;
+          }
+        }
+        for (int r = 0; r < half; ++r)
+          for (int ci = 0; ci < H; ++ci) {
+            const float v = (float)comp[(size_t)r * H + ci], hi = op_round(v);
+            base[(size_t)(H + r) * 2 * H + ci] = hi;
+            base[(size_t)(H + r) * 2 * H + H + ci] = op_round(v - hi);
+          }
+        for (int k2 = 0; k2 < H; ++k2) bskip[k2] += rsb[l]->v[skip0 + k2];
+      }
+      // biases: cumulative h bias per layer, and the composed bias of m
+      fw.b_cum = h_bias.size();
+      {
+        std::vector<float> cum(bpre->v.begin(), bpre->v.end());
+        for (int l = 0; l < nl; ++l) {
+          for (int nn = 0; nn < H; ++nn) h_bias.push_back(cum[nn]);
+          if (l < nl - 1) for (int nn = 0; nn < H; ++nn) cum[nn] += rsb[l]->v[nn];
+        }
+      }
+      fw.b_m = h_bias.size();
+      for (int r = 0; r < half; ++r) {
+        const int pr = flipped ? half - 1 - r : r;
+        double acc = bpost->v[pr];
+        for (int k2 = 0; k2 < H; ++k2) acc += (double)wpost->v[(size_t)pr * H + k2] * bskip[k2];
+        h_bias.push_back((float)acc);
+      }
+      while (h_bias.size() % 4) h_bias.push_back(0.f);
+      flop_per_frame += cp.flop_per_pos;
+      couplings.push_back(std::move(cp));
+      continue;
+    }
     // pre: 1x1 conv over the logical first half; K is the full physical row (zeros on the other half)
     {
       std::vector<int> cols(IC, -1);
@@ -271,10 +433,11 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
                           pick_nt(half), nullptr, nullptr, 0, H, true);
     }
     if (!ok) break;
-    flop_per_frame += cp.pre.flop_per_pos + cp.post.flop_per_pos;
-    for (auto& x : cp.in_layers) flop_per_frame += x.flop_per_pos;
-    for (auto& x : cp.res) flop_per_frame += x.flop_per_pos;
-    for (auto& x : cp.skip) flop_per_frame += x.flop_per_pos;
+    cp.flop_per_pos = cp.pre.flop_per_pos + cp.post.flop_per_pos;
+    for (auto& x : cp.in_layers) cp.flop_per_pos += x.flop_per_pos;
+    for (auto& x : cp.res) cp.flop_per_pos += x.flop_per_pos;
+    for (auto& x : cp.skip) cp.flop_per_pos += x.flop_per_pos;
+    flop_per_frame += cp.flop_per_pos;
     couplings.push_back(std::move(cp));
   }
 
@@ -359,13 +522,29 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
   }
   if (!ok) return fail(VITSB_ERR_WEIGHTS, L.err.empty() ? "weight packing failed" : L.err);
 
+  // every conv the 16-bit plan hands to the tensor-core kernel must be inside its envelope (otherwise the failure
+  // would surface as an opaque launch error in the middle of a call)
+  if (op != OP_F32) {
+    std::vector<const PackedConv*> tc = {&conv_pre};
+    for (const Coupling& cp : couplings) {
+      if (flow_fused) break;
+      tc.push_back(&cp.pre); tc.push_back(&cp.post);
+      for (auto& x : cp.in_layers) tc.push_back(&x);
+      for (auto& x : cp.res) tc.push_back(&x);
+      for (auto& x : cp.skip) tc.push_back(&x);
+    }
+    for (const Stage& st : stages) {
+      tc.push_back(&st.ups);
+      if (!rb_fused) for (auto& br : st.rb) for (auto& it : br) { tc.push_back(&it.c1); tc.push_back(&it.c2); }
+    }
+    for (const PackedConv* pc : tc)
+      if (!conv_tc_supported(pc->Cin, pc->in_ld > 0 ? pc->in_ld : pc->in_cols, pc->N, pc->NT, pc->k) || (pc->gate && pc->NT % 32 != 0))
+        return fail(VITSB_ERR_UNSUPPORTED, "unsupported config: a conv shape is outside the tensor-core kernel's envelope "
+                                           "(channels per tap must be 16, 32 or a multiple of 64)");
+  }
+
   // ---------------- upload ----------------
-  if (d_w) { cudaFree(d_w); d_w = nullptr; }
-  if (d_bias) { cudaFree(d_bias); d_bias = nullptr; }
-  if (d_condW) { cudaFree(d_condW); d_condW = nullptr; }
-  if (d_condB) { cudaFree(d_condB); d_condB = nullptr; }
-  if (d_post) { cudaFree(d_post); d_post = nullptr; }
-  loaded = false;
+  free_device();
   cudaError_t e = cudaSetDevice(device);
   auto up = [&](void** dptr, const void* src, size_t bytes) {
     if (e != cudaSuccess) return;
@@ -387,7 +566,8 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
   up((void**)&d_condW, h_condW.data(), h_condW.size() * 4);
   up((void**)&d_condB, h_condB.data(), h_condB.size() * 4);
   up((void**)&d_post, h_post.data(), h_post.size() * 4);
-  if (e != cudaSuccess) return fail(VITSB_ERR_CUDA, std::string("weight upload: ") + cudaGetErrorString(e));
+  if (e != cudaSuccess) { free_device(); return fail(VITSB_ERR_CUDA, std::string("weight upload: ") + cudaGetErrorString(e)); }
+  if (cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || num_sms <= 0) num_sms = 148;
   std::vector<float>().swap(h_w); std::vector<float>().swap(h_condW);
   loaded = true;
   return VITSB_OK;

@@ -61,7 +61,7 @@ namespace vitsb {
 #define VITSB_BIAS_SMEM_MINC 64
 #endif
 constexpr int kBiasSmemMinC = VITSB_BIAS_SMEM_MINC;      // channel count from which the epilogues read biases from shared memory
-constexpr int kRbMaxB = 512;
+constexpr int kRbMaxB = kMaxBatchRows;
 constexpr uint32_t kRbSmemBudget = 220 * 1024;
 constexpr int kRbMaxSlab = 16, kRbBars = 97;
 
@@ -121,70 +121,7 @@ struct RbRt {
   int dbg;                   // VITSB_RB_DBG ablation mask (timing experiments only; results are wrong when set)
 };
 
-// Swizzle<B,4,3> on a byte address whose buffer base is 1024-aligned: XOR bits [4,4+B) with bits [7,7+B)
-template <int ROWBYTES>
-__device__ __forceinline__ uint32_t swz_addr(uint32_t addr) {
-  constexpr uint32_t mask = ROWBYTES == 128 ? 7u : (ROWBYTES == 64 ? 3u : 1u);
-  return addr ^ (((addr >> 7) & mask) << 4);
-}
-__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
-  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
-}
-__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
-  uint4 v;
-  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
-  return v;
-}
-// Prefetching global load that the compiler may not sink to its first use (plain __ldg of read-only data is
-// free to move across the memory-clobbering tcgen05 asm statements, which silently undoes a software prefetch).
-__device__ __forceinline__ uint4 ldg_nc_v4_pinned(const void* p) {
-  uint4 v;
-  asm volatile("ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
-  return v;
-}
-// 16 consecutive floats from shared memory (all lanes read the same address: broadcast, conflict-free)
-__device__ __forceinline__ void lds16(uint32_t addr, float (&v)[16]) {
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    const uint4 x = ld_shared_v4(addr + 16 * i);
-    v[4 * i] = __uint_as_float(x.x); v[4 * i + 1] = __uint_as_float(x.y); v[4 * i + 2] = __uint_as_float(x.z); v[4 * i + 3] = __uint_as_float(x.w);
-  }
-}
-__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
-// ring / buffer cursor without integer division
-struct Cursor {
-  int idx; uint32_t phase;
-  __device__ __forceinline__ void next(int n) { if (++idx == n) { idx = 0; phase ^= 1u; } }
-};
-
-// tanh(a) * sigmoid(b) for the G tile (rounded to the 16-bit operand type right after).
-//   default: 2 MUFU.TANH, sigmoid(b) = 0.5 + 0.5 tanh(b/2); tanh.approx has ~2^-11 relative
-//   error, the same size as the fp16 rounding of the result (parity measured in tests).
-//   VITSB_GATE_EXACT: 2x ex2 + rcp, ~1e-6 relative: (1 - e^-2a) / ((1 + e^-2a)(1 + e^-b)),
-//   a clamped at -20 and b at -40 so the denominator stays inside the __fdividef range.
-__device__ __forceinline__ float tanh_approx(float x) {
-  float y;
-  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ float ex2_approx(float x) {
-  float y;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ float gate_fast(float a, float b) {
-#ifdef VITSB_GATE_EXACT
-  const float ea = ex2_approx(-2.885390081777927f * fmaxf(a, -20.f));
-  const float eb = ex2_approx(-1.4426950408889634f * fmaxf(b, -40.f));
-  return __fdividef(1.0f - ea, (1.0f + ea) * (1.0f + eb));
-#else
-  const float th = 0.5f * tanh_approx(a);
-  return fmaf(th, tanh_approx(0.5f * b), th);
-#endif
-}
-
-template <typename OpT, int C, int KT, bool LAST>
+template <typename OpT, int C, int KT>
 __global__ void __launch_bounds__((RbT<C, KT>::THREADS), 1)
 rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmW1,
                 const __grid_constant__ CUtensorMap tmW2, const RbArgs a, const RbRt rt) {
@@ -204,7 +141,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   const uint32_t sG = sSlab + rt.nSlab * slab_set;                             // [NBUF][nCB2][G_BYTES]
   const uint32_t sW = sG + G::NBUF * G::G_SET;                                 // all boxes (c1 then c2), or the ring
   const uint32_t sW2 = sW + G::NBOX1 * G::W1_TX;                               // resident mode: c2 boxes
-  constexpr bool kStage = !LAST && G::STAGE_OUT;                               // TMA-stored output rows (mid iterations)
+  constexpr bool kStage = G::STAGE_OUT;                                        // TMA-stored output rows
   const uint32_t sStage = sW + (G::STATIONARY ? G::W_ALL : rt.nW * G::W_SLOT); // [NGRP][128][CB_O] output staging
   const uint32_t bars = sStage + (kStage ? G::STG_ALL : 0u);
   // mbarriers: up to kRbMaxSlab slabs, 8 accumulator / G-tile sets, 8 weight-ring slots (kRbBars in total)
@@ -569,8 +506,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     }
   } else if (warp >= 8) {
     // =================== epilogue 2: bias + residual + leaky_relu -> global ===================
-    // LAST = false: mid iteration, y_out = op(leaky_relu(c2 + bias + x)) only.
-    // LAST = true : last iteration of a branch: v = scale * (c2 + bias + x) [+ acc]; acc / next-stage stores (MRF).
+    // y_out = op(leaky_relu(c2 + bias + x)).  The MRF average over the branches' final y streams (models.py:311-314) is
+    // a separate coalesced pass (mrf_sum_kernel / conv_post's tile load): summing the other branches here cost one
+    // exposed DRAM round trip per 16-column chunk of this row-per-thread epilogue.
     const int q = warp & 3, r = q * 32 + lane;
     const int nSlab = rt.nSlab;
     const uint32_t slab_bytes = rt.slab_bytes;
@@ -669,7 +607,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
               ptx::bulk_commit();
             }
           }
-        } else if (!LAST) {
+        } else {
           if (in_range && !RB_DBG(1)) {
             uint32_t pk[8];
 #pragma unroll
@@ -683,42 +621,6 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
             d[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
             d[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
           }
-        } else if (in_range && !RB_DBG(1)) {
-          // MRF: the other branches' final x_j arrive as 16-bit y streams (models.py:311-314: xs += resblock(x))
-#pragma unroll
-          for (int s2 = 0; s2 < 2; ++s2) {
-            const void* ap = s2 == 0 ? a.add0 : a.add1;
-            if (ap && !RB_DBG(2)) {
-              const uint4* yp = reinterpret_cast<const uint4*>(reinterpret_cast<const OpT*>(ap) + orow + c0);
-              const uint4 z0 = __ldg(yp), z1 = __ldg(yp + 1);
-              const uint32_t zw[8] = {z0.x, z0.y, z0.z, z0.w, z1.x, z1.y, z1.z, z1.w};
-#pragma unroll
-              for (int i = 0; i < 8; ++i) {
-                const float2 y = Pack16<OpT>::unpack2(zw[i]);
-                v[2 * i] += fminf(y.x, 10.f * y.x);
-                v[2 * i + 1] += fminf(y.y, 10.f * y.y);
-              }
-            }
-          }
-#pragma unroll
-          for (int i = 0; i < 16; ++i) v[i] *= a.scale;
-          if ((a.acc_mode & RB_ACC_READ) && !RB_DBG(2)) {
-            float x[16];
-            load16(a.acc + orow + c0, x);
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] += x[i];
-          }
-          if (!live) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) v[i] = 0.f;
-          }
-          if (a.acc_mode & RB_ACC_STORE) store16(a.acc + orow + c0, v);
-          if (a.acc_mode & RB_EMIT_NEXT) {
-            if (a.nxt_f32) store16(a.nxt_f32 + orow + c0, v);
-            if (a.nxt_op) store_op16<OpT>(reinterpret_cast<OpT*>(a.nxt_op) + (a.nxt_split ? 2 : 1) * orow + c0, v, 0.1f,
-                                          a.nxt_split ? C : 0);
-          }
-          if (a.y_out) store_op16<OpT>(reinterpret_cast<OpT*>(a.y_out) + orow + c0, v, 0.1f, 0);
         }
       }
       ptx::tc_fence_before();
@@ -755,24 +657,22 @@ bool rb_fused_supported(int C, int k, int dil, int B) {
 
 namespace {
 
-template <typename OpT, int C, int KT, bool LAST>
-cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
+template <typename OpT, int C, int KT>
+cudaError_t launch_t(const RbLaunch& L, int op, const LaunchOpts& lo, cudaStream_t stream) {
   using G = RbT<C, KT>;
   RbRt rt{};
   rt.dil = L.dil; rt.p1 = (KT - 1) * L.dil / 2;
   rt.R1 = (kTileM + (KT - 1) * L.dil + 7) & ~7;
   rt.slab_bytes = ((uint32_t)rt.R1 * G::rb1 + 1023u) & ~1023u;
   const uint32_t slab_set = G::nCB1 * rt.slab_bytes;
-  const uint32_t fixed = 1024 + 8 * kRbBars + 64 + G::NBUF * G::G_SET + (LAST ? 0u : G::STG_ALL);
+  const uint32_t fixed = 1024 + 8 * kRbBars + 64 + G::NBUF * G::G_SET + G::STG_ALL;
   if (G::STATIONARY) {
     if (fixed + G::W_ALL + 2 * slab_set > kRbSmemBudget) return cudaErrorNotSupported;
     rt.nSlab = (int)((kRbSmemBudget - fixed - G::W_ALL) / slab_set);
     // slab lifetime: load + c1 only (RES_GLOBAL), or the whole 4-stage pipeline (C = 32 reads the residual from the slab:
     // ~6.7 k cycles from TMA issue to the store epilogue's release, so the tile period is that latency / nSlab - measured
     // 1.1 k cycles per tile with 6 slabs against ~0.4 k of tensor work; use all 8 barrier slots)
-    static int want_env = -1;
-    if (want_env < 0) { const char* e = getenv("VITSB_RB_NSLAB"); want_env = e ? atoi(e) : 0; }
-    const int want = want_env > 0 ? (want_env > kRbMaxSlab ? kRbMaxSlab : want_env) : (G::RES_GLOBAL ? 4 : G::NBUF + 4);
+    const int want = lo.rb_nslab > 0 ? (lo.rb_nslab > kRbMaxSlab ? kRbMaxSlab : lo.rb_nslab) : (G::RES_GLOBAL ? 4 : G::NBUF + 4);
     if (rt.nSlab > want) rt.nSlab = want;
   } else {
     // streamed weights: slabs first (2 when the accumulators are double-buffered), the rest to the ring
@@ -783,7 +683,9 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
     if (rt.nW > 8) rt.nW = 8;
   }
   rt.idesc = ptx::umma_idesc_f16(op == OP_BF16, kTileM * G::NCL, C);
+#ifdef VITSB_RB_DEBUG
   { static int dbg = -1; if (dbg < 0) { const char* e = getenv("VITSB_RB_DBG"); dbg = e ? atoi(e) : 0; } rt.dbg = dbg; }
+#endif
 
   TmaEncodeFn enc = tma_encode_fn();
   if (!enc) return cudaErrorNotSupported;
@@ -824,19 +726,17 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   }
   if (!ok) { fprintf(stderr, "rb_fused: tensor map encode failed (C=%d k=%d)\n", C, KT); return cudaErrorInvalidValue; }
   const size_t wbytes = G::STATIONARY ? (size_t)G::W_ALL : (size_t)rt.nW * G::W_SLOT;
-  const size_t smem = 1024 + (size_t)rt.nSlab * slab_set + (size_t)G::NBUF * G::G_SET + wbytes + (LAST ? 0u : G::STG_ALL) + 8 * kRbBars + 64;
-  static int num_sms = 0;
-  static std::once_flag once;     // one flag per template instantiation
-  static cudaError_t attr_err = cudaSuccess;
-  std::call_once(once, [] {
+  const size_t smem = 1024 + (size_t)rt.nSlab * slab_set + (size_t)G::NBUF * G::G_SET + wbytes + G::STG_ALL + 8 * kRbBars + 64;
+  const int num_sms = lo.num_sms > 0 ? lo.num_sms : 148;
+  static PerDeviceOnce smem_optin;     // one per template instantiation; the opt-in itself is per device
+  const cudaError_t attr_err = smem_optin.run([] {
     // opt-in limit is 227 KB per CTA INCLUDING the kernel's static shared memory (tile table)
     cudaFuncAttributes fa{};
-    attr_err = cudaFuncGetAttributes(&fa, rb_fused_kernel<OpT, C, KT, LAST>);
-    if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(rb_fused_kernel<OpT, C, KT, LAST>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                      232448 - (int)fa.sharedSizeBytes);
-    int dev = 0; cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaError_t e = cudaFuncGetAttributes(&fa, rb_fused_kernel<OpT, C, KT>);
+    if (e == cudaSuccess)
+      e = cudaFuncSetAttribute(rb_fused_kernel<OpT, C, KT>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                               232448 - (int)fa.sharedSizeBytes);
+    return e;
   });
   if (attr_err != cudaSuccess) { fprintf(stderr, "rb_fused: cudaFuncSetAttribute failed: %s\n", cudaGetErrorString(attr_err)); return attr_err; }
   // upper bound on tiles -> grid (persistent: at most one CTA per SM)
@@ -850,12 +750,14 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   args.y_res = L.y_in;
   static long long* d_trace = nullptr;
   static int trace_C = -1, trace_K = 0, trace_left = 0, trace_first = 0;
+#ifdef VITSB_RB_DEBUG
   if (trace_C < 0) {
     const char* e = getenv("VITSB_RB_TRACE");      // "C,k,count": dump the CTA-0 timeline of the first `count` launches of that shape
     trace_C = 0;
     if (e && sscanf(e, "%d,%d,%d,%d", &trace_C, &trace_K, &trace_left, &trace_first) >= 3) cudaMalloc(&d_trace, 7 * 16 * 2 * sizeof(long long));
   }
-  const bool tracing = d_trace && trace_C == C && trace_K == KT && trace_left > 0 && !LAST;
+#endif
+  const bool tracing = d_trace && trace_C == C && trace_K == KT && trace_left > 0;
   if (tracing) { cudaMemsetAsync(d_trace, 0, 7 * 16 * 2 * sizeof(long long), stream); args.trace = d_trace; rt.trace_t0 = trace_first; }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid, 1, 1);
@@ -867,8 +769,8 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
   at[0].val.clusterDim.x = G::NCL; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
   at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   at[1].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = at; cfg.numAttrs = pdl_enabled() ? 2 : 1;
-  cudaError_t le = cudaLaunchKernelEx(&cfg, rb_fused_kernel<OpT, C, KT, LAST>, tmY, tmO, tmW1, tmW2, args, rt);
+  cfg.attrs = at; cfg.numAttrs = lo.pdl ? 2 : 1;
+  cudaError_t le = cudaLaunchKernelEx(&cfg, rb_fused_kernel<OpT, C, KT>, tmY, tmO, tmW1, tmW2, args, rt);
   if (le == cudaSuccess) le = cudaGetLastError();
   if (tracing && le == cudaSuccess) {
     --trace_left;
@@ -896,10 +798,9 @@ cudaError_t launch_t(const RbLaunch& L, int op, cudaStream_t stream) {
 }
 
 template <typename OpT>
-cudaError_t dispatch(const RbLaunch& L, int op, cudaStream_t s) {
-  // mid iterations only write y_out; anything else (MRF accumulate / next-stage emit / scale) takes the general epilogue
-  const bool last = L.a.acc_mode != 0 || L.a.scale != 1.f || !L.a.y_out;
-#define VITSB_RB_CASE(CC, KK) if (L.C == CC && L.k == KK) return last ? launch_t<OpT, CC, KK, true>(L, op, s) : launch_t<OpT, CC, KK, false>(L, op, s);
+cudaError_t dispatch(const RbLaunch& L, int op, const LaunchOpts& lo, cudaStream_t s) {
+  if (!L.a.y_out) return cudaErrorInvalidValue;
+#define VITSB_RB_CASE(CC, KK) if (L.C == CC && L.k == KK) return launch_t<OpT, CC, KK>(L, op, lo, s);
   VITSB_RB_CASE(32, 3) VITSB_RB_CASE(32, 7) VITSB_RB_CASE(32, 11)
   VITSB_RB_CASE(64, 3) VITSB_RB_CASE(64, 7) VITSB_RB_CASE(64, 11)
   VITSB_RB_CASE(128, 3) VITSB_RB_CASE(128, 7) VITSB_RB_CASE(128, 11)
@@ -910,9 +811,9 @@ cudaError_t dispatch(const RbLaunch& L, int op, cudaStream_t s) {
 
 }  // namespace
 
-cudaError_t launch_rb_fused(const RbLaunch& L, int op, cudaStream_t stream) {
+cudaError_t launch_rb_fused(const RbLaunch& L, int op, const LaunchOpts& lo, cudaStream_t stream) {
   if (op == OP_F32 || !rb_fused_supported(L.C, L.k, L.dil, L.B)) return cudaErrorNotSupported;
-  return op == OP_BF16 ? dispatch<__nv_bfloat16>(L, op, stream) : dispatch<__half>(L, op, stream);
+  return op == OP_BF16 ? dispatch<__nv_bfloat16>(L, op, lo, stream) : dispatch<__half>(L, op, lo, stream);
 }
 
 }  // namespace vitsb

@@ -59,18 +59,82 @@ __device__ __forceinline__ void store16(float* dst, const float (&v)[16]) {
   for (int i = 0; i < 4; ++i) d[i] = make_float4(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
 }
 
+// Swizzle<B,4,3> on a byte address whose buffer base is 1024-aligned: XOR bits [4,4+B) with bits [7,7+B)
+template <int ROWBYTES>
+__device__ __forceinline__ uint32_t swz_addr(uint32_t addr) {
+  constexpr uint32_t mask = ROWBYTES == 128 ? 7u : (ROWBYTES == 64 ? 3u : 1u);
+  return addr ^ (((addr >> 7) & mask) << 4);
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+// Prefetching global load that the compiler may not sink to its first use (plain __ldg of read-only data is
+// free to move across the memory-clobbering tcgen05 asm statements, which silently undoes a software prefetch).
+__device__ __forceinline__ uint4 ldg_nc_v4_pinned(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.nc.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+// 16 consecutive floats from shared memory (all lanes read the same address: broadcast, conflict-free)
+__device__ __forceinline__ void lds16(uint32_t addr, float (&v)[16]) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const uint4 x = ld_shared_v4(addr + 16 * i);
+    v[4 * i] = __uint_as_float(x.x); v[4 * i + 1] = __uint_as_float(x.y); v[4 * i + 2] = __uint_as_float(x.z); v[4 * i + 3] = __uint_as_float(x.w);
+  }
+}
+__device__ __forceinline__ void fence_proxy_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// ring / buffer cursor without integer division
+struct Cursor {
+  int idx; uint32_t phase;
+  __device__ __forceinline__ void next(int n) { if (++idx == n) { idx = 0; phase ^= 1u; } }
+};
+
+// tanh(a) * sigmoid(b) for the G tile (rounded to the 16-bit operand type right after).
+//   default: 2 MUFU.TANH, sigmoid(b) = 0.5 + 0.5 tanh(b/2); tanh.approx has ~2^-11 relative
+//   error, the same size as the fp16 rounding of the result (parity measured in tests).
+//   VITSB_GATE_EXACT: 2x ex2 + rcp, ~1e-6 relative: (1 - e^-2a) / ((1 + e^-2a)(1 + e^-b)),
+//   a clamped at -20 and b at -40 so the denominator stays inside the __fdividef range.
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float ex2_approx(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float gate_fast(float a, float b) {
+#ifdef VITSB_GATE_EXACT
+  const float ea = ex2_approx(-2.885390081777927f * fmaxf(a, -20.f));
+  const float eb = ex2_approx(-1.4426950408889634f * fmaxf(b, -40.f));
+  return __fdividef(1.0f - ea, (1.0f + ea) * (1.0f + eb));
+#else
+  const float th = 0.5f * tanh_approx(a);
+  return fmaf(th, tanh_approx(0.5f * b), th);
+#endif
+}
+
 // Tile table of a ragged batch, built by ONE full warp: prefix[b] = number of `tile_rows`-row tiles before batch
 // row b, prefix[B] = total.  Tiles of row b cover rows [0, min(L, valid_b + kHaloRows)).  Lane-parallel length
 // loads + a shuffle scan: a single thread walking len[] paid one dependent global-load latency per few rows in
 // the prologue of every launch.
-__device__ __forceinline__ void build_tile_prefix(int* prefix, int B, const int* len, int len_mul, int L, int tile_rows, int lane) {
+__device__ __forceinline__ void build_tile_prefix(int* prefix, int B, const int* len, int len_mul, int L, int tile_rows, int lane,
+                                                  int extra_rows = kHaloRows) {
   int carry = 0;
   for (int b0 = 0; b0 < B; b0 += 32) {
     const int b = b0 + lane;
     int n = 0;
     if (b < B) {
       const int valid = len ? len[b] * len_mul : L;
-      const int rows = valid + kHaloRows < L ? valid + kHaloRows : L;   // rows nobody reads are skipped
+      const int rows = valid + extra_rows < L ? valid + extra_rows : L;   // rows nobody reads are skipped
       n = (rows + tile_rows - 1) / tile_rows;
     }
     int inc = n;

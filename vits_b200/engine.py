@@ -33,7 +33,9 @@ def _hot_items(state_dict):
 
 
 class FlowDecoder:
-    def __init__(self, cfg, state_dict: Dict[str, torch.Tensor], device="cuda:0", precision: str = "fp16"):
+    def __init__(self, cfg, state_dict: Dict[str, torch.Tensor], device="cuda:0", precision: str = "fp16",
+                 options: Optional[Dict[str, int]] = None):
+        """`options`: vitsb_set_option keys (include/vitsb200.h), applied before the weights are packed."""
         if not torch.cuda.is_available():
             raise RuntimeError("vits_b200.FlowDecoder needs a CUDA device (sm_100a); there is no CPU fallback")
         self.lib = L.load_library()
@@ -52,6 +54,8 @@ class FlowDecoder:
             raise L.VitsbError(rc, self.lib.vitsb_last_error(None).decode())
         self._h = h
         self._ws: Optional[torch.Tensor] = None
+        for k, v in (options or {}).items():
+            self.set_option(k, v)
         self.load_state_dict(state_dict)
         self.total_upsample = self.lib.vitsb_total_upsample(self._h)
         self.flop_per_frame = self.lib.vitsb_flop_per_frame(self._h)
@@ -87,6 +91,15 @@ class FlowDecoder:
                 arr[i].shape[d] = t.shape[d]
         self._check(self.lib.vitsb_load_weights(self._h, arr, len(keep)))
 
+    def set_option(self, key: str, value: int):
+        self._check(self.lib.vitsb_set_option(self._h, key.encode(), int(value)))
+
+    def get_option(self, key: str) -> int:
+        v = C.c_int()
+        if self.lib.vitsb_get_option(self._h, key.encode(), C.byref(v)) != 0:
+            raise KeyError(key)
+        return int(v.value)
+
     # -- helpers -------------------------------------------------------------
     def workspace_bytes(self, B: int, T: int) -> int:
         return int(self.lib.vitsb_workspace_bytes(self._h, B, T))
@@ -95,7 +108,7 @@ class FlowDecoder:
         return int(self.lib.vitsb_launches_per_call(self._h, B, T))
 
     TAG_NAMES = {0: "pack", 1: "cond_gemv", 2: "unpack", 3: "conv_post", 4: "mrf_sum", 10: "flow.pre", 11: "flow.in_layers",
-                 12: "flow.res", 13: "flow.skip", 14: "flow.post", 20: "conv_pre"}
+                 12: "flow.res", 13: "flow.skip", 14: "flow.post", 15: "flow.fused", 20: "conv_pre"}
 
     def profile(self, enable: bool):
         self._check(self.lib.vitsb_profile(self._h, int(enable)))
@@ -181,13 +194,13 @@ class FlowDecoder:
 
     @torch.no_grad()
     def synthesize_pcm16(self, z_p: torch.Tensor, g: torch.Tensor, lengths: Optional[Sequence[int]] = None,
-                         ragged: bool = True, volume: float = 1.0) -> torch.Tensor:
+                         ragged: bool = True, volume: float = 1.0, out: Optional[torch.Tensor] = None) -> torch.Tensor:
         """synthesize() + VITSWrap.speaking's output step (vits_wrap.py:195) in the last kernel: int16 [B,1,192*T] =
         clip(wav * volume * 32767, -32768, 32767) truncated toward zero; half the D2H bytes."""
         z_p, g, lens, B, T = self._prep(z_p, g, lengths)
         with torch.cuda.device(self.device):
             ws = self._workspace(B, T)
-            pcm = torch.empty(B, 1, T * self.total_upsample, dtype=torch.int16, device=self.device)
+            pcm = out if out is not None else torch.empty(B, 1, T * self.total_upsample, dtype=torch.int16, device=self.device)
             self._check(self.lib.vitsb_synthesize_pcm16(self._h, z_p.data_ptr(), g.data_ptr(), lens, B, T, int(bool(ragged)),
                                                         float(volume), pcm.data_ptr(), ws.data_ptr(), ws.numel(), self._stream()))
         return pcm
@@ -265,9 +278,9 @@ class FlowDecoder:
             pos += n
         return out
 
-    def host_pipeline(self, B: int, T_max: int, depth: int = 2) -> "HostPipeline":
+    def host_pipeline(self, B: int, T_max: int, depth: int = 2, pcm16: bool = False, volume: float = 1.0) -> "HostPipeline":
         """Serving loop for HOST buffers: see HostPipeline."""
-        return HostPipeline(self, B, T_max, depth)
+        return HostPipeline(self, B, T_max, depth, pcm16, volume)
 
 
 class HostPipeline:
@@ -279,14 +292,18 @@ class HostPipeline:
     synthesis of request i (PCIe moves ~10 MB each way per 16-utterance batch, ~8 % of the synthesis time).
     Every request still pays its own H2D and D2H; nothing is cached between requests."""
 
-    def __init__(self, eng: FlowDecoder, B: int, T_max: int, depth: int = 2):
+    def __init__(self, eng: FlowDecoder, B: int, T_max: int, depth: int = 2, pcm16: bool = False, volume: float = 1.0):
+        """pcm16: the last kernel writes int16 PCM (vits_wrap.py:195, `volume` applied) and that is what travels to the
+        host: half the device->host bytes of the float waveform."""
         self.eng, self.B, self.T, self.depth = eng, B, T_max, depth
+        self.pcm16, self.volume = pcm16, volume
+        self.out_dtype = torch.int16 if pcm16 else torch.float32
         dev = eng.device
         with torch.cuda.device(dev):
             self.h2d, self.d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
             self.z = [torch.empty(B, eng.inter_channels, T_max, dtype=torch.float32, device=dev) for _ in range(depth)]
             self.g = [torch.empty(B, eng.gin_channels, dtype=torch.float32, device=dev) for _ in range(depth)]
-            self.wav = [torch.empty(B, 1, T_max * eng.total_upsample, dtype=torch.float32, device=dev) for _ in range(depth)]
+            self.wav = [torch.empty(B, 1, T_max * eng.total_upsample, dtype=self.out_dtype, device=dev) for _ in range(depth)]
             self.ev_in = [torch.cuda.Event() for _ in range(depth)]      # latents of the slot are on the device
             self.ev_comp = [torch.cuda.Event() for _ in range(depth)]    # synthesis of the slot has finished
             self.ev_out = [torch.cuda.Event() for _ in range(depth)]     # waveform of the slot is in host memory
@@ -311,7 +328,10 @@ class HostPipeline:
             cur.wait_event(self.ev_in[s])
             if self.n >= self.depth:
                 cur.wait_event(self.ev_out[s])               # the slot's previous waveform has left the device
-            self.eng.synthesize(self.z[s], self.g[s], lengths, ragged, out=self.wav[s])
+            if self.pcm16:
+                self.eng.synthesize_pcm16(self.z[s], self.g[s], lengths, ragged, volume=self.volume, out=self.wav[s])
+            else:
+                self.eng.synthesize(self.z[s], self.g[s], lengths, ragged, out=self.wav[s])
             self.ev_comp[s].record(cur)
             self.d2h.wait_event(self.ev_comp[s])
             with torch.cuda.stream(self.d2h):
@@ -321,8 +341,8 @@ class HostPipeline:
         return self.n - 1
 
     def wait(self, ticket: int) -> None:
-        if ticket < self.n - self.depth:
-            return                                           # its slot has been reused: it completed long ago
+        # The slot's event may have been re-recorded by a later request that reused the slot; the D2H stream is in
+        # order, so that later event also covers `ticket`'s copy.
         self.ev_out[ticket % self.depth].synchronize()
 
     def join_event(self, ticket: int) -> torch.cuda.Event:

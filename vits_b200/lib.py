@@ -40,6 +40,8 @@ SYMBOLS = {
     "vitsb_create": (C.c_int, [C.POINTER(VitsbConfig), C.c_int, C.POINTER(_P)]),
     "vitsb_destroy": (None, [_P]),
     "vitsb_last_error": (C.c_char_p, [_P]),
+    "vitsb_set_option": (C.c_int, [_P, C.c_char_p, C.c_int]),
+    "vitsb_get_option": (C.c_int, [_P, C.c_char_p, C.POINTER(C.c_int)]),
     "vitsb_load_weights": (C.c_int, [_P, C.POINTER(VitsbTensorDesc), C.c_int]),
     "vitsb_workspace_bytes": (C.c_size_t, [_P, C.c_int, C.c_int]),
     "vitsb_flow_reverse": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.c_int, C.c_int, _P, _P, C.c_size_t, _P]),
