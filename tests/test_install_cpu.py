@@ -1,5 +1,5 @@
 """CPU: the stand-in model used by the GPU drop-in tests is faithful to the reference's own `SynthesizerTrn`
-(attribute names `vits_b200.install.config_from_model` reads, state_dict keys and shapes).  Needs the reference tree
+(attribute names `vits_b200.dropin.config_from_model` reads, state_dict keys and shapes).  Needs the reference tree
 (build container only); the stand-in's own consistency is checked everywhere."""
 import json
 import os
@@ -12,7 +12,7 @@ import torch
 from oracle import fixtures as FX
 from oracle import vits_oracle as O
 from tests.ref_standin import SynthesizerStandIn, load_fixture
-from vits_b200.install import config_from_model
+from vits_b200.dropin import config_from_model
 
 REF = os.environ.get("VITS_REF_PATH", "/root/reference/emotional-vits")
 

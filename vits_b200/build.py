@@ -46,10 +46,12 @@ def needs_build() -> bool:
     return any(os.path.getmtime(d) > t for d in deps)
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
-    if not force and not needs_build():
+def build(force: bool = False, verbose: bool = False, lib: str = LIB, extra_flags=()) -> str:
+    """lib / extra_flags: a differently built library next to the product one (e.g. libvitsb200_dbg.so with
+    -DVITSB_RB_DEBUG: timing-experiment hooks and clock64 traces; select it at run time with VITSB_LIB)."""
+    if lib == LIB and not force and not needs_build():
         return LIB
-    extra = os.environ.get("VITSB_EXTRA_NVCC", "").split()          # e.g. -DVITSB_RB_DEBUG for the timing-experiment hooks
+    extra = os.environ.get("VITSB_EXTRA_NVCC", "").split() + list(extra_flags)
     tag = hashlib.sha1(" ".join(NVCC_FLAGS + extra).encode()).hexdigest()[:8]
     os.makedirs(OBJ, exist_ok=True)
     nvcc = _nvcc()
@@ -74,11 +76,14 @@ def build(force: bool = False, verbose: bool = False) -> str:
                 raise RuntimeError(f"nvcc failed on {name}:\n" + r.stdout + r.stderr)
             if verbose:
                 print(r.stderr)
-    r = subprocess.run([nvcc] + NVCC_FLAGS + LINK_FLAGS + ["-o", LIB] + objs, capture_output=True, text=True)
+    r = subprocess.run([nvcc] + NVCC_FLAGS + LINK_FLAGS + ["-o", lib] + objs, capture_output=True, text=True)
     if r.returncode != 0:
         raise RuntimeError("nvcc link failed:\n" + r.stdout + r.stderr)
-    return LIB
+    return lib
 
 
 if __name__ == "__main__":
-    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))
+    if "--debug" in sys.argv:
+        print(build(lib=os.path.join(HERE, "libvitsb200_dbg.so"), extra_flags=["-DVITSB_RB_DEBUG"]))
+    else:
+        print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

@@ -31,6 +31,7 @@
 #include "tc_common.cuh"
 
 #include <cstdio>
+#include <cstdlib>
 #include <type_traits>
 
 namespace vitsb {
@@ -102,6 +103,12 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = s_tmem;
+  // clock64 timeline of CTA 0's first tile (debug build only): trace[slot] = cycles
+#ifdef VITSB_RB_DEBUG
+  auto trace = [&](int slot) { if (a.trace && blockIdx.x == 0 && lane == 0 && slot < 256) a.trace[slot] = clock64(); };
+#else
+  auto trace = [&](int) {};
+#endif
 
   const int total_tiles = s_prefix[a.B];
   const int my_tiles = total_tiles > (int)blockIdx.x ? (total_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
@@ -190,9 +197,11 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
     auto commit = [&](int b_) { if (leader) ptx::umma_commit(bar(b_)); };
     for (int n = 0; n < my_tiles; ++n) {
       // ---- pre: h = x0 * Wpre (3-term split), TMEM h columns written fresh ----
+      if (n == 0) trace(0);
       ptx::mbar_wait(bar(B_PRE + 0), n & 1);
       ptx::mbar_wait(bar(B_PRE + 1), n & 1);
       ptx::tc_fence_after();
+      if (n == 0) trace(1);
       for (int part = 0; part < 2; ++part)
         for (int kb = 0; kb < 2; ++kb)
           for (int nh = 0; nh < 2; ++nh) {
@@ -204,6 +213,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           }
       commit(B_AEMPTY + 0); commit(B_AEMPTY + 1);
       commit(B_HREADY);
+      if (n == 0) trace(2);
       for (int l = 0; l < nl; ++l) {
         const bool last = l == nl - 1;
         const int hh = n * nl + l;
@@ -211,6 +221,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           const int ai = (n * nl + l) * NPASS + p;        // accumulator use index: needs completion ai - 1 of acc_empty
           ptx::mbar_wait(bar(B_ACCE), (uint32_t)(ai & 1) ^ 1u);
           ptx::tc_fence_after();
+          if (n == 0) trace(16 + l * 16 + p * 2);           // in(p) may start
           const uint32_t d = tmem_base + TM_ACC;
           for (int j = 0; j < KT; ++j)
             for (int kb = 0; kb < NPASS; ++kb) {
@@ -219,6 +230,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
               stage_done();
             }
           commit(B_ACCF);
+          if (n == 0) trace(16 + l * 16 + p * 2 + 1);       // in(p) issued
         };
         auto do_rs = [&](int p) {
           const int s = p & 1;
@@ -226,6 +238,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           ptx::mbar_wait(bar(B_AFULL + s), fi & 1);
           if (l == 0 && p == 0) ptx::mbar_wait(bar(B_MEMPTY), (uint32_t)(n & 1) ^ 1u);   // previous tile's m has been read
           ptx::tc_fence_after();
+          if (n == 0) trace(16 + l * 16 + 8 + p * 2);       // rs(p) may start
           const uint64_t ahi = d16(sA + s * SLOT_B), alo = d16(sA + s * SLOT_B + TILE_B);
           for (int part = 0; part < 2; ++part) {
             if (!last) {
@@ -244,9 +257,11 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
             stage_done();
           }
           commit(B_AEMPTY + s);
+          if (n == 0) trace(16 + l * 16 + 8 + p * 2 + 1);   // rs(p) issued
         };
         ptx::mbar_wait(bar(B_HFULL), hh & 1);
         ptx::tc_fence_after();
+        if (n == 0) trace(3 + l);                            // h operand of layer l ready
         do_in(0);
         for (int p = 1; p < NPASS; ++p) { do_in(p); do_rs(p - 1); }
         do_rs(NPASS - 1);
@@ -278,6 +293,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
         // ---- h operand of layer l: TMEM h + cumulative bias -> 16-bit slab rows (zero outside the sequence) ----
         ptx::mbar_wait(bar(B_HREADY), (n * nl + l) & 1);
         ptx::tc_fence_after();
+        if (n == 0 && warp == 4) trace(96 + l * 16);         // h epilogue starts
 #pragma unroll 2
         for (int c = 0; c < 8; ++c) {
           const int ch = hf * 128 + c * 16;
@@ -300,6 +316,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) ptx::mbar_arrive(bar(B_HFULL));
+        if (n == 0 && warp == 4) trace(96 + l * 16 + 1);     // h epilogue done
         // ---- gate passes: acts[64 p .. 64 p + 63] = tanh(a + cond_a) * sigmoid(b + cond_b) as [hi | lo] tiles ----
         for (int p = 0; p < NPASS; ++p) {
           const int s = p & 1;
@@ -308,6 +325,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           ptx::mbar_wait(bar(B_ACCF), ai & 1);
           ptx::mbar_wait(bar(B_AEMPTY + s), (uint32_t)(k & 1) ^ 1u);
           ptx::tc_fence_after();
+          if (n == 0 && warp == 4) trace(96 + l * 16 + 2 + p * 2);     // gate(p) starts
           const float* cb = s_cond + l * 2 * H + p * 128;
 #pragma unroll
           for (int c = 0; c < 2; ++c) {
@@ -339,11 +357,13 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           ptx::tc_fence_before();
           __syncwarp();
           if (lane == 0) { ptx::mbar_arrive(bar(B_AFULL + s)); ptx::mbar_arrive(bar(B_ACCE)); }
+          if (n == 0 && warp == 4) trace(96 + l * 16 + 2 + p * 2 + 1); // gate(p) done
         }
       }
       // ---- x1 -= m + b_m on the tile's inner rows (modules.py:370-372; logs == 0), fp32 state + [hi | lo] operand copy ----
       ptx::mbar_wait(bar(B_MREADY), n & 1);
       ptx::tc_fence_after();
+      if (n == 0 && warp == 4) trace(12);                    // m ready
       const bool mine = live && r >= halo && r < kTileM - halo;
       const long long row = (long long)b * a.T + t;
 #pragma unroll
@@ -366,6 +386,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(bar(B_MEMPTY));
+      if (n == 0 && warp == 4) trace(13);                    // tile done
     }
   }
 
@@ -439,9 +460,36 @@ cudaError_t launch_flow_fused(const FlowFusedArgs& a, int op, const LaunchOpts& 
   const int num_sms = lo.num_sms > 0 ? lo.num_sms : 148;
   int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
   if (grid < 1) grid = 1;
-  if (op == OP_BF16) flow_fused_kernel<__nv_bfloat16><<<grid, THREADS, smem, stream>>>(tmZ, tmPre, tmIn, tmRS, tmRSm, a);
-  else flow_fused_kernel<__half><<<grid, THREADS, smem, stream>>>(tmZ, tmPre, tmIn, tmRS, tmRSm, a);
+  FlowFusedArgs args = a;
+#ifdef VITSB_RB_DEBUG
+  static long long* d_trace = nullptr;
+  static int trace_left = -1;
+  if (trace_left < 0) { const char* e = getenv("VITSB_FF_TRACE"); trace_left = e ? atoi(e) : 0; if (trace_left > 0) cudaMalloc(&d_trace, 256 * sizeof(long long)); }
+  const bool tracing = d_trace && trace_left > 0;
+  if (tracing) { cudaMemsetAsync(d_trace, 0, 256 * sizeof(long long), stream); args.trace = d_trace; }
+#endif
+  if (op == OP_BF16) flow_fused_kernel<__nv_bfloat16><<<grid, THREADS, smem, stream>>>(tmZ, tmPre, tmIn, tmRS, tmRSm, args);
+  else flow_fused_kernel<__half><<<grid, THREADS, smem, stream>>>(tmZ, tmPre, tmIn, tmRS, tmRSm, args);
   const cudaError_t le = cudaGetLastError();
+#ifdef VITSB_RB_DEBUG
+  if (tracing && le == cudaSuccess) {
+    --trace_left;
+    long long h[256];
+    cudaStreamSynchronize(stream);
+    cudaMemcpy(h, d_trace, sizeof(h), cudaMemcpyDeviceToHost);
+    long long t0 = h[0];
+    auto rel = [&](int i) { return h[i] ? h[i] - t0 : -1; };
+    fprintf(stderr, "flow_fused trace (cycles, CTA 0 tile 0; grid=%d): pre_wait %lld pre_issued %lld m_ready %lld tile_done %lld\n", grid, rel(1), rel(2), rel(12), rel(13));
+    for (int l = 0; l < nl; ++l) {
+      fprintf(stderr, "  L%d mma: h_full %lld |", l, rel(3 + l));
+      for (int p = 0; p < 4; ++p) fprintf(stderr, " in%d[%lld,%lld]", p, rel(16 + l * 16 + p * 2), rel(16 + l * 16 + p * 2 + 1));
+      for (int p = 0; p < 4; ++p) fprintf(stderr, " rs%d[%lld,%lld]", p, rel(16 + l * 16 + 8 + p * 2), rel(16 + l * 16 + 8 + p * 2 + 1));
+      fprintf(stderr, "\n  L%d epi: h[%lld,%lld]", l, rel(96 + l * 16), rel(96 + l * 16 + 1));
+      for (int p = 0; p < 4; ++p) fprintf(stderr, " g%d[%lld,%lld]", p, rel(96 + l * 16 + 2 + p * 2), rel(96 + l * 16 + 2 + p * 2 + 1));
+      fprintf(stderr, "\n");
+    }
+  }
+#endif
   if (le != cudaSuccess) fprintf(stderr, "flow_fused launch failed (%s): grid=%d smem=%zu nl=%d\n", cudaGetErrorString(le), grid, smem, nl);
   return le;
 }

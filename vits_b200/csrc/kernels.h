@@ -90,6 +90,7 @@ struct FlowFusedArgs {
   int T, B;
   const int* len;          // device [B] or null
   int m_tiles;             // host-known tile count (0 -> upper bound)
+  long long* trace;        // debug build: clock64 timeline of CTA 0 (VITSB_FF_TRACE), normally null
 };
 bool flow_fused_supported(int inter, int hidden, int kernel, int n_layers, const int* dilation_rates, int n_flows, int op);
 int flow_fused_tile_rows(int n_layers);          // output rows per 128-row tile
