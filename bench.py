@@ -8,8 +8,9 @@ A step is one `synthesize` pass (reverse flow + decoder)
 over one batch of synthetic latents.  Workload at N=1 is BASELINE.json
 configs[1]: 16 mixed-length utterances (1-10 s, masked/ragged), emotional-vits
 default config, random-init weights at fan-in scale, explicitly injected noise.
-For N>1 the global batch is 16*N utterances sharded by utterance (LPT by
-length), one process per GPU, no collective on the synthesis path (weak scaling).
+For N>1 the global batch is 16*N utterances sharded by utterance, one process
+per GPU, the same length set on every rank (so per-GPU work is identical at every
+N), no collective on the synthesis path (weak scaling).
 
 Prints ONE JSON line (rank 0).  `--impl reference` times the CPU oracle port of
 the reference path on the host cores instead (see oracle/vits_oracle.py).
@@ -43,7 +44,7 @@ def parse():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--precision", default="fp16", choices=["fp16", "bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--e2e-sync", action="store_true", help="time e2e as one blocking synthesize_host call per step instead of the depth-2 host pipeline")
+    ap.add_argument("--no-side-legs", action="store_true", help="skip the sustained / varying-lengths / C1 / C3 / C4 side records")
     ap.add_argument("--profile-out", default=None, help="write the per-launch-family table to this file")
     ap.add_argument("--batch-per-gpu", type=int, default=PER_GPU_BATCH,
                     help="utterances per GPU and step (default 16 = BASELINE config C2; 64-512 are C4 sweep points, not the headline)")
@@ -60,8 +61,11 @@ def peaks():
 
 
 def global_lengths(n_gpus: int):
+    """Weak scaling with IDENTICAL per-GPU work: every rank gets the same 16-length set of config C2 (seed 1234), so
+    the per-N efficiency the driver computes isolates scaling from workload (latents and speakers differ per rank)."""
     from oracle import fixtures as FX
-    return FX.make_lengths(PER_GPU_BATCH * n_gpus, LEN_LO, LEN_HI, seed=1234 if n_gpus == 1 else 1234 + n_gpus)
+    base = FX.make_lengths(PER_GPU_BATCH, LEN_LO, LEN_HI, seed=1234)
+    return base * n_gpus
 
 
 def lpt_shard(lengths, n):
@@ -190,8 +194,8 @@ def run_b200(args):
     import torch
     import torch.distributed as dist
     from oracle import fixtures as FX            # input/weight generator only (never on the timed path)
-    from vits_b200.config import HotPathConfig
     from vits_b200 import FlowDecoder
+    from vits_b200.config import HotPathConfig
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -207,15 +211,15 @@ def run_b200(args):
     sd = FX.make_state_dict(cfg, seed=1234)
     eng = FlowDecoder(cfg, sd, device=dev, precision=args.precision)
     all_len = global_lengths(world)
-    mine = lpt_shard(all_len, world)[rank]
+    mine = list(range(rank * PER_GPU_BATCH, (rank + 1) * PER_GPU_BATCH))          # identical length set on every rank
     lens = [all_len[i] for i in mine]
-    lat = FX.make_latents(cfg, lens, seed=1234 + rank)
+    lat = FX.make_latents(cfg, lens, seed=1234 + rank)                           # distinct latents and speakers (g) per rank and row
     B, T = len(lens), max(lens)
+    up = eng.total_upsample
     z_host = lat["z_p"].pin_memory()
     g_host = lat["g"].pin_memory()
     z_dev, g_dev = z_host.to(dev), g_host.to(dev)
-    wav_dev = torch.empty(B, 1, T * eng.total_upsample, dtype=torch.float32, device=dev)
-    wav_host = torch.empty(B, 1, T * eng.total_upsample, dtype=torch.float32).pin_memory()
+    wav_dev = torch.empty(B, 1, T * up, dtype=torch.float32, device=dev)
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)       # > 126 MB L2
     audio_s = sum(lens) * FRAME_SEC
     frames = sum(lens)
@@ -229,12 +233,9 @@ def run_b200(args):
     def step_resident():
         eng.synthesize(z_dev, g_dev, lens, ragged=True, out=wav_dev)
 
-    def step_e2e():
-        eng.synthesize_host(z_host, g_host, lens, ragged=True, out_host=wav_host)
-
-    def timed(fn, steps, warmup):
+    def timed(fn, steps, warmup, flush_l2=True, sample=True):
         sampler = ClockSampler(local)
-        if rank == 0:
+        if rank == 0 and sample:
             sampler.start()                                  # started before warm-up: nvidia-smi needs ~0.5 s to attach
         for _ in range(warmup):
             fn()
@@ -242,7 +243,8 @@ def run_b200(args):
         evs = []
         t0 = sampler.mark()
         for _ in range(steps):
-            flush.fill_(1)                                   # evict L2 between timed iterations (untimed)
+            if flush_l2:
+                flush.fill_(1)                               # evict L2 between timed iterations (untimed)
             a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             a.record()
             fn()
@@ -250,18 +252,20 @@ def run_b200(args):
             evs.append((a, b))
         barrier()
         t1 = sampler.mark()
-        clocks = sampler.stop(t0, t1) if rank == 0 else None
+        clocks = sampler.stop(t0, t1) if (rank == 0 and sample) else None
         ms = sum(a.elapsed_time(b) for a, b in evs)
         return reduce_job(0.0, 0, ms, world, dev)[2], clocks
 
-    def timed_pipeline(steps, warmup):
+    def timed_pipeline(steps, warmup, pcm16):
         """End-to-end through the serving API (FlowDecoder.host_pipeline, depth 2): every step copies its latents
-        from pinned host memory and its waveform back to host memory inside the timed region; the copies of
-        neighbouring steps overlap the synthesis.  Timed as ONE region with CUDA events on the compute stream
+        from pinned host memory and its result back to pinned host memory inside the timed region; the copies of
+        neighbouring steps overlap the synthesis.  pcm16: the result is the int16 PCM the serving path returns
+        (vits_wrap.py:195), written by the last kernel.  Timed as ONE region with CUDA events on the compute stream
         (first H2D ordered after the start event, end event ordered after the last D2H).  No L2 flush here: the
         inputs come from the host every step and a step's activation traffic (GBs) is far beyond the 126 MB L2."""
-        pipe = eng.host_pipeline(B, T)
-        outs = [wav_host, torch.empty_like(wav_host).pin_memory()]
+        pipe = eng.host_pipeline(B, T, pcm16=pcm16)
+        dt = torch.int16 if pcm16 else torch.float32
+        outs = [torch.empty(B, 1, T * up, dtype=dt).pin_memory() for _ in range(2)]
         prev = None
         for i in range(warmup):
             t = pipe.submit(z_host, g_host, lens, outs[i % 2])
@@ -282,16 +286,71 @@ def run_b200(args):
         ev1.record()
         pipe.wait(prev)
         barrier()
-        return reduce_job(0.0, 0, ev0.elapsed_time(ev1), world, dev)[2]
+        return reduce_job(0.0, 0, ev0.elapsed_time(ev1), world, dev)[2], outs[0].numel() * outs[0].element_size()
 
-    ms_res, clocks = timed(step_resident, args.steps, max(3, args.warmup))
-    if args.e2e_sync:
-        ms_e2e, _ = timed(step_e2e, args.steps, max(3, args.warmup))
-    else:
-        ms_e2e = timed_pipeline(args.steps, max(3, args.warmup))
+    W = max(3, args.warmup)
+    ms_res, clocks = timed(step_resident, args.steps, W)
+    ms_e2e, d2h_bytes = timed_pipeline(args.steps, W, pcm16=True)
+    ms_e2e_f32, d2h_f32 = timed_pipeline(args.steps, W, pcm16=False)
     audio_all, frames_all, _ = reduce_job(audio_s, frames, 0.0, world, dev)
 
-    # per-launch-family device time (separate, untimed pass): roofline of the dominant kernel
+    # ---- side legs (rank-local, N = 1 only): sustained clocks, varying lengths, the other BASELINE configs ----
+    side = {}
+    if world == 1 and not args.no_side_legs:
+        # (a) sustained: >= 3 s of back-to-back steps, no flush, clocks sampled throughout (the power-capped regime)
+        n_sus = max(args.steps, int(3000.0 / max(ms_res / args.steps, 0.1)))
+        ms_sus, clk_sus = timed(step_resident, n_sus, 3, flush_l2=False)
+        side["sustained"] = {"steps": n_sus, "seconds": ms_sus * 1e-3, "ms_per_step": ms_sus / n_sus,
+                             "value": audio_s * n_sus / (ms_sus * 1e-3), "clocks": clk_sus}
+        # (b) a fresh length draw every step (same distribution): a server never sees the same 16 lengths twice, so this
+        # leg cannot be served by replaying one CUDA graph per length vector
+        draws = [FX.make_lengths(B, LEN_LO, LEN_HI, seed=5000 + i) for i in range(args.steps + W)]
+        Tv = max(max(d) for d in draws)
+        latv = FX.make_latents(cfg, [Tv] * B, seed=77)
+        zv, gv = latv["z_p"].to(dev), latv["g"].to(dev)
+        wv = torch.empty(B, 1, Tv * up, dtype=torch.float32, device=dev)
+        it = iter(draws)
+        fr = [0]
+
+        def step_vary():
+            d = next(it)
+            fr[0] += sum(d)
+            eng.synthesize(zv, gv, d, ragged=True, out=wv)
+        for _ in range(W):
+            step_vary()
+        fr[0] = 0
+        ms_v, _ = timed(step_vary, args.steps, 0, sample=False)
+        side["vary_lengths"] = {"value": fr[0] * FRAME_SEC / (ms_v * 1e-3), "ms_per_step": ms_v / args.steps,
+                                "note": "fresh U{84..834} length draw per step, T_max fixed; lengths are device data, graphs are keyed on tile counts"}
+        # (c) BASELINE configs C1 (5 s, B=1), C3 (60 s, B=1): single-stream latency; C4: 64-512 utterances on this GPU
+        def latency(Tn, reps):
+            l1 = FX.make_latents(cfg, [Tn], seed=3)
+            z1, g1 = l1["z_p"].to(dev), l1["g"].to(dev)
+            o1 = torch.empty(1, 1, Tn * up, dtype=torch.float32, device=dev)
+            f = lambda: eng.synthesize(z1, g1, None, ragged=True, out=o1)
+            ms, _ = timed(f, reps, 3, sample=False)
+            return {"frames": Tn, "audio_s": Tn * FRAME_SEC, "latency_ms": ms / reps, "value": Tn * FRAME_SEC * reps / (ms * 1e-3)}
+        side["C1_latency"] = latency(417, 20)
+        side["C3_latency"] = latency(5000, 10)
+        c4 = {}
+        for Bn in (64, 128, 256, 512):
+            ln = sorted(FX.make_lengths(Bn, LEN_LO, LEN_HI, seed=1234 + Bn), reverse=True)   # length-sorted rows: chunks of similar length
+            Tn = max(ln)
+            zb = torch.randn(Bn, cfg.inter_channels, Tn, device=dev)
+            for r_, L_ in enumerate(ln):
+                zb[r_, :, L_:] = 0
+            gb = torch.randn(Bn, cfg.gin_channels, device=dev)
+            ob = torch.empty(Bn, 1, Tn * up, dtype=torch.int16, device=dev)
+            f = lambda: eng.synthesize_pcm16(zb, gb, ln, ragged=True, out=ob)
+            ms, _ = timed(f, 3, 2, sample=False)
+            c4[str(Bn)] = {"audio_s": sum(ln) * FRAME_SEC, "ms_per_step": ms / 3, "value": sum(ln) * FRAME_SEC * 3 / (ms * 1e-3),
+                           "workspace_gb": eng.workspace_bytes(Bn, Tn) / 2 ** 30}
+            del zb, gb, ob
+            eng._ws = None
+            torch.cuda.empty_cache()
+        side["C4_batch_sweep_1gpu"] = c4
+
+    # per-launch-family device time (separate, untimed pass): which share of the step the tensor-core launches are
     eng.profile(True)
     for _ in range(3):
         step_resident()
@@ -302,8 +361,16 @@ def run_b200(args):
     all_ms = sum(r[1] for r in table) / 3
     conv_flops = sum(r[3] for r in conv_rows) / 3
     conv_launches = sum(r[2] for r in conv_rows) // 3
+    gen_rows = [r for r in conv_rows if not r[0].startswith("flow")]
+    gen_ms, gen_flops = sum(r[1] for r in gen_rows) / 3, sum(r[3] for r in gen_rows) / 3
     pk = peaks()
-    achieved_tf = conv_flops / (conv_ms * 1e-3) / 1e12 if conv_ms > 0 else 0.0
+    share = conv_ms / all_ms if all_ms else 0.0
+    step_ms = ms_res / args.steps
+    # tensor-core launches' achieved rate INSIDE the timed pass: their algorithmic FLOP over their share of the
+    # driver-timed step (share from the per-launch event pass above; recomputable from ms_per_step)
+    achieved_tf = conv_flops / (step_ms * share * 1e-3) / 1e12 if share > 0 else 0.0
+    gen_share = gen_ms / all_ms if all_ms else 0.0
+    gen_tf = gen_flops / (step_ms * gen_share * 1e-3) / 1e12 if gen_share > 0 else 0.0
 
     if rank == 0:
         value = audio_all * args.steps / (ms_res * 1e-3)
@@ -314,31 +381,45 @@ def run_b200(args):
             traffic = json.load(open(tf)).get("dram_bytes_per_launch")
         out = {
             "metric": "audio-sec/sec (RTF^-1)", "value": value, "unit": "audio-s/s", "n_gpus": world,
-            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms_res / args.steps,
+            "steps": args.steps, "warmup": W, "ms_per_step": step_ms,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": {"fp16": "f16", "bf16": "bf16", "fp32": "f32"}[args.precision] + " operands, f32 accumulate",
             "data": "synthetic",
             "config": {"workload": f"{'C2' if PER_GPU_BATCH == 16 else 'C4 sweep point'}: emotional-vits base config, {PER_GPU_BATCH} mixed-length utterances per GPU "
-                                   f"(1-10 s, ragged/masked), flow-reverse + Generator",
+                                   f"(1-10 s, ragged/masked), flow-reverse + Generator"
+                                   + ("; at N>1 this is C5-shaped: every row of every rank has its own speaker embedding g" if world > 1 else ""),
                        "global_batch": PER_GPU_BATCH * world, "valid_audio_s_per_step": audio_all,
-                       "parallelism": f"utterance-sharded replicas x{world} (LPT), no collective",
+                       "parallelism": f"utterance-sharded replicas x{world}, the same 16-length set on every rank, no collective",
                        "l2": "256 MiB flush between timed steps; per-step activation traffic >> 126 MB L2",
                        "precision": args.precision},
             "e2e": {"value": e2e, "unit": "audio-s/s", "h2d_bytes_per_step": int(z_host.numel() * 4 + g_host.numel() * 4 + 4 * B) * world,
-                    "d2h_bytes_per_step": int(wav_host.numel() * 4) * world, "ms_per_step": ms_e2e / args.steps,
-                    "api": "FlowDecoder.synthesize_host (one blocking call per step)" if args.e2e_sync else
-                           "FlowDecoder.host_pipeline depth 2 (per-step H2D/D2H overlap the neighbouring steps' synthesis)"},
+                    "d2h_bytes_per_step": int(d2h_bytes) * world, "ms_per_step": ms_e2e / args.steps,
+                    "api": "FlowDecoder.host_pipeline(pcm16=True) depth 2: per-step H2D of the latents and D2H of the int16 PCM the serving "
+                           "path returns (vits_wrap.py:195, written by the last kernel) overlap the neighbouring steps' synthesis",
+                    "float32_result": {"value": audio_all * args.steps / (ms_e2e_f32 * 1e-3), "d2h_bytes_per_step": int(d2h_f32) * world}},
             "gpu_launches": eng.launches_per_call(B, T) * args.steps,
             "clocks": clocks,
-            "roofline": {"bound": "tensor", "kernel": "rb_fused_kernel + conv_tc_kernel (all tcgen05 launches of a step; rb_fused is ~75 % of it)",
-                         "achieved": achieved_tf, "peak": pk["tflops_sustained"], "unit": "TFLOP/s",
-                         "frac": achieved_tf / pk["tflops_sustained"], "peak_source": pk["source"] + " (sustained cuBLAS bf16)",
+            "roofline": {"bound": "tensor", "kernel": "rb_fused_kernel + flow_fused_kernel + conv_tc_kernel (all tcgen05 launches of a step; rb_fused is ~80 % of it)",
+                         "achieved": achieved_tf, "peak": pk["tflops_burst"], "unit": "TFLOP/s",
+                         "frac": achieved_tf / pk["tflops_burst"],
+                         "peak_source": pk["source"] + " (burst cuBLAS bf16: the timed region is < 1 s at full clocks)",
+                         "frac_of_sustained_peak": achieved_tf / pk["tflops_sustained"], "sustained_peak": pk["tflops_sustained"],
+                         "formula": "achieved = algorithmic FLOP of the tensor-core launches per step / (ms_per_step * kernel_share_of_step)",
                          "traffic": traffic, "launches_per_step": conv_launches,
-                         "avg_launch_ms": conv_ms / max(1, conv_launches),
+                         "avg_launch_ms": step_ms * share / max(1, conv_launches),
                          "flop_per_launch": conv_flops / max(1, conv_launches),
-                         "kernel_share_of_step": conv_ms / all_ms if all_ms else None,
+                         "kernel_share_of_step": share,
+                         "generator_convs": {"tflops": gen_tf, "frac_burst": gen_tf / pk["tflops_burst"],
+                                             "frac_sustained": gen_tf / pk["tflops_sustained"], "share_of_step": gen_share},
                          "step_level_tflops": eng.flop_per_frame * frames_all * args.steps / (ms_res * 1e-3) / 1e12},
         }
+        if "sustained" in side:
+            sus = side["sustained"]
+            sus_tf = eng.flop_per_frame * frames * 1e-12 / (sus["ms_per_step"] * 1e-3)
+            sus["step_level_tflops"] = sus_tf
+            sus["frac_of_sustained_peak"] = sus_tf / pk["tflops_sustained"]
+        if side:
+            out["configs"] = side
         if args.profile_out:
             with open(args.profile_out, "w") as f:
                 f.write(f"# per-launch-family device time, mean of 3 steps, B={B} T_max={T} precision={args.precision}\n")

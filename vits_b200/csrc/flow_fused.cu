@@ -52,7 +52,7 @@ constexpr int MAX_LAYERS = 4;
 
 // barrier slots (8 bytes each)
 enum { B_FULL = 0, B_EMPTY = B_FULL + NST, B_PRE = B_EMPTY + NST, B_AFULL = B_PRE + 2, B_AEMPTY = B_AFULL + 2,
-       B_ACCF = B_AEMPTY + 2, B_ACCE, B_HREADY, B_HFULL, B_MREADY, B_MEMPTY, B_COUNT };
+       B_ACCF = B_AEMPTY + 2, B_ACCE, B_HREADY, B_HFULL, B_MREADY = B_HFULL + NPASS, B_MEMPTY, B_COUNT };
 
 __host__ __device__ inline uint32_t smem_bytes(int nl) {
   return 1024u + NPASS * HBLK + 2 * SLOT_B + NST * STAGE_B + (uint32_t)nl * 2 * H * 4u + 8u * B_COUNT + 64u;
@@ -94,7 +94,8 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
     for (int s = 0; s < NST; ++s) { ptx::mbar_init(bar(B_FULL + s), 1); ptx::mbar_init(bar(B_EMPTY + s), 1); }
     for (int s = 0; s < 2; ++s) { ptx::mbar_init(bar(B_PRE + s), 1); ptx::mbar_init(bar(B_AFULL + s), 8); ptx::mbar_init(bar(B_AEMPTY + s), 1); }
     ptx::mbar_init(bar(B_ACCF), 1);   ptx::mbar_init(bar(B_ACCE), 8);
-    ptx::mbar_init(bar(B_HREADY), 1); ptx::mbar_init(bar(B_HFULL), 8);
+    ptx::mbar_init(bar(B_HREADY), 1);
+    for (int kb = 0; kb < NPASS; ++kb) ptx::mbar_init(bar(B_HFULL + kb), 4);      // one per 64-channel block of the h slab
     ptx::mbar_init(bar(B_MREADY), 1); ptx::mbar_init(bar(B_MEMPTY), 8);
     ptx::mbar_fence_init();
   }
@@ -121,7 +122,27 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
   };
   const int fills_per_tile = 1 + 2 * nl;                  // fills of one acts slot per tile: x0 tiles of `pre` + two gate passes per layer
 
-  if (warp == 0) {
+  if (warp == 2 || warp == 3) {
+    // =================== L2 prefetch of this coupling's weights ===================
+    // Every CTA streams the same 6.8 MB of weights, in lockstep, through a ring that holds ~2 k cycles of tensor work:
+    // when a box misses L2 every CTA waits out the HBM latency together (first timeline: 305-350 cycles per stage
+    // against 256 of MMA).  Here the grid pulls the whole set into L2 once, each CTA a 1 / gridDim slice, roughly in
+    // the order of first use; the ring loads that follow are L2 hits.
+    constexpr uint32_t CH = 8192;
+    const char* wbase = reinterpret_cast<const char*>(a.w);
+    const size_t seg_off[3] = {a.fw.w_pre * 2, a.fw.w_in * 2, a.fw.w_rs * 2};
+    const size_t seg_len[3] = {(size_t)H * 2 * XW * 2, (size_t)nl * 2 * H * KT * H * 2, (size_t)nl * RS_ROWS * 2 * H * 2};
+    const int lane64 = (warp - 2) * 32 + lane;
+    const size_t nch[3] = {(seg_len[0] + CH - 1) / CH, (seg_len[1] + CH - 1) / CH, (seg_len[2] + CH - 1) / CH};
+    // chunk g of the concatenated segments goes to CTA g % gridDim, lane (g / gridDim) % 64
+    for (size_t g = blockIdx.x + (size_t)gridDim.x * lane64; g < nch[0] + nch[1] + nch[2]; g += (size_t)gridDim.x * 64) {
+      const int sg = g < nch[0] ? 0 : (g < nch[0] + nch[1] ? 1 : 2);
+      const size_t c = g - (sg == 0 ? 0 : (sg == 1 ? nch[0] : nch[0] + nch[1]));
+      const size_t off = c * CH;
+      const uint32_t bytes = (uint32_t)(seg_len[sg] - off < CH ? seg_len[sg] - off : CH);
+      ptx::prefetch_l2_bulk(wbase + seg_off[sg] + off, bytes);
+    }
+  } else if (warp == 0) {
     // =================== TMA producer: x0 operand tiles + every weight box, in the MMA warp's order ===================
     const bool leader = ptx::elect_one();
     Cursor rg{0, 0};
@@ -154,8 +175,10 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
       for (int l = 0; l < nl; ++l) {
         const bool last = l == nl - 1;
         auto put_in = [&](int p) {
-          for (int j = 0; j < KT; ++j)
-            for (int kb = 0; kb < NPASS; ++kb) put(&tmIn, j * H + kb * 64, l * 2 * H + p * 128, STAGE_B);
+          for (int kbi = 0; kbi < NPASS; ++kbi) {           // block order 0, 2, 1, 3: the order the h epilogue completes them in
+            const int kb = ((kbi & 1) << 1) | (kbi >> 1);
+            for (int j = 0; j < KT; ++j) put(&tmIn, j * H + kb * 64, l * 2 * H + p * 128, STAGE_B);
+          }
         };
         auto put_rs = [&](int p) {
           for (int part = 0; part < 2; ++part) {          // Wh then Wl
@@ -223,12 +246,19 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           ptx::tc_fence_after();
           if (n == 0) trace(16 + l * 16 + p * 2);           // in(p) may start
           const uint32_t d = tmem_base + TM_ACC;
-          for (int j = 0; j < KT; ++j)
-            for (int kb = 0; kb < NPASS; ++kb) {
+          for (int kbi = 0; kbi < NPASS; ++kbi) {
+            const int kb = ((kbi & 1) << 1) | (kbi >> 1);
+            if (p == 0) {                                   // first pass of the layer: the h blocks arrive one by one
+              ptx::mbar_wait(bar(B_HFULL + kb), hh & 1);
+              ptx::tc_fence_after();
+              if (n == 0 && kbi == 0) trace(3 + l);         // first h block of layer l ready
+            }
+            for (int j = 0; j < KT; ++j) {
               const uint64_t bd = stage_wait();
-              group(d, d16(sH + kb * HBLK + j * 128), bd, id128, j == 0 && kb == 0);     // tap j = slab shifted by j rows
+              group(d, d16(sH + kb * HBLK + j * 128), bd, id128, j == 0 && kbi == 0);    // tap j = slab shifted by j rows
               stage_done();
             }
+          }
           commit(B_ACCF);
           if (n == 0) trace(16 + l * 16 + p * 2 + 1);       // in(p) issued
         };
@@ -259,9 +289,6 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           commit(B_AEMPTY + s);
           if (n == 0) trace(16 + l * 16 + 8 + p * 2 + 1);   // rs(p) issued
         };
-        ptx::mbar_wait(bar(B_HFULL), hh & 1);
-        ptx::tc_fence_after();
-        if (n == 0) trace(3 + l);                            // h operand of layer l ready
         do_in(0);
         for (int p = 1; p < NPASS; ++p) { do_in(p); do_rs(p - 1); }
         do_rs(NPASS - 1);
@@ -294,28 +321,33 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
         ptx::mbar_wait(bar(B_HREADY), (n * nl + l) & 1);
         ptx::tc_fence_after();
         if (n == 0 && warp == 4) trace(96 + l * 16);         // h epilogue starts
-#pragma unroll 2
-        for (int c = 0; c < 8; ++c) {
-          const int ch = hf * 128 + c * 16;
-          uint32_t ra[16];
-          ptx::tmem_ld16(tmem_base + TM_H + lane_base + ch, ra);
-          float bv[16];
-          load16(bcum + l * H + ch, bv);
-          ptx::tmem_ld_wait();
-          uint32_t pk[8];
+#pragma unroll 1
+        for (int half_i = 0; half_i < 2; ++half_i) {           // one 64-channel block of the slab per iteration
+          const int kb = hf * 2 + half_i;
+          uint32_t ra[4][16];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const uint32_t w = Pack16<OpT>::pack2(__uint_as_float(ra[2 * i]) + bv[2 * i], __uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1]);
-            pk[i] = live ? w : 0u;
+          for (int c = 0; c < 4; ++c) ptx::tmem_ld16(tmem_base + TM_H + lane_base + kb * 64 + c * 16, ra[c]);
+          float bv[4][16];
+#pragma unroll
+          for (int c = 0; c < 4; ++c) load16(bcum + l * H + kb * 64 + c * 16, bv[c]);
+          ptx::tmem_ld_wait();
+          const uint32_t rowaddr = sH + kb * HBLK + (r + 2) * 128;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            uint32_t pk[8];
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const uint32_t w = Pack16<OpT>::pack2(__uint_as_float(ra[c][2 * i]) + bv[c][2 * i], __uint_as_float(ra[c][2 * i + 1]) + bv[c][2 * i + 1]);
+              pk[i] = live ? w : 0u;
+            }
+            st_shared_v4(swz_addr<128>(rowaddr + c * 32), pk[0], pk[1], pk[2], pk[3]);
+            st_shared_v4(swz_addr<128>(rowaddr + c * 32 + 16), pk[4], pk[5], pk[6], pk[7]);
           }
-          const uint32_t addr = sH + (ch >> 6) * HBLK + (r + 2) * 128 + (ch & 63) * 2;
-          st_shared_v4(swz_addr<128>(addr), pk[0], pk[1], pk[2], pk[3]);
-          st_shared_v4(swz_addr<128>(addr + 16), pk[4], pk[5], pk[6], pk[7]);
+          fence_proxy_async_smem();
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(bar(B_HFULL + kb));
         }
-        fence_proxy_async_smem();
-        ptx::tc_fence_before();
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(bar(B_HFULL));
         if (n == 0 && warp == 4) trace(96 + l * 16 + 1);     // h epilogue done
         // ---- gate passes: acts[64 p .. 64 p + 63] = tanh(a + cond_a) * sigmoid(b + cond_b) as [hi | lo] tiles ----
         for (int p = 0; p < NPASS; ++p) {
@@ -323,25 +355,33 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           const int ai = (n * nl + l) * NPASS + p;
           const int k = n * fills_per_tile + 1 + 2 * l + (p >> 1);
           ptx::mbar_wait(bar(B_ACCF), ai & 1);
-          ptx::mbar_wait(bar(B_AEMPTY + s), (uint32_t)(k & 1) ^ 1u);
           ptx::tc_fence_after();
           if (n == 0 && warp == 4) trace(96 + l * 16 + 2 + p * 2);     // gate(p) starts
           const float* cb = s_cond + l * 2 * H + p * 128;
+          // drain this warp's 32 gate channels (tanh + sigmoid halves) into registers and hand the accumulator back
+          // at once: the MUFU-bound gate math below then runs under the next pass's MMAs
+          uint32_t ra[2][16], rb[2][16];
+#pragma unroll
+          for (int c = 0; c < 2; ++c) {
+            ptx::tmem_ld16(tmem_base + TM_ACC + lane_base + hf * 32 + c * 16, ra[c]);
+            ptx::tmem_ld16(tmem_base + TM_ACC + lane_base + 64 + hf * 32 + c * 16, rb[c]);
+          }
+          ptx::tmem_ld_wait();
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) ptx::mbar_arrive(bar(B_ACCE));
+          ptx::mbar_wait(bar(B_AEMPTY + s), (uint32_t)(k & 1) ^ 1u);
 #pragma unroll
           for (int c = 0; c < 2; ++c) {
             const int g0 = hf * 32 + c * 16;            // gate channel inside the pass
-            uint32_t ra[16], rb[16];
-            ptx::tmem_ld16(tmem_base + TM_ACC + lane_base + g0, ra);
-            ptx::tmem_ld16(tmem_base + TM_ACC + lane_base + 64 + g0, rb);
             float ba[16], bb[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) { ba[i] = cb[g0 + i]; bb[i] = cb[64 + g0 + i]; }
-            ptx::tmem_ld_wait();
             uint32_t ph[8], pl[8];
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
-              float v0 = gate_fn<false>(__uint_as_float(ra[2 * i]) + ba[2 * i], __uint_as_float(rb[2 * i]) + bb[2 * i]);
-              float v1 = gate_fn<false>(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1]);
+              float v0 = gate_exact3(__uint_as_float(ra[c][2 * i]) + ba[2 * i], __uint_as_float(rb[c][2 * i]) + bb[2 * i]);
+              float v1 = gate_exact3(__uint_as_float(ra[c][2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[c][2 * i + 1]) + bb[2 * i + 1]);
               if (!live) { v0 = 0.f; v1 = 0.f; }
               ph[i] = Pack16<OpT>::pack2(v0, v1);
               const float2 hi = Pack16<OpT>::unpack2(ph[i]);
@@ -354,9 +394,8 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
             st_shared_v4(swz_addr<128>(addr + TILE_B + 16), pl[4], pl[5], pl[6], pl[7]);
           }
           fence_proxy_async_smem();
-          ptx::tc_fence_before();
           __syncwarp();
-          if (lane == 0) { ptx::mbar_arrive(bar(B_AFULL + s)); ptx::mbar_arrive(bar(B_ACCE)); }
+          if (lane == 0) ptx::mbar_arrive(bar(B_AFULL + s));
           if (n == 0 && warp == 4) trace(96 + l * 16 + 2 + p * 2 + 1); // gate(p) done
         }
       }
