@@ -156,6 +156,22 @@ int vitsb_synthesize_pcm16(vitsb_handle* h, const float* z_p, const float* g, co
 int vitsb_length_regulate(vitsb_handle* h, const float* attn, const float* m_p, const float* s_p, const float* noise,
                           int B, int T, int Tx, float* z_p, vitsb_stream stream);
 
+/* No counterpart in the reference: added for callers that cannot allocate
+ * (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc) and so cannot hand
+ * vitsb_flow_reverse a workspace.  Same computation and arguments as vitsb_flow_reverse (fused coupling-layer plan
+ * only: fp16 / bf16 precision), but the scratch - time-major flow state, its operand copy, the flow's conditioning
+ * vectors, the device copy of len - lives in ONE static device array of VITSB_NOALLOC_SCRATCH_BYTES that every GPU
+ * which loads the library holds until exit.  The call allocates nothing (no cudaMalloc / cudaFree, no stream or graph
+ * creation).  Shapes whose scratch exceeds the array (more than about 5 000 padded frames B * T_max, plus 32 KB per batch row) are rejected with
+ * VITSB_ERR_WORKSPACE and a message; other plans with VITSB_ERR_UNSUPPORTED.  Every call shares the array, which keeps
+ * the previous call's contents (nothing in it needs to start at zero: each region is written before it is read within a
+ * call).  Calls that overlap on the GPU - different streams, or different handles on one device - RACE on it:
+ * serialise them. */
+#define VITSB_NOALLOC_SCRATCH_BYTES (8u << 20)
+int vitsb_flow_reverse_noalloc(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len,
+                               int B, int T_max, float* z, vitsb_stream stream);
+size_t vitsb_noalloc_scratch_bytes(void);   /* = VITSB_NOALLOC_SCRATCH_BYTES, as built */
+
 /* Introspection for tests and bench.py. */
 int vitsb_total_upsample(const vitsb_handle* h);
 /* Number of kernels one vitsb_synthesize call launches for (B, T_max). */

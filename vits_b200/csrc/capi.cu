@@ -7,7 +7,6 @@
 
 using namespace vitsb;
 
-struct vitsb_handle { Engine eng; };
 
 static thread_local std::string g_create_err;
 

@@ -142,3 +142,6 @@ struct Engine {
 };
 
 }  // namespace vitsb
+
+// the opaque handle of include/vitsb200.h
+struct vitsb_handle { vitsb::Engine eng; };

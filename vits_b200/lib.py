@@ -51,6 +51,8 @@ SYMBOLS = {
     "vitsb_synthesize_pcm16": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_float, _P, _P,
                                          C.c_size_t, _P]),
     "vitsb_length_regulate": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "vitsb_flow_reverse_noalloc": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.c_int, C.c_int, _P, _P]),
+    "vitsb_noalloc_scratch_bytes": (C.c_size_t, []),
     "vitsb_total_upsample": (C.c_int, [_P]),
     "vitsb_launches_per_call": (C.c_int, [_P, C.c_int, C.c_int]),
     "vitsb_flop_per_frame": (C.c_double, [_P]),
