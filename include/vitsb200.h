@@ -106,6 +106,8 @@ int vitsb_load_weights(vitsb_handle* h, const vitsb_tensor_desc* tensors, int n)
  *   "pdl" 0/1 (0)          programmatic dependent launch between the tensor-core kernels
  *   "tc_pair" 0/1 (1)      CTA-pair (cta_group::2) mode of the generic conv kernel
  *   "rb_nslab" 0..16 (0)   fused-ResBlock slab count override, 0 = automatic
+ *   "ups_split_mask" -1..255 bit i: upsampler i runs 3-term split precision (16-bit paths; -1 = automatic: fp16 the
+ *       first two, bf16 all); next vitsb_load_weights
  *   "ws_cap_mb" (24576)    workspace cap; batches whose layout exceeds it run in row chunks
  *   "rb_fused", "flow_fused", "flow_in_split" -1/0/1 (-1 = automatic): launch-plan / packing choices; they take
  *       effect at the next vitsb_load_weights.

@@ -78,7 +78,7 @@ struct Engine {
 
   // options (vitsb_set_option); -1 = automatic.  Packing / plan options take effect at the next vitsb_load_weights.
   int opt_graph = 1, opt_pdl = 0, opt_tc_pair = 1, opt_rb_fused = -1, opt_flow_fused = -1, opt_flow_in_split = -1,
-      opt_rb_nslab = 0, opt_ws_cap_mb = 24576;
+      opt_rb_nslab = 0, opt_ws_cap_mb = 24576, opt_ups_split_mask = -1;
   int set_option(const char* key, int value);
   int get_option(const char* key, int* value) const;
   LaunchOpts lopts() const { LaunchOpts o; o.pdl = opt_pdl != 0; o.pair = opt_tc_pair != 0; o.num_sms = num_sms; o.rb_nslab = opt_rb_nslab; return o; }

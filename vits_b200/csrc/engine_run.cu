@@ -296,7 +296,7 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
 
   if (what & RUN_DEC) {
     // x = conv_pre(z); the next op's leaky_relu(0.1) is folded into the operand copy   models.py:307-309
-    { Epilogue ep = epi_base(); set_out_op_split(ep, P(W.nxt_op), conv_pre.N, T, 0.1f, split16);
+    { Epilogue ep = epi_base(); set_out_op_split(ep, P(W.nxt_op), conv_pre.N, T, 0.1f, !stages.empty() && stages[0].ups.split);
       cx.conv(T_CONV_PRE, conv_pre, P(W.zop), T, 1, cx.len_dec, ep); }
     int L = T;              // rows per batch item at the current rate
     int mul = 1;            // valid rows = len * mul
@@ -365,7 +365,7 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
             ep.alpha = inv; ep.beta = inv;
             if (j > 0) set_accum(ep, F(W.acc_f), C, L);
             if (j < nk - 1 || s == ns - 1) set_out_f32(ep, F(W.acc_f), C, L);   // last stage: conv_post reads fp32
-            else set_out_op_split(ep, P(W.nxt_op), C, L, next_slope, split16);
+            else set_out_op_split(ep, P(W.nxt_op), C, L, next_slope, stages[s + 1].ups.split);
           }
           cx.conv(T_RB_C2 + s, it.c2, P(W.g_op), L, mul, cx.len_dec, ep);
         }
@@ -374,7 +374,7 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
         if (s < ns - 1) {
           // x = sum_j resblock_j(x) / num_kernels; next operand = leaky_relu(x, 0.1)      models.py:309-314
           AUX_LAUNCH(T_MRF, launch_mrf_sum(br[0], nk > 1 ? br[1] : nullptr, nk > 2 ? br[2] : nullptr, B, L, C, cx.len_dec, mul,
-                                           inv, next_slope, P(W.nxt_op), split16 ? 1 : 0, nullptr, op, stream));
+                                           inv, next_slope, P(W.nxt_op), stages[s + 1].ups.split ? 1 : 0, nullptr, op, stream));
         } else if (!post_from_y) {
           AUX_LAUNCH(T_MRF, launch_mrf_sum(br[0], nk > 1 ? br[1] : nullptr, nk > 2 ? br[2] : nullptr, B, L, C, cx.len_dec, mul,
                                            inv, 1.f, nullptr, 0, F(W.acc_f), op, stream));

@@ -52,6 +52,7 @@ const OptDesc kOpts[] = {
     {"flow_fused", &Engine::opt_flow_fused, -1, 1},       // fused coupling-layer kernel (-1 auto); applies at the next load
     {"flow_in_split", &Engine::opt_flow_in_split, -1, 1}, // 3-term split WN in_layers (-1: bf16 yes, fp16 no); applies at the next load
     {"rb_nslab", &Engine::opt_rb_nslab, 0, 16},           // rb_fused slab count override (0 auto)
+    {"ups_split_mask", &Engine::opt_ups_split_mask, -1, 255}, // bit i: upsampler i runs 3-term split precision (16-bit paths); applies at the next load
     {"ws_cap_mb", &Engine::opt_ws_cap_mb, 64, 1 << 20},   // workspace cap: larger batches are processed in row chunks
 };
 }  // namespace
@@ -466,7 +467,10 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
         dmin = dlt < dmin ? dlt : dmin; dmax = dlt > dmax ? dlt : dmax;
       }
     PackedConv& pc = st.ups;
-    pc.split = split16;
+    // automatic: fp16 splits the first two upsamplers only - un-splitting the last two costs 2e-4 of C2 max-abs error
+    // (1.43e-3 -> 1.63e-3 of the 2e-3 budget) for 0.25 ms of a 4.4 ms step; bf16 operands keep every split
+    const int ups_mask = opt_ups_split_mask >= 0 ? opt_ups_split_mask : (op == OP_BF16 ? 255 : 3);
+    pc.split = split16 && ((ups_mask >> i) & 1);       // per-stage choice: DESIGN.md section 3 (error budget of the trunk convs)
     pc.Cin = pc.split ? 3 * Cin : Cin; pc.in_cols = pc.split ? 2 * Cin : Cin;
     pc.N = u * Cout; pc.NT = pick_nt(pc.N); pc.k = dmax - dmin + 1; pc.dil = 1; pc.pad = -dmin; pc.gate = false;
     pc.flop_per_pos = 2.0 * Cin * Cout * k;          // per INPUT position
