@@ -133,3 +133,72 @@ def make_p2_inputs(cfg: HotPathConfig, T: int, seed: int = 1234, noise_scale: fl
     noise = torch.randn(1, C, T, generator=gen) * noise_scale
     g = torch.randn(1, cfg.gin_channels, generator=gen)
     return {"attn": attn, "m_p": m_p, "s_p": s_p, "g": g, "noise": noise}
+
+
+def p1_param_specs(cfg: HotPathConfig) -> List[Tuple[str, Tuple[int, ...], str, int]]:
+    """[(key, shape, kind, fan_in)] of the `enc_p.*`, `dp.*`, `emb_g.*` keys (models.py:20-47, 117-164;
+    attentions.py:12-33, 58-77, 128-146; none of them weight-normed)."""
+    H, F_, tc, gin, k = cfg.hidden_channels, cfg.filter_channels, cfg.text_channels, cfg.gin_channels, cfg.kernel_size
+    sp = [("enc_p.alpha", (), "scalar", 0),
+          ("enc_p.emb.0.weight", (H, tc), "linear", tc), ("enc_p.emb.0.bias", (H,), "bias", 0),
+          ("enc_p.emb.1.weight", (H,), "gamma", 0), ("enc_p.emb.1.bias", (H,), "bias", 0),
+          ("enc_p.emo_proj.weight", (H, cfg.emo_channels), "linear", cfg.emo_channels), ("enc_p.emo_proj.bias", (H,), "bias", 0)]
+    for i in range(cfg.n_layers):
+        a = f"enc_p.encoder.attn_layers.{i}."
+        for n in ("q", "k", "v", "o"):
+            sp += [(a + f"conv_{n}.weight", (H, H, 1), "conv", H), (a + f"conv_{n}.bias", (H,), "bias", 0)]
+        sp += [(f"enc_p.encoder.norm_layers_1.{i}.gamma", (H,), "gamma", 0), (f"enc_p.encoder.norm_layers_1.{i}.beta", (H,), "bias", 0)]
+        f = f"enc_p.encoder.ffn_layers.{i}."
+        sp += [(f + "conv_1.weight", (2 * F_, H, k), "conv", H * k), (f + "conv_1.bias", (2 * F_,), "bias", 0),
+               (f + "conv_2.weight", (H, F_, k), "conv", F_ * k), (f + "conv_2.bias", (H,), "bias", 0),
+               (f + "cond.weight", (2 * F_, gin), "linear", gin), (f + "cond.bias", (2 * F_,), "bias", 0)]
+        sp += [(f"enc_p.encoder.norm_layers_2.{i}.gamma", (H,), "gamma", 0), (f"enc_p.encoder.norm_layers_2.{i}.beta", (H,), "bias", 0)]
+    sp += [("enc_p.proj.weight", (2 * cfg.inter_channels, H, 1), "conv", H), ("enc_p.proj.bias", (2 * cfg.inter_channels,), "bias", 0)]
+    D, kd = cfg.hidden_size_d, cfg.kernel_size_d
+    sp += [("dp.pre.weight", (D, H, 1), "conv", H), ("dp.pre.bias", (D,), "bias", 0),
+           ("dp.conv_1.weight", (D, D, kd), "conv", D * kd), ("dp.conv_1.bias", (D,), "bias", 0),
+           ("dp.norm_1.gamma", (D,), "gamma", 0), ("dp.norm_1.beta", (D,), "bias", 0),
+           ("dp.conv_2.weight", (D, D, kd), "conv", D * kd), ("dp.conv_2.bias", (D,), "bias", 0),
+           ("dp.norm_2.gamma", (D,), "gamma", 0), ("dp.norm_2.beta", (D,), "bias", 0),
+           ("dp.proj.weight", (1, D, 1), "conv", D), ("dp.proj.bias", (1,), "bias", 0),
+           ("dp.cond1.weight", (D, gin), "linear", gin), ("dp.cond1.bias", (D,), "bias", 0),
+           ("dp.cond2.weight", (D, gin), "linear", gin), ("dp.cond2.bias", (D,), "bias", 0),
+           ("emb_g.weight", (cfg.n_speakers, gin), "embed", 0)]
+    return sp
+
+
+def make_p1_state_dict(cfg: HotPathConfig, seed: int = 4321) -> Dict[str, torch.Tensor]:
+    """fp32 `enc_p.*` / `dp.*` / `emb_g.*` state_dict at fan-in scale (LayerNorm gains around 1, biases +-0.1,
+    emb_g ~ N(0, 1) as nn.Embedding's default); the duration head is biased so that durations land around 3-12 frames."""
+    gen = torch.Generator().manual_seed(seed)
+    sd: Dict[str, torch.Tensor] = {}
+    for key, shape, kind, fan_in in p1_param_specs(cfg):
+        if kind == "scalar":
+            sd[key] = torch.tensor(1.0) + 0.1 * torch.randn((), generator=gen)
+        elif kind == "bias":
+            sd[key] = torch.rand(shape, generator=gen) * 0.2 - 0.1
+        elif kind == "gamma":
+            sd[key] = 1.0 + 0.2 * (torch.rand(shape, generator=gen) - 0.5)
+        elif kind == "embed":
+            sd[key] = torch.randn(shape, generator=gen)
+        else:
+            scale = 1.0 / math.sqrt(fan_in)
+            if kind == "linear" and fan_in == cfg.gin_channels:
+                scale *= 0.5
+            sd[key] = torch.randn(shape, generator=gen) * scale
+    sd["dp.proj.bias"] = torch.tensor([1.6])
+    sd["dp.proj.weight"] = sd["dp.proj.weight"] * 0.5
+    return sd
+
+
+def make_p1_inputs(cfg: HotPathConfig, lengths: List[int], seed: int = 99):
+    """Inputs of infer_p1 / the batched encoder head: text features [B, Tx, text_channels] (zero beyond each row's
+    length), emo [B, 1024], sid [B]."""
+    gen = torch.Generator().manual_seed(seed)
+    B, Tm = len(lengths), max(lengths)
+    text = torch.zeros(B, Tm, cfg.text_channels)
+    for b, L in enumerate(lengths):
+        text[b, :L] = torch.randn(L, cfg.text_channels, generator=gen)
+    emo = torch.randn(B, cfg.emo_channels, generator=gen)
+    sid = torch.tensor([(b * 37 + 5) % cfg.n_speakers for b in range(B)], dtype=torch.long)
+    return {"text": text, "emo": emo, "sid": sid, "lengths": torch.tensor(lengths, dtype=torch.int64)}

@@ -97,6 +97,28 @@ def main():
     np.savez_compressed(os.path.join(OUT, "base_batch3.npz"), z_padded=zb.numpy(), o_padded=ob.numpy(),
                         lengths=np.array(lens), **rag)
 
+    # ---------------- infer_p1: text encoder + duration predictor ----------------
+    sd1 = FX.make_p1_state_dict(cfg, seed=4321)
+    ref_p1 = {k: v for k, v in m.state_dict().items() if k.startswith(("enc_p.", "dp.", "emb_g."))}
+    assert set(ref_p1) == set(sd1), sorted(set(ref_p1) ^ set(sd1))[:6]
+    for k in sd1:
+        assert tuple(ref_p1[k].shape) == tuple(sd1[k].shape), k
+    missing, unexpected = m.load_state_dict(sd1, strict=False)
+    assert not unexpected and all(not k.startswith(("enc_p.", "dp.", "emb_g.")) for k in missing)
+    p1 = {}
+    for Tx, seed in ((60, 99), (1, 3), (5, 4), (131, 7)):
+        inp1 = FX.make_p1_inputs(cfg, [Tx], seed=seed)
+        m_p, s_p, logw, g1 = m.infer_p1(inp1["text"], inp1["emo"], inp1["sid"])      # models.py:558-566
+        p1.update({f"m_p_T{Tx}": m_p.numpy(), f"s_p_T{Tx}": s_p.numpy(), f"logw_T{Tx}": logw.numpy(), f"g_T{Tx}": g1.numpy()})
+    # batched, masked head of inference() (models.py:518-522)
+    lens1 = [23, 60, 7]
+    inpb = FX.make_p1_inputs(cfg, lens1, seed=11)
+    gb = m.emb_g(inpb["sid"])
+    xb, mb, logsb, xmask = m.enc_p(inpb["text"], inpb["lengths"], inpb["emo"], g=gb)
+    logwb = m.dp(xb, xmask, g=gb)
+    p1.update({"m_p_batch": mb.numpy(), "logs_p_batch": logsb.numpy(), "logw_batch": logwb.numpy(), "lengths_batch": np.array(lens1)})
+    np.savez_compressed(os.path.join(OUT, "base_p1.npz"), **p1)
+
     # ---------------- sat/configs/adapt.json (second shape set) ----------------
     cfga = json.load(open(os.path.join(REF, "sat", "configs", "adapt.json")))
     cfga["data"].setdefault("hop_length", 96)

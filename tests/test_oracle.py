@@ -115,3 +115,32 @@ def test_logmel_sane():
     peak = lm.mean(-1)[0].argmax().item()
     centre = np.argmax(mb[:, round(1000 / (16000 / 1024))])
     assert abs(peak - centre) <= 1
+
+
+def test_p1_oracle_matches_reference_golden(base_cfg, golden_dir):
+    """oracle/p1_oracle.py against outputs of the reference's own infer_p1 (models.py:558-566) and
+    the masked batched head of inference() (models.py:518-522), generated by oracle/gen_golden.py."""
+    import numpy as np
+    import torch
+    from oracle import fixtures as FX
+    from oracle import p1_oracle as P
+    gold = np.load(os.path.join(golden_dir, "base_p1.npz"))
+    sd = FX.make_p1_state_dict(base_cfg, seed=4321)
+    with torch.no_grad():
+        for Tx, seed in ((60, 99), (1, 3), (5, 4), (131, 7)):
+            inp = FX.make_p1_inputs(base_cfg, [Tx], seed=seed)
+            m_p, s_p, logw, g = P.infer_p1(sd, inp["text"], inp["emo"], inp["sid"], base_cfg)
+            assert np.abs(m_p.numpy() - gold[f"m_p_T{Tx}"]).max() <= 2e-5
+            assert np.abs(s_p.numpy() / gold[f"s_p_T{Tx}"] - 1).max() <= 2e-5
+            assert np.abs(logw.numpy() - gold[f"logw_T{Tx}"]).max() <= 2e-5
+            assert np.array_equal(g.numpy(), gold[f"g_T{Tx}"])
+        lens = [int(x) for x in gold["lengths_batch"]]
+        inp = FX.make_p1_inputs(base_cfg, lens, seed=11)
+        m_p, s_p, logw, _ = P.infer_p1(sd, inp["text"], inp["emo"], inp["sid"], base_cfg, x_lengths=inp["lengths"])
+        assert np.abs(m_p.numpy() - gold["m_p_batch"]).max() <= 2e-5
+        assert np.abs(torch.log(s_p).numpy() - gold["logs_p_batch"]).max() <= 2e-5
+        assert np.abs(logw.numpy() - gold["logw_batch"]).max() <= 2e-5
+        # glue: durations -> path equals commons.infer_path semantics (one source position per frame, row sums 1)
+        logw60 = torch.from_numpy(gold["logw_T60"])
+        w_ceil, y_len, path = P.durations_to_path(logw60)
+        assert path.shape == (1, y_len, 60) and torch.all(path.sum(-1) == 1) and torch.equal(path.sum(1).view(-1), w_ceil.view(-1))

@@ -26,6 +26,16 @@ class HotPathConfig:
     upsample_kernel_sizes: Sequence[int] = (16, 12, 4, 4)
     sampling_rate: int = 16000
     hop_length: int = 192
+    # infer_p1 side (text encoder + duration predictor; models.py:421-448, 462-465)
+    text_channels: int = 256
+    filter_channels: int = 512
+    n_heads: int = 2
+    n_layers: int = 6
+    kernel_size: int = 5
+    hidden_size_d: int = 256
+    kernel_size_d: int = 5
+    n_speakers: int = 2048
+    emo_channels: int = 1024           # models.py:147 hard-codes nn.Linear(1024, hidden_channels)
 
     @staticmethod
     def from_json(cfg: dict) -> "HotPathConfig":
@@ -43,6 +53,14 @@ class HotPathConfig:
             upsample_kernel_sizes=tuple(m["upsample_kernel_sizes"]),
             sampling_rate=d.get("sampling_rate", 16000),
             hop_length=d.get("hop_length", 192),
+            text_channels=d.get("text_channels", 256),
+            filter_channels=m.get("filter_channels", 512),
+            n_heads=m.get("n_heads", 2),
+            n_layers=m.get("n_layers", 6),
+            kernel_size=m.get("kernel_size", 5),
+            hidden_size_d=m.get("hidden_size_d", 256),
+            kernel_size_d=m.get("kernel_size_d", 5),
+            n_speakers=d.get("n_speakers", 2048),
         )
 
     @property
