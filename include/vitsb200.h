@@ -74,6 +74,8 @@ typedef struct {
   int32_t upsample_kernel_sizes[VITSB_MAX_LIST]; /* 16,12,4,4 */
   int32_t upsample_initial_channel;       /* 512 */
   int32_t precision;                      /* vitsb_precision */
+  int32_t enc_n_heads;                    /* 2   text-encoder attention heads (infer_p1 side; 0 = 2).  Every other
+                                             encoder / duration-predictor size is read off the checkpoint tensors */
 } vitsb_config;
 
 typedef enum { VITSB_F32 = 0, VITSB_F16 = 1, VITSB_BF16 = 2 } vitsb_dtype;
@@ -157,6 +159,19 @@ int vitsb_synthesize_pcm16(vitsb_handle* h, const float* z_p, const float* g, co
  *   attn : device fp32 [B, T, Tx];  m_p, s_p : device fp32 [B, inter, Tx];  noise, z_p : device fp32 [B, inter, T]. */
 int vitsb_length_regulate(vitsb_handle* h, const float* attn, const float* m_p, const float* s_p, const float* noise,
                           int B, int T, int Tx, float* z_p, vitsb_stream stream);
+
+/* Replaces: SynthesizerTrn.infer_p1(x, emo, sid) (models.py:558-566) - speaker embedding, TextEncoder.infer
+ * (models.py:180-189; attentions.py:48-54, 78-102, 160-166), exp(logs_p), DurationPredictor.infer (models.py:59-67) -
+ * in fp32 (the durations feed ceil(exp(logw)), infer.py:169-171).  Available when vitsb_load_weights was given the
+ * checkpoint's enc_p.* / dp.* / emb_g.* entries, else VITSB_ERR_WEIGHTS.  Rows are ragged: row b equals the B = 1 call on
+ * its own x_len[b] phonemes (x_len = NULL: every row has Tx_max), outputs are zero beyond.
+ *   text : device fp32 [B, Tx_max, text_channels];  emo : device fp32 [B, 1024];  sid, x_len : HOST int32 [B]
+ *   m_p, s_p : device fp32 [B, inter, Tx_max];  logw : device fp32 [B, 1, Tx_max];  g : device fp32 [B, gin]
+ *   Tx_max <= 1024. */
+size_t vitsb_p1_workspace_bytes(const vitsb_handle* h, int B, int Tx_max);
+int vitsb_infer_p1(vitsb_handle* h, const float* text, const float* emo, const int32_t* sid, const int32_t* x_len,
+                   int B, int Tx_max, float* m_p, float* s_p, float* logw, float* g,
+                   void* ws, size_t ws_bytes, vitsb_stream stream);
 
 /* No counterpart in the reference: added for callers that cannot allocate
  * (code under CUDA-graph capture, tight serving loops, harnesses that forbid cudaMalloc) and so cannot hand

@@ -186,6 +186,10 @@ def make_p1_state_dict(cfg: HotPathConfig, seed: int = 4321) -> Dict[str, torch.
             if kind == "linear" and fan_in == cfg.gin_channels:
                 scale *= 0.5
             sd[key] = torch.randn(shape, generator=gen) * scale
+    # log-scale head of the prior: s_p = exp(logs_p) around 0.3 .. 1.1, the range SURVEY 8(d) states for the path's inputs
+    ic = cfg.inter_channels
+    sd["enc_p.proj.weight"][ic:] *= 0.25
+    sd["enc_p.proj.bias"][ic:] -= 0.5
     sd["dp.proj.bias"] = torch.tensor([1.6])
     sd["dp.proj.weight"] = sd["dp.proj.weight"] * 0.5
     return sd

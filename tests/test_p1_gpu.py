@@ -1,0 +1,96 @@
+"""GPU: infer_p1 (text encoder + duration predictor) through the C ABI against the reference-generated
+goldens (tests/golden/base_p1.npz, made by oracle/gen_golden.py from the reference's own SynthesizerTrn.infer_p1) and the
+CPU oracle (oracle/p1_oracle.py).  fp32 arithmetic on the device; tolerance 2e-4 absolute on m_p / logw (values of
+O(1)), 2e-4 relative on s_p = exp(logs_p)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import fixtures as FX
+from oracle import p1_oracle as P
+from oracle import vits_oracle as O
+
+pytestmark = pytest.mark.gpu
+TOL = 2e-4
+
+_eng = {}
+
+
+def engine(base_cfg, base_sd, prec="fp16"):
+    from vits_b200 import FlowDecoder
+    if prec not in _eng:
+        sd = dict(base_sd)
+        sd.update(FX.make_p1_state_dict(base_cfg, seed=4321))
+        _eng[prec] = FlowDecoder(base_cfg, sd, device="cuda:0", precision=prec)
+    return _eng[prec]
+
+
+def test_infer_p1_golden(base_cfg, base_sd, golden_dir):
+    gold = np.load(os.path.join(golden_dir, "base_p1.npz"))
+    eng = engine(base_cfg, base_sd)
+    for Tx, seed in ((60, 99), (1, 3), (5, 4), (131, 7)):
+        inp = FX.make_p1_inputs(base_cfg, [Tx], seed=seed)
+        m_p, s_p, logw, g = eng.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"])
+        assert m_p.shape == (1, 192, Tx) and s_p.shape == (1, 192, Tx) and logw.shape == (1, 1, Tx) and g.shape == (1, 1024)
+        assert np.array_equal(g.cpu().numpy(), gold[f"g_T{Tx}"])
+        assert np.abs(m_p.cpu().numpy() - gold[f"m_p_T{Tx}"]).max() <= TOL
+        assert np.abs(s_p.cpu().numpy() / gold[f"s_p_T{Tx}"] - 1).max() <= TOL
+        assert np.abs(logw.cpu().numpy() - gold[f"logw_T{Tx}"]).max() <= TOL
+        # the quantity that matters downstream: integer durations (infer.py:169-171)
+        w_ref = np.ceil(np.exp(gold[f"logw_T{Tx}"]))
+        w = np.ceil(np.exp(logw.cpu().numpy()))
+        near = np.abs(np.exp(gold[f"logw_T{Tx}"]) - np.round(np.exp(gold[f"logw_T{Tx}"]))) < 1e-3      # within tolerance of an integer
+        assert np.array_equal(w[~near], w_ref[~near])
+
+
+def test_infer_p1_ragged_batch_equals_per_row_calls(base_cfg, base_sd):
+    eng = engine(base_cfg, base_sd)
+    sd1 = FX.make_p1_state_dict(base_cfg, seed=4321)
+    lens = [23, 60, 7, 1]
+    inp = FX.make_p1_inputs(base_cfg, lens, seed=11)
+    m_p, s_p, logw, g = eng.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"], lens)
+    for b, L in enumerate(lens):
+        with torch.no_grad():
+            mr, sr, lr, gr = P.infer_p1(sd1, inp["text"][b:b + 1, :L], inp["emo"][b:b + 1], inp["sid"][b:b + 1], base_cfg)
+        assert (m_p[b:b + 1, :, :L].cpu() - mr).abs().max().item() <= TOL
+        assert (s_p[b:b + 1, :, :L].cpu() / sr - 1).abs().max().item() <= TOL
+        assert (logw[b:b + 1, :, :L].cpu() - lr).abs().max().item() <= TOL
+        assert torch.equal(g[b:b + 1].cpu(), gr)
+        assert m_p[b, :, L:].abs().sum().item() == 0 and s_p[b, :, L:].abs().sum().item() == 0 and logw[b, :, L:].abs().sum().item() == 0
+        # bit-identical to the B = 1 call on that row
+        m1, s1, l1, _ = eng.infer_p1(inp["text"][b:b + 1, :L].contiguous().cuda(), inp["emo"][b:b + 1].cuda(), inp["sid"][b:b + 1])
+        assert torch.equal(m1[0], m_p[b, :, :L]) and torch.equal(l1[0], logw[b, :, :L]) and torch.equal(s1[0], s_p[b, :, :L])
+
+
+@pytest.mark.parametrize("prec,tol", [("fp32", 5e-4), ("fp16", 2e-3)])
+def test_infer_chain_p1_glue_p2_vs_oracle(base_cfg, base_sd, prec, tol):
+    """EmoVITS.infer's chain (infer.py:166-182): infer_p1 -> w_ceil / path glue -> infer_p2, against the CPU oracle chain
+    on the same noise."""
+    eng = engine(base_cfg, base_sd, prec)
+    sd1 = FX.make_p1_state_dict(base_cfg, seed=4321)
+    inp = FX.make_p1_inputs(base_cfg, [40], seed=21)
+    with torch.no_grad():
+        mr, sr, lr, gr = P.infer_p1(sd1, inp["text"], inp["emo"], inp["sid"], base_cfg)
+        w_ref, y_ref, path_ref = P.durations_to_path(lr)
+        noise = torch.randn(1, 192, y_ref, generator=torch.Generator().manual_seed(5)) * 0.707
+        o_ref = O.infer_p2(base_sd, path_ref, mr, sr, gr, noise, base_cfg)
+    m_p, s_p, logw, g = eng.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"])
+    w, y_len, path = P.durations_to_path(logw.cpu())                 # host glue, as the reference does it (infer.py:169-176)
+    assert y_len == y_ref and torch.equal(w, w_ref)
+    o = eng.infer_p2(path.cuda(), m_p, s_p, g, noise.cuda()).cpu()
+    assert o.shape == o_ref.shape == (1, 1, y_ref * 192)
+    assert (o - o_ref).abs().max().item() <= tol
+
+
+def test_infer_p1_needs_its_weights(base_cfg, base_sd):
+    from vits_b200 import FlowDecoder
+    from vits_b200 import lib as L
+    eng = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision="fp16")      # dec.* / flow.* only
+    inp = FX.make_p1_inputs(base_cfg, [5], seed=1)
+    with pytest.raises(L.VitsbError):
+        eng.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"])
+    full = engine(base_cfg, base_sd)
+    with pytest.raises(L.VitsbError):
+        full.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), [99999])          # sid out of range (infer.py:145)

@@ -63,8 +63,13 @@ struct Call {
   cudaStream_t stream = nullptr;
 };
 
+struct P1State;                 // packed text encoder + duration predictor (p1.cu)
+void p1_destroy(P1State* s);
+bool p1_present(const vitsb_tensor_desc* t, int n);
+
 struct Engine {
   vitsb_config cfg{};
+  P1State* p1 = nullptr;        // infer_p1 side, present when the state_dict carried enc_p.* / dp.* / emb_g.*
   int device = 0;
   int num_sms = 148;
   int op = OP_F16;

@@ -36,6 +36,7 @@ void Engine::free_device() {
 }
 
 Engine::~Engine() {
+  p1_destroy(p1);
   drop_graphs();
   if (cap_stream) cudaStreamDestroy(cap_stream);
   free_device();
@@ -216,6 +217,8 @@ std::vector<int> gate_rows(int N_total, int NT) {
 std::vector<int> iota_rows(int n0, int n) { std::vector<int> r(n); for (int i = 0; i < n; ++i) r[i] = n0 + i; return r; }
 
 }  // namespace
+
+int p1_load(Engine& e, const vitsb_tensor_desc* t, int n);
 
 int Engine::load(const vitsb_tensor_desc* tens, int n) {
   if (!tens || n <= 0) return fail(VITSB_ERR_BAD_ARG, "no tensors");
@@ -574,6 +577,9 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
   if (cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || num_sms <= 0) num_sms = 148;
   std::vector<float>().swap(h_w); std::vector<float>().swap(h_condW);
   loaded = true;
+  // optional infer_p1 side (text encoder, duration predictor, speaker table): packed when the checkpoint carries it
+  p1_destroy(p1); p1 = nullptr;
+  if (p1_present(tens, n)) return p1_load(*this, tens, n);
   return VITSB_OK;
 }
 

@@ -28,7 +28,7 @@ _TORCH_DT = {torch.float32: L.DT_F32, torch.float16: L.DT_F16, torch.bfloat16: L
 
 def _hot_items(state_dict):
     for k, v in state_dict.items():
-        if k.startswith("dec.") or k.startswith("flow."):
+        if k.startswith(("dec.", "flow.", "enc_p.", "dp.", "emb_g.")):
             yield k, v
 
 
@@ -54,6 +54,7 @@ class FlowDecoder:
             raise L.VitsbError(rc, self.lib.vitsb_last_error(None).decode())
         self._h = h
         self._ws: Optional[torch.Tensor] = None
+        self._ws1: Optional[torch.Tensor] = None
         for k, v in (options or {}).items():
             self.set_option(k, v)
         self.load_state_dict(state_dict)
@@ -221,6 +222,42 @@ class FlowDecoder:
             self._check(self.lib.vitsb_length_regulate(self._h, attn.data_ptr(), m_p.data_ptr(), s_p.data_ptr(), noise.data_ptr(),
                                                        B, Ty, Tx, z_p.data_ptr(), self._stream()))
         return z_p
+
+    @torch.no_grad()
+    def infer_p1(self, text: torch.Tensor, emo: torch.Tensor, sid, x_lengths: Optional[Sequence[int]] = None):
+        """SynthesizerTrn.infer_p1 (models.py:558-566) on the library, fp32: text [B,Tx,text_channels], emo [B,1024],
+        sid [B] -> (m_p [B,inter,Tx], s_p, logw [B,1,Tx], g [B,gin]).  B > 1 rows are ragged (x_lengths), each equal to
+        its own B = 1 call.  Needs the checkpoint's enc_p.* / dp.* / emb_g.* entries."""
+        dev = self.device
+        text = text.to(dev, torch.float32).contiguous()
+        emo = emo.to(dev, torch.float32).reshape(text.size(0), -1).contiguous()
+        if text.dim() != 3:
+            raise ValueError("expected text [B,Tx,text_channels]")
+        B, Tx, _ = text.shape
+        sid_l = [int(v) for v in (sid.tolist() if torch.is_tensor(sid) else sid)]
+        if len(sid_l) != B:
+            raise ValueError("sid must have B entries")
+        sid_a = (C.c_int32 * B)(*sid_l)
+        len_a = None
+        if x_lengths is not None:
+            ll = [int(v) for v in (x_lengths.tolist() if torch.is_tensor(x_lengths) else x_lengths)]
+            if len(ll) != B:
+                raise ValueError("x_lengths must have B entries")
+            len_a = (C.c_int32 * B)(*ll)
+        with torch.cuda.device(dev):
+            need = int(self.lib.vitsb_p1_workspace_bytes(self._h, B, Tx))
+            if need == 0:
+                raise L.VitsbError(3, "infer_p1 weights not loaded (state_dict had no enc_p.* / dp.* / emb_g.* entries)")
+            if self._ws1 is None or self._ws1.numel() < need:
+                self._ws1 = torch.empty(need, dtype=torch.uint8, device=dev)
+            m_p = torch.empty(B, self.inter_channels, Tx, dtype=torch.float32, device=dev)
+            s_p = torch.empty_like(m_p)
+            logw = torch.empty(B, 1, Tx, dtype=torch.float32, device=dev)
+            g = torch.empty(B, self.gin_channels, dtype=torch.float32, device=dev)
+            self._check(self.lib.vitsb_infer_p1(self._h, text.data_ptr(), emo.data_ptr(), sid_a, len_a, B, Tx, m_p.data_ptr(),
+                                                s_p.data_ptr(), logw.data_ptr(), g.data_ptr(), self._ws1.data_ptr(),
+                                                self._ws1.numel(), self._stream()))
+        return m_p, s_p, logw, g
 
     @torch.no_grad()
     def infer_p2(self, attn, m_p, s_p, g, noise) -> torch.Tensor:

@@ -25,7 +25,7 @@ class VitsbConfig(C.Structure):
         ("n_resblock_dilations", C.c_int32), ("resblock_dilation_sizes", (C.c_int32 * MAX_LIST) * MAX_LIST),
         ("n_upsamples", C.c_int32), ("upsample_rates", C.c_int32 * MAX_LIST),
         ("upsample_kernel_sizes", C.c_int32 * MAX_LIST), ("upsample_initial_channel", C.c_int32),
-        ("precision", C.c_int32),
+        ("precision", C.c_int32), ("enc_n_heads", C.c_int32),
     ]
 
 
@@ -51,6 +51,9 @@ SYMBOLS = {
     "vitsb_synthesize_pcm16": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_float, _P, _P,
                                          C.c_size_t, _P]),
     "vitsb_length_regulate": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "vitsb_p1_workspace_bytes": (C.c_size_t, [_P, C.c_int, C.c_int]),
+    "vitsb_infer_p1": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int, C.c_int, _P, _P, _P, _P, _P,
+                                 C.c_size_t, _P]),
     "vitsb_flow_reverse_noalloc": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.c_int, C.c_int, _P, _P]),
     "vitsb_noalloc_scratch_bytes": (C.c_size_t, []),
     "vitsb_total_upsample": (C.c_int, [_P]),
@@ -131,4 +134,5 @@ def make_config(cfg, precision: str) -> VitsbConfig:
         c.upsample_kernel_sizes[i] = k
     c.upsample_initial_channel = get("upsample_initial_channel")
     c.precision = PRECISIONS[precision]
+    c.enc_n_heads = int(get("n_heads", 2) or 2)
     return c
