@@ -160,6 +160,26 @@ int vitsb_synthesize_pcm16(vitsb_handle* h, const float* z_p, const float* g, co
 int vitsb_length_regulate(vitsb_handle* h, const float* attn, const float* m_p, const float* s_p, const float* noise,
                           int B, int T, int Tx, float* z_p, vitsb_stream stream);
 
+/* Replaces: the host glue between infer_p1 and infer_p2 in EmoVITS.infer (infer.py:169-176: w = exp(logw) * rate,
+ * w_ceil = ceil(w), y_length = clamp_min(sum, 1).item(), attn = infer_path(...); commons.py:143-155), the head of infer_p2
+ * (models.py:570-572) and its tail (flow + decoder) in ONE stream-ordered call with no host synchronisation: durations,
+ * their cumulative sum and the output lengths are computed on the device, the gather m_p + noise * s_p is written
+ * straight into the time-major flow state (no dense attn, no channel-major z_p), and every kernel reads the lengths
+ * from device memory (grids use upper bounds).  SURVEY 8(f) N1.
+ *   m_p, s_p : device fp32 [B, inter, Tx_max];  logw : device fp32 [B, 1, Tx_max];  g : device fp32 [B, gin]
+ *   x_len    : HOST int32 [B] phonemes per row, or NULL (all Tx_max);  Tx_max <= 1024
+ *   noise    : device fp32, already scaled by noise_scale (infer.py:69); noise_stride >= T_cap: [B, inter, noise_stride];
+ *              noise_stride = 0: the reference's compact form - row b is a contiguous [inter, y_len[b]] block placed
+ *              after the blocks of the rows before it (infer.py:172-174 views a flat pool as [1, inter, y_length])
+ *   T_cap    : frame capacity of the outputs; rows longer than T_cap are truncated to it
+ *   wav / pcm: device fp32 / int16 [B, 1, T_cap * prod(upsample_rates)], one of them may be NULL; zero beyond y_len[b]
+ *   z_out    : optional device fp32 [B, inter, T_cap];  y_len : optional device int32 [B] (frames per row)
+ *   ws       : vitsb_workspace_bytes(h, B, T_cap) bytes (this entry point does not chunk rows). */
+int vitsb_synthesize_durations(vitsb_handle* h, const float* m_p, const float* s_p, const float* logw, const float* g,
+                               const int32_t* x_len, const float* noise, long long noise_stride, int B, int Tx_max, int T_cap,
+                               float length_scale, int ragged, float* z_out, float* wav, int16_t* pcm, float volume,
+                               int32_t* y_len, void* ws, size_t ws_bytes, vitsb_stream stream);
+
 /* Replaces: SynthesizerTrn.infer_p1(x, emo, sid) (models.py:558-566) - speaker embedding, TextEncoder.infer
  * (models.py:180-189; attentions.py:48-54, 78-102, 160-166), exp(logs_p), DurationPredictor.infer (models.py:59-67) -
  * in fp32 (the durations feed ceil(exp(logw)), infer.py:169-171).  Available when vitsb_load_weights was given the

@@ -94,3 +94,60 @@ def test_infer_p1_needs_its_weights(base_cfg, base_sd):
     full = engine(base_cfg, base_sd)
     with pytest.raises(L.VitsbError):
         full.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), [99999])          # sid out of range (infer.py:145)
+
+
+@pytest.mark.parametrize("prec", ["fp32", "fp16"])
+def test_device_side_durations_equal_the_host_glue(base_cfg, base_sd, prec):
+    """vitsb_synthesize_durations (durations, cumsum, lengths and the gather on the device, lengths never
+    on the host) == infer_p1 -> host glue (infer.py:169-176) -> infer_p2, and == the CPU oracle chain."""
+    eng = engine(base_cfg, base_sd, prec)
+    sd1 = FX.make_p1_state_dict(base_cfg, seed=4321)
+    tol = {"fp32": 5e-4, "fp16": 2e-3}[prec]
+    for Tx, seed, scale in ((40, 21, 1.0), (7, 22, 1.3), (1, 23, 1.0)):
+        inp = FX.make_p1_inputs(base_cfg, [Tx], seed=seed)
+        m_p, s_p, logw, g = eng.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"])
+        w, y_len, path = P.durations_to_path(logw.cpu(), scale)
+        T_cap = y_len + 37
+        noise = torch.randn(1, 192, T_cap, generator=torch.Generator().manual_seed(seed)) * 0.707
+        ref = eng.infer_p2(path.cuda(), m_p, s_p, g, noise[:, :, :y_len].contiguous().cuda())           # existing path, host glue
+        wav, yl, z = eng.synthesize_durations(m_p, s_p, logw, g, noise.cuda(), T_cap, length_scale=scale, return_z=True)
+        assert int(yl.item()) == y_len
+        assert wav.shape == (1, 1, T_cap * 192)
+        assert wav[:, :, y_len * 192:].abs().sum().item() == 0 and z[:, :, y_len:].abs().sum().item() == 0
+        assert (wav[:, :, :y_len * 192] - ref).abs().max().item() <= 1e-6
+        # compact noise: the reference's flat pool viewed as [1, inter, y_length] (infer.py:172-174)
+        pool = noise[:, :, :y_len].contiguous().view(-1)
+        pool = torch.cat([pool, torch.zeros(192 * T_cap - pool.numel())])
+        wav_c, _ = eng.synthesize_durations(m_p, s_p, logw, g, pool.cuda(), T_cap, length_scale=scale, compact_noise=True)
+        assert torch.equal(wav_c, wav)
+        # against the CPU oracle chain
+        with torch.no_grad():
+            mr, sr, lr, gr = P.infer_p1(sd1, inp["text"], inp["emo"], inp["sid"], base_cfg)
+            wr, yr, pr = P.durations_to_path(lr, scale)
+            assert yr == y_len
+            o_ref = O.infer_p2(base_sd, pr, mr, sr, gr, noise[:, :, :yr], base_cfg)
+        assert (wav[:, :, :yr * 192].cpu() - o_ref).abs().max().item() <= tol
+    # ragged batch, truncation at T_cap, int16 output, end-to-end infer()
+    lens = [23, 40, 7]
+    inp = FX.make_p1_inputs(base_cfg, lens, seed=31)
+    m_p, s_p, logw, g = eng.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"], lens)
+    T_cap = 150                                                      # shorter than the longest row: truncated
+    noise = torch.randn(3, 192, T_cap, generator=torch.Generator().manual_seed(9)) * 0.707
+    wav, yl = eng.synthesize_durations(m_p, s_p, logw, g, noise.cuda(), T_cap, x_lengths=lens)
+    yl = yl.tolist()
+    for b, L in enumerate(lens):
+        _, y_b, path = P.durations_to_path(logw[b:b + 1, :, :L].cpu())
+        assert yl[b] == min(y_b, T_cap)
+        if y_b <= T_cap:
+            one = eng.infer_p2(path.cuda(), m_p[b:b + 1, :, :L].contiguous(), s_p[b:b + 1, :, :L].contiguous(), g[b:b + 1],
+                               noise[b:b + 1, :, :y_b].contiguous().cuda())
+            assert (wav[b:b + 1, :, :y_b * 192] - one).abs().max().item() <= 1e-6
+        assert wav[b, :, yl[b] * 192:].abs().sum().item() == 0
+    wav2, yl2 = eng.infer(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"], noise.cuda(), T_cap, x_lengths=lens)
+    assert torch.equal(wav2, wav) and yl2.tolist() == yl
+    pcm, _ = eng.synthesize_durations(m_p, s_p, logw, g, noise.cuda(), T_cap, x_lengths=lens, pcm16=True, volume=0.8)
+    assert np.array_equal(pcm.cpu().numpy(), np.clip(wav.cpu().numpy() * np.float32(0.8) * 32767, -32768, 32767).astype(np.int16))
+    # repeated calls (graph capture + replay of the workspace-only launches) stay identical
+    for _ in range(3):
+        w3, _ = eng.synthesize_durations(m_p, s_p, logw, g, noise.cuda(), T_cap, x_lengths=lens)
+        assert torch.equal(w3, wav)

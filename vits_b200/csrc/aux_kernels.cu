@@ -471,3 +471,131 @@ cudaError_t launch_conv_post_y(const void* y0, const void* y1, const void* y2, f
 }
 
 }  // namespace vitsb
+
+namespace vitsb {
+
+// ---------------------------------------------------------------------------
+// Device-side durations.  Replaces the host glue between infer_p1 and infer_p2
+//   w = exp(logw) * length_scale; w_ceil = ceil(w); y_length = clamp_min(sum(w_ceil), 1).item()      infer.py:169-171, models.py:544-547
+//   attn = infer_path(w_ceil, x_length, y_length)                                                   commons.py:143-155
+// and the head of infer_p2 (models.py:570-572) without the dense 0/1 attn matrix, without the .item() host sync and
+// without a channel-major z_p: frame t of row b takes source position x(t) with cum[x-1] <= t < cum[x].
+// ---------------------------------------------------------------------------
+// One block per batch row: cum[b][x] = inclusive cumsum of ceil(exp(logw) * scale) over x < x_len[b] (integers, exact),
+// y_len[b] = min(max(cum[last], 1), T_cap); noise_off[b] = C * sum_{b' < b} y_len[b'] is filled by a second tiny pass.
+__global__ void __launch_bounds__(256)
+durations_scan_kernel(const float* __restrict__ logw, const int* __restrict__ x_len, int Tx, float scale, int T_cap,
+                      int* __restrict__ cum, int* __restrict__ y_len, int* __restrict__ y_len_out) {
+  __shared__ int s_part[256];
+  const int b = blockIdx.x, tid = threadIdx.x;
+  const int n = x_len ? x_len[b] : Tx;
+  const int per = (Tx + 255) / 256;                    // consecutive positions per thread
+  int local[4];                                         // Tx <= 1024
+  int sum = 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int x = tid * per + i;
+    int w = 0;
+    if (i < per && x < n) {
+      const float v = ceilf(__fmul_rn(expf(logw[(long long)b * Tx + x]), scale));       // torch.ceil(torch.exp(logw) * length_scale)
+      w = v > 0.f ? (v < 1e9f ? (int)v : 1000000000) : 0;
+    }
+    sum += w;
+    local[i] = sum;
+  }
+  s_part[tid] = sum;
+  __syncthreads();
+  for (int o = 1; o < 256; o <<= 1) {                   // Hillis-Steele inclusive scan of the per-thread sums
+    const int v = tid >= o ? s_part[tid - o] : 0;
+    __syncthreads();
+    s_part[tid] += v;
+    __syncthreads();
+  }
+  const int before = tid > 0 ? s_part[tid - 1] : 0;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int x = tid * per + i;
+    if (i < per && x < Tx) {
+      long long c = (long long)before + local[i];
+      cum[(long long)b * Tx + x] = c > 2000000000LL ? 2000000000 : (int)c;
+    }
+  }
+  if (tid == 255) {
+    int y = s_part[255] < 1 ? 1 : s_part[255];          // clamp_min(sum, 1)
+    if (n == 0) y = 0;                                  // an empty row stays empty
+    y = y > T_cap ? T_cap : y;
+    y_len[b] = y;
+    if (y_len_out) y_len_out[b] = y;
+  }
+}
+
+// z[b][t][c] = m_p[b][c][x(t)] + noise[b][c][t] * s_p[b][c][x(t)] for t < y_len[b], else 0; written time-major as the fp32
+// flow state and its operand copy ([hi | lo] when split).  Tile 32 frames x 32 channels through shared memory: the
+// noise reads are coalesced along t, the stores along c.  noise_stride > 0: noise is [B][C][noise_stride]; 0: the
+// reference's compact form, row b = a contiguous [C][y_len[b]] block after the blocks of the rows before it
+// (infer.py:172-174 views a flat pool as [1, C, y_length]).
+template <typename OpT>
+__global__ void __launch_bounds__(256)
+durations_gather_kernel(const float* __restrict__ m_p, const float* __restrict__ s_p, const float* __restrict__ noise,
+                        const int* __restrict__ cum, const int* __restrict__ y_len, const int* __restrict__ x_len, int B, int C, int Tx,
+                        int T, long long noise_stride, float* __restrict__ zf, OpT* __restrict__ zop, int split) {
+  __shared__ float tile[32][33];
+  __shared__ int s_x[32];
+  const int b = blockIdx.z, t0 = blockIdx.x * 32, c0 = blockIdx.y * 32;
+  const int yl = y_len[b];
+  if (t0 < yl) {
+    const int n = x_len ? x_len[b] : Tx;
+    if (threadIdx.y == 0) {                             // source position of each of the 32 frames: first x with cum[x] > t
+      const int t = t0 + threadIdx.x;
+      int lo = 0, hi = n > 0 ? n - 1 : 0;
+      const int* cb = cum + (long long)b * Tx;
+      while (lo < hi) { const int mid = (lo + hi) >> 1; if (cb[mid] > t) hi = mid; else lo = mid + 1; }
+      s_x[threadIdx.x] = lo;
+    }
+    long long nbase, nstr;
+    if (noise_stride > 0) { nstr = noise_stride; nbase = (long long)b * C * noise_stride; }
+    else { nstr = yl; nbase = 0; for (int bb = 0; bb < b; ++bb) nbase += (long long)C * y_len[bb]; }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += 8) {
+      const int c = c0 + i, t = t0 + threadIdx.x;
+      float v = 0.f;
+      if (c < C && t < yl) {
+        const long long so = ((long long)b * C + c) * Tx + s_x[threadIdx.x];
+        v = __fadd_rn(m_p[so], __fmul_rn(noise[nbase + (long long)c * nstr + t], s_p[so]));    // m + noise * s, two roundings (models.py:572)
+      }
+      tile[i][threadIdx.x] = v;
+    }
+    __syncthreads();
+  }
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int t = t0 + i, c = c0 + threadIdx.x;
+    if (t >= T || c >= C) continue;
+    const float v = t0 < yl ? tile[threadIdx.x][i] : 0.f;
+    const long long o = ((long long)b * T + t) * C + c;
+    if (zf) zf[o] = v;
+    if (split) {
+      const long long os = ((long long)b * T + t) * (2 * C) + c;
+      const OpT hi = to_op<OpT>(v);
+      zop[os] = hi;
+      zop[os + C] = to_op<OpT>(v - from_op<OpT>(hi));
+    } else {
+      zop[o] = to_op<OpT>(v);
+    }
+  }
+}
+
+cudaError_t launch_durations(const float* logw, const int* x_len, const float* m_p, const float* s_p, const float* noise,
+                             long long noise_stride, int B, int C, int Tx, int T, float scale, int* cum, int* y_len, int* y_len_out,
+                             float* zf, void* zop, int op, int split, cudaStream_t stream) {
+  if (Tx < 1 || Tx > 1024 || B < 1 || B > 65535) return cudaErrorInvalidValue;
+  durations_scan_kernel<<<B, 256, 0, stream>>>(logw, x_len, Tx, scale, T, cum, y_len, y_len_out);
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return e;
+  dim3 grid(ceil_div(T, 32), ceil_div(C, 32), B), block(32, 8);
+  if (op == OP_F16) durations_gather_kernel<__half><<<grid, block, 0, stream>>>(m_p, s_p, noise, cum, y_len, x_len, B, C, Tx, T, noise_stride, zf, (__half*)zop, split);
+  else if (op == OP_BF16) durations_gather_kernel<__nv_bfloat16><<<grid, block, 0, stream>>>(m_p, s_p, noise, cum, y_len, x_len, B, C, Tx, T, noise_stride, zf, (__nv_bfloat16*)zop, split);
+  else durations_gather_kernel<float><<<grid, block, 0, stream>>>(m_p, s_p, noise, cum, y_len, x_len, B, C, Tx, T, noise_stride, zf, (float*)zop, 0);
+  return cudaGetLastError();
+}
+
+}  // namespace vitsb

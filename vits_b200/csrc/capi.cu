@@ -104,6 +104,21 @@ int vitsb_synthesize_pcm16(vitsb_handle* h, const float* z_p, const float* g, co
   return h->eng.run(c, false, nullptr);
 }
 
+int vitsb_synthesize_durations(vitsb_handle* h, const float* m_p, const float* s_p, const float* logw, const float* g,
+                               const int32_t* x_len, const float* noise, long long noise_stride, int B, int Tx_max, int T_cap,
+                               float length_scale, int ragged, float* z_out, float* wav, int16_t* pcm, float volume,
+                               int32_t* y_len, void* ws, size_t ws_bytes, vitsb_stream stream) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  std::lock_guard<std::mutex> lk(h->eng.mu);
+  if (!wav && !pcm) return h->eng.fail(VITSB_ERR_BAD_ARG, "null wav / pcm");
+  DurFront d;
+  d.m_p = m_p; d.s_p = s_p; d.logw = logw; d.noise = noise; d.noise_stride = noise_stride; d.x_len = x_len; d.Tx = Tx_max;
+  d.scale = length_scale; d.y_len_out = reinterpret_cast<int*>(y_len);
+  Call c = make_call(Engine::RUN_FLOW | Engine::RUN_DEC, nullptr, g, nullptr, B, T_cap, ragged, ws, ws_bytes, stream);
+  c.dur = &d; c.z_out = z_out; c.wav = wav; c.pcm = reinterpret_cast<short*>(pcm); c.volume = volume;
+  return h->eng.run(c, false, nullptr);
+}
+
 int vitsb_length_regulate(vitsb_handle* h, const float* attn, const float* m_p, const float* s_p, const float* noise,
                           int B, int T, int Tx, float* z_p, vitsb_stream stream) {
   if (!h) return VITSB_ERR_BAD_ARG;

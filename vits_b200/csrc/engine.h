@@ -41,7 +41,7 @@ struct Stage {             // ups[i] + its MRF (num_kernels ResBlock2 x iteratio
 };
 
 struct WsLayout {
-  size_t len = 0, cond = 0;
+  size_t len = 0, cond = 0, xlen = 0, cum = 0;      // cum: int [B][1024] cumulative durations (durations front end)
   size_t zf = 0, zop = 0, hf = 0, hop = 0, acts = 0, skipf = 0, skipop = 0;   // flow (h / acts / skip: layer-at-a-time flow only)
   size_t xin_f = 0, xb_f = 0, acc_f = 0, g_op = 0;                            // decoder, layer-at-a-time plan (fp32 build)
   size_t xin_op = 0, xb_op = 0, xb2_op = 0, br0 = 0, br1 = 0, nxt_op = 0;     // decoder, 16-bit streams
@@ -49,6 +49,19 @@ struct WsLayout {
 };
 
 // One call through the C ABI (all pointers caller-owned; nothing here outlives the call).
+// Device-side durations front end: the call starts from infer_p1's outputs instead of z_p.
+struct DurFront {
+  const float* m_p = nullptr;     // [B][inter][Tx]
+  const float* s_p = nullptr;     // [B][inter][Tx]
+  const float* logw = nullptr;    // [B][1][Tx]
+  const float* noise = nullptr;   // [B][inter][noise_stride], or compact [inter][y_len[b]] blocks when noise_stride == 0
+  long long noise_stride = 0;
+  const int32_t* x_len = nullptr; // host [B] or null
+  int Tx = 0;
+  float scale = 1.f;              // length_scale / duration_rate
+  int* y_len_out = nullptr;       // device [B], optional
+};
+
 struct Call {
   int what = 0;                   // Engine::RUN_FLOW | Engine::RUN_DEC
   const float* z_in = nullptr;    // [B][inter][T] fp32, reference layout
@@ -61,6 +74,7 @@ struct Call {
   float volume = 1.f;
   void* ws = nullptr; size_t ws_bytes = 0;
   cudaStream_t stream = nullptr;
+  const DurFront* dur = nullptr;  // set: z_in / len are unused, T is the frame capacity, the lengths live on the device only
 };
 
 struct P1State;                 // packed text encoder + duration predictor (p1.cu)

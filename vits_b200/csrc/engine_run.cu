@@ -29,6 +29,8 @@ WsLayout Engine::layout(int B, int T) const {
   const size_t sm = split16 ? 2 : 1;             // split-precision operand rows are [hi | lo]
   w.len = take(sizeof(int) * (size_t)B);
   w.cond = take(sizeof(float) * (size_t)B * (Ncond > 0 ? Ncond : 1));
+  w.xlen = take(sizeof(int) * (size_t)B);
+  w.cum = take(sizeof(int) * (size_t)B * 1024);
   w.zf = take(4 * BT * IC);  w.zop = take(ob * BT * IC * sm);
   if (!flow_fused) {                             // the fused coupling kernel keeps h / acts / skip on chip
     w.hf = take(4 * BT * H);   w.hop = take(ob * BT * H * sm);
@@ -190,7 +192,16 @@ void set_out_op_hi(Epilogue& ep, void* p, int C, long long L, bool split_pitch, 
 int Engine::check_call(const Call& c, bool dry) {
   if (!dry) {
     if (!loaded) return fail(VITSB_ERR_WEIGHTS, "weights not loaded");
-    if (!c.z_in || !c.g || !c.ws) return fail(VITSB_ERR_BAD_ARG, "null pointer");
+    if (c.dur) {
+      const DurFront& d = *c.dur;
+      if (!d.m_p || !d.s_p || !d.logw || !d.noise || !c.g || !c.ws) return fail(VITSB_ERR_BAD_ARG, "null pointer");
+      if (d.Tx < 1 || d.Tx > 1024) return fail(VITSB_ERR_BAD_ARG, "Tx_max must be in [1, 1024]");
+      if (d.noise_stride != 0 && d.noise_stride < c.T) return fail(VITSB_ERR_BAD_ARG, "noise_stride must be 0 (compact) or >= T_cap");
+      if (c.len) return fail(VITSB_ERR_BAD_ARG, "durations front end computes the lengths itself");
+      if (d.x_len) for (int b = 0; b < c.B; ++b)
+        if (d.x_len[b] < 0 || d.x_len[b] > d.Tx) return fail(VITSB_ERR_BAD_ARG, "x_len[b] out of [0, Tx_max]");
+    } else if (!c.z_in) return fail(VITSB_ERR_BAD_ARG, "null pointer");
+    if (!c.g || !c.ws) return fail(VITSB_ERR_BAD_ARG, "null pointer");
     if ((c.what & RUN_DEC) && !c.wav && !c.pcm) return fail(VITSB_ERR_BAD_ARG, "null wav");
   }
   if (c.B < 1 || c.T < 1) return fail(VITSB_ERR_BAD_ARG, "B and T_max must be >= 1");
@@ -220,8 +231,9 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
   cx.h_len = len;
   cx.lo = lopts();
   int* d_len = reinterpret_cast<int*>(base + W.len);
-  cx.len_flow = len ? d_len : nullptr;
-  cx.len_dec = (len && c.ragged) ? d_len : nullptr;
+  const bool dev_len = c.dur != nullptr;               // lengths computed on the device: the host never sees them, grids use upper bounds
+  cx.len_flow = (len || dev_len) ? d_len : nullptr;
+  cx.len_dec = ((len || dev_len) && c.ragged) ? d_len : nullptr;
 
 #define AUX_LAUNCH(tag, expr) do { if (cx.skip) break; ++cx.launches; if (!dry && cx.ok()) { cx.ev_begin(tag, 0.0); cx.err = (expr); cx.ev_end(); } } while (0)
   if (!dry) {
@@ -235,6 +247,15 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
     if (len && (phases & PH_FRONT)) cx.err = cudaMemcpyAsync(d_len, len, sizeof(int) * B, cudaMemcpyHostToDevice, stream);
   }
   cx.skip = !(phases & PH_FRONT);
+  if (dev_len) {
+    // durations -> y_len, cumulative durations; gather m_p + noise * s_p straight into the time-major state   infer.py:169-176, models.py:570-572
+    const DurFront& d = *c.dur;
+    int* d_xlen = reinterpret_cast<int*>(base + W.xlen);
+    if (!dry && !cx.skip && d.x_len && cx.ok()) cx.err = cudaMemcpyAsync(d_xlen, d.x_len, sizeof(int) * B, cudaMemcpyHostToDevice, stream);
+    if (!cx.skip) ++cx.launches;                         // two kernels
+    AUX_LAUNCH(T_PACK, launch_durations(d.logw, d.x_len ? d_xlen : nullptr, d.m_p, d.s_p, d.noise, d.noise_stride, B, IC, d.Tx, T, d.scale,
+                                        reinterpret_cast<int*>(base + W.cum), d_len, d.y_len_out, F(W.zf), P(W.zop), op, split16 ? 1 : 0, stream));
+  } else
   // seam: channel-major fp32 -> time-major (masked beyond len)
   AUX_LAUNCH(T_PACK, launch_pack_time_major(c.z_in, B, IC, T, cx.len_flow, (what & RUN_FLOW) ? F(W.zf) : nullptr, P(W.zop), op, split16 ? 1 : 0, stream));
   // all conditioning Linears of the call: flow cond_layers (modules.py:161) + ResBlock conds (modules.py:254)
@@ -413,7 +434,7 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
 // per-rate tile counts the launchers size their grids with.  The lengths themselves are read from device memory.
 std::vector<long long> Engine::graph_key(const Call& c) const {
   std::vector<long long> key = {c.what, (long long)(uintptr_t)c.ws, (long long)c.ws_bytes, c.B, c.T, c.ragged, c.len ? 1 : 0,
-                                opt_pdl, opt_tc_pair, opt_rb_nslab};
+                                opt_pdl, opt_tc_pair, opt_rb_nslab, c.dur ? 1 : 0};
   if (c.len) {
     int mul = 1;
     key.push_back(Ctx::count_tiles(c.len, c.B, c.T, 1, true, kTileM, kHaloRows));
@@ -499,6 +520,7 @@ int Engine::run(const Call& c, bool dry, int* launches) {
   const int rows = chunk_rows(c.B, c.T, c.ws_bytes);
   if (rows < 1) return fail(VITSB_ERR_WORKSPACE, "workspace too small (needs at least the layout of one row: vitsb_workspace_bytes(h, 1, T_max))");
   if (rows >= c.B) return run_chunk(c, false, launches);
+  if (c.dur) return fail(VITSB_ERR_WORKSPACE, "the durations front end does not chunk rows: pass a workspace of vitsb_workspace_bytes(h, B, T_cap)");
   const size_t IC = cfg.inter_channels, gin = cfg.gin_channels, LT = (size_t)c.T * up_total;
   int total = 0;
   for (int b0 = 0; b0 < c.B; b0 += rows) {

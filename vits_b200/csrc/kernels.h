@@ -120,6 +120,11 @@ bool conv_post_supported(int C, int k);
 // head of infer_p2 (models.py:570-572): z_p[B][C][T] = attn @ m_p^T + noise * (attn @ s_p^T), reference layouts, fp32
 cudaError_t launch_length_regulate(const float* attn, const float* m_p, const float* s_p, const float* noise,
                                    int B, int C, int T, int Tx, float* z_p, cudaStream_t stream);
+// device-side durations + length regulation straight into the time-major flow state (aux_kernels.cu):
+// cum / y_len: device int [B][Tx] / [B] scratch; y_len_out: optional second copy for the caller
+cudaError_t launch_durations(const float* logw, const int* x_len, const float* m_p, const float* s_p, const float* noise,
+                             long long noise_stride, int B, int C, int Tx, int T, float scale, int* cum, int* y_len, int* y_len_out,
+                             float* zf, void* zop, int op, int split, cudaStream_t stream);
 // MRF average over the branches' final 16-bit y streams (16-bit paths): next upsampler operand rows `out` (16-bit,
 // [hi | lo] when split, leaky_relu(slope) applied) or, when out_f32 is given instead, the fp32 average itself
 // (conv_post input of shapes conv_post_y does not cover)

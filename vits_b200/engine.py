@@ -260,6 +260,50 @@ class FlowDecoder:
         return m_p, s_p, logw, g
 
     @torch.no_grad()
+    def synthesize_durations(self, m_p, s_p, logw, g, noise, T_cap: int, x_lengths: Optional[Sequence[int]] = None,
+                             length_scale: float = 1.0, compact_noise: bool = False, ragged: bool = True, pcm16: bool = False,
+                             volume: float = 1.0, return_z: bool = False):
+        """infer_p1's outputs -> waveform with the durations handled on the device (replaces the glue of
+        infer.py:169-176 and infer_p2, models.py:568-575): no `.item()` sync, no dense attn.  `noise` is [B,inter,>=T_cap]
+        (already scaled, infer.py:69) or, with compact_noise, the reference's flat pool viewed as [inter, y_len] blocks.
+        Returns (wav or pcm [B,1,T_cap*up] - zero beyond each row's length, y_len int32 [B] on the device[, z])."""
+        dev = self.device
+        m_p, s_p, logw, g, noise = (t.to(dev, torch.float32).contiguous() for t in (m_p, s_p, logw, g, noise))
+        B, IC, Tx = m_p.shape
+        if IC != self.inter_channels or tuple(s_p.shape) != (B, IC, Tx) or logw.numel() != B * Tx or tuple(g.shape) != (B, self.gin_channels):
+            raise ValueError("expected m_p, s_p [B,inter,Tx], logw [B,1,Tx], g [B,gin]")
+        if compact_noise:
+            stride = 0
+            if noise.numel() < B * IC * T_cap:
+                raise ValueError("compact noise pool must hold B * inter * T_cap values")
+        else:
+            if noise.dim() != 3 or noise.size(0) != B or noise.size(1) != IC or noise.size(2) < T_cap:
+                raise ValueError("expected noise [B,inter,>=T_cap]")
+            stride = noise.size(2)
+        len_a = None
+        if x_lengths is not None:
+            ll = [int(v) for v in (x_lengths.tolist() if torch.is_tensor(x_lengths) else x_lengths)]
+            len_a = (C.c_int32 * B)(*ll)
+        with torch.cuda.device(dev):
+            ws = self._workspace(B, T_cap)
+            out = torch.empty(B, 1, T_cap * self.total_upsample, dtype=torch.int16 if pcm16 else torch.float32, device=dev)
+            y_len = torch.empty(B, dtype=torch.int32, device=dev)
+            z = torch.empty(B, IC, T_cap, dtype=torch.float32, device=dev) if return_z else None
+            self._check(self.lib.vitsb_synthesize_durations(
+                self._h, m_p.data_ptr(), s_p.data_ptr(), logw.data_ptr(), g.data_ptr(), len_a, noise.data_ptr(), stride, B, Tx, int(T_cap),
+                float(length_scale), int(bool(ragged)), z.data_ptr() if return_z else None, None if pcm16 else out.data_ptr(),
+                out.data_ptr() if pcm16 else None, float(volume), y_len.data_ptr(), ws.data_ptr(), ws.numel(), self._stream()))
+        return (out, y_len, z) if return_z else (out, y_len)
+
+    @torch.no_grad()
+    def infer(self, text, emo, sid, noise, T_cap: int, x_lengths: Optional[Sequence[int]] = None, length_scale: float = 1.0,
+              **kw):
+        """SynthesizerTrn.infer (models.py:537-556) / EmoVITS.infer (infer.py:136-184) end to end on the library with
+        injected noise: infer_p1 -> device-side durations -> reverse flow -> decoder, no host synchronisation in between."""
+        m_p, s_p, logw, g = self.infer_p1(text, emo, sid, x_lengths)
+        return self.synthesize_durations(m_p, s_p, logw, g, noise, T_cap, x_lengths, length_scale, **kw)
+
+    @torch.no_grad()
     def infer_p2(self, attn, m_p, s_p, g, noise) -> torch.Tensor:
         """SynthesizerTrn.infer_p2 (models.py:568-575): length regulation, reverse flow, decoder - all on the CUDA path."""
         return self.synthesize(self.length_regulate(attn, m_p, s_p, noise), g)
