@@ -12,7 +12,7 @@
 
 namespace vitsb {
 
-constexpr int FT_M = 64, FT_N = 64, FT_K = 16;
+constexpr int FT_K = 16;
 
 __device__ __forceinline__ int packed_col_for_gate(int gc, int NT, int which) {
   // gate channel gc -> packed column of its tanh (which=0) / sigmoid (which=1) pre-activation
@@ -20,84 +20,115 @@ __device__ __forceinline__ int packed_col_for_gate(int gc, int NT, int which) {
   return (gc / half) * NT + (gc % half) + which * half;
 }
 
+// TM x TN output tile per CTA (64 x 64: 4 x 4 outputs per thread; 32 x 32: 2 x 2 - four times the CTAs, for the small
+// problems of the text encoder where a 64 x 64 grid leaves most SMs idle).  K slices stream through a 4-stage cp.async
+// ring, so the global-load latency is off the per-slice critical path (one barrier per slice).
+template <int TM, int TN>
 __global__ void __launch_bounds__(256)
 conv_f32_kernel(const ConvArgs a) {
+  constexpr int RM = TM / 16, RN = TN / 16;       // outputs per thread
+  constexpr int GH = TN / 2;                      // gate channels per CTA (tanh half | sigmoid half of the smem columns)
   const Epilogue& ep = a.epi;
   const int b = blockIdx.z;
-  const int t0 = blockIdx.x * FT_M;
+  const int t0 = blockIdx.x * TM;
   const int valid = a.len ? a.len[b] * a.len_mul : a.L;
   if (t0 >= valid + kHaloRows) return;   // nothing downstream reads these rows
 
-  __shared__ float As[FT_K][FT_M + 4];
-  __shared__ float Bs[FT_K][FT_N + 4];
+  constexpr int NS = 4;                           // cp.async stages in flight
+  __shared__ float As[NS][FT_K][TM + 4];
+  __shared__ float Bs[NS][FT_K][TN + 4];
   const int tid = threadIdx.x;
   const int tx = tid & 15, ty = tid >> 4;
 
-  // packed weight rows handled by this CTA's 64 smem columns
-  // linear: n0 + c ; gate: first 32 = tanh rows of 32 gate channels, last 32 = their sigmoid rows
+  // packed weight rows handled by this CTA's TN smem columns
+  // linear: n0 + c ; gate: first half = tanh rows of GH gate channels, second half = their sigmoid rows
   const int nblk = blockIdx.y;
   const int n_out_total = ep.gate ? a.N / 2 : a.N;
   auto wrow = [&](int c) -> int {
-    if (!ep.gate) { int n = nblk * FT_N + c; return n < a.N ? n : -1; }
-    int gc = nblk * 32 + (c & 31);
+    if (!ep.gate) { int n = nblk * TN + c; return n < a.N ? n : -1; }
+    int gc = nblk * GH + (c % GH);
     if (gc >= n_out_total) return -1;
-    return packed_col_for_gate(gc, a.gate_group > 0 ? a.gate_group : a.NT, c >> 5);
+    return packed_col_for_gate(gc, a.gate_group > 0 ? a.gate_group : a.NT, c / GH);
   };
 
-  float acc[4][4];
+  float acc[RM][RN];
 #pragma unroll
-  for (int i = 0; i < 4; ++i)
+  for (int i = 0; i < RM; ++i)
 #pragma unroll
-    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+    for (int j = 0; j < RN; ++j) acc[i][j] = 0.f;
 
   const float* in = reinterpret_cast<const float*>(a.in) + (long long)b * a.in_bstride;
   const float* w = reinterpret_cast<const float*>(a.w);
   const int Ktot = a.k * a.Cin;
-  // loader mapping: thread -> (row r = tid/4, 4 consecutive k = (tid%4)*4)
+  // loader mapping: thread -> (row r = tid/4, 4 consecutive k = (tid%4)*4); rows beyond the tile load nothing.
+  // 4-byte cp.async with a transposing destination (smem is [k][row] so that the inner product reads are conflict
+  // free); src-size 0 zero-fills (conv padding rows, weight rows beyond N).
   const int lr = tid >> 2, lk = (tid & 3) * 4;
-  const int my_wrow = wrow(lr);
-
-  for (int j = 0; j < a.k; ++j) {
-    const int trow = t0 + lr + j * a.dil - a.pad;
-    const bool row_ok = (trow >= 0) && (trow < a.L);
-    for (int c0 = 0; c0 < a.Cin; c0 += FT_K) {
-      float4 av = make_float4(0.f, 0.f, 0.f, 0.f), bv = av;
-      if (row_ok) av = *reinterpret_cast<const float4*>(in + (long long)trow * a.in_ld + (c0 % a.in_cols) + lk);
-      if (my_wrow >= 0) bv = *reinterpret_cast<const float4*>(w + (long long)my_wrow * Ktot + j * a.Cin + c0 + lk);
-      __syncthreads();
-      As[lk + 0][lr] = av.x; As[lk + 1][lr] = av.y; As[lk + 2][lr] = av.z; As[lk + 3][lr] = av.w;
-      Bs[lk + 0][lr] = bv.x; Bs[lk + 1][lr] = bv.y; Bs[lk + 2][lr] = bv.z; Bs[lk + 3][lr] = bv.w;
-      __syncthreads();
+  const bool a_thr = lr < TM, b_thr = lr < TN;
+  const int my_wrow = b_thr ? wrow(lr) : -1;
+  const int kslices = a.Cin / FT_K, nsl = a.k * kslices;
+  auto cp4 = [](float* dst, const float* src, bool ok) {
+    const unsigned d = (unsigned)__cvta_generic_to_shared(dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4, %2;" ::"r"(d), "l"(src), "r"(ok ? 4 : 0) : "memory");
+  };
+  auto issue = [&](int s) {
+    if (s < nsl) {
+      const int slot = s % NS;
+      const int j = s / kslices, c0 = (s - j * kslices) * FT_K;
+      if (a_thr) {
+        const int trow = t0 + lr + j * a.dil - a.pad;
+        const bool ok = trow >= 0 && trow < a.L;
+        const float* src = ok ? in + (long long)trow * a.in_ld + (c0 % a.in_cols) + lk : in;
 #pragma unroll
-      for (int kk = 0; kk < FT_K; ++kk) {
-        float ar[4], br[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) { ar[i] = As[kk][ty + 16 * i]; br[i] = Bs[kk][tx + 16 * i]; }
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-#pragma unroll
-          for (int jn = 0; jn < 4; ++jn) acc[i][jn] = fmaf(ar[i], br[jn], acc[i][jn]);
+        for (int q = 0; q < 4; ++q) cp4(&As[slot][lk + q][lr], src + (ok ? q : 0), ok);
       }
+      if (b_thr) {
+        const bool ok = my_wrow >= 0;
+        const float* src = ok ? w + (long long)my_wrow * Ktot + j * a.Cin + c0 + lk : w;
+#pragma unroll
+        for (int q = 0; q < 4; ++q) cp4(&Bs[slot][lk + q][lr], src + (ok ? q : 0), ok);
+      }
+    }
+    asm volatile("cp.async.commit_group;" ::: "memory");       // one group per slice, empty past the end
+  };
+#pragma unroll
+  for (int s = 0; s < NS - 1; ++s) issue(s);
+  for (int s = 0; s < nsl; ++s) {
+    asm volatile("cp.async.wait_group %0;" ::"n"(NS - 2) : "memory");   // slice s has landed
+    __syncthreads();                                            // ... for every thread; slot (s - 1) % NS is free again
+    issue(s + NS - 1);
+    const int slot = s % NS;
+#pragma unroll
+    for (int kk = 0; kk < FT_K; ++kk) {
+      float ar[RM], br[RN];
+#pragma unroll
+      for (int i = 0; i < RM; ++i) ar[i] = As[slot][kk][ty + 16 * i];
+#pragma unroll
+      for (int i = 0; i < RN; ++i) br[i] = Bs[slot][kk][tx + 16 * i];
+#pragma unroll
+      for (int i = 0; i < RM; ++i)
+#pragma unroll
+        for (int jn = 0; jn < RN; ++jn) acc[i][jn] = fmaf(ar[i], br[jn], acc[i][jn]);
     }
   }
 
   // ---- fused epilogue ----
   const float* bias = ep.bias + (long long)b * ep.bias_bstride;
 #pragma unroll
-  for (int i = 0; i < 4; ++i) {
+  for (int i = 0; i < RM; ++i) {
     const int t = t0 + ty + 16 * i;
     if (t >= a.L) continue;
     const bool live = t < valid;
     if (ep.gate) {
 #pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const int c = tx + 16 * h;                 // smem col of tanh part; sigmoid part at c+32
-        const int gc = nblk * 32 + c;
+      for (int h = 0; h < RN / 2; ++h) {
+        const int c = tx + 16 * h;                 // smem col of tanh part; sigmoid part at c + GH
+        const int gc = nblk * GH + c;
         if (gc >= n_out_total) continue;
         const int GG = a.gate_group > 0 ? a.gate_group : a.NT;
         const int na = packed_col_for_gate(gc, GG, 0), nb = packed_col_for_gate(gc, GG, 1);
         float va = ep.alpha * (acc[i][h] + bias[na]);
-        float vb = ep.alpha * (acc[i][h + 2] + bias[nb]);
+        float vb = ep.alpha * (acc[i][h + RN / 2] + bias[nb]);
         float v = live ? gate_fn<true>(va, vb) : 0.f;
         if (ep.out_f32) ep.out_f32[(long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + gc] = v;
         if (ep.out_op) {
@@ -107,8 +138,8 @@ conv_f32_kernel(const ConvArgs a) {
       }
     } else {
 #pragma unroll
-      for (int jn = 0; jn < 4; ++jn) {
-        const int n = nblk * FT_N + tx + 16 * jn;
+      for (int jn = 0; jn < RN; ++jn) {
+        const int n = nblk * TN + tx + 16 * jn;
         if (n >= a.N) continue;
         float v = ep.alpha * (acc[i][jn] + bias[n]);
         if (ep.res) v += ep.beta * ep.res[(long long)b * ep.res_bstride + (long long)t * ep.res_ld + n];
@@ -125,9 +156,14 @@ conv_f32_kernel(const ConvArgs a) {
 }
 
 cudaError_t launch_conv_f32(const ConvArgs& a, cudaStream_t stream) {
-  const int ncols = a.epi.gate ? ceil_div(a.N / 2, 32) : ceil_div(a.N, FT_N);
-  dim3 grid(ceil_div(a.L, FT_M), ncols, a.B);
-  conv_f32_kernel<<<grid, 256, 0, stream>>>(a);
+  const long long ctas64 = (long long)ceil_div(a.L, 64) * (a.epi.gate ? ceil_div(a.N / 2, 32) : ceil_div(a.N, 64)) * a.B;
+  if (ctas64 < 120) {                             // fewer CTAs than SMs: quarter-size tiles
+    dim3 grid(ceil_div(a.L, 32), a.epi.gate ? ceil_div(a.N / 2, 16) : ceil_div(a.N, 32), a.B);
+    conv_f32_kernel<32, 32><<<grid, 256, 0, stream>>>(a);
+  } else {
+    dim3 grid(ceil_div(a.L, 64), a.epi.gate ? ceil_div(a.N / 2, 32) : ceil_div(a.N, 64), a.B);
+    conv_f32_kernel<64, 64><<<grid, 256, 0, stream>>>(a);
+  }
   return cudaGetLastError();
 }
 

@@ -103,38 +103,233 @@ p1_attention_kernel(const float* __restrict__ qkv, int H, int kc, int T, const i
   const float* base = qkv + (long long)b * T * 3 * H;
   const float* q = base + (long long)tq * 3 * H + h * kc;
   float* sc = s_scores + warp * T;
-  // pass 1: scores (lane = key), q / sqrt(kc) first as the reference does
+  // pass 1: scores.  lane = 4 consecutive dims (kc / 4 lanes active; kc <= 128), four keys per step: every K row is one
+  // coalesced read, the partial dots of the four keys reduce through independent shuffle trees (ILP).
+  const int d0 = lane * 4;
+  const bool dl_ok = d0 < kc;
+  float4 q4 = dl_ok ? *reinterpret_cast<const float4*>(q + d0) : make_float4(0.f, 0.f, 0.f, 0.f);
+  q4.x *= qscale; q4.y *= qscale; q4.z *= qscale; q4.w *= qscale;      // query / sqrt(k_channels) first, as attentions.py:92 does
   float mx = -3.4e38f;
-  for (int j = lane; j < Tk; j += 32) {
-    const float* k = base + (long long)j * 3 * H + H + h * kc;
-    float acc = 0.f;
-    for (int d = 0; d < kc; d += 4) {
-      const float4 q4 = *reinterpret_cast<const float4*>(q + d), k4 = *reinterpret_cast<const float4*>(k + d);
-      acc = fmaf(q4.x * qscale, k4.x, acc); acc = fmaf(q4.y * qscale, k4.y, acc);
-      acc = fmaf(q4.z * qscale, k4.z, acc); acc = fmaf(q4.w * qscale, k4.w, acc);
-    }
-    sc[j] = acc;
-    mx = fmaxf(mx, acc);
-  }
+  for (int j0 = 0; j0 < Tk; j0 += 4) {
+    float p[4];
 #pragma unroll
-  for (int d = 16; d > 0; d >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+    for (int u = 0; u < 4; ++u) {
+      const int j = j0 + u < Tk ? j0 + u : Tk - 1;
+      const float* k = base + (long long)j * 3 * H + H + h * kc;
+      const float4 k4 = dl_ok ? *reinterpret_cast<const float4*>(k + d0) : make_float4(0.f, 0.f, 0.f, 0.f);
+      p[u] = fmaf(q4.x, k4.x, fmaf(q4.y, k4.y, fmaf(q4.z, k4.z, q4.w * k4.w)));
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) p[u] += __shfl_xor_sync(0xffffffffu, p[u], d);
+    }
+    if (lane < 4 && j0 + lane < Tk) sc[j0 + lane] = lane == 0 ? p[0] : (lane == 1 ? p[1] : (lane == 2 ? p[2] : p[3]));
+#pragma unroll
+    for (int u = 0; u < 4; ++u) if (j0 + u < Tk) mx = fmaxf(mx, p[u]);
+  }
+  __syncwarp();
   float sum = 0.f;
   for (int j = lane; j < Tk; j += 32) { const float e = expf(sc[j] - mx); sc[j] = e; sum += e; }
 #pragma unroll
   for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
   __syncwarp();
   const float inv = 1.f / sum;
-  // pass 2: out[d] = sum_j p_j v[j][d]   (lane = 4 consecutive dims, coalesced rows of v)
-  for (int d0 = lane * 4; d0 < kc; d0 += 128) {
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+  // pass 2: out[d] = sum_j p_j v[j][d]   (coalesced rows of v, four independent accumulators)
+  if (dl_ok) {
+    float4 acc[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
     const float* v = base + 2 * H + h * kc + d0;
-    for (int j = 0; j < Tk; ++j) {
-      const float p = sc[j] * inv;
-      const float4 v4 = *reinterpret_cast<const float4*>(v + (long long)j * 3 * H);
-      acc.x = fmaf(p, v4.x, acc.x); acc.y = fmaf(p, v4.y, acc.y); acc.z = fmaf(p, v4.z, acc.z); acc.w = fmaf(p, v4.w, acc.w);
+    for (int j0 = 0; j0 < Tk; j0 += 4) {
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        if (j0 + u < Tk) {
+          const float p = sc[j0 + u];
+          const float4 v4 = *reinterpret_cast<const float4*>(v + (long long)(j0 + u) * 3 * H);
+          acc[u].x = fmaf(p, v4.x, acc[u].x); acc[u].y = fmaf(p, v4.y, acc[u].y); acc[u].z = fmaf(p, v4.z, acc[u].z); acc[u].w = fmaf(p, v4.w, acc[u].w);
+        }
+      }
     }
-    *reinterpret_cast<float4*>(orow + d0) = acc;
+    float4 o4;
+    o4.x = ((acc[0].x + acc[1].x) + (acc[2].x + acc[3].x)) * inv; o4.y = ((acc[0].y + acc[1].y) + (acc[2].y + acc[3].y)) * inv;
+    o4.z = ((acc[0].z + acc[1].z) + (acc[2].z + acc[3].z)) * inv; o4.w = ((acc[0].w + acc[1].w) + (acc[2].w + acc[3].w)) * inv;
+    *reinterpret_cast<float4*>(orow + d0) = o4;
   }
+}
+
+// Same attention for short sequences: K and V of one (b, head) staged ONCE in shared memory (coalesced), 32 queries per
+// block (4 per warp).  The global-memory form above is latency bound (one dependent round trip per four keys).
+constexpr int kAttQS = 8;            // one query per warp: at ~100 phonemes this gives 2 x 11 blocks instead of 2 x 3
+__global__ void __launch_bounds__(256)
+p1_attention_smem_kernel(const float* __restrict__ qkv, int H, int kc, int T, const int* __restrict__ len, float qscale,
+                         float* __restrict__ out) {
+  extern __shared__ float s_att[];                           // K [Tk][kc + 4] | V [Tk][kc] | scores [8][T] | q [8][kc] (pre-scaled)
+  const int b = blockIdx.z, h = blockIdx.y, warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int Tk = len ? len[b] : T;
+  const int ks = kc + 4;                                     // padded K row: conflict-free float4 reads with lane = key
+  float* sK = s_att;
+  float* sV = sK + (size_t)T * ks;
+  float* sc = sV + (size_t)T * kc + warp * T;
+  float* sQ = sV + (size_t)T * kc + 8 * (size_t)T + warp * kc;
+  const float* base = qkv + (long long)b * T * 3 * H;
+  const int c4 = kc >> 2;
+  for (int i = threadIdx.x; i < Tk * c4; i += 256) {
+    const int j = i / c4, d = (i - j * c4) * 4;
+    const float* row = base + (long long)j * 3 * H + h * kc + d;
+    *reinterpret_cast<float4*>(sK + (size_t)j * ks + d) = *reinterpret_cast<const float4*>(row + H);
+    *reinterpret_cast<float4*>(sV + (size_t)j * kc + d) = *reinterpret_cast<const float4*>(row + 2 * H);
+  }
+  __syncthreads();
+  for (int qi = 0; qi < kAttQS / 8; ++qi) {
+    const int tq = blockIdx.x * kAttQS + qi * 8 + warp;
+    if (tq >= T) break;
+    float* orow = out + ((long long)b * T + tq) * H + h * kc;
+    if (tq >= Tk) {
+      for (int d = lane; d < kc; d += 32) orow[d] = 0.f;
+      continue;
+    }
+    const float* qg = base + (long long)tq * 3 * H + h * kc;
+    for (int d = lane; d < kc; d += 32) sQ[d] = qg[d] * qscale;          // query / sqrt(k_channels) first (attentions.py:92)
+    __syncwarp();
+    const float* q = sQ;
+    // pass 1: lane = key, the (scaled) query row is broadcast from shared memory
+    float mx = -3.4e38f;
+    for (int j = lane; j < Tk; j += 32) {
+      const float* k = sK + (size_t)j * ks;
+      float a0 = 0.f, a1 = 0.f;
+#pragma unroll 4
+      for (int d = 0; d < kc; d += 8) {
+        const float4 q0 = *reinterpret_cast<const float4*>(q + d), q1 = *reinterpret_cast<const float4*>(q + d + 4);
+        const float4 k0 = *reinterpret_cast<const float4*>(k + d), k1 = *reinterpret_cast<const float4*>(k + d + 4);
+        a0 = fmaf(q0.x, k0.x, a0); a0 = fmaf(q0.y, k0.y, a0); a0 = fmaf(q0.z, k0.z, a0); a0 = fmaf(q0.w, k0.w, a0);
+        a1 = fmaf(q1.x, k1.x, a1); a1 = fmaf(q1.y, k1.y, a1); a1 = fmaf(q1.z, k1.z, a1); a1 = fmaf(q1.w, k1.w, a1);
+      }
+      const float a = a0 + a1;
+      sc[j] = a;
+      mx = fmaxf(mx, a);
+    }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+    float sum = 0.f;
+    for (int j = lane; j < Tk; j += 32) { const float e = expf(sc[j] - mx); sc[j] = e; sum += e; }
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+    __syncwarp();
+    const float inv = 1.f / sum;
+    // pass 2: lane = 4 consecutive dims
+    const int d0 = lane * 4;
+    if (d0 < kc) {
+      float4 acc[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int j0 = 0; j0 < Tk; j0 += 4) {
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+          if (j0 + u < Tk) {
+            const float p = sc[j0 + u];
+            const float4 v4 = *reinterpret_cast<const float4*>(sV + (size_t)(j0 + u) * kc + d0);
+            acc[u].x = fmaf(p, v4.x, acc[u].x); acc[u].y = fmaf(p, v4.y, acc[u].y); acc[u].z = fmaf(p, v4.z, acc[u].z); acc[u].w = fmaf(p, v4.w, acc[u].w);
+          }
+        }
+      }
+      *reinterpret_cast<float4*>(orow + d0) = make_float4(((acc[0].x + acc[1].x) + (acc[2].x + acc[3].x)) * inv, ((acc[0].y + acc[1].y) + (acc[2].y + acc[3].y)) * inv,
+                                                         ((acc[0].z + acc[1].z) + (acc[2].z + acc[3].z)) * inv, ((acc[0].w + acc[1].w) + (acc[2].w + acc[3].w)) * inv);
+    }
+    __syncwarp();
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Skinny fp32 conv / GEMM for the text encoder's shapes (tens of rows, K up to a few thousand): K ACROSS THE LANES of a
+// warp.  A warp owns an 8-row x 4-column output block; lane l multiplies channels c = 4 l + 128 i of every tap (all
+// global loads are coalesced 16-byte reads, no shared memory, no barriers, dozens of independent loads in flight per
+// lane), and a 31-shuffle transpose-reduce leaves output (row l / 4, column l % 4) in lane l.  The tiled kernel of
+// conv_f32.cu is built for thousands of rows: here it runs 24-96 CTAs with a barrier per 16-wide K slice.
+//   out[b][t][n] = epi( sum_{j, c} w[n][j * Cin + c] * in[b][t + j - pad][c] + bias[b][n] )
+// epilogue: + res (residual) | relu | gate (columns n and n + N/2 = tanh / sigmoid halves, attentions.py:162-164);
+// rows t >= len[b] are stored as zeros.
+// ---------------------------------------------------------------------------
+struct SkinnyArgs {
+  const float* in; int Cin; int T; int B;
+  const float* w; int N; int k; int pad;
+  const float* bias; long long bias_bstride;
+  const float* res;                 // [B][T][N_out] or null
+  float* out;                       // [B][T][N_out]
+  const int* len;
+  int gate, relu;
+};
+
+__global__ void __launch_bounds__(256)
+p1_skinny_conv_kernel(const SkinnyArgs a) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int n_out = a.gate ? a.N / 2 : a.N;
+  const int cgroups = a.gate ? n_out / 2 : a.N / 4;          // column groups: 4 linear columns, or 2 gate channels (tanh, sigmoid of each)
+  const int cg = blockIdx.x * 8 + warp;
+  if (cg >= cgroups) return;
+  const int b = blockIdx.z, t0 = blockIdx.y * 8;
+  const int valid = a.len ? a.len[b] : a.T;
+  int wr[4];                                                 // weight rows of this warp's 4 columns
+  if (a.gate) { wr[0] = cg * 2; wr[1] = cg * 2 + 1; wr[2] = n_out + cg * 2; wr[3] = n_out + cg * 2 + 1; }
+  else { wr[0] = cg * 4; wr[1] = cg * 4 + 1; wr[2] = cg * 4 + 2; wr[3] = cg * 4 + 3; }
+  float acc[32];
+#pragma unroll
+  for (int i = 0; i < 32; ++i) acc[i] = 0.f;
+  const int Ktot = a.k * a.Cin;
+  const float* in = a.in + (long long)b * a.T * a.Cin;
+  if (t0 < valid) {
+    for (int j = 0; j < a.k; ++j) {
+      const int tr0 = t0 + j - a.pad;
+      for (int c = lane * 4; c < a.Cin; c += 128) {
+        float4 wv[4], av[8];
+#pragma unroll
+        for (int n = 0; n < 4; ++n) wv[n] = __ldg(reinterpret_cast<const float4*>(a.w + (long long)wr[n] * Ktot + j * a.Cin + c));
+#pragma unroll
+        for (int r = 0; r < 8; ++r) {
+          const int tr = tr0 + r;
+          av[r] = (tr >= 0 && tr < a.T) ? *reinterpret_cast<const float4*>(in + (long long)tr * a.Cin + c) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+#pragma unroll
+        for (int r = 0; r < 8; ++r)
+#pragma unroll
+          for (int n = 0; n < 4; ++n) {
+            float s = acc[r * 4 + n];
+            s = fmaf(av[r].x, wv[n].x, s); s = fmaf(av[r].y, wv[n].y, s); s = fmaf(av[r].z, wv[n].z, s); s = fmaf(av[r].w, wv[n].w, s);
+            acc[r * 4 + n] = s;
+          }
+      }
+    }
+  }
+  // transpose-reduce: after the step with offset o each lane keeps the half of its values whose index bit matches its
+  // lane bit; 16 + 8 + 4 + 2 + 1 shuffles, and lane l ends with the full sum of element l
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) {
+    const bool up = (lane & o) != 0;
+#pragma unroll
+    for (int i = 0; i < o; ++i) {
+      const float send = up ? acc[i] : acc[i + o];
+      const float keep = up ? acc[i + o] : acc[i];
+      acc[i] = keep + __shfl_xor_sync(0xffffffffu, send, o);
+    }
+  }
+  const int r = lane >> 2, n = lane & 3, t = t0 + r;
+  const bool live = t < valid;
+  const float* bias = a.bias + (long long)b * a.bias_bstride;
+  float v = acc[0] + bias[wr[n]];
+  // gate: lanes n = 0, 1 hold the tanh pre-activations of gate channels 2 cg, 2 cg + 1; lanes n = 2, 3 their sigmoid halves
+  const float other = __shfl_xor_sync(0xffffffffu, v, 2);
+  if (t >= a.T) return;
+  if (a.gate) {
+    if (n < 2) {
+      const float g = live ? gate_fn<true>(v, other) : 0.f;
+      a.out[((long long)b * a.T + t) * n_out + cg * 2 + n] = g;
+    }
+    return;
+  }
+  const long long o = ((long long)b * a.T + t) * a.N + wr[n];
+  if (a.res) v += a.res[o];
+  if (a.relu) v = fmaxf(v, 0.f);
+  a.out[o] = live ? v : 0.f;
 }
 
 // stats [B][T][2*IC] time-major -> m_p [B][IC][T], s_p = exp(logs) [B][IC][T] (reference layouts; models.py:186-188,563),
@@ -290,7 +485,7 @@ int p1_load(Engine& e, const vitsb_tensor_desc* tens, int n) {
   auto bad = [&](const char* m) { p1_destroy(S); return e.fail(VITSB_ERR_UNSUPPORTED, std::string("infer_p1 weights: ") + m); };
   if (H <= 0 || H > 1024 || H % 16 || S->text_ch <= 0 || S->text_ch % 16 || F <= 0 || F % 16 || D <= 0 || D > 1024 || D % 16)
     return bad("channel counts must be multiples of 16 (hidden / duration hidden <= 1024)");
-  if (S->n_layers < 1 || S->IC != e.cfg.inter_channels || gin != e.cfg.gin_channels || H % S->n_heads || (H / S->n_heads) % 4 ||
+  if (S->n_layers < 1 || S->IC != e.cfg.inter_channels || gin != e.cfg.gin_channels || H % S->n_heads || (H / S->n_heads) % 4 || (H / S->n_heads) > 128 ||
       S->k % 2 != 1 || S->kd % 2 != 1 || S->emo_ch % 4 || gin % 4)
     return bad("shape set does not match the handle's config");
 
@@ -443,6 +638,17 @@ int p1_run(Engine& e, const float* text, const float* emo, const int32_t* sid, c
     if (c.cond >= 0) { ep.bias = Fp(W.cond) + c.cond; ep.bias_bstride = S.Ncond; }
     else { ep.bias = P + c.b; ep.bias_bstride = 0; }
     const int No = gate ? c.N / 2 : c.N;
+    if (rows <= 4096 && c.Cin % 4 == 0 && c.N % 4 == 0 && (!gate || c.N % 8 == 0)) {
+      // the encoder's regime: few rows, long K - K across the lanes of a warp (p1_skinny_conv_kernel)
+      SkinnyArgs sa{};
+      sa.in = in; sa.Cin = c.Cin; sa.T = T; sa.B = B; sa.w = P + c.w; sa.N = c.N; sa.k = c.k; sa.pad = (c.k - 1) / 2;
+      sa.bias = ep.bias; sa.bias_bstride = ep.bias_bstride; sa.res = res; sa.out = out; sa.len = dl; sa.gate = gate; sa.relu = relu ? 1 : 0;
+      const int cgroups = gate ? c.N / 4 : c.N / 4;
+      dim3 grid((cgroups + 7) / 8, (T + 7) / 8, B);
+      p1_skinny_conv_kernel<<<grid, 256, 0, stream>>>(sa);
+      chk();
+      return;
+    }
     if (res) { ep.res = res; ep.res_ld = No; ep.res_bstride = (long long)T * No; }
     if (relu) { ep.out_op = out; ep.out_op_ld = No; ep.out_op_bstride = (long long)T * No; ep.out_slope = 0.f; }
     else { ep.out_f32 = out; ep.out_f32_ld = No; ep.out_f32_bstride = (long long)T * No; }
@@ -467,9 +673,20 @@ int p1_run(Engine& e, const float* text, const float* emo, const int32_t* sid, c
   for (const P1State::Layer& L : S.layers) {
     conv(L.qkv, Fp(W.X), Fp(W.QKV), nullptr, 0, false);                                  // attentions.py:79-81
     if (ok()) {
-      dim3 grid((T + kAttQ - 1) / kAttQ, S.n_heads, B);
-      p1_attention_kernel<<<grid, 32 * kAttQ, sizeof(float) * kAttQ * T, stream>>>(Fp(W.QKV), H, kc, T, dl, 1.0f / std::sqrt((float)kc), Fp(W.A));
-      chk();
+      const size_t smem_s = sizeof(float) * ((size_t)T * (kc + 4) + (size_t)T * kc + 8 * (size_t)T + 8 * (size_t)kc);
+      if (smem_s <= 200 * 1024) {                           // K, V of one (row, head) fit shared memory
+        static PerDeviceOnce optin;
+        ce = optin.run([] { return cudaFuncSetAttribute(p1_attention_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); });
+        if (ok()) {
+          dim3 grid((T + kAttQS - 1) / kAttQS, S.n_heads, B);
+          p1_attention_smem_kernel<<<grid, 256, smem_s, stream>>>(Fp(W.QKV), H, kc, T, dl, 1.0f / std::sqrt((float)kc), Fp(W.A));
+          chk();
+        }
+      } else {
+        dim3 grid((T + kAttQ - 1) / kAttQ, S.n_heads, B);
+        p1_attention_kernel<<<grid, 32 * kAttQ, sizeof(float) * kAttQ * T, stream>>>(Fp(W.QKV), H, kc, T, dl, 1.0f / std::sqrt((float)kc), Fp(W.A));
+        chk();
+      }
     }
     conv(L.o, Fp(W.A), Fp(W.Y), Fp(W.X), 0, false);                                       // x + conv_o(attn)        attentions.py:83, 50-51
     ln(Fp(W.Y), Fp(W.X), H, L.g1, L.b1, nullptr, 0, false);
