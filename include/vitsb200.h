@@ -113,7 +113,8 @@ int vitsb_load_weights(vitsb_handle* h, const vitsb_tensor_desc* tensors, int n)
  *   "ws_cap_mb" (24576)    workspace cap; batches whose layout exceeds it run in row chunks
  *   "rb_fused", "flow_fused", "flow_in_split" -1/0/1 (-1 = automatic): launch-plan / packing choices; they take
  *       effect at the next vitsb_load_weights.
- * vitsb_get_option also answers "plan.rb_fused", "plan.flow_fused", "plan.flow_in_split" (the plan in force). */
+ * vitsb_get_option also answers "plan.rb_fused", "plan.flow_fused", "plan.flow_in_split" (the plan in force) and
+ * "plan.p1" (1 when the infer_p1 weights were loaded). */
 int vitsb_set_option(vitsb_handle* h, const char* key, int value);
 int vitsb_get_option(const vitsb_handle* h, const char* key, int* value);
 

@@ -123,6 +123,25 @@ class SynthesizerStandIn(nn.Module):
         return self.dec((z * y_mask)[:, :, :max_len], g=g), z             # models.py:534
 
 
+def attach_param_tree(model: nn.Module, sd: dict):
+    """Register the tensors of a flat state_dict (e.g. the enc_p.* / dp.* / emb_g.* keys of the reference model,
+    models.py:117-164, 20-47, 465) as parameters under the same dotted names, so that model.state_dict() carries them."""
+    for key, val in sd.items():
+        parts = key.split(".")
+        mod = model
+        for p_ in parts[:-1]:
+            if isinstance(mod, nn.ModuleDict):
+                if p_ not in mod:
+                    mod[p_] = nn.ModuleDict()
+                mod = mod[p_]
+            else:
+                if not hasattr(mod, p_):
+                    setattr(mod, p_, nn.ModuleDict())
+                mod = getattr(mod, p_)
+        mod.register_parameter(parts[-1], nn.Parameter(val.clone(), requires_grad=False))
+    return model
+
+
 def load_fixture(model: nn.Module, sd: dict, weight_normed: bool):
     """Strict load of the fixture state_dict (weight_g / weight_v form when the model still carries weight norm)."""
     own = model.state_dict()

@@ -88,3 +88,24 @@ def test_reinstall_after_load_state_dict_repacks(base_cfg):
     from vits_b200 import FlowDecoder
     ref = FlowDecoder(base_cfg, sd2, device="cuda:0", precision="fp32").decode(lat["z_p"].cuda(), lat["g"].cuda())
     assert torch.equal(w2, ref) and not torch.equal(w1, w2)
+
+
+def test_install_rebinds_infer_p1_when_the_checkpoint_has_it(base_cfg, golden_dir):
+    """models.py:558-566: with enc_p.* / dp.* / emb_g.* in the state_dict, install() also routes infer_p1 through the library."""
+    import vits_b200
+    from tests.ref_standin import attach_param_tree
+    m = _model(base_cfg, weight_normed=False).cpu()
+    attach_param_tree(m, FX.make_p1_state_dict(base_cfg, seed=4321))
+    m = m.cuda()
+    assert "infer_p1" not in m.__dict__
+    eng = vits_b200.install(m, precision="fp16")
+    assert eng.get_option("plan.p1") == 1 and "infer_p1" in m.__dict__
+    gold = np.load(os.path.join(golden_dir, "base_p1.npz"))
+    inp = FX.make_p1_inputs(base_cfg, [60], seed=99)
+    m_p, s_p, logw, g = m.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"].cuda())
+    assert m_p.dtype == torch.float32 and m_p.is_cuda
+    assert np.abs(m_p.cpu().numpy() - gold["m_p_T60"]).max() <= 2e-4
+    assert np.abs(logw.cpu().numpy() - gold["logw_T60"]).max() <= 2e-4
+    m2 = _model(base_cfg, weight_normed=False)                      # no encoder weights: infer_p1 is left alone
+    vits_b200.install(m2, precision="fp16")
+    assert "infer_p1" not in m2.__dict__

@@ -77,6 +77,7 @@ int Engine::get_option(const char* key, int* value) const {
   if (std::strcmp(key, "plan.rb_fused") == 0) { *value = rb_fused; return VITSB_OK; }
   if (std::strcmp(key, "plan.flow_fused") == 0) { *value = flow_fused; return VITSB_OK; }
   if (std::strcmp(key, "plan.flow_in_split") == 0) { *value = flow_in_split; return VITSB_OK; }
+  if (std::strcmp(key, "plan.p1") == 0) { *value = p1 != nullptr; return VITSB_OK; }          // infer_p1 weights are loaded
   return VITSB_ERR_BAD_ARG;
 }
 

@@ -8,9 +8,11 @@ What is rebound (signatures unchanged; paths relative to emotional-vits/):
   model.infer_p2                      models.py:568-575
   model.flow.infer / .forward(reverse=True)   models.py:219-235   (forward(reverse=False) keeps the reference code)
   model.dec.forward / .infer          models.py:304-318
+  model.infer_p1                      models.py:558-566   (when the state_dict carries enc_p.* / dp.* / emb_g.*)
 `model.infer` (models.py:537-556) and `model.inference` (models.py:517-535) call
 `self.flow`/`self.dec` and therefore pick the new path up without being touched.
-The text encoder, duration predictor and length regulation stay reference PyTorch.
+The text encoder and duration predictor run on the library too (fp32) when their weights are present; `model.infer`'s own
+noise sampling and length regulation stay reference PyTorch (they call the rebound `flow` / `dec`).
 """
 from __future__ import annotations
 
@@ -80,6 +82,14 @@ def install(model, precision: str = "fp16", device: Optional[torch.device] = Non
     def infer_p2(self, attn, m_p, s_p, g, noise):
         return eng.infer_p2(attn, m_p, s_p, g, noise).to(_dtype())
 
+    def infer_p1(self, x, emo, sid):
+        # models.py:558-566 asserts B == 1; outputs in the model's dtype, as the reference returns them
+        assert x.size(0) == 1
+        dt = _dtype()
+        return tuple(t.to(dt) for t in eng.infer_p1(x, emo, sid))
+
+    if eng.get_option("plan.p1") == 1:                  # the checkpoint carried enc_p.* / dp.* / emb_g.*
+        model.infer_p1 = types.MethodType(infer_p1, model)
     model.flow.infer = types.MethodType(flow_infer, model.flow)
     model.flow.forward = types.MethodType(flow_forward, model.flow)
     model.dec.forward = types.MethodType(dec_forward, model.dec)
