@@ -34,6 +34,7 @@ SR, HOP = 16000, 192
 FRAME_SEC = HOP / SR
 PER_GPU_BATCH = 16
 LEN_LO, LEN_HI = 84, 834          # 1-10 s in 12 ms frames
+C2_WORKLOAD = "C2: emotional-vits base config, 16 mixed-length utterances per GPU (1-10 s, ragged/masked), flow-reverse + Generator"
 
 
 def parse():
@@ -180,7 +181,9 @@ def run_reference(args):
     out = {"impl": "reference", "metric": "audio-sec/sec (RTF^-1)", "value": val, "unit": "audio-s/s", "n_gpus": args.gpus,
            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * secs / max(1, len(rec)),
            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-           "config": {"workload": "C2: emotional-vits base config, 16 mixed-length utterances (1-10 s); bounded sample per step"},
+           "config": {"workload": C2_WORKLOAD, "global_batch": 16, "valid_audio_s_per_step": rec[0]["audio_s"],
+                      "parallelism": "host cores of rank 0", "precision": "fp32",
+                      "sample": "all utterances of the batch that fit the per-step CPU budget, per utterance at B = 1"},
            "cpu_baseline": {"value": val, "unit": "audio-s/s", "cores": rec[0]["threads"], "kind": "port", "sample": sample},
            "e2e": {"value": val, "unit": "audio-s/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
            "gpu_launches": 0}
@@ -209,6 +212,7 @@ def run_b200(args):
 
     cfg = HotPathConfig()
     sd = FX.make_state_dict(cfg, seed=1234)
+    sd.update(FX.make_p1_state_dict(cfg, seed=4321))       # text encoder + duration predictor, for the end-to-end infer() side leg
     eng = FlowDecoder(cfg, sd, device=dev, precision=args.precision)
     all_len = global_lengths(world)
     mine = list(range(rank * PER_GPU_BATCH, (rank + 1) * PER_GPU_BATCH))          # identical length set on every rank
@@ -330,6 +334,19 @@ def run_b200(args):
             f = lambda: eng.synthesize(z1, g1, None, ragged=True, out=o1)
             ms, _ = timed(f, reps, 3, sample=False)
             return {"frames": Tn, "audio_s": Tn * FRAME_SEC, "latency_ms": ms / reps, "value": Tn * FRAME_SEC * reps / (ms * 1e-3)}
+        # (d) the whole of EmoVITS.infer for one utterance (infer.py:136-184): text -> infer_p1 -> device-side durations ->
+        # flow -> decoder -> int16 PCM, no host synchronisation inside
+        p1in = FX.make_p1_inputs(cfg, [84], seed=99)
+        tx, em, sid1 = p1in["text"].to(dev), p1in["emo"].to(dev), p1in["sid"]
+        Tc = 768
+        nz = (torch.randn(1, cfg.inter_channels, Tc, generator=torch.Generator().manual_seed(1)) * 0.707).to(dev)
+        _, yl1 = eng.infer(tx, em, sid1, nz, Tc, pcm16=True)
+        yl1 = int(yl1.item())
+        ms_p1, _ = timed(lambda: eng.infer_p1(tx, em, sid1), 20, 3, sample=False)
+        ms_inf, _ = timed(lambda: eng.infer(tx, em, sid1, nz, Tc, pcm16=True), 20, 3, sample=False)
+        side["infer_text_to_pcm_B1"] = {"phonemes": 84, "frames": yl1, "audio_s": yl1 * FRAME_SEC, "infer_p1_ms": ms_p1 / 20,
+                                        "latency_ms": ms_inf / 20, "value": yl1 * FRAME_SEC * 20 / (ms_inf * 1e-3),
+                                        "note": "vitsb_infer_p1 (fp32) + vitsb_synthesize_durations; device-timed, L2 flushed between calls"}
         side["C1_latency"] = latency(417, 20)
         side["C3_latency"] = latency(5000, 10)
         c4 = {}
@@ -385,9 +402,9 @@ def run_b200(args):
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": {"fp16": "f16", "bf16": "bf16", "fp32": "f32"}[args.precision] + " operands, f32 accumulate",
             "data": "synthetic",
-            "config": {"workload": f"{'C2' if PER_GPU_BATCH == 16 else 'C4 sweep point'}: emotional-vits base config, {PER_GPU_BATCH} mixed-length utterances per GPU "
-                                   f"(1-10 s, ragged/masked), flow-reverse + Generator"
-                                   + ("; at N>1 this is C5-shaped: every row of every rank has its own speaker embedding g" if world > 1 else ""),
+            "config": {"workload": C2_WORKLOAD if PER_GPU_BATCH == 16 else
+                                   f"C4 sweep point: emotional-vits base config, {PER_GPU_BATCH} mixed-length utterances per GPU (1-10 s, ragged/masked), flow-reverse + Generator",
+                       "note": "at N>1 this is C5-shaped: every row of every rank has its own speaker embedding g" if world > 1 else "",
                        "global_batch": PER_GPU_BATCH * world, "valid_audio_s_per_step": audio_all,
                        "parallelism": f"utterance-sharded replicas x{world}, the same 16-length set on every rank, no collective",
                        "l2": "256 MiB flush between timed steps; per-step activation traffic >> 126 MB L2",
@@ -397,7 +414,7 @@ def run_b200(args):
                     "api": "FlowDecoder.host_pipeline(pcm16=True) depth 2: per-step H2D of the latents and D2H of the int16 PCM the serving "
                            "path returns (vits_wrap.py:195, written by the last kernel) overlap the neighbouring steps' synthesis",
                     "float32_result": {"value": audio_all * args.steps / (ms_e2e_f32 * 1e-3), "d2h_bytes_per_step": int(d2h_f32) * world}},
-            "gpu_launches": eng.launches_per_call(B, T) * args.steps,
+            "gpu_launches": eng.launches_per_call(B, T) * args.steps * world,
             "clocks": clocks,
             "roofline": {"bound": "tensor", "kernel": "rb_fused_kernel + flow_fused_kernel + conv_tc_kernel (all tcgen05 launches of a step; rb_fused is ~80 % of it)",
                          "achieved": achieved_tf, "peak": pk["tflops_burst"], "unit": "TFLOP/s",

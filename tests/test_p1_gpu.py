@@ -51,6 +51,14 @@ def test_infer_p1_ragged_batch_equals_per_row_calls(base_cfg, base_sd):
     lens = [23, 60, 7, 1]
     inp = FX.make_p1_inputs(base_cfg, lens, seed=11)
     m_p, s_p, logw, g = eng.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"], lens)
+    for _ in range(3):                 # direct issue, graph capture, replay: identical; new inputs flow through the replay
+        m2, s2, l2, _ = eng.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"], lens)
+        assert torch.equal(m2, m_p) and torch.equal(s2, s_p) and torch.equal(l2, logw)
+    inp_b = FX.make_p1_inputs(base_cfg, lens, seed=12)
+    m3, _, l3, _ = eng.infer_p1(inp_b["text"].cuda(), inp_b["emo"].cuda(), inp_b["sid"], lens)
+    with torch.no_grad():
+        mr3, _, lr3, _ = P.infer_p1(sd1, inp_b["text"][1:2, :60], inp_b["emo"][1:2], inp_b["sid"][1:2], base_cfg)
+    assert (m3[1:2, :, :60].cpu() - mr3).abs().max().item() <= TOL and (l3[1:2, :, :60].cpu() - lr3).abs().max().item() <= TOL
     for b, L in enumerate(lens):
         with torch.no_grad():
             mr, sr, lr, gr = P.infer_p1(sd1, inp["text"][b:b + 1, :L], inp["emo"][b:b + 1], inp["sid"][b:b + 1], base_cfg)

@@ -41,6 +41,7 @@ struct TcGeom {
   uint32_t tmem_cols;
   uint32_t idesc;
   int dbg;           // VITSB_TC_DBG timing-experiment mask (only with -DVITSB_RB_DEBUG; results are wrong when set)
+  int staged;        // 16-bit output rows leave through shared-memory blocks + TMA stores (tc_common.cuh TcStage)
 };
 
 #ifdef VITSB_RB_DEBUG
@@ -63,7 +64,7 @@ constexpr int kTcMaxB = kMaxBatchRows;
 template <typename OpT, bool TWO>
 __global__ void __launch_bounds__(kTcThreads, 1)
 conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-               const ConvArgs a, const TcGeom g) {
+               const __grid_constant__ CUtensorMap tmO, const ConvArgs a, const TcGeom g) {
   extern __shared__ uint8_t smem_raw[];
   __shared__ int s_prefix[kTcMaxB + 1];          // m-tiles before batch row b
   __shared__ uint32_t s_tmem;
@@ -71,7 +72,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sA = smem_base;
   const uint32_t sB = sA + g.stages * g.a_bytes;
-  const uint32_t bars = sB + g.stages * g.b_stride;          // 8-byte aligned (multiples of 1024 above)
+  const uint32_t sStg = sB + g.stages * g.b_stride;          // staged stores: [epilogue group][2][128 rows x 32 B]
+  const uint32_t bars = sStg + (g.staged ? kTcEpiGroups * 2 * 4096u : 0u);          // 8-byte aligned (multiples of 1024 above)
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (8 + s); };
   auto acc_full = [&](int i) { return bars + 8u * (16 + i); };
@@ -204,6 +206,8 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // ===== epilogue groups: TMEM -> registers -> fused math -> global =====
     // All groups work on every tile (tc_epilogue deals the column units out); accumulators alternate per item.
     const int grp = (warp - 2) >> 2;
+    TcStage stg;
+    if (g.staged) { stg.smem = sStg + grp * 2 * 4096u; stg.tm = &tmO; stg.bar_id = 1 + grp; }
     for (int n = 0; n < my_items; ++n) {
       int b, t0, ntile; bool live;
       coords(cl_id + n * n_cl, b, t0, ntile, live);
@@ -212,7 +216,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       auto wait_acc = [&]() { ptx::mbar_wait(acc_full(buf), (n >> 1) & 1); ptx::tc_fence_after(); };
       if (live && !TC_DBG(4)) {
         const int nsplit_tile = a.n_split > 0 ? a.n_split / a.NT : nNT;
-        if (ntile < nsplit_tile) tc_epilogue<OpT>(a, a.epi, b, t0, ntile, valid, tmem_base + buf * a.NT, warp & 3, lane, grp, kTcEpiGroups, wait_acc, g.dbg);
+        if (ntile < nsplit_tile) tc_epilogue<OpT>(a, a.epi, b, t0, ntile, valid, tmem_base + buf * a.NT, warp & 3, lane, grp, kTcEpiGroups, wait_acc, g.dbg, &stg);
         else tc_epilogue<OpT>(a, a.epi_b, b, t0, ntile - nsplit_tile, valid, tmem_base + buf * a.NT, warp & 3, lane, grp, kTcEpiGroups, wait_acc, g.dbg);
       } else {
         wait_acc();
@@ -221,6 +225,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       __syncwarp();
       if (lane == 0) { if (TWO) ptx::mbar_arrive_leader(acc_empty(buf)); else ptx::mbar_arrive(acc_empty(buf)); }
     }
+    if (g.staged && (warp & 3) == 0 && lane == 0) ptx::bulk_wait0();     // staged rows are in global memory before the CTA retires
   }
 
   // ---- teardown: all TMEM reads (and, in pair mode, the peer's) done before dealloc ----
@@ -272,6 +277,12 @@ static bool make_geom(const ConvArgs& a, int op, int ncl, TcGeom* g) {
   // one persistent CTA per SM: as deep a ring as fits (<= 8 stages, no deeper than two tiles' worth)
   const uint32_t stage = g->a_bytes + g->b_stride;
   int st = (int)((200u * 1024u) / stage);
+  if (st > 8) st = 8;
+  // staged 16-bit output: unsplit operand rows only, dense rows, nothing else written or read by the epilogue
+  const Epilogue& ep = a.epi;
+  g->staged = (!ep.gate && ep.out_op && !ep.out_f32 && !ep.res && !ep.accum && ep.out_op_split == 0 && a.n_split == 0 &&
+               (ep.out_op_ld * 2) % 16 == 0 && ep.out_op_bstride == (long long)a.L * ep.out_op_ld) ? 1 : 0;
+  if (g->staged) st = (int)((200u * 1024u - kTcEpiGroups * 2 * 4096u) / stage);
   if (st > 8) st = 8;
   const int iters2 = 2 * a.k * g->kchunks;
   if (st > iters2) st = iters2;
@@ -343,7 +354,17 @@ cudaError_t launch_conv_tc(const ConvArgs& a_in, int op, const LaunchOpts& lo, c
                      CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
   }
-  const size_t smem = 1024 + (size_t)g.stages * (g.a_bytes + g.b_stride) + 8 * 20 + 16;
+  CUtensorMap tmO = tmA;                           // placeholder when the output is not staged (never dereferenced)
+  if (g.staged) {
+    cuuint64_t dims[3] = {(cuuint64_t)a.epi.out_op_ld, (cuuint64_t)a.L, (cuuint64_t)a.B};
+    cuuint64_t strides[2] = {(cuuint64_t)a.epi.out_op_ld * 2, (cuuint64_t)a.epi.out_op_bstride * 2};
+    cuuint32_t box[3] = {16, (cuuint32_t)kTileM, 1};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = enc(&tmO, dt, 3, a.epi.out_op, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                     CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
+  }
+  const size_t smem = 1024 + (size_t)g.stages * (g.a_bytes + g.b_stride) + (g.staged ? kTcEpiGroups * 2 * 4096 : 0) + 8 * 20 + 16;
   static PerDeviceOnce smem_optin;             // the opt-in is per device: a second engine on another GPU needs its own
   const cudaError_t attr_err = smem_optin.run([] {
     cudaError_t e[4] = {
@@ -372,11 +393,11 @@ cudaError_t launch_conv_tc(const ConvArgs& a_in, int op, const LaunchOpts& lo, c
   cfg.attrs = at; cfg.numAttrs = lo.pdl ? 2 : 1;
   cudaError_t le;
   if (ncl == 2) {
-    le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, conv_tc_kernel<__nv_bfloat16, true>, tmA, tmB, a, g)
-                       : cudaLaunchKernelEx(&cfg, conv_tc_kernel<__half, true>, tmA, tmB, a, g);
+    le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, conv_tc_kernel<__nv_bfloat16, true>, tmA, tmB, tmO, a, g)
+                       : cudaLaunchKernelEx(&cfg, conv_tc_kernel<__half, true>, tmA, tmB, tmO, a, g);
   } else {
-    le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, conv_tc_kernel<__nv_bfloat16, false>, tmA, tmB, a, g)
-                       : cudaLaunchKernelEx(&cfg, conv_tc_kernel<__half, false>, tmA, tmB, a, g);
+    le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, conv_tc_kernel<__nv_bfloat16, false>, tmA, tmB, tmO, a, g)
+                       : cudaLaunchKernelEx(&cfg, conv_tc_kernel<__half, false>, tmA, tmB, tmO, a, g);
   }
   if (le == cudaSuccess) le = cudaGetLastError();
   if (le != cudaSuccess)

@@ -96,7 +96,7 @@ struct Engine {
   bool flow_fused = false;      // 16-bit paths: each coupling layer runs as one cluster kernel (flow_fused.cu)
 
   // options (vitsb_set_option); -1 = automatic.  Packing / plan options take effect at the next vitsb_load_weights.
-  int opt_graph = 1, opt_pdl = 0, opt_tc_pair = 1, opt_rb_fused = -1, opt_flow_fused = -1, opt_flow_in_split = -1,
+  int opt_graph = 1, opt_pdl = 1, opt_tc_pair = 1, opt_rb_fused = -1, opt_flow_fused = -1, opt_flow_in_split = -1,
       opt_rb_nslab = 0, opt_ws_cap_mb = 24576, opt_ups_split_mask = -1;
   int set_option(const char* key, int value);
   int get_option(const char* key, int* value) const;

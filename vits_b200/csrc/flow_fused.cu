@@ -104,6 +104,10 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
   __syncthreads();
   ptx::tc_fence_after();
   const uint32_t tmem_base = s_tmem;
+  // Programmatic dependent launch: everything above (and the L2 weight prefetch below, which reads constants only) may
+  // overlap the previous kernel's tail; every other role waits here for that kernel's writes (z state, cond vectors).
+  ptx::pdl_launch_dependents();
+  if (warp != 2 && warp != 3) ptx::pdl_wait();
   // clock64 timeline of CTA 0's first tile (debug build only): trace[slot] = cycles
 #ifdef VITSB_RB_DEBUG
   auto trace = [&](int slot) { if (a.trace && blockIdx.x == 0 && lane == 0 && slot < 256) a.trace[slot] = clock64(); };
@@ -507,9 +511,18 @@ cudaError_t launch_flow_fused(const FlowFusedArgs& a, int op, const LaunchOpts& 
   const bool tracing = d_trace && trace_left > 0;
   if (tracing) { cudaMemsetAsync(d_trace, 0, 256 * sizeof(long long), stream); args.trace = d_trace; }
 #endif
-  if (op == OP_BF16) flow_fused_kernel<__nv_bfloat16><<<grid, THREADS, smem, stream>>>(tmZ, tmPre, tmIn, tmRS, tmRSm, args);
-  else flow_fused_kernel<__half><<<grid, THREADS, smem, stream>>>(tmZ, tmPre, tmIn, tmRS, tmRSm, args);
-  const cudaError_t le = cudaGetLastError();
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid, 1, 1);
+  cfg.blockDim = dim3(THREADS, 1, 1);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = lo.pdl ? 1 : 0;
+  cudaError_t le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, flow_fused_kernel<__nv_bfloat16>, tmZ, tmPre, tmIn, tmRS, tmRSm, args)
+                                 : cudaLaunchKernelEx(&cfg, flow_fused_kernel<__half>, tmZ, tmPre, tmIn, tmRS, tmRSm, args);
+  if (le == cudaSuccess) le = cudaGetLastError();
 #ifdef VITSB_RB_DEBUG
   if (tracing && le == cudaSuccess) {
     --trace_left;

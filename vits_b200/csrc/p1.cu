@@ -395,10 +395,15 @@ struct P1State {
   int cond2_col = 0;
   float* d_pool = nullptr;
   size_t pool_elems = 0;
+  // CUDA-graph replay of the workspace-only middle of a call (48 of its 55 launches), keyed by what the captured launches
+  // depend on: workspace, shape, masked or not.  Same scheme as the synthesis path (engine_run.cu).
+  struct Graph { const void* ws; int B, T, masked; int seen; cudaGraphExec_t exec; };
+  std::vector<Graph> graphs;
 };
 
 void p1_destroy(P1State* s) {
   if (!s) return;
+  for (P1State::Graph& g : s->graphs) if (g.exec) cudaGraphExecDestroy(g.exec);
   if (s->d_pool) cudaFree(s->d_pool);
   delete s;
 }
@@ -601,7 +606,7 @@ size_t p1_workspace_bytes(const Engine& e, int B, int T) {
 int p1_run(Engine& e, const float* text, const float* emo, const int32_t* sid, const int32_t* x_len, int B, int T, float* m_p,
            float* s_p, float* logw, float* g_out, void* ws, size_t ws_bytes, cudaStream_t stream) {
   if (!e.p1) return e.fail(VITSB_ERR_WEIGHTS, "infer_p1 weights not loaded (the state_dict had no enc_p.* / dp.* / emb_g.* entries)");
-  const P1State& S = *e.p1;
+  P1State& S = *e.p1;
   if (!text || !emo || !sid || !m_p || !s_p || !logw || !g_out || !ws) return e.fail(VITSB_ERR_BAD_ARG, "null pointer");
   if (B < 1 || B > 65535 || T < 1) return e.fail(VITSB_ERR_BAD_ARG, "B and Tx_max must be >= 1");
   if (T > S.max_T) return e.fail(VITSB_ERR_BAD_ARG, "Tx_max too large (at most 1024 phonemes per row)");
@@ -625,6 +630,7 @@ int p1_run(Engine& e, const float* text, const float* emo, const int32_t* sid, c
   if (ce == cudaSuccess) ce = cudaMemcpyAsync(d_sid, sid, 4 * (size_t)B, cudaMemcpyHostToDevice, stream);
   auto ok = [&]() { return ce == cudaSuccess; };
   auto chk = [&]() { if (ok()) ce = cudaGetLastError(); };
+  cudaStream_t st = stream;                             // the stream the launch helpers below issue on (the capture stream while capturing)
 
   // one fused conv launch: out = epilogue(W * in)
   auto conv = [&](const P1Conv& c, const float* in, float* out, const float* res, int gate, bool relu) {
@@ -645,18 +651,18 @@ int p1_run(Engine& e, const float* text, const float* emo, const int32_t* sid, c
       sa.bias = ep.bias; sa.bias_bstride = ep.bias_bstride; sa.res = res; sa.out = out; sa.len = dl; sa.gate = gate; sa.relu = relu ? 1 : 0;
       const int cgroups = gate ? c.N / 4 : c.N / 4;
       dim3 grid((cgroups + 7) / 8, (T + 7) / 8, B);
-      p1_skinny_conv_kernel<<<grid, 256, 0, stream>>>(sa);
+      p1_skinny_conv_kernel<<<grid, 256, 0, st>>>(sa);
       chk();
       return;
     }
     if (res) { ep.res = res; ep.res_ld = No; ep.res_bstride = (long long)T * No; }
     if (relu) { ep.out_op = out; ep.out_op_ld = No; ep.out_op_bstride = (long long)T * No; ep.out_slope = 0.f; }
     else { ep.out_f32 = out; ep.out_f32_ld = No; ep.out_f32_bstride = (long long)T * No; }
-    ce = launch_conv_f32(a, stream);
+    ce = launch_conv_f32(a, st);
   };
   auto ln = [&](const float* in, float* out, int C, size_t gamma, size_t beta, const float* add, long long add_bs, bool pos) {
     if (!ok()) return;
-    p1_layernorm_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(in, C, T, dl, P + gamma, P + beta, add, add_bs, std::sqrt((float)H),
+    p1_layernorm_kernel<<<(rows + 7) / 8, 256, 0, st>>>(in, C, T, dl, P + gamma, P + beta, add, add_bs, std::sqrt((float)H),
                                                            pos ? P + S.pe : nullptr, P + S.alpha, 1e-5f, out, rows);
     chk();
   };
@@ -668,8 +674,10 @@ int p1_run(Engine& e, const float* text, const float* emo, const int32_t* sid, c
   if (ok()) ce = launch_cond_gemv(P + S.emoW, P + S.emoB, emo, B, H, S.emo_ch, Fp(W.emo), stream);
   // x = (LayerNorm(Linear(text)) + emo_proj(emo)) * sqrt(H) + pe * alpha                models.py:181-183, 157-164
   conv(S.emb, text, Fp(W.Y), nullptr, 0, false);
-  ln(Fp(W.Y), Fp(W.X), H, S.emb_g, S.emb_b, Fp(W.emo), H, true);
   const int kc = H / S.n_heads;
+  // ---- middle: workspace and weights only (captured / replayed as a CUDA graph from the second identical call on) ----
+  auto mid = [&]() {
+  ln(Fp(W.Y), Fp(W.X), H, S.emb_g, S.emb_b, Fp(W.emo), H, true);
   for (const P1State::Layer& L : S.layers) {
     conv(L.qkv, Fp(W.X), Fp(W.QKV), nullptr, 0, false);                                  // attentions.py:79-81
     if (ok()) {
@@ -679,12 +687,12 @@ int p1_run(Engine& e, const float* text, const float* emo, const int32_t* sid, c
         ce = optin.run([] { return cudaFuncSetAttribute(p1_attention_smem_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024); });
         if (ok()) {
           dim3 grid((T + kAttQS - 1) / kAttQS, S.n_heads, B);
-          p1_attention_smem_kernel<<<grid, 256, smem_s, stream>>>(Fp(W.QKV), H, kc, T, dl, 1.0f / std::sqrt((float)kc), Fp(W.A));
+          p1_attention_smem_kernel<<<grid, 256, smem_s, st>>>(Fp(W.QKV), H, kc, T, dl, 1.0f / std::sqrt((float)kc), Fp(W.A));
           chk();
         }
       } else {
         dim3 grid((T + kAttQ - 1) / kAttQ, S.n_heads, B);
-        p1_attention_kernel<<<grid, 32 * kAttQ, sizeof(float) * kAttQ * T, stream>>>(Fp(W.QKV), H, kc, T, dl, 1.0f / std::sqrt((float)kc), Fp(W.A));
+        p1_attention_kernel<<<grid, 32 * kAttQ, sizeof(float) * kAttQ * T, st>>>(Fp(W.QKV), H, kc, T, dl, 1.0f / std::sqrt((float)kc), Fp(W.A));
         chk();
       }
     }
@@ -696,17 +704,44 @@ int p1_run(Engine& e, const float* text, const float* emo, const int32_t* sid, c
   }
   // stats = proj(x); m_p, s_p = exp(logs_p)                                             models.py:185-188, 563
   conv(S.proj, Fp(W.X), Fp(W.QKV), nullptr, 0, false);
-  if (ok()) {
-    dim3 grid((T + 31) / 32, (2 * S.IC + 31) / 32, B), block(32, 8);
-    p1_stats_out_kernel<<<grid, block, 0, stream>>>(Fp(W.QKV), S.IC, T, dl, m_p, s_p);
-    chk();
-  }
   // duration predictor                                                                 models.py:59-67
   conv(S.dp_pre, Fp(W.X), Fp(W.Y), nullptr, 0, false);                                    // pre(x) + cond1(g)
   conv(S.dp_c1, Fp(W.Y), Fp(W.A), nullptr, 0, true);                                      // relu(conv_1)
   ln(Fp(W.A), Fp(W.Y), D, S.dn1g, S.dn1b, Fp(W.cond) + S.cond2_col, S.Ncond, false);      // norm_1(.) + cond2(g)
   conv(S.dp_c2, Fp(W.Y), Fp(W.A), nullptr, 0, true);
   ln(Fp(W.A), Fp(W.Y), D, S.dn2g, S.dn2b, nullptr, 0, false);
+  };   // mid
+
+  P1State::Graph* ge = nullptr;
+  if (e.opt_graph) {
+    for (P1State::Graph& g : S.graphs) if (g.ws == ws && g.B == B && g.T == T && g.masked == (dl != nullptr)) { ge = &g; break; }
+    if (!ge) {
+      if (S.graphs.size() >= 8) { if (S.graphs.front().exec) cudaGraphExecDestroy(S.graphs.front().exec); S.graphs.erase(S.graphs.begin()); }
+      S.graphs.push_back(P1State::Graph{ws, B, T, dl != nullptr, 0, nullptr});      // first sighting: issue directly
+    } else if (!ge->exec && ge->seen >= 0 && ok()) {                                  // second: capture on the private stream
+      if (!e.cap_stream && cudaStreamCreateWithFlags(&e.cap_stream, cudaStreamNonBlocking) != cudaSuccess) e.cap_stream = nullptr;
+      cudaGraph_t graph = nullptr;
+      bool good = e.cap_stream && cudaStreamBeginCapture(e.cap_stream, cudaStreamCaptureModeRelaxed) == cudaSuccess;
+      if (good) {
+        st = e.cap_stream;
+        mid();
+        st = stream;
+        const cudaError_t ee = cudaStreamEndCapture(e.cap_stream, &graph);
+        good = ok() && ee == cudaSuccess && graph != nullptr;
+        if (good) good = cudaGraphInstantiate(&ge->exec, graph, 0) == cudaSuccess;
+        if (graph) cudaGraphDestroy(graph);
+      }
+      if (!good) { cudaGetLastError(); ce = cudaSuccess; ge->exec = nullptr; ge->seen = -1; }    // never retry this shape
+    }
+  }
+  if (ge && ge->exec) { if (ok()) ce = cudaGraphLaunch(ge->exec, stream); }
+  else mid();
+  // ---- back: the caller's outputs ----
+  if (ok()) {
+    dim3 grid((T + 31) / 32, (2 * S.IC + 31) / 32, B), block(32, 8);
+    p1_stats_out_kernel<<<grid, block, 0, stream>>>(Fp(W.QKV), S.IC, T, dl, m_p, s_p);
+    chk();
+  }
   if (ok()) {
     p1_rowdot_kernel<<<(rows + 7) / 8, 256, 0, stream>>>(Fp(W.Y), D, T, dl, P + S.dproj_w, P + S.dproj_b, logw, rows);
     chk();

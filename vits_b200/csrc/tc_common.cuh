@@ -165,9 +165,21 @@ __device__ __forceinline__ void build_tile_prefix(int* prefix, int B, const int*
 // ~170 registers per thread, more than 18 warps leave; more warps won.)
 // Must be called by all 32 lanes (tcgen05.ld is .sync.aligned); wait_acc() must end with a
 // tcgen05.fence::after_thread_sync.
+// Staged stores (optional): when the epilogue only writes unsplit 16-bit operand rows (the upsamplers), each 16-column
+// unit is packed into a [128 rows][32 B] block of shared memory and written by ONE TMA store instead of 32-byte pieces
+// of 32 different rows per warp instruction.  Two blocks per epilogue group, alternating; thread 0 of the group issues
+// the stores (bulk async-groups are per thread) and waits for the block's previous store to have read it.
+struct TcStage {
+  uint32_t smem = 0;               // this group's two 4 KB blocks (0 = direct global stores)
+  const CUtensorMap* tm = nullptr; // (columns, rows, batch) map of the output, box 16 x 128 x 1, no swizzle
+  int bar_id = 0;                  // named barrier of the group's 128 threads
+  int unit = 0;                    // units staged so far by this group (selects the block)
+};
+
 template <typename OpT, typename WaitFn>
 __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& ep, int b, int t0, int ntile, int valid,
-                                            uint32_t tmem_acc, int q, int lane, int ugrp, int ngrp, WaitFn wait_acc, int dbg = 0) {
+                                            uint32_t tmem_acc, int q, int lane, int ugrp, int ngrp, WaitFn wait_acc, int dbg = 0,
+                                            TcStage* stg = nullptr) {
 #ifdef VITSB_RB_DEBUG
 #define TCE_DBG(m) ((dbg & (m)) != 0)      // timing ablations: 8 no global stores, 16 no bias / residual / accumulator loads, 32 no gate math
 #else
@@ -251,7 +263,29 @@ __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& e
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] = 0.f;
         }
-        if (in_range && !TCE_DBG(8)) {
+        if (stg && stg->smem) {
+          const uint32_t blk = stg->smem + (stg->unit & 1) * 4096u;
+          const bool issuer = q == 0 && lane == 0;
+          if (issuer) ptx::bulk_wait_read1();            // the store that last used this block has read it
+          asm volatile("bar.sync %0, 128;" ::"r"(stg->bar_id) : "memory");
+          uint32_t pk[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            float x = v[2 * i], y = v[2 * i + 1];
+            x = x >= 0.f ? x : ep.out_slope * x;
+            y = y >= 0.f ? y : ep.out_slope * y;
+            pk[i] = Pack16<OpT>::pack2(x, y);
+          }
+          st_shared_v4(blk + row * 32, pk[0], pk[1], pk[2], pk[3]);
+          st_shared_v4(blk + row * 32 + 16, pk[4], pk[5], pk[6], pk[7]);
+          fence_proxy_async_smem();
+          asm volatile("bar.sync %0, 128;" ::"r"(stg->bar_id) : "memory");
+          if (issuer && t0 < a.L) {                      // rows beyond L are clipped by the map
+            ptx::tma_store_3d(stg->tm, blk, (int)n0 + c0, t0, b);
+            ptx::bulk_commit();
+          }
+          ++stg->unit;
+        } else if (in_range && !TCE_DBG(8)) {
           if (ep.out_f32)
             store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + n0 + c0, v);
           if (ep.out_op)
