@@ -62,6 +62,10 @@ struct ConvArgs {
   // N tiles with first column >= n_split use epi_b, with columns counted from n_split.  0 = single epilogue.
   int n_split;
   Epilogue epi_b;
+  // Structural zeros of the phase-stacked transposed conv (3 taps, each output phase uses 2 of them): packed columns
+  // < tap_split_n use taps [0, k-1) only, columns >= tap_split_n taps [1, k).  An N tile on one side of the split skips
+  // the unused tap (its weights are exact zeros, so the result is bit-identical); 0 = every tap for every column.
+  int tap_split_n;
 };
 
 __host__ __device__ inline int ceil_div(int a, int b) { return (a + b - 1) / b; }

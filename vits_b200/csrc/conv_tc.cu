@@ -120,6 +120,16 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     t0 = (mt - s_prefix[cur_b]) * kTileM;
   };
 
+  // taps an N tile needs (see ConvArgs::tap_split_n)
+  auto tap_range = [&](int ntile, int& j0, int& j1) {
+    j0 = 0; j1 = a.k;
+    if (a.tap_split_n > 0) {
+      const int n_lo = ntile * a.NT, n_hi = n_lo + a.NT;
+      if (n_hi <= a.tap_split_n) j1 = a.k - 1;
+      else if (n_lo >= a.tap_split_n) j0 = 1;
+    }
+  };
+
   // Role loops are warp-uniform; only the single-thread instructions are predicated on one
   // elected lane (see ptx::elect_one) so that descriptors / coordinates stay in uniform registers.
   const int stages = g.stages, kchunks = g.kchunks, BK = g.BK, ktaps = a.k;
@@ -135,7 +145,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       coords(cl_id + n * n_cl, b, t0, ntile, live);
       const int row0 = (live ? t0 : a.L + 1024) - a.pad;      // dead tile: every row out of range -> TMA zero fill
       const int n0 = ntile * a.NT + rank * (a.NT / ncl);
-      for (int j = 0; j < ktaps; ++j) {
+      int j_lo, j_hi;
+      tap_range(ntile, j_lo, j_hi);
+      for (int j = j_lo; j < j_hi; ++j) {
         int col = 0;                                  // (kc * BK) % in_cols without the division
         for (int kc = 0; kc < kchunks; ++kc) {
           ptx::mbar_wait(empty_bar(s), ph ^ 1u);
@@ -175,7 +187,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       const bool leader = ptx::elect_one();
       const uint64_t dhi = ptx::umma_smem_desc(0, BK * 2, 0);
       const uint32_t idesc = g.idesc;
-      const int nk = BK / 16, iters = ktaps * kchunks;
+      const int nk = BK / 16;
       const uint32_t a16 = a_bytes >> 4, b16 = b_stride >> 4;
       const uint32_t sA16 = (sA & 0x3FFFFu) >> 4, sB16 = (sB & 0x3FFFFu) >> 4;
       int s = 0; uint32_t ph = 0;
@@ -184,6 +196,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         ptx::mbar_wait(acc_empty(buf), ((n >> 1) & 1) ^ 1u);
         ptx::tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * a.NT;
+        int j_lo, j_hi;
+        { const int item = cl_id + n * n_cl; tap_range(item - (item / nNT) * nNT, j_lo, j_hi); }
+        const int iters = (j_hi - j_lo) * kchunks;
         for (int it = 0; it < iters; ++it) {
           ptx::mbar_wait(full_bar(s), ph);
           ptx::tc_fence_after();
@@ -310,7 +325,9 @@ static int pick_launch_nt(const ConvArgs& a, int num_sms, bool pair_ok) {
     const long long items = (long long)ceil_div(q, ncl) * (a.N / nt);
     const int groups = num_sms / ncl;
     const double waves = (double)((items + groups - 1) / groups);
-    const double cost = waves * (nt + 40.0);
+    // tiles that do not straddle the tap split run k - 1 of the k taps
+    const bool aligned = a.tap_split_n > 0 && a.tap_split_n % nt == 0 && a.k > 1;
+    const double cost = waves * (nt * (aligned ? (double)(a.k - 1) / a.k : 1.0) + 40.0);
     if (cost < best_cost - 1e-9) { best_cost = cost; best = nt; }
   }
   return best;

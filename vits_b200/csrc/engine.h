@@ -22,6 +22,7 @@ struct PackedConv {
   size_t bias_off = 0;     // offset into the static fp32 bias pool (packed column order)
   int cond_off = -1;       // >=0: bias = per-call conditioning vector at this column (conv bias folded in)
   double flop_per_pos = 0; // algorithmic 2*Cin*Cout*k (true taps/channels only)
+  int tap_split_n = 0;     // ConvArgs::tap_split_n (upsamplers)
 };
 
 struct Coupling {          // modules.ResidualCouplingLayer (reverse, mean_only) with Flip folded in

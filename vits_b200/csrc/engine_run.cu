@@ -149,6 +149,7 @@ struct Ctx {
     a.w = reinterpret_cast<const char*>(e->d_w) + p.w_off * op_bytes(e->op);
     a.N = p.N; a.NT = p.NT; a.k = p.k; a.dil = p.dil; a.pad = p.pad; a.L = L; a.B = B;
     a.gate_group = p.gate_group; a.m_tiles = m_tiles(L, len_mul, len != nullptr);
+    a.tap_split_n = p.tap_split_n;
     a.len = len; a.len_mul = len_mul;
     a.epi = ep_in;
     a.epi.gate = p.gate ? 1 : 0;

@@ -490,6 +490,20 @@ int Engine::load(const vitsb_tensor_desc* tens, int n) {
           for (int ci = 0; ci < Cin; ++ci)
             put_w(dst, pc, ph * Cout + co, jj, ci, Cin, w->v[((size_t)ci * Cout + co) * k + j]);
         }
+    // which of the packed taps each phase really uses: with 3 taps the early phases use taps {0, 1} and the late ones
+    // {1, 2}; the launcher skips the structurally zero tap for N tiles on one side of that boundary
+    if (pc.k == 3) {
+      int ps = u;                                        // first phase that uses tap 2
+      bool pattern = true;
+      for (int ph = 0; ph < u; ++ph) {
+        bool use[3] = {false, false, false};
+        for (int jj = 0; jj < 3; ++jj) { const int j = ph + pd - u * (jj + dmin); use[jj] = j >= 0 && j < k; }
+        if (use[2] && ps == u) ps = ph;
+        if (ph < ps && use[2]) pattern = false;
+        if (ph >= ps && use[0]) pattern = false;
+      }
+      if (pattern && ps > 0 && ps < u) pc.tap_split_n = ps * Cout;
+    }
     pc.bias_off = h_bias.size();
     for (int ph = 0; ph < u; ++ph) for (int co = 0; co < Cout; ++co) h_bias.push_back(b->v[co]);
     while (h_bias.size() % 4) h_bias.push_back(0.f);
