@@ -95,7 +95,13 @@ struct RbT {
   // C >= 128 (COOP): the pipeline is bound by the LATENCY of one tile's epilogues (few accumulator sets), so both
   // groups work on EVERY tile and split its columns; C <= 64 (MMA-bound, 4 sets): groups take alternate tiles.
   static constexpr bool COOP = C >= 128;
-  static constexpr int NGRP = 2;
+#ifndef VITSB_RB_NGRP_SMALL
+#define VITSB_RB_NGRP_SMALL 2
+#endif
+  // C <= 64: the epilogue groups take alternate tiles; C >= 128 splits columns between two groups.  A third group for
+  // C <= 64 (-DVITSB_RB_NGRP_SMALL=3: 28 warps, 72 registers, no spills) was measured in round 2: s3 -2 %, s2 +-0 -
+  // the narrow stages are not short of epilogue warps (shared-memory bandwidth of the N <= 64 MMAs)
+  static constexpr int NGRP = C <= 64 ? VITSB_RB_NGRP_SMALL : 2;
   static constexpr int TSTEP = COOP ? 1 : NGRP;                                   // tile stride of one epilogue group
   static constexpr int NARR = 4 * NCL * (COOP ? NGRP : 1);                        // epilogue-warp arrivals per barrier phase
   static constexpr int THREADS = 128 + NGRP * 256;
@@ -133,7 +139,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   // and the residual stream flushes it, so per-chunk bias loads from global paid an L2 round trip each.
   constexpr int kSB = C >= kBiasSmemMinC ? C : 4;                   // small C reads its biases from global / L1 (measured faster there)
   __shared__ __align__(16) float s_bias2[kSB];            // conv2 bias
-  __shared__ __align__(16) float s_bias1[2][kSB];         // per epilogue group: conv1 bias + conditioning of the current batch row
+  __shared__ __align__(16) float s_bias1[G::NGRP][kSB];         // per epilogue group: conv1 bias + conditioning of the current batch row
 
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t slab_set = G::nCB1 * rt.slab_bytes;
@@ -199,7 +205,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 
   // static round-robin schedule; b only grows along a CTA's tile sequence
   // epilogue group of this warp (warps 4-11: group 0, warps 12-19: group 1) and its tile stride
-  const int grp = warp >= 12 ? 1 : 0;
+  const int grp = warp >= 4 ? (warp - 4) >> 3 : 0;
   const bool is_epi = warp >= 4;
   const int tstep = is_epi ? G::TSTEP : 1;
   const int n_first = is_epi && !G::COOP ? grp : 0;          // first tile (of this CTA's sequence) the warp works on
@@ -394,7 +400,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       }
     }
     __syncwarp();
-  } else if ((warp >= 4 && warp < 8) || (warp >= 12 && warp < 16)) {
+  } else if (warp >= 4 && ((warp - 4) & 4) == 0) {
     // =================== epilogue 1: gate -> G tile in shared memory ===================
     const int q = warp & 3, r = q * 32 + lane;
     constexpr int NCH = G::C2 / 16;              // 16-gate chunks per row
@@ -519,7 +525,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     const int ch0 = G::COOP ? grp * NCH_S : 0;
     constexpr int PF = NCH_S < 4 ? NCH_S : 4;    // residual chunks kept in flight (2 x uint4 each; 96-register cap with 20 warps)
     Cursor sl{0, 0};
-    if (grp == 1 && !G::COOP) sl.next(nSlab);
+    if (!G::COOP) for (int i = 0; i < grp; ++i) sl.next(nSlab);
     // output staging (kStage): row r of this group's block, written in place of a TMA-load image; thread 0 of the
     // group issues the stores and is the one that waits for them (bulk async-groups are per thread)
     const uint32_t stg = sStage + grp * G::STG_BYTES, stg_row = stg + r * G::RB_O;
@@ -587,7 +593,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         if (kStage) {
           if (cc % CH_BLK == 0) {                // block buffer reuse: the previous store must have read it
             if (issuer) ptx::bulk_wait_read0();
-            asm volatile("bar.sync %0, 128;" ::"r"(3 + grp) : "memory");
+            asm volatile("bar.sync %0, 128;" ::"r"(4 + grp) : "memory");
           }
           uint32_t pk[8];
 #pragma unroll
@@ -601,7 +607,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           st_shared_v4(swz_addr<G::RB_O>(saddr + 16), pk[4], pk[5], pk[6], pk[7]);
           if (cc % CH_BLK == CH_BLK - 1) {       // block complete: rows [t0, t0 + T_OUT) x 64 channels, clipped at L by the map
             fence_proxy_async_smem();
-            asm volatile("bar.sync %0, 128;" ::"r"(3 + grp) : "memory");
+            asm volatile("bar.sync %0, 128;" ::"r"(4 + grp) : "memory");
             if (issuer && t0 < a.L && !RB_DBG(1)) {
               ptx::tma_store_3d(&tmO, stg, (c / CH_BLK) * G::CB_O, t0, b);
               ptx::bulk_commit();
