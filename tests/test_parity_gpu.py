@@ -479,3 +479,49 @@ def test_synthesize_segments_equals_sequential_calls(base_cfg, base_sd):
             assert a.shape == b.shape and torch.equal(a, b)
     with pytest.raises(ValueError):
         eng.synthesize_segments([(segs[0][0][:, :10], segs[0][1])])
+
+
+def test_dynamic_batcher_across_threads(base_cfg, base_sd):
+    """requests submitted from several threads are grouped into ragged batches by one dispatcher and every
+    caller gets exactly its B = 1 result."""
+    import threading
+    from vits_b200.serving import DynamicBatcher
+    eng = engine(base_cfg, base_sd, "fp16")
+    lens = [33, 120, 7, 64, 90, 15, 1, 50, 77, 21, 40, 9]
+    lats = [FX.make_latents(base_cfg, [T], seed=800 + i) for i, T in enumerate(lens)]
+    refs = [eng.synthesize(l["z_p"].cuda(), l["g"].cuda()).clone() for l in lats]
+    got = [None] * len(lens)
+    with DynamicBatcher(eng, max_batch=5, max_wait_ms=50.0) as bt:
+        def worker(idx):
+            for i in idx:
+                got[i] = bt.submit(lats[i]["z_p"], lats[i]["g"]).result(timeout=60)
+        th = [threading.Thread(target=worker, args=(range(k, len(lens), 4),)) for k in range(4)]
+        [t.start() for t in th]
+        [t.join() for t in th]
+        assert sum(bt.batches) == len(lens) and max(bt.batches) <= 5 and max(bt.batches) > 1      # really batched
+        with pytest.raises(ValueError):
+            bt.submit(lats[0]["z_p"][:, :10], lats[0]["g"])
+    for a, b in zip(got, refs):
+        assert a.shape == b.shape and torch.equal(a, b)
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_engines_on_two_devices_in_one_process(base_cfg, base_sd):
+    """The dynamic shared-memory opt-in is per device: a second engine on another GPU of the same process must work."""
+    from vits_b200 import FlowDecoder
+    lens = [50, 33]
+    lat = FX.make_latents(base_cfg, lens, seed=5)
+    e0 = engine(base_cfg, base_sd, "fp16")
+    w0 = e0.synthesize(lat["z_p"].cuda(0), lat["g"].cuda(0), lens)
+    e1 = FlowDecoder(base_cfg, base_sd, device="cuda:1", precision="fp16")
+    w1 = e1.synthesize(lat["z_p"].cuda(1), lat["g"].cuda(1), lens)
+    assert w1.device.index == 1 and torch.equal(w0.cpu(), w1.cpu())
+    z0 = e0.flow_reverse(lat["z_p"].cuda(0), lat["g"].cuda(0), lens)
+    rc_dev = torch.empty_like(z0, device="cuda:1")
+    import ctypes as C
+    arr = (C.c_int32 * 2)(*lens)
+    with torch.cuda.device(1):
+        zp1, g1 = lat["z_p"].cuda(1).contiguous(), lat["g"].cuda(1).contiguous()
+        rc = e1.lib.vitsb_flow_reverse_noalloc(e1._h, zp1.data_ptr(), g1.data_ptr(), arr, 2, max(lens), rc_dev.data_ptr(), e1._stream())
+        torch.cuda.synchronize()
+    assert rc == 0 and torch.equal(rc_dev.cpu(), z0.cpu())          # the static scratch array's address is per device
