@@ -375,7 +375,7 @@ def test_host_pipeline_matches_blocking_calls(base_cfg, base_sd):
 
 
 @pytest.mark.parametrize("opts", [{"flow_fused": 0}, {"flow_fused": 0, "flow_in_split": 1}, {"rb_fused": 0}, {"tc_pair": 0},
-                                  {"cuda_graph": 0, "pdl": 0}])
+                                  {"cuda_graph": 0, "pdl": 0}, {"branch_streams": 0}])
 def test_alternative_launch_plans_agree(base_cfg, base_sd, opts):
     """The launch-plan options (layer-at-a-time flow instead of the fused coupling kernel, 3-term split in_layers,
     layer-at-a-time ResBlocks, no CTA pairs, no graphs + PDL) stay within the same tolerance of the CPU oracle and of

@@ -45,7 +45,7 @@ struct WsLayout {
   size_t len = 0, cond = 0, xlen = 0, cum = 0;      // cum: int [B][1024] cumulative durations (durations front end)
   size_t zf = 0, zop = 0, hf = 0, hop = 0, acts = 0, skipf = 0, skipop = 0;   // flow (h / acts / skip: layer-at-a-time flow only)
   size_t xin_f = 0, xb_f = 0, acc_f = 0, g_op = 0;                            // decoder, layer-at-a-time plan (fp32 build)
-  size_t xin_op = 0, xb_op = 0, xb2_op = 0, br0 = 0, br1 = 0, nxt_op = 0;     // decoder, 16-bit streams
+  size_t xin_op = 0, xb_op = 0, xb2_op = 0, br0 = 0, br1 = 0, x3a = 0, x3b = 0, nxt_op = 0;     // decoder, 16-bit streams
   size_t total = 0;
 };
 
@@ -98,7 +98,7 @@ struct Engine {
 
   // options (vitsb_set_option); -1 = automatic.  Packing / plan options take effect at the next vitsb_load_weights.
   int opt_graph = 1, opt_pdl = 1, opt_tc_pair = 1, opt_rb_fused = -1, opt_flow_fused = -1, opt_flow_in_split = -1,
-      opt_rb_nslab = 0, opt_ws_cap_mb = 24576, opt_ups_split_mask = -1;
+      opt_rb_nslab = 0, opt_ws_cap_mb = 24576, opt_ups_split_mask = -1, opt_branch_streams = 1;
   int set_option(const char* key, int value);
   int get_option(const char* key, int* value) const;
   LaunchOpts lopts() const { LaunchOpts o; o.pdl = opt_pdl != 0; o.pair = opt_tc_pair != 0; o.num_sms = num_sms; o.rb_nslab = opt_rb_nslab; return o; }
@@ -146,6 +146,11 @@ struct Engine {
   struct GraphEntry { std::vector<long long> key; int seen = 0; int launches = 0; cudaGraphExec_t exec = nullptr; unsigned long long stamp = 0; };
   std::vector<GraphEntry> graphs;
   cudaStream_t cap_stream = nullptr;
+  // the MRF branches of a stage run concurrently: two side streams + fork / join events (engine_run.cu)
+  cudaStream_t side_stream[2] = {nullptr, nullptr};
+  cudaEvent_t ev_fork = nullptr, ev_join[2] = {nullptr, nullptr};
+  bool side_failed = false;
+  bool side_streams_ready();
   unsigned long long graph_clock = 0;
   void drop_graphs();
   std::vector<long long> graph_key(const Call& c) const;

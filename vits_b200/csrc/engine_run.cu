@@ -48,6 +48,7 @@ WsLayout Engine::layout(int B, int T) const {
     // 16-bit streams only: stage input, ping / pong, two branch results (the third lands in ping), next operand
     w.xin_op = take(ob * BT * E); w.xb_op = take(ob * BT * E); w.xb2_op = take(ob * BT * E);
     w.br0 = take(ob * BT * E); w.br1 = take(ob * BT * E);
+    w.x3a = take(ob * BT * E); w.x3b = take(ob * BT * E);       // third branch's ping / pong (branches run concurrently)
     const bool need_f32_post = !conv_post_y_supported(post_C, post_k, T * up_total);
     if (need_f32_post) w.acc_f = take(4 * BT * E);
   } else {
@@ -189,6 +190,17 @@ void set_out_op_hi(Epilogue& ep, void* p, int C, long long L, bool split_pitch, 
 }
 
 }  // namespace
+
+bool Engine::side_streams_ready() {
+  if (side_stream[0]) return true;
+  if (side_failed) return false;
+  bool ok = true;
+  for (int i = 0; i < 2 && ok; ++i) ok = cudaStreamCreateWithFlags(&side_stream[i], cudaStreamNonBlocking) == cudaSuccess;
+  if (ok) ok = cudaEventCreateWithFlags(&ev_fork, cudaEventDisableTiming) == cudaSuccess;
+  for (int i = 0; i < 2 && ok; ++i) ok = cudaEventCreateWithFlags(&ev_join[i], cudaEventDisableTiming) == cudaSuccess;
+  if (!ok) { cudaGetLastError(); side_failed = true; side_stream[0] = nullptr; }
+  return ok;
+}
 
 int Engine::check_call(const Call& c, bool dry) {
   if (!dry) {
@@ -337,10 +349,21 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
       const int nk = (int)st.rb.size();
       const float inv = 1.0f / nk;
       const float next_slope = 0.1f;                           // models.py:309 (the 0.01 of models.py:315 is in conv_post)
-      // results of the MRF branches (16-bit plan): the third one lands in the ping buffer, free during its last iteration
-      void* br[3] = {P(W.br0), P(W.br1), P(W.xb_op)};
+      // 16-bit plan: every MRF branch (models.py:311-314) is an independent chain of fused launches with its own ping / pong
+      // buffers, so the branches run CONCURRENTLY on three streams (fork after the upsampler, join before the MRF pass):
+      // another branch's CTAs fill the partial last wave of each persistent launch (stage 0 at 16 utterances: 3.4 tiles
+      // per CTA), and at one utterance the launches do not fill the GPU at all.  Works the same under graph capture.
+      void* bufs[3][2] = {{P(W.xb_op), P(W.xb2_op)}, {P(W.br0), P(W.br1)}, {P(W.x3a), P(W.x3b)}};
+      void* br[3] = {nullptr, nullptr, nullptr};             // result buffer of each branch = the one its last iteration writes
+      for (int j = 0; j < nk && j < 3; ++j) br[j] = bufs[j][((int)st.rb[j].size() - 1) & 1];   // (known without issuing: the PH_BACK pass needs it)
+      const bool fork = rb_fused && opt_branch_streams && !profile && !dry && !cx.skip && nk > 1 && nk <= 3 && side_streams_ready();
+      if (fork && cx.ok()) {
+        cx.err = cudaEventRecord(ev_fork, stream);
+        for (int j = 1; j < nk && cx.ok(); ++j) cx.err = cudaStreamWaitEvent(side_stream[j - 1], ev_fork, 0);
+      }
       for (int j = 0; j < nk; ++j) {
         const int ni = (int)st.rb[j].size();
+        cudaStream_t bstream = (fork && j > 0) ? side_stream[j - 1] : stream;
         for (int d = 0; d < ni; ++d) {
           const ResIter& it = st.rb[j][d];
           if (rb_fused) {
@@ -351,8 +374,8 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
             ++cx.launches;
             if (dry || !cx.ok()) continue;
             RbLaunch rl{};
-            void* ping = (d & 1) ? P(W.xb2_op) : P(W.xb_op);        // out of iteration d
-            void* pong = (d & 1) ? P(W.xb_op) : P(W.xb2_op);        // out of iteration d-1
+            void* ping = bufs[j][d & 1];                            // out of iteration d
+            void* pong = bufs[j][(d & 1) ^ 1];                      // out of iteration d-1
             rl.y_in = d == 0 ? P(W.xin_op) : pong;
             rl.w1 = reinterpret_cast<const char*>(d_w) + it.c1.w_off * ob;
             rl.w2 = reinterpret_cast<const char*>(d_w) + it.c2.w_off * ob;
@@ -361,14 +384,9 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
             ra.L = L; ra.B = B; ra.len = cx.len_dec; ra.len_mul = mul;
             ra.bias1 = cx.cond + it.c1.cond_off; ra.bias1_bstride = Ncond;
             ra.bias2 = d_bias + it.c2.bias_off;
-            // the last iteration writes the branch result; br[2] aliases a ping / pong buffer, which must not be the one
-            // this iteration reads
-            void* dst = d < ni - 1 ? ping : br[j];
-            if (dst == rl.y_in) dst = P(W.xb2_op) == rl.y_in ? P(W.xb_op) : P(W.xb2_op);
-            ra.y_out = dst;
-            if (d == ni - 1) br[j] = dst;
+            ra.y_out = ping;                                        // the last iteration's output is the branch result br[j]
             cx.ev_begin(T_RB_FUSED + s, (it.c1.flop_per_pos + it.c2.flop_per_pos) * (cx.len_dec ? cx.valid_frames : (double)B * T) * mul);
-            cx.err = launch_rb_fused(rl, op, cx.lo, stream);
+            cx.err = launch_rb_fused(rl, op, cx.lo, bstream);
             cx.ev_end();
             continue;
           }
@@ -390,6 +408,12 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
             else set_out_op_split(ep, P(W.nxt_op), C, L, next_slope, stages[s + 1].ups.split);
           }
           cx.conv(T_RB_C2 + s, it.c2, P(W.g_op), L, mul, cx.len_dec, ep);
+        }
+      }
+      if (fork) {
+        for (int j = 1; j < nk && cx.ok(); ++j) {
+          cx.err = cudaEventRecord(ev_join[j - 1], side_stream[j - 1]);
+          if (cx.ok()) cx.err = cudaStreamWaitEvent(stream, ev_join[j - 1], 0);
         }
       }
       if (rb_fused) {
@@ -435,7 +459,7 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
 // per-rate tile counts the launchers size their grids with.  The lengths themselves are read from device memory.
 std::vector<long long> Engine::graph_key(const Call& c) const {
   std::vector<long long> key = {c.what, (long long)(uintptr_t)c.ws, (long long)c.ws_bytes, c.B, c.T, c.ragged, c.len ? 1 : 0,
-                                opt_pdl, opt_tc_pair, opt_rb_nslab, c.dur ? 1 : 0};
+                                opt_pdl, opt_tc_pair, opt_rb_nslab, c.dur ? 1 : 0, opt_branch_streams};
   if (c.len) {
     int mul = 1;
     key.push_back(Ctx::count_tiles(c.len, c.B, c.T, 1, true, kTileM, kHaloRows));

@@ -38,6 +38,8 @@ void Engine::free_device() {
 Engine::~Engine() {
   p1_destroy(p1);
   drop_graphs();
+  for (int i = 0; i < 2; ++i) { if (side_stream[i]) cudaStreamDestroy(side_stream[i]); if (ev_join[i]) cudaEventDestroy(ev_join[i]); }
+  if (ev_fork) cudaEventDestroy(ev_fork);
   if (cap_stream) cudaStreamDestroy(cap_stream);
   free_device();
 }
@@ -54,6 +56,7 @@ const OptDesc kOpts[] = {
     {"flow_in_split", &Engine::opt_flow_in_split, -1, 1}, // 3-term split WN in_layers (-1: bf16 yes, fp16 no); applies at the next load
     {"rb_nslab", &Engine::opt_rb_nslab, 0, 16},           // rb_fused slab count override (0 auto)
     {"ups_split_mask", &Engine::opt_ups_split_mask, -1, 255}, // bit i: upsampler i runs 3-term split precision (16-bit paths); applies at the next load
+    {"branch_streams", &Engine::opt_branch_streams, 0, 1}, // the MRF branches of a stage run concurrently on three streams
     {"ws_cap_mb", &Engine::opt_ws_cap_mb, 64, 1 << 20},   // workspace cap: larger batches are processed in row chunks
 };
 }  // namespace
