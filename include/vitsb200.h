@@ -11,8 +11,9 @@
  *     the ABI; vitsb_last_error(h) gives the message of the last failure.
  *   - the caller owns every input, output and workspace buffer.  The handle
  *     owns the packed weights, its options, a small cache of instantiated CUDA
- *     graphs (replay of the workspace-only launches of a repeated shape) and the
- *     private stream those are captured on.  Calls are asynchronous on `stream`.
+ *     graphs (replay of the workspace-only launches of a repeated shape), the
+ *     private stream those are captured on and two side streams for the decoder's
+ *     concurrent MRF branches.  Calls are asynchronous on `stream`.
  *   - threads: every entry point takes the handle's mutex, so a handle may be
  *     shared between threads; calls on ONE handle are serialised on the host
  *     (their device work is ordered by the streams passed in) and concurrent
