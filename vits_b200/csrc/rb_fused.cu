@@ -532,6 +532,37 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     const bool issuer = r == 0;
     constexpr int CH_BLK = G::CB_O / 16;         // 16-column chunks per staged block
     static_assert(!G::COOP || (NCH_S % CH_BLK == 0 && NCH_S % PF == 0), "column split must be block aligned");
+    // Residual rows from global memory (C >= 64) are software-pipelined ACROSS tiles: while the last PF chunks of a tile
+    // are processed, the first PF chunks of this group's NEXT tile are already being loaded into the registers just
+    // freed.  Loading them at the top of the next tile exposed one L2 round trip (~1.2 k cycles) per tile on the group
+    // that sets the tile period of the k = 3 shapes (4.1 k cycles of work + that gap = the 5.3 k cycles measured).
+#ifdef VITSB_RB_NO_LOOKAHEAD
+    constexpr bool kLook = false;                 // A/B switch: load each tile's first chunks at the top of that tile
+#else
+    constexpr bool kLook = G::RES_GLOBAL;
+#endif
+    uint4 yq[PF][2];
+    // row pointer of this thread in tile nn of the CTA's sequence (nullptr: no such tile / row outside the tensor)
+    auto res_row = [&](int nn) -> const uint4* {
+      if (nn >= my_tiles) return nullptr;
+      const int unit = unit_id + nn * n_units;
+      const int tt = G::PAIR ? unit * 2 + rank : unit;
+      if (tt >= total_tiles) return nullptr;
+      int bb = cur_b;
+      while (s_tile_prefix[bb + 1] <= tt) ++bb;
+      const int tn = (tt - s_tile_prefix[bb]) * G::T_OUT + r;
+      if (r >= G::T_OUT || tn >= a.L) return nullptr;
+      return reinterpret_cast<const uint4*>(reinterpret_cast<const OpT*>(a.y_res) + ((long long)bb * a.L + tn) * C);
+    };
+    auto load_res = [&](const uint4* row, int c, uint4 (&dst)[2]) {
+      dst[0] = dst[1] = make_uint4(0u, 0u, 0u, 0u);
+      if (row && !RB_DBG(2)) { dst[0] = ldg_nc_v4_pinned(row + 2 * c); dst[1] = ldg_nc_v4_pinned(row + 2 * c + 1); }
+    };
+    if (kLook) {
+      const uint4* row0 = res_row(n_first);
+#pragma unroll
+      for (int c = 0; c < PF; ++c) load_res(row0, ch0 + c, yq[c]);
+    }
     for (int n = n_first; n < my_tiles; n += G::TSTEP, tile_next()) {
       const Cursor ab{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
       tile_seek();
@@ -542,28 +573,23 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const bool live = t < valid;
       const int s = ab.idx, ss = sl.idx;
       const long long orow = ((long long)b * a.L + t) * C;
-      const long long orow_ld = RB_DBG(16384) ? (long long)r * C : orow;     // ablation: residual reads always hit the same hot rows
-      const uint4* yres = reinterpret_cast<const uint4*>(reinterpret_cast<const OpT*>(a.y_res) + orow_ld);
+      const uint4* yres = in_range ? reinterpret_cast<const uint4*>(reinterpret_cast<const OpT*>(a.y_res) + orow) : nullptr;
+      const uint4* ynext = kLook ? res_row(n + G::TSTEP) : nullptr;       // this group's next tile
       const uint32_t yrow = sSlab + ss * slab_set + srow * G::rb1;
-      // residual rows: issued before the accumulator wait so their latency hides behind c2
-      uint4 yq[PF][2];
       auto load_y = [&](int c, uint4 (&dst)[2]) {
         if (G::RES_GLOBAL) {
-          dst[0] = dst[1] = make_uint4(0u, 0u, 0u, 0u);
-          if (in_range && !RB_DBG(2)) {
-            // C >= 128: pinned loads = a real software prefetch; C = 64 measured faster when ptxas places the loads itself
-            if (C >= 128) { dst[0] = ldg_nc_v4_pinned(yres + 2 * c); dst[1] = ldg_nc_v4_pinned(yres + 2 * c + 1); }
-            else { dst[0] = __ldg(yres + 2 * c); dst[1] = __ldg(yres + 2 * c + 1); }
-          }
+          load_res(yres, c, dst);
         } else {
           const int c0 = 16 * c, cb = c0 / G::BK1, cin = c0 - cb * G::BK1;
           const uint32_t yaddr = yrow + cb * slab_bytes + cin * 2;
           dst[0] = ld_shared_v4(swz_addr<G::rb1>(yaddr)); dst[1] = ld_shared_v4(swz_addr<G::rb1>(yaddr + 16));
         }
       };
-      if (!G::RES_GLOBAL) ptx::mbar_wait(slab_full(ss), sl.phase);      // acquire the TMA-written slab for the residual reads
+      if (!kLook) {
+        if (!G::RES_GLOBAL) ptx::mbar_wait(slab_full(ss), sl.phase);      // acquire the TMA-written slab for the residual reads
 #pragma unroll
-      for (int c = 0; c < PF; ++c) load_y(ch0 + c, yq[c]);
+        for (int c = 0; c < PF; ++c) load_y(ch0 + c, yq[c]);
+      }
       ptx::mbar_wait(acc2_full(s), ab.phase);
       ptx::tc_fence_after();
       if ((warp & 3) == 0) trace(4, n, 0);
@@ -581,6 +607,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         }
         const uint4 y0 = yq[cc % PF][0], y1 = yq[cc % PF][1];
         if (cc + PF < NCH_S) load_y(c + PF, yq[cc % PF]);
+        else if (kLook) load_res(ynext, ch0 + cc + PF - NCH_S, yq[cc % PF]);      // first chunks of the next tile
         const uint32_t yw[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
         float v[16];
 #pragma unroll
