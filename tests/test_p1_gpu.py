@@ -159,3 +159,37 @@ def test_device_side_durations_equal_the_host_glue(base_cfg, base_sd, prec):
     for _ in range(3):
         w3, _ = eng.synthesize_durations(m_p, s_p, logw, g, noise.cuda(), T_cap, x_lengths=lens)
         assert torch.equal(w3, wav)
+
+
+def test_infer_p1_long_text_and_empty_rows(base_cfg, base_sd):
+    """Tx = 300 takes the global-memory attention kernel (K / V of a head no longer fit shared memory); a row of zero
+    phonemes stays empty through infer_p1 and the durations front end; Tx beyond the table limit is refused."""
+    from vits_b200 import lib as L
+    eng = engine(base_cfg, base_sd)
+    sd1 = FX.make_p1_state_dict(base_cfg, seed=4321)
+    inp = FX.make_p1_inputs(base_cfg, [300], seed=41)
+    m_p, s_p, logw, g = eng.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"])
+    with torch.no_grad():
+        mr, sr, lr, _ = P.infer_p1(sd1, inp["text"], inp["emo"], inp["sid"], base_cfg)
+    assert (m_p.cpu() - mr).abs().max().item() <= TOL and (logw.cpu() - lr).abs().max().item() <= TOL
+    assert (s_p.cpu() / sr - 1).abs().max().item() <= TOL
+    # ragged batch with an empty row
+    lens = [9, 0, 14]
+    inp = FX.make_p1_inputs(base_cfg, [9, 1, 14], seed=42)
+    m_p, s_p, logw, g = eng.infer_p1(inp["text"].cuda(), inp["emo"].cuda(), inp["sid"], lens)
+    assert m_p[1].abs().sum().item() == 0 and logw[1].abs().sum().item() == 0
+    T_cap = 160
+    noise = torch.randn(3, 192, T_cap, generator=torch.Generator().manual_seed(2)) * 0.707
+    wav, yl = eng.synthesize_durations(m_p, s_p, logw, g, noise.cuda(), T_cap, x_lengths=lens)
+    yl = yl.tolist()
+    assert yl[1] == 0 and wav[1].abs().sum().item() == 0 and torch.isfinite(wav).all()
+    for b in (0, 2):
+        L_ = lens[b]
+        _, y_b, path = P.durations_to_path(logw[b:b + 1, :, :L_].cpu())
+        assert yl[b] == y_b
+        one = eng.infer_p2(path.cuda(), m_p[b:b + 1, :, :L_].contiguous(), s_p[b:b + 1, :, :L_].contiguous(), g[b:b + 1],
+                           noise[b:b + 1, :, :y_b].contiguous().cuda())
+        assert (wav[b:b + 1, :, :y_b * 192] - one).abs().max().item() <= 1e-6
+    big = FX.make_p1_inputs(base_cfg, [1030], seed=43)
+    with pytest.raises(L.VitsbError):
+        eng.infer_p1(big["text"].cuda(), big["emo"].cuda(), big["sid"])
