@@ -101,6 +101,27 @@ def test_adapt_shape_set_golden(adapt_cfg, golden_dir, prec):
     assert np.abs(wav.cpu().numpy() - gold["o"]).max() <= TOL_WAV[prec]
 
 
+@pytest.mark.parametrize("gin", [1280, 72])
+def test_conditioning_width_other_than_base_vs_oracle(gin):
+    """The conditioning GEMV has a register-resident kernel for gin <= 1024 and a generic one above; neither the base
+    (1024) nor the adapt (256) shape set reaches the generic kernel or a gin that leaves a K quarter partly empty."""
+    from vits_b200 import FlowDecoder
+    from vits_b200.config import HotPathConfig
+    cfg = HotPathConfig(gin_channels=gin)
+    sd = FX.make_state_dict(cfg, seed=77)
+    lens = [23, 9, 31, 17, 5, 12, 30, 2, 19, 27, 8, 14, 25, 3, 21, 11, 16, 29, 7]        # 19 rows: a second batch pass of 16
+    lat = FX.make_latents(cfg, lens, seed=3)
+    eng = FlowDecoder(cfg, sd, device="cuda:0", precision="fp32")
+    wav, z = eng.synthesize(lat["z_p"].cuda(), lat["g"].cuda(), lat["lengths"], return_z=True)
+    wav, z = wav.cpu(), z.cpu()
+    for b, n in enumerate(lens):
+        with torch.no_grad():
+            z_ref = O.flow_reverse(sd, lat["z_p"][b:b + 1, :, :n], lat["g"][b:b + 1], cfg)
+            o_ref = O.generator(sd, z_ref, lat["g"][b:b + 1], cfg)
+        assert (z[b, :, :n] - z_ref[0]).abs().max().item() <= TOL_Z["fp32"]
+        assert (wav[b, :, :n * cfg.hop_length] - o_ref[0]).abs().max().item() <= TOL_WAV["fp32"]
+
+
 def test_weight_norm_state_dict_packs_identically(base_cfg, base_sd):
     from vits_b200 import FlowDecoder
     sd_wn = FX.make_state_dict(base_cfg, seed=1234, weight_norm=True)

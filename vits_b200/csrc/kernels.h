@@ -131,7 +131,7 @@ cudaError_t launch_durations(const float* logw, const int* x_len, const float* m
 // (conv_post input of shapes conv_post_y does not cover)
 cudaError_t launch_mrf_sum(const void* y0, const void* y1, const void* y2, int B, int L, int C, const int* len, int len_mul,
                            float scale, float slope, void* out, int split, float* out_f32, int op, cudaStream_t stream);
-// conv_post whose input is the MRF average of up to three y streams, formed in the tile load (base shape only)
+// conv_post whose input is the MRF average of up to three y streams, formed in the row load (base shape only)
 bool conv_post_y_supported(int C, int k, int L);
 cudaError_t launch_conv_post_y(const void* y0, const void* y1, const void* y2, float scale, int B, int L, int C, int k, float slope,
                                const float* w, const int* len, int len_mul, float* wav, short* pcm, float volume, int op,
