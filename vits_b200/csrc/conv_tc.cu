@@ -42,6 +42,7 @@ struct TcGeom {
   uint32_t idesc;
   int dbg;           // VITSB_TC_DBG timing-experiment mask (only with -DVITSB_RB_DEBUG; results are wrong when set)
   int staged;        // 16-bit output rows leave through shared-memory blocks + TMA stores (tc_common.cuh TcStage)
+  int stage_cols;    // columns per staged block (32 or 64); one block per epilogue group
 };
 
 #ifdef VITSB_RB_DEBUG
@@ -72,8 +73,9 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   const uint32_t smem_base = (ptx::smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t sA = smem_base;
   const uint32_t sB = sA + g.stages * g.a_bytes;
-  const uint32_t sStg = sB + g.stages * g.b_stride;          // staged stores: [epilogue group][2][128 rows x 32 B]
-  const uint32_t bars = sStg + (g.staged ? kTcEpiGroups * 2 * 4096u : 0u);          // 8-byte aligned (multiples of 1024 above)
+  const uint32_t stg_bytes = g.staged ? (uint32_t)kTileM * g.stage_cols * 2u : 0u;  // staged stores: [epilogue group][128 rows x stage_cols], swizzled
+  const uint32_t sStg = sB + g.stages * g.b_stride;
+  const uint32_t bars = sStg + kTcEpiGroups * stg_bytes;                             // 8-byte aligned (multiples of 1024 above)
   auto full_bar = [&](int s) { return bars + 8u * s; };
   auto empty_bar = [&](int s) { return bars + 8u * (8 + s); };
   auto acc_full = [&](int i) { return bars + 8u * (16 + i); };
@@ -222,7 +224,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     // All groups work on every tile (tc_epilogue deals the column units out); accumulators alternate per item.
     const int grp = (warp - 2) >> 2;
     TcStage stg;
-    if (g.staged) { stg.smem = sStg + grp * 2 * 4096u; stg.tm = &tmO; stg.bar_id = 1 + grp; }
+    if (g.staged) { stg.smem = sStg + grp * stg_bytes; stg.tm = &tmO; stg.bar_id = 1 + grp; stg.cols = g.stage_cols; }
     for (int n = 0; n < my_items; ++n) {
       int b, t0, ntile; bool live;
       coords(cl_id + n * n_cl, b, t0, ntile, live);
@@ -296,8 +298,10 @@ static bool make_geom(const ConvArgs& a, int op, int ncl, TcGeom* g) {
   // staged 16-bit output: unsplit operand rows only, dense rows, nothing else written or read by the epilogue
   const Epilogue& ep = a.epi;
   g->staged = (!ep.gate && ep.out_op && !ep.out_f32 && !ep.res && !ep.accum && ep.out_op_split == 0 && a.n_split == 0 &&
-               (ep.out_op_ld * 2) % 16 == 0 && ep.out_op_bstride == (long long)a.L * ep.out_op_ld) ? 1 : 0;
-  if (g->staged) st = (int)((200u * 1024u - kTcEpiGroups * 2 * 4096u) / stage);
+               a.NT % 32 == 0 && (ep.out_op_ld * 2) % 16 == 0 && ep.out_op_bstride == (long long)a.L * ep.out_op_ld) ? 1 : 0;
+  // block width: 64 columns when that still gives every epilogue group a block, else 32
+  g->stage_cols = g->staged ? (a.NT % (64 * kTcEpiGroups) == 0 ? 64 : 32) : 0;
+  if (g->staged) st = (int)((200u * 1024u - kTcEpiGroups * (uint32_t)kTileM * g->stage_cols * 2u) / stage);
   if (st > 8) st = 8;
   const int iters2 = 2 * a.k * g->kchunks;
   if (st > iters2) st = iters2;
@@ -375,13 +379,14 @@ cudaError_t launch_conv_tc(const ConvArgs& a_in, int op, const LaunchOpts& lo, c
   if (g.staged) {
     cuuint64_t dims[3] = {(cuuint64_t)a.epi.out_op_ld, (cuuint64_t)a.L, (cuuint64_t)a.B};
     cuuint64_t strides[2] = {(cuuint64_t)a.epi.out_op_ld * 2, (cuuint64_t)a.epi.out_op_bstride * 2};
-    cuuint32_t box[3] = {16, (cuuint32_t)kTileM, 1};
+    cuuint32_t box[3] = {(cuuint32_t)g.stage_cols, (cuuint32_t)kTileM, 1};
     cuuint32_t estr[3] = {1, 1, 1};
-    CUresult r = enc(&tmO, dt, 3, a.epi.out_op, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+    CUresult r = enc(&tmO, dt, 3, a.epi.out_op, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                     g.stage_cols == 64 ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_64B,
                      CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return cudaErrorInvalidValue;
   }
-  const size_t smem = 1024 + (size_t)g.stages * (g.a_bytes + g.b_stride) + (g.staged ? kTcEpiGroups * 2 * 4096 : 0) + 8 * 20 + 16;
+  const size_t smem = 1024 + (size_t)g.stages * (g.a_bytes + g.b_stride) + (size_t)kTcEpiGroups * kTileM * g.stage_cols * 2 + 8 * 20 + 16;
   static PerDeviceOnce smem_optin;             // the opt-in is per device: a second engine on another GPU needs its own
   const cudaError_t attr_err = smem_optin.run([] {
     cudaError_t e[4] = {

@@ -170,11 +170,53 @@ __device__ __forceinline__ void build_tile_prefix(int* prefix, int B, const int*
 // of 32 different rows per warp instruction.  Two blocks per epilogue group, alternating; thread 0 of the group issues
 // the stores (bulk async-groups are per thread) and waits for the block's previous store to have read it.
 struct TcStage {
-  uint32_t smem = 0;               // this group's two 4 KB blocks (0 = direct global stores)
-  const CUtensorMap* tm = nullptr; // (columns, rows, batch) map of the output, box 16 x 128 x 1, no swizzle
+  uint32_t smem = 0;               // this group's staging block: [128 rows][cols] 16-bit, TMA-swizzled (0 = direct global stores)
+  const CUtensorMap* tm = nullptr; // (columns, rows, batch) map of the output, box cols x 128 x 1, SWIZZLE_64B (cols 32) / 128B (cols 64)
   int bar_id = 0;                  // named barrier of the group's 128 threads
-  int unit = 0;                    // units staged so far by this group (selects the block)
+  int cols = 0;                    // columns per staged block: 32 or 64
 };
+
+// One staged block: W output columns of the tile's 128 rows.  Every thread turns its row's W accumulator columns into
+// packed 16-bit values first (TMEM loads, bias, alpha, leaky_relu - everything that does not touch the staging block),
+// then the group waits until the TMA store that last used the block has read it, writes the block (16-byte chunks at
+// the swizzled position the tensor map expects: conflict-free for 8 consecutive rows), and one thread stores it.
+// One fence + two named barriers + one TMA store per W columns; the first version staged 16 columns at a time and its
+// per-unit barriers / store round trips made the narrow upsamplers latency-bound (1.7 k cycles per unit, ncu).
+template <typename OpT, int W>
+__device__ __forceinline__ void tc_stage_block(const Epilogue& ep, const TcStage& stg, const float* bias, uint32_t trow, int col0,
+                                               int row, bool live, bool issuer, bool store_ok, int gcol, int t0, int b) {
+  constexpr int SUB = W / 16;
+  uint32_t raw[SUB][16];
+#pragma unroll
+  for (int s = 0; s < SUB; ++s) ptx::tmem_ld16(trow + col0 + 16 * s, raw[s]);
+  uint32_t pk[W / 2];
+  ptx::tmem_ld_wait();
+#pragma unroll
+  for (int s = 0; s < SUB; ++s) {
+    float bv[16];
+    load16(bias + col0 + 16 * s, bv);
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float x = ep.alpha * (__uint_as_float(raw[s][2 * i]) + bv[2 * i]), y = ep.alpha * (__uint_as_float(raw[s][2 * i + 1]) + bv[2 * i + 1]);
+      x = x >= 0.f ? x : ep.out_slope * x;
+      y = y >= 0.f ? y : ep.out_slope * y;
+      pk[8 * s + i] = live ? Pack16<OpT>::pack2(x, y) : 0u;
+    }
+  }
+  if (issuer) ptx::bulk_wait_read0();              // the store that last used this block has read it
+  asm volatile("bar.sync %0, 128;" ::"r"(stg.bar_id) : "memory");
+  constexpr int RB = W * 2;                        // row bytes: 64 (SWIZZLE_64B) or 128 (SWIZZLE_128B)
+  const int sw = RB == 128 ? (row & 7) : ((row >> 1) & 3);
+#pragma unroll
+  for (int c = 0; c < RB / 16; ++c)
+    st_shared_v4(stg.smem + row * RB + ((c ^ sw) << 4), pk[4 * c], pk[4 * c + 1], pk[4 * c + 2], pk[4 * c + 3]);
+  fence_proxy_async_smem();
+  asm volatile("bar.sync %0, 128;" ::"r"(stg.bar_id) : "memory");
+  if (issuer && store_ok) {                        // rows beyond L are clipped by the map
+    ptx::tma_store_3d(stg.tm, stg.smem, gcol, t0, b);
+    ptx::bulk_commit();
+  }
+}
 
 template <typename OpT, typename WaitFn>
 __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& ep, int b, int t0, int ntile, int valid,
@@ -234,6 +276,18 @@ __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& e
       const bool has_res = in_range && ep.res != nullptr, has_acc = in_range && ep.accum != nullptr;
       const float* res = ep.res + (long long)b * ep.res_bstride + (long long)t * ep.res_ld + n0;
       const float* accum = ep.accum + (long long)b * ep.accum_bstride + (long long)t * ep.accum_ld + n0;
+      if (stg && stg->smem) {
+        // staged output (no residual / accumulate / fp32 copy by construction, make_geom): blocks of stg->cols columns dealt to the groups
+        const bool issuer = q == 0 && lane == 0, store_ok = t0 < a.L;
+        const int nblk = a.NT / stg->cols;
+#pragma unroll 1
+        for (int k = ugrp; k < nblk; k += ngrp) {
+          const int col0 = k * stg->cols;
+          if (stg->cols == 64) tc_stage_block<OpT, 64>(ep, *stg, bias, trow, col0, row, live, issuer, store_ok, (int)n0 + col0, t0, b);
+          else tc_stage_block<OpT, 32>(ep, *stg, bias, trow, col0, row, live, issuer, store_ok, (int)n0 + col0, t0, b);
+        }
+        return;
+      }
 #pragma unroll 1
       for (int u = ugrp; u < nu; u += ngrp) {
         const int c0 = u << 4;
@@ -263,29 +317,7 @@ __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& e
 #pragma unroll
           for (int i = 0; i < 16; ++i) v[i] = 0.f;
         }
-        if (stg && stg->smem) {
-          const uint32_t blk = stg->smem + (stg->unit & 1) * 4096u;
-          const bool issuer = q == 0 && lane == 0;
-          if (issuer) ptx::bulk_wait_read1();            // the store that last used this block has read it
-          asm volatile("bar.sync %0, 128;" ::"r"(stg->bar_id) : "memory");
-          uint32_t pk[8];
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            float x = v[2 * i], y = v[2 * i + 1];
-            x = x >= 0.f ? x : ep.out_slope * x;
-            y = y >= 0.f ? y : ep.out_slope * y;
-            pk[i] = Pack16<OpT>::pack2(x, y);
-          }
-          st_shared_v4(blk + row * 32, pk[0], pk[1], pk[2], pk[3]);
-          st_shared_v4(blk + row * 32 + 16, pk[4], pk[5], pk[6], pk[7]);
-          fence_proxy_async_smem();
-          asm volatile("bar.sync %0, 128;" ::"r"(stg->bar_id) : "memory");
-          if (issuer && t0 < a.L) {                      // rows beyond L are clipped by the map
-            ptx::tma_store_3d(stg->tm, blk, (int)n0 + c0, t0, b);
-            ptx::bulk_commit();
-          }
-          ++stg->unit;
-        } else if (in_range && !TCE_DBG(8)) {
+        if (in_range && !TCE_DBG(8)) {
           if (ep.out_f32)
             store16(ep.out_f32 + (long long)b * ep.out_f32_bstride + (long long)t * ep.out_f32_ld + n0 + c0, v);
           if (ep.out_op)
