@@ -46,6 +46,8 @@ def parse():
     ap.add_argument("--precision", default="fp16", choices=["fp16", "bf16", "fp32"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-side-legs", action="store_true", help="skip the sustained / varying-lengths / C1 / C3 / C4 side records")
+    ap.add_argument("--option", action="append", default=[], metavar="KEY=INT",
+                    help="library option for an A/B run (vitsb_set_option), e.g. --option tc_pair=0; recorded in config.options")
     ap.add_argument("--profile-out", default=None, help="write the per-launch-family table to this file")
     ap.add_argument("--batch-per-gpu", type=int, default=PER_GPU_BATCH,
                     help="utterances per GPU and step (default 16 = BASELINE config C2; 64-512 are C4 sweep points, not the headline)")
@@ -213,7 +215,8 @@ def run_b200(args):
     cfg = HotPathConfig()
     sd = FX.make_state_dict(cfg, seed=1234)
     sd.update(FX.make_p1_state_dict(cfg, seed=4321))       # text encoder + duration predictor, for the end-to-end infer() side leg
-    eng = FlowDecoder(cfg, sd, device=dev, precision=args.precision)
+    lib_options = {kv.split("=", 1)[0]: int(kv.split("=", 1)[1]) for kv in args.option}
+    eng = FlowDecoder(cfg, sd, device=dev, precision=args.precision, options=lib_options or None)
     all_len = global_lengths(world)
     mine = list(range(rank * PER_GPU_BATCH, (rank + 1) * PER_GPU_BATCH))          # identical length set on every rank
     lens = [all_len[i] for i in mine]
@@ -408,7 +411,7 @@ def run_b200(args):
                        "global_batch": PER_GPU_BATCH * world, "valid_audio_s_per_step": audio_all,
                        "parallelism": f"utterance-sharded replicas x{world}, the same 16-length set on every rank, no collective",
                        "l2": "256 MiB flush between timed steps; per-step activation traffic >> 126 MB L2",
-                       "precision": args.precision},
+                       "precision": args.precision, **({"options": lib_options} if lib_options else {})},
             "e2e": {"value": e2e, "unit": "audio-s/s", "h2d_bytes_per_step": int(z_host.numel() * 4 + g_host.numel() * 4 + 4 * B) * world,
                     "d2h_bytes_per_step": int(d2h_bytes) * world, "ms_per_step": ms_e2e / args.steps,
                     "api": "FlowDecoder.host_pipeline(pcm16=True) depth 2: per-step H2D of the latents and D2H of the int16 PCM the serving "

@@ -207,6 +207,10 @@ cond_gemv_regs_kernel(const float* __restrict__ W, const float* __restrict__ bia
         const long long e = ((long long)(s + 4 * (int)gridDim.x) * 2) * gin + threadIdx.x * 32;
         if (threadIdx.x * 32 < 2 * gin && e < (long long)Ncond * gin) asm volatile("prefetch.global.L2 [%0];" ::"l"(W + e));
       }
+      const int comb = (s / (int)gridDim.x) & 3;             // warp that combines this step's K quarters (rotates: balanced)
+      const int n_out = 2 * s + (lane >> 4);
+      float bias_n = 0.f;
+      if (q == comb && n_out < Ncond) bias_n = __ldg(bias + n_out);      // needed after the barrier: in flight under the FMAs
       unsigned long long acc[2][kGvB / 2];
 #pragma unroll
       for (int r = 0; r < 2; ++r)
@@ -242,10 +246,10 @@ cond_gemv_regs_kernel(const float* __restrict__ W, const float* __restrict__ bia
       }
       part[par][q][lane] = v[0];
       __syncthreads();                                         // one barrier per step: `part` is double-buffered by step parity
-      if (q == 0) {
-        const int n = 2 * s + (lane >> 4), b = b0 + (lane & 15);
-        if (n < Ncond && b < B)
-          out[(long long)b * Ncond + n] = ((part[par][0][lane] + part[par][1][lane]) + (part[par][2][lane] + part[par][3][lane])) + bias[n];
+      if (q == comb) {
+        const int b = b0 + (lane & 15);
+        if (n_out < Ncond && b < B)
+          out[(long long)b * Ncond + n_out] = ((part[par][0][lane] + part[par][1][lane]) + (part[par][2][lane] + part[par][3][lane])) + bias_n;
       }
     }
     __syncthreads();

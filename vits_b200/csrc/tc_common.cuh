@@ -134,13 +134,14 @@ __device__ __forceinline__ float gate_fast(float a, float b) {
 // loads + a shuffle scan: a single thread walking len[] paid one dependent global-load latency per few rows in
 // the prologue of every launch.
 __device__ __forceinline__ void build_tile_prefix(int* prefix, int B, const int* len, int len_mul, int L, int tile_rows, int lane,
-                                                  int extra_rows = kHaloRows) {
+                                                  int extra_rows = kHaloRows, int* valid_out = nullptr) {
   int carry = 0;
   for (int b0 = 0; b0 < B; b0 += 32) {
     const int b = b0 + lane;
     int n = 0;
     if (b < B) {
       const int valid = len ? len[b] * len_mul : L;
+      if (valid_out) valid_out[b] = valid;                                // valid rows per batch row, for the epilogues
       const int rows = valid + extra_rows < L ? valid + extra_rows : L;   // rows nobody reads are skipped
       n = (rows + tile_rows - 1) / tile_rows;
     }
@@ -182,10 +183,16 @@ struct TcStage {
 // the swizzled position the tensor map expects: conflict-free for 8 consecutive rows), and one thread stores it.
 // One fence + two named barriers + one TMA store per W columns; the first version staged 16 columns at a time and its
 // per-unit barriers / store round trips made the narrow upsamplers latency-bound (1.7 k cycles per unit, ncu).
-template <typename OpT, int W>
+template <typename OpT, int W, typename WaitFn>
 __device__ __forceinline__ void tc_stage_block(const Epilogue& ep, const TcStage& stg, const float* bias, uint32_t trow, int col0,
-                                               int row, bool live, bool issuer, bool store_ok, int gcol, int t0, int b) {
+                                               int row, bool live, bool issuer, bool store_ok, int gcol, int t0, int b,
+                                               bool first, WaitFn wait_acc) {
   constexpr int SUB = W / 16;
+  // bias values come from global memory (the L1 next to ~200 KB of shared memory is a few KB: an L2 round trip); the
+  // first 16 are requested before the accumulator wait, the next 16 under each sub-unit's math
+  float bv[2][16];
+  load16(bias + col0, bv[0]);
+  if (first) wait_acc();
   uint32_t raw[SUB][16];
 #pragma unroll
   for (int s = 0; s < SUB; ++s) ptx::tmem_ld16(trow + col0 + 16 * s, raw[s]);
@@ -193,11 +200,10 @@ __device__ __forceinline__ void tc_stage_block(const Epilogue& ep, const TcStage
   ptx::tmem_ld_wait();
 #pragma unroll
   for (int s = 0; s < SUB; ++s) {
-    float bv[16];
-    load16(bias + col0 + 16 * s, bv);
+    if (s + 1 < SUB) load16(bias + col0 + 16 * (s + 1), bv[(s + 1) & 1]);
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
-      float x = ep.alpha * (__uint_as_float(raw[s][2 * i]) + bv[2 * i]), y = ep.alpha * (__uint_as_float(raw[s][2 * i + 1]) + bv[2 * i + 1]);
+      float x = ep.alpha * (__uint_as_float(raw[s][2 * i]) + bv[s & 1][2 * i]), y = ep.alpha * (__uint_as_float(raw[s][2 * i + 1]) + bv[s & 1][2 * i + 1]);
       x = x >= 0.f ? x : ep.out_slope * x;
       y = y >= 0.f ? y : ep.out_slope * y;
       pk[8 * s + i] = live ? Pack16<OpT>::pack2(x, y) : 0u;
@@ -233,6 +239,21 @@ __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& e
     const bool live = t < valid;
     const uint32_t trow = tmem_acc + (static_cast<uint32_t>(q * 32) << 16);
     const float* bias = ep.bias + (long long)b * ep.bias_bstride + (long long)ntile * a.NT;
+    if (stg && stg->smem) {
+      // staged output (no gate / residual / accumulate / fp32 copy by construction, make_geom): blocks of stg->cols columns
+      // dealt to the groups; the accumulator wait sits inside the first block, after its first bias request
+      const bool issuer = q == 0 && lane == 0, store_ok = t0 < a.L;
+      const int nblk = a.NT / stg->cols, n0 = ntile * a.NT;
+      if (ugrp >= nblk) { wait_acc(); return; }
+      bool first = true;
+#pragma unroll 1
+      for (int k = ugrp; k < nblk; k += ngrp, first = false) {
+        const int col0 = k * stg->cols;
+        if (stg->cols == 64) tc_stage_block<OpT, 64>(ep, *stg, bias, trow, col0, row, live, issuer, store_ok, n0 + col0, t0, b, first, wait_acc);
+        else tc_stage_block<OpT, 32>(ep, *stg, bias, trow, col0, row, live, issuer, store_ok, n0 + col0, t0, b, first, wait_acc);
+      }
+      return;
+    }
     wait_acc();
     if (ep.gate) {
       // packed columns: groups of GG = [tanh GG/2 | sigmoid GG/2]; output channel = packed gate index.
@@ -276,18 +297,6 @@ __device__ __forceinline__ void tc_epilogue(const ConvArgs& a, const Epilogue& e
       const bool has_res = in_range && ep.res != nullptr, has_acc = in_range && ep.accum != nullptr;
       const float* res = ep.res + (long long)b * ep.res_bstride + (long long)t * ep.res_ld + n0;
       const float* accum = ep.accum + (long long)b * ep.accum_bstride + (long long)t * ep.accum_ld + n0;
-      if (stg && stg->smem) {
-        // staged output (no residual / accumulate / fp32 copy by construction, make_geom): blocks of stg->cols columns dealt to the groups
-        const bool issuer = q == 0 && lane == 0, store_ok = t0 < a.L;
-        const int nblk = a.NT / stg->cols;
-#pragma unroll 1
-        for (int k = ugrp; k < nblk; k += ngrp) {
-          const int col0 = k * stg->cols;
-          if (stg->cols == 64) tc_stage_block<OpT, 64>(ep, *stg, bias, trow, col0, row, live, issuer, store_ok, (int)n0 + col0, t0, b);
-          else tc_stage_block<OpT, 32>(ep, *stg, bias, trow, col0, row, live, issuer, store_ok, (int)n0 + col0, t0, b);
-        }
-        return;
-      }
 #pragma unroll 1
       for (int u = ugrp; u < nu; u += ngrp) {
         const int c0 = u << 4;
