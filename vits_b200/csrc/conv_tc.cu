@@ -47,6 +47,7 @@ struct TcGeom {
   int dbg;           // VITSB_TC_DBG timing-experiment mask (only with -DVITSB_RB_DEBUG; results are wrong when set)
   int staged;        // 16-bit output rows leave through shared-memory blocks + TMA stores (tc_common.cuh TcStage)
   int stage_cols;    // columns per staged block (32 or 64); one block per epilogue group
+  int epi_alt;       // 1: an N tile is a single staged block, the epilogue groups take alternate tiles (group = accumulator index)
   long long* trace;  // debug build: clock64 timeline of CTA 0 (VITSB_TC_TRACE), normally null
   int trace_t0;      // first traced item of the CTA's sequence
 };
@@ -100,7 +101,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     ptx::prefetch_tmap(&tmA);
     ptx::prefetch_tmap(&tmB);
     for (int s = 0; s < 8; ++s) { ptx::mbar_init(full_bar(s), 1); ptx::mbar_init(empty_bar(s), 1); }
-    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full(i), 1); ptx::mbar_init(acc_empty(i), 4 * kTcEpiGroups * ncl); }
+    for (int i = 0; i < 2; ++i) { ptx::mbar_init(acc_full(i), 1); ptx::mbar_init(acc_empty(i), 4 * (g.epi_alt ? 1 : kTcEpiGroups) * ncl); }
     ptx::mbar_fence_init();
   }
   if (warp == 1) { if (TWO) ptx::tmem_alloc_2sm(ptx::smem_u32(&s_tmem), g.tmem_cols); else ptx::tmem_alloc(ptx::smem_u32(&s_tmem), g.tmem_cols); }
@@ -288,11 +289,15 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else {
     // ===== epilogue groups: TMEM -> registers -> fused math -> global =====
     // All groups work on every tile (tc_epilogue deals the column units out); accumulators alternate per item.
+    // epi_alt (an N tile of one staged block, i.e. NT <= 64): group i owns accumulator i and takes every second tile,
+    // so a tile's fixed costs (accumulator wait, fence, two named barriers, store issue) are paid by one group only.
     const int grp = (warp - 3) >> 2;
+    const bool alt = g.epi_alt != 0;
     TcStage stg;
     if (g.staged) { stg.smem = sStg + grp * stg_bytes; stg.tm = &tmO; stg.bar_id = 1 + grp; stg.cols = g.stage_cols; }
     ItemIter iti = item_iter(cl_id);
     for (int n = 0; n < my_items; ++n, iti.next()) {
+      if (alt && (n & 1) != grp) continue;
       int b, t0, ntile; bool live;
       if (warp == 4) trace(5, n, 0);
       coords(iti, b, t0, ntile, live);
@@ -305,7 +310,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
       };
       if (live && !TC_DBG(4)) {
         const int nsplit_tile = a.n_split > 0 ? a.n_split / a.NT : nNT;
-        if (ntile < nsplit_tile) tc_epilogue<OpT>(a, a.epi, b, t0, ntile, valid, tmem_base + buf * a.NT, warp & 3, lane, grp, kTcEpiGroups, wait_acc, g.dbg, &stg);
+        if (ntile < nsplit_tile) tc_epilogue<OpT>(a, a.epi, b, t0, ntile, valid, tmem_base + buf * a.NT, warp & 3, lane, alt ? 0 : grp, alt ? 1 : kTcEpiGroups, wait_acc, g.dbg, &stg);
         else tc_epilogue<OpT>(a, a.epi_b, b, t0, ntile - nsplit_tile, valid, tmem_base + buf * a.NT, warp & 3, lane, grp, kTcEpiGroups, wait_acc, g.dbg);
       } else {
         wait_acc();
@@ -369,7 +374,8 @@ static bool make_geom(const ConvArgs& a, int op, int ncl, TcGeom* g) {
   g->staged = (!ep.gate && ep.out_op && !ep.out_f32 && !ep.res && !ep.accum && ep.out_op_split == 0 && a.n_split == 0 &&
                a.NT % 32 == 0 && (ep.out_op_ld * 2) % 16 == 0 && ep.out_op_bstride == (long long)a.L * ep.out_op_ld) ? 1 : 0;
   // block width: 64 columns when that still gives every epilogue group a block, else 32
-  g->stage_cols = g->staged ? (a.NT % (64 * kTcEpiGroups) == 0 ? 64 : 32) : 0;
+  g->epi_alt = (g->staged && (a.NT == 64 || a.NT == 32)) ? 1 : 0;
+  g->stage_cols = g->staged ? ((g->epi_alt ? a.NT == 64 : a.NT % (64 * kTcEpiGroups) == 0) ? 64 : 32) : 0;
   // One persistent CTA per SM.  A ring slot holds `grp` (tap, channel-block) boxes and costs one full / empty barrier
   // round trip: a tile with few k-blocks (the narrow upsamplers: 3 or 6) is otherwise bound by those round trips
   // (timeline: ~700 cycles per box against ~320 of MMA issue).  grp = the largest count <= 4 that divides a tile's
@@ -383,7 +389,9 @@ static bool make_geom(const ConvArgs& a, int op, int ncl, TcGeom* g) {
   int grp = 1;
   if (it_full <= 8)                      // long K loops keep one box per slot: finer-grained overlap matters more there
     for (int c = 2; c <= 4; ++c)
-      if ((!has_full || it_full % c == 0) && (!has_skip || it_skip % c == 0) && (uint32_t)c * box * 3u <= budget) grp = c;
+      if ((!has_full || it_full % c == 0) && (!has_skip || it_skip % c == 0) &&
+          (uint32_t)c * box * (c == it_full ? 2u : 3u) <= budget)       // three slots, or two when a slot is a whole tile
+        grp = c;
   g->grp = grp;
   int st = (int)(budget / (box * grp));
   if (st > 8) st = 8;
