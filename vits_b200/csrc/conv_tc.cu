@@ -47,7 +47,7 @@ struct TcGeom {
   int dbg;           // VITSB_TC_DBG timing-experiment mask (only with -DVITSB_RB_DEBUG; results are wrong when set)
   int staged;        // 16-bit output rows leave through shared-memory blocks + TMA stores (tc_common.cuh TcStage)
   int stage_cols;    // columns per staged block (32 or 64); one block per epilogue group
-  int epi_alt;       // 1: an N tile is a single staged block, the epilogue groups take alternate tiles (group = accumulator index)
+  int epi_alt;       // 1: an N tile is one or two staged blocks, the epilogue groups take alternate tiles (group = accumulator index)
   long long* trace;  // debug build: clock64 timeline of CTA 0 (VITSB_TC_TRACE), normally null
   int trace_t0;      // first traced item of the CTA's sequence
 };
@@ -289,7 +289,7 @@ conv_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
   } else {
     // ===== epilogue groups: TMEM -> registers -> fused math -> global =====
     // All groups work on every tile (tc_epilogue deals the column units out); accumulators alternate per item.
-    // epi_alt (an N tile of one staged block, i.e. NT <= 64): group i owns accumulator i and takes every second tile,
+    // epi_alt (an N tile of one or two staged blocks, i.e. NT <= 128): group i owns accumulator i and takes every second tile,
     // so a tile's fixed costs (accumulator wait, fence, two named barriers, store issue) are paid by one group only.
     const int grp = (warp - 3) >> 2;
     const bool alt = g.epi_alt != 0;
@@ -374,8 +374,8 @@ static bool make_geom(const ConvArgs& a, int op, int ncl, TcGeom* g) {
   g->staged = (!ep.gate && ep.out_op && !ep.out_f32 && !ep.res && !ep.accum && ep.out_op_split == 0 && a.n_split == 0 &&
                a.NT % 32 == 0 && (ep.out_op_ld * 2) % 16 == 0 && ep.out_op_bstride == (long long)a.L * ep.out_op_ld) ? 1 : 0;
   // block width: 64 columns when that still gives every epilogue group a block, else 32
-  g->epi_alt = (g->staged && (a.NT == 64 || a.NT == 32)) ? 1 : 0;
-  g->stage_cols = g->staged ? ((g->epi_alt ? a.NT == 64 : a.NT % (64 * kTcEpiGroups) == 0) ? 64 : 32) : 0;
+  g->epi_alt = (g->staged && a.NT <= 128) ? 1 : 0;
+  g->stage_cols = g->staged ? ((g->epi_alt ? a.NT % 64 == 0 : a.NT % (64 * kTcEpiGroups) == 0) ? 64 : 32) : 0;
   // One persistent CTA per SM.  A ring slot holds `grp` (tap, channel-block) boxes and costs one full / empty barrier
   // round trip: a tile with few k-blocks (the narrow upsamplers: 3 or 6) is otherwise bound by those round trips
   // (timeline: ~700 cycles per box against ~320 of MMA issue).  grp = the largest count <= 4 that divides a tile's
