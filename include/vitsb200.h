@@ -231,7 +231,9 @@ const char* vitsb_build_info(void);
 
 /* Bring-up self-test of one implicit-GEMM conv tile configuration on the
  * tcgen05 path against the CUDA-core fp32 path (tests/test_conv_unit.py).
- * Returns max-abs difference in *max_err. */
+ * Returns max-abs difference in *max_err.  gate: 0 = plain conv with residual and fp32 + 16-bit outputs, 1 = gated,
+ * 2 = 16-bit output only (the staged TMA-store epilogue; *max_err compares 16-bit values, so one ulp of the operand
+ * type at the output scale is expected where the fp32 sums straddle a rounding boundary). */
 int vitsb_selftest_conv(int device, int precision, int Cin, int N, int k, int dil, int L, int B,
                         int gate, uint32_t seed, double* max_err, double* ref_scale);
 
