@@ -151,7 +151,9 @@ int vitsb_synthesize(vitsb_handle* h, const float* z_p, const float* g, const in
 /* vitsb_synthesize with the serving path's output post-processing fused into the last kernel:
  * pcm = int16(clip(wav * volume * 32767, -32768, 32767)), float32 products, truncation toward zero, exactly
  * VITSWrap.speaking's np.clip(...).astype(np.int16) (vits_wrap.py:195) on infer.py:182's float waveform.
- *   pcm : device int16 [B, 1, T_max*prod(upsample_rates)], zero beyond len[b] when ragged. */
+ *   pcm : int16 [B, 1, T_max*prod(upsample_rates)], zero beyond len[b] when ragged.  Device memory, or page-locked host
+ *         memory (device-accessible under unified addressing): the last kernel then writes the samples over PCIe and the
+ *         caller needs no device buffer and no copy.  The same holds for `wav` of vitsb_synthesize / vitsb_decode. */
 int vitsb_synthesize_pcm16(vitsb_handle* h, const float* z_p, const float* g, const int32_t* len,
                            int B, int T_max, int ragged, float volume, int16_t* pcm,
                            void* ws, size_t ws_bytes, vitsb_stream stream);

@@ -483,6 +483,26 @@ def test_pcm16_output_matches_reference_postprocessing(base_cfg, base_sd, prec):
     assert np.abs(pcm).max() == 32767
 
 
+def test_pcm16_written_straight_into_pinned_host_memory(base_cfg, base_sd):
+    """SURVEY 8(f) N2, "write to pinned host memory": the output pointer of the C ABI may be page-locked host memory
+    (device-accessible under unified addressing); the last kernel then stores the int16 samples over PCIe itself and the
+    request needs no device buffer and no separate D2H copy.  Same samples as the device-buffer call."""
+    eng = engine(base_cfg, base_sd, "fp16")
+    lens = [50, 21, 64]
+    lat = FX.make_latents(base_cfg, lens, seed=909)
+    zp, g = lat["z_p"].cuda(), lat["g"].cuda()
+    ref = eng.synthesize_pcm16(zp, g, lens, volume=0.7).cpu()
+    host = torch.zeros(ref.shape, dtype=torch.int16).pin_memory()
+    out = eng.synthesize_pcm16(zp, g, lens, volume=0.7, out=host)
+    torch.cuda.synchronize()
+    assert out.data_ptr() == host.data_ptr() and not host.is_cuda
+    assert torch.equal(host, ref)
+    wav_host = torch.zeros(ref.shape, dtype=torch.float32).pin_memory()
+    eng.synthesize(zp, g, lens, out=wav_host)
+    torch.cuda.synchronize()
+    assert torch.equal(wav_host, eng.synthesize(zp, g, lens).cpu())
+
+
 def test_synthesize_segments_equals_sequential_calls(base_cfg, base_sd):
     """the serving loop's sequential per-segment calls (vits_wrap.py:177-183) as ragged batches -
     same waveforms bit for bit, original order, whatever the batch split."""
