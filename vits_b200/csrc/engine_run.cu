@@ -260,6 +260,11 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
     if (len && (phases & PH_FRONT)) cx.err = cudaMemcpyAsync(d_len, len, sizeof(int) * B, cudaMemcpyHostToDevice, stream);
   }
   cx.skip = !(phases & PH_FRONT);
+  const bool front_fork = opt_branch_streams && !profile && !dry && !cx.skip && side_streams_ready();
+  if (front_fork && cx.ok()) {
+    cx.err = cudaEventRecord(ev_fork, stream);               // after everything earlier on the caller's stream (the workspace is reused)
+    if (cx.ok()) cx.err = cudaStreamWaitEvent(side_stream[0], ev_fork, 0);
+  }
   if (dev_len) {
     // durations -> y_len, cumulative durations; gather m_p + noise * s_p straight into the time-major state   infer.py:169-176, models.py:570-572
     const DurFront& d = *c.dur;
@@ -271,7 +276,15 @@ int Engine::issue(int phases, const Call& c, bool dry, int* launches) {
   } else
   // seam: channel-major fp32 -> time-major (masked beyond len)
   AUX_LAUNCH(T_PACK, launch_pack_time_major(c.z_in, B, IC, T, cx.len_flow, (what & RUN_FLOW) ? F(W.zf) : nullptr, P(W.zop), op, split16 ? 1 : 0, stream));
-  // all conditioning Linears of the call: flow cond_layers (modules.py:161) + ResBlock conds (modules.py:254)
+  // all conditioning Linears of the call: flow cond_layers (modules.py:161) + ResBlock conds (modules.py:254).  The GEMV reads
+  // only g, the seam kernel above only the latents: with the handle's side streams available the two run concurrently
+  // (fork before the seam kernel, join before the first coupling layer).
+  if (front_fork && cx.ok()) {
+    cudaStream_t gs = side_stream[0];
+    AUX_LAUNCH(T_COND, launch_cond_gemv(d_condW, d_condB, c.g, B, Ncond, cfg.gin_channels, F(W.cond), gs));
+    if (cx.ok()) cx.err = cudaEventRecord(ev_join[0], gs);
+    if (cx.ok()) cx.err = cudaStreamWaitEvent(stream, ev_join[0], 0);
+  } else
   AUX_LAUNCH(T_COND, launch_cond_gemv(d_condW, d_condB, c.g, B, Ncond, cfg.gin_channels, F(W.cond), stream));
 
   cx.skip = !(phases & PH_MID);

@@ -200,25 +200,41 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
   };
   const int total_tiles = s_tile_prefix[a.B];
   const int total_units = (total_tiles + G::NCL - 1) / G::NCL;      // pair mode: tiles 2u and 2u+1 (the last may be missing)
+  // Tile schedule: every CTA (or pair) takes a CONTIGUOUS run of units.  With a round-robin schedule consecutive tiles of a
+  // CTA are n_units apart while a batch row has 64-640 tiles at the C2 sizes, so the batch row changed on every second
+  // tile or so - and with it the conditioning vector of the gate epilogue (two group barriers around an exposed global
+  // load: the 1.5-1.9 k cycle set-up gap per tile in the debug timeline, 36 % of the tiles) and the cached length.
+#ifndef VITSB_RB_ROUND_ROBIN
+  const int units_q = total_units / n_units, units_r = total_units - units_q * n_units;
+  const int unit_base = unit_id * units_q + (unit_id < units_r ? unit_id : units_r), unit_step = 1;
+  const int my_tiles = RB_DBG(256) ? 0 : units_q + (unit_id < units_r ? 1 : 0);
+#else
+  const int unit_base = unit_id, unit_step = n_units;
   const int my_tiles = RB_DBG(256) ? 0 : (total_units > unit_id ? (total_units - 1 - unit_id) / n_units + 1 : 0);
+#endif
   constexpr uint32_t acc1_col = 0, acc2_col = G::NBUF * C;       // TMEM columns: [acc1 x NBUF][acc2 x NBUF]
 
-  // static round-robin schedule; b only grows along a CTA's tile sequence
+  // static schedule; b only grows along a CTA's tile sequence
   // epilogue group of this warp (warps 4-11: group 0, warps 12-19: group 1) and its tile stride
   const int grp = warp >= 4 ? (warp - 4) >> 3 : 0;
   const bool is_epi = warp >= 4;
   const int tstep = is_epi ? G::TSTEP : 1;
   const int n_first = is_epi && !G::COOP ? grp : 0;          // first tile (of this CTA's sequence) the warp works on
-  int cur_unit = unit_id + n_first * n_units, cur_b = 0, cur_tile = 0;
+  int cur_unit = unit_base + n_first * unit_step, cur_b = 0, cur_tile = 0;
+  // Tile range [cur_lo, cur_hi) of batch row cur_b, kept in registers: under the epilogues' and the tensor core's
+  // shared-memory traffic a dependent LDS takes ~500 cycles (debug timeline, phases 8-9), and the table walk plus the
+  // t0 lookup were two of them in series at the top of every tile of every role.  Now the table is read only when a
+  // CTA's tile sequence crosses into another batch row.
+  int cur_lo = s_tile_prefix[0], cur_hi = s_tile_prefix[1];
   bool cur_dead = false;                          // pair mode, odd tile count: rank 1 of the last pair runs the protocol on zeros
   auto tile_seek = [&]() {
     const int t = G::PAIR ? cur_unit * 2 + rank : cur_unit;
     cur_dead = t >= total_tiles;
     cur_tile = cur_dead ? total_tiles - 1 : t;
-    while (s_tile_prefix[cur_b + 1] <= cur_tile) ++cur_b;
+    while (cur_hi <= cur_tile) { ++cur_b; cur_lo = cur_hi; cur_hi = s_tile_prefix[cur_b + 1]; }
   };
-  auto tile_t0 = [&]() { return cur_dead ? a.L + 4096 : (cur_tile - s_tile_prefix[cur_b]) * G::T_OUT; };   // dead: every row out of range
-  auto tile_next = [&]() { cur_unit += tstep * n_units; };
+  auto tile_t0 = [&]() { return cur_dead ? a.L + 4096 : (cur_tile - cur_lo) * G::T_OUT; };   // dead: every row out of range
+  auto tile_next = [&]() { cur_unit += tstep * unit_step; };
 
   if (warp == 0) {
     // =================== activation-slab TMA producer ===================
@@ -408,15 +424,26 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     // flushes it); global / L1 for small C, where the smem bandwidth belongs to the MMA operands (N <= 64 is smem-bound)
     constexpr bool kBiasSmem = C >= kBiasSmemMinC;
     const uint32_t sb1 = ptx::smem_u32(&s_bias1[grp][0]);
-    int bias_b = -1;                             // batch row whose cond/bias vector is staged in s_bias1[grp]
+    int bias_b = -1;                             // batch row whose cond/bias vector is staged in s_bias1[grp] (or held in pa / pb)
+    // small C: the whole cond/bias row lives in registers (32 for C = 32), loaded when the batch row changes
+    constexpr bool kBiasRegs = !kBiasSmem && G::C2 <= 32;
+    float pa[kBiasRegs ? G::C2 : 1], pb[kBiasRegs ? G::C2 : 1];
+    int len_b = -1, valid = a.L;                 // valid rows of batch row len_b (one global load per batch row, not per tile)
     constexpr int NCH_G = G::COOP ? NCH / G::NGRP : NCH;      // chunks of a row this group handles
     const int ch0 = G::COOP ? grp * NCH_G : 0;
     static_assert(!G::COOP || NCH % G::NGRP == 0, "column split");
     for (int n = n_first; n < my_tiles; n += G::TSTEP, tile_next()) {
       const Cursor gb{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
+      // debug timeline: phases 8-11 = the hand-over from the traced tile to this group's next one (top of loop, set-up done,
+      // accumulator full, G buffer free)
+      auto gtrace = [&](int phase) {
+        if (RB_TRACE_ON && (warp & 7) == 4 && n == rt.trace_t0 + 4 + n_first + G::TSTEP && a.trace && blockIdx.x == 0 && lane == 0)
+          a.trace[(5 * 16 + phase) * 2 + grp] = clock64();
+      };
+      gtrace(8);
       tile_seek();
       const int b = cur_b, t0 = tile_t0();
-      const int valid = a.len ? a.len[b] * a.len_mul : a.L;
+      if (a.len && b != len_b) { valid = a.len[b] * a.len_mul; len_b = b; }
       const int t = t0 - G::P2 + r;
       const bool live = t >= 0 && t < valid;     // G outside the sequence is the conv's zero padding
       const float* gbias = a.bias1 + (long long)b * a.bias1_bstride;
@@ -427,10 +454,8 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         asm volatile("bar.sync %0, 128;" ::"r"(1 + grp) : "memory");
         bias_b = b;
       }
-      // small C: the whole cond/bias row is loaded before the accumulator wait (its latency hides behind c1)
-      constexpr bool kBiasRegs = !kBiasSmem && G::C2 <= 32;
-      float pa[kBiasRegs ? G::C2 : 1], pb[kBiasRegs ? G::C2 : 1];
-      if (kBiasRegs) {
+      if (kBiasRegs && b != bias_b) {            // the row stays in registers until the batch row changes
+        bias_b = b;
 #pragma unroll
         for (int i = 0; i < G::C2; i += 4) {
           const float4 x = *reinterpret_cast<const float4*>(gbias + i), y = *reinterpret_cast<const float4*>(gbias + G::C2 + i);
@@ -439,8 +464,33 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         }
       }
       const int s = gb.idx;
+      // bias / conditioning values of a 16-gate chunk: requested BEFORE the accumulator wait for the first chunk and right
+      // after the previous chunk's math for the others - under this kernel's shared-memory load a dependent LDS takes
+      // ~500 cycles (debug timeline), which used to sit between the accumulator becoming full and the first TMEM load.
+      float ba[16], bb[16];
+      auto load_bias = [&](int c0) {
+        if (!RB_DBG(2048)) {
+          if (kBiasSmem) {
+            lds16(sb1 + 4 * c0, ba);
+            lds16(sb1 + 4 * (G::C2 + c0), bb);
+          } else if (kBiasRegs) {
+#pragma unroll
+            for (int i = 0; i < 16; ++i) { ba[i] = pa[kBiasRegs ? c0 + i : 0]; bb[i] = pb[kBiasRegs ? c0 + i : 0]; }
+          } else {
+            load16(gbias + c0, ba);
+            load16(gbias + G::C2 + c0, bb);
+          }
+        } else {
+#pragma unroll
+          for (int i = 0; i < 16; ++i) ba[i] = bb[i] = 0.f;
+        }
+      };
+      load_bias(16 * ch0);
+      gtrace(9);
       ptx::mbar_wait(acc1_full(s), gb.phase);
+      gtrace(10);
       ptx::mbar_wait(g_empty(s), gb.phase ^ 1u);
+      gtrace(11);
       ptx::tc_fence_after();
       if ((warp & 3) == 0) trace(3, n, 0);
       // per-phase timestamps of warps 4 and 12 (quarter 0 of each gate group) on tile 4 (role 5: slot = phase, kind = group)
@@ -454,22 +504,6 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 #pragma unroll
       for (int cc = 0; cc < NCH_G; ++cc) {
         const int c0 = 16 * (ch0 + cc);
-        float ba[16], bb[16];
-        if (!RB_DBG(2048)) {
-          if (kBiasSmem) {
-            lds16(sb1 + 4 * c0, ba);             // issued before the TMEM loads so both latencies overlap
-            lds16(sb1 + 4 * (G::C2 + c0), bb);
-          } else if (kBiasRegs) {
-#pragma unroll
-            for (int i = 0; i < 16; ++i) { ba[i] = pa[kBiasRegs ? c0 + i : 0]; bb[i] = pb[kBiasRegs ? c0 + i : 0]; }
-          } else {
-            load16(gbias + c0, ba);
-            load16(gbias + G::C2 + c0, bb);
-          }
-        } else {
-#pragma unroll
-          for (int i = 0; i < 16; ++i) ba[i] = bb[i] = 0.f;
-        }
         uint32_t ra[16], rb[16];
         if (!RB_DBG(1024)) {
           ptx::tmem_ld16(trow + c0, ra);
@@ -488,6 +522,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           const float v1 = gate_fast(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1]);
           p[i] = live ? Pack16<OpT>::pack2(v0, v1) : 0u;
         }
+        if (cc + 1 < NCH_G) load_bias(c0 + 16);
         // channel c0..c0+15 of row r -> block cb2, two 16-byte chunks, swizzled like a TMA write would
         const int cb2 = c0 / G::BK2, cin = c0 - cb2 * G::BK2;
         const uint32_t rowaddr = grow + cb2 * G::G_BYTES + cin * 2;
@@ -525,6 +560,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     const int ch0 = G::COOP ? grp * NCH_S : 0;
     constexpr int PF = NCH_S < 4 ? NCH_S : 4;    // residual chunks kept in flight (2 x uint4 each; 96-register cap with 20 warps)
     Cursor sl{0, 0};
+    int len_b = -1, valid = a.L;                 // valid rows of batch row len_b (one global load per batch row, not per tile)
     if (!G::COOP) for (int i = 0; i < grp; ++i) sl.next(nSlab);
     // output staging (kStage): row r of this group's block, written in place of a TMA-load image; thread 0 of the
     // group issues the stores and is the one that waits for them (bulk async-groups are per thread)
@@ -545,12 +581,15 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     // row pointer of this thread in tile nn of the CTA's sequence (nullptr: no such tile / row outside the tensor)
     auto res_row = [&](int nn) -> const uint4* {
       if (nn >= my_tiles) return nullptr;
-      const int unit = unit_id + nn * n_units;
+      const int unit = unit_base + nn * unit_step;
       const int tt = G::PAIR ? unit * 2 + rank : unit;
       if (tt >= total_tiles) return nullptr;
-      int bb = cur_b;
-      while (s_tile_prefix[bb + 1] <= tt) ++bb;
-      const int tn = (tt - s_tile_prefix[bb]) * G::T_OUT + r;
+      int bb = cur_b, lo = cur_lo;
+      if (tt >= cur_hi) {                           // the next tile is in a later batch row: walk the table (rare)
+        while (s_tile_prefix[bb + 1] <= tt) ++bb;
+        lo = s_tile_prefix[bb];
+      }
+      const int tn = (tt - lo) * G::T_OUT + r;
       if (r >= G::T_OUT || tn >= a.L) return nullptr;
       return reinterpret_cast<const uint4*>(reinterpret_cast<const OpT*>(a.y_res) + ((long long)bb * a.L + tn) * C);
     };
@@ -567,7 +606,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       const Cursor ab{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
       tile_seek();
       const int b = cur_b, t0 = tile_t0();
-      const int valid = a.len ? a.len[b] * a.len_mul : a.L;
+      if (a.len && b != len_b) { valid = a.len[b] * a.len_mul; len_b = b; }
       const int t = t0 + r;
       const bool in_range = r < G::T_OUT && t < a.L;
       const bool live = t < valid;
@@ -590,6 +629,11 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 #pragma unroll
         for (int c = 0; c < PF; ++c) load_y(ch0 + c, yq[c]);
       }
+      // conv2 bias of a chunk: requested before the accumulator wait (first chunk) / after the previous chunk's math
+      float bv[16];
+      auto load_bias2 = [&](int c0) { if (C >= kBiasSmemMinC) lds16(sb2 + 4 * c0, bv); else load16(a.bias2 + c0, bv); };
+      constexpr bool kAhead2 = C < 256;          // C = 256: 4 residual chunks in flight leave no registers for it (spills)
+      if (kAhead2) load_bias2(16 * ch0);
       ptx::mbar_wait(acc2_full(s), ab.phase);
       ptx::tc_fence_after();
       if ((warp & 3) == 0) trace(4, n, 0);
@@ -597,8 +641,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 #pragma unroll
       for (int cc = 0; cc < NCH_S; ++cc) {
         const int c = ch0 + cc, c0 = 16 * c;
-        float bv[16];
-        if (C >= kBiasSmemMinC) lds16(sb2 + 4 * c0, bv); else load16(a.bias2 + c0, bv);
+        if (!kAhead2) load_bias2(c0);
         uint32_t ra[16];
         if (!RB_DBG(32)) { ptx::tmem_ld16(trow + c0, ra); ptx::tmem_ld_wait(); }
         else {
@@ -617,6 +660,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           v[2 * i] = (__uint_as_float(ra[2 * i]) + bv[2 * i]) + fminf(y.x, 10.f * y.x);
           v[2 * i + 1] = (__uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1]) + fminf(y.y, 10.f * y.y);
         }
+        if (kAhead2 && cc + 1 < NCH_S) load_bias2(c0 + 16);
         if (kStage) {
           if (cc % CH_BLK == 0) {                // block buffer reuse: the previous store must have read it
             if (issuer) ptx::bulk_wait_read0();
