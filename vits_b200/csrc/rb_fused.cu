@@ -57,10 +57,25 @@ namespace vitsb {
 #define RB_TRACE_ON 0
 #endif
 
+// Biases / conditioning vectors: shared memory from C = 128 up, global / L1 below.  With contiguous tile runs per CTA the
+// batch row - hence the L1 lines - stays the same for tens of tiles, and for C <= 64 every LDS competes with the N <= 64
+// MMAs' operand reads for the shared-memory pipe (ncu, per launch: C = 64 k = 3 / 7 / 11 59.6 / 77.0 / 107.4 -> 57.1 / 70.2 /
+// 100.9 us when its biases moved from shared memory to global; C = 128 loses 3-4 % there).
 #ifndef VITSB_BIAS_SMEM_MINC
-#define VITSB_BIAS_SMEM_MINC 64
+#define VITSB_BIAS_SMEM_MINC 128
 #endif
 constexpr int kBiasSmemMinC = VITSB_BIAS_SMEM_MINC;      // channel count from which the epilogues read biases from shared memory
+#ifndef VITSB_RB_EARLY_MAXC
+#define VITSB_RB_EARLY_MAXC 256
+#endif
+constexpr int kEarlyMaxC = VITSB_RB_EARLY_MAXC;           // epilogues hand an accumulator back as soon as its last chunk is in registers (0: at the end of the tile)
+// Requesting a chunk's bias / conditioning values one chunk ahead (the first chunk's before the accumulator wait) was
+// measured and is off: the values stay live across the wait and the kernels got 1-10 % slower (C = 32 / k = 3: 49.3 -> 55 us).
+#ifdef VITSB_RB_BIAS_AHEAD
+constexpr bool kBiasAhead = true;
+#else
+constexpr bool kBiasAhead = false;
+#endif
 constexpr int kRbMaxB = kMaxBatchRows;
 constexpr uint32_t kRbSmemBudget = 220 * 1024;
 constexpr int kRbMaxSlab = 16, kRbBars = 97;
@@ -88,7 +103,10 @@ struct RbT {
   static constexpr int NBUF = C <= 32 ? VITSB_RB_NBUF32 : (C <= 64 ? 4 : (C <= 128 ? 2 : 1));   // G tiles / TMEM accumulator sets
   static constexpr uint32_t G_SET = nCB2 * G_BYTES;
   static constexpr bool STATIONARY = C <= 64;                                     // W_ALL <= 135 KB: resident weights, two issuers
-  static constexpr bool RES_GLOBAL = C >= 64;                                     // residual rows re-read from global (L2)
+#ifndef VITSB_RB_RES_GLOBAL_MINC
+#define VITSB_RB_RES_GLOBAL_MINC 64
+#endif
+  static constexpr bool RES_GLOBAL = C >= VITSB_RB_RES_GLOBAL_MINC;                                     // residual rows re-read from global (L2)
   static constexpr uint32_t TMEM_COLS = 2 * NBUF * C <= 256 ? 256 : 512;
   // epilogue warp groups: with >= 2 accumulator sets, two groups of (4 gate + 4 store) warps take alternate
   // tiles - the epilogues are latency / issue bound (one warp per scheduler reaches IPC ~0.3), not MUFU bound
@@ -132,6 +150,7 @@ __global__ void __launch_bounds__((RbT<C, KT>::THREADS), 1)
 rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmW1,
                 const __grid_constant__ CUtensorMap tmW2, const RbArgs a, const RbRt rt) {
   using G = RbT<C, KT>;
+  constexpr bool kEarly = C <= kEarlyMaxC;
   extern __shared__ uint8_t smem_raw[];
   __shared__ int s_tile_prefix[kRbMaxB + 1];
   __shared__ uint32_t s_tmem;
@@ -485,7 +504,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           for (int i = 0; i < 16; ++i) ba[i] = bb[i] = 0.f;
         }
       };
-      load_bias(16 * ch0);
+      if (kBiasAhead) load_bias(16 * ch0);
       gtrace(9);
       ptx::mbar_wait(acc1_full(s), gb.phase);
       gtrace(10);
@@ -504,6 +523,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 #pragma unroll
       for (int cc = 0; cc < NCH_G; ++cc) {
         const int c0 = 16 * (ch0 + cc);
+        if (!kBiasAhead) load_bias(c0);
         uint32_t ra[16], rb[16];
         if (!RB_DBG(1024)) {
           ptx::tmem_ld16(trow + c0, ra);
@@ -512,6 +532,11 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         } else {
 #pragma unroll
           for (int i = 0; i < 16; ++i) ra[i] = rb[i] = 0u;
+        }
+        if (kEarly && cc == NCH_G - 1) {         // c1's accumulator is in registers: hand it back before the last chunk's math
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) { if (G::PAIR) ptx::mbar_arrive_leader(acc1_empty(s)); else ptx::mbar_arrive(acc1_empty(s)); }
         }
         ptrace(1 + 3 * cc);                    // bias + TMEM loads done
         uint32_t p[8];
@@ -522,7 +547,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           const float v1 = gate_fast(__uint_as_float(ra[2 * i + 1]) + ba[2 * i + 1], __uint_as_float(rb[2 * i + 1]) + bb[2 * i + 1]);
           p[i] = live ? Pack16<OpT>::pack2(v0, v1) : 0u;
         }
-        if (cc + 1 < NCH_G) load_bias(c0 + 16);
+        if (kBiasAhead && cc + 1 < NCH_G) load_bias(c0 + 16);
         // channel c0..c0+15 of row r -> block cb2, two 16-byte chunks, swizzled like a TMA write would
         const int cb2 = c0 / G::BK2, cin = c0 - cb2 * G::BK2;
         const uint32_t rowaddr = grow + cb2 * G::G_BYTES + cin * 2;
@@ -539,8 +564,8 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       ptx::tc_fence_before();
       __syncwarp();
       if (lane == 0) {
-        if (G::PAIR) { ptx::mbar_arrive_leader(g_full(s)); ptx::mbar_arrive_leader(acc1_empty(s)); }
-        else { ptx::mbar_arrive(g_full(s)); ptx::mbar_arrive(acc1_empty(s)); }
+        if (G::PAIR) ptx::mbar_arrive_leader(g_full(s)); else ptx::mbar_arrive(g_full(s));
+        if (!kEarly) { if (G::PAIR) ptx::mbar_arrive_leader(acc1_empty(s)); else ptx::mbar_arrive(acc1_empty(s)); }
       }
       ptrace(14);
       if ((warp & 3) == 0) trace(3, n, 1);
@@ -577,7 +602,11 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 #else
     constexpr bool kLook = G::RES_GLOBAL;
 #endif
-    uint4 yq[PF][2];
+    // Two register sets for the residual rows: the tile in hand reads `yq`, the look-ahead loads of this group's next tile
+    // land in `yn`, and the tile loop is unrolled by two with the sets swapped.  With one loop-carried set ptxas rotated the
+    // ~32 registers at the back edge, and the first of those moves waited for the loads just issued (9 % of the store
+    // warps' samples, ahead of the accumulator release).
+    uint4 yqA[PF][2], yqB[PF][2];
     // row pointer of this thread in tile nn of the CTA's sequence (nullptr: no such tile / row outside the tensor)
     auto res_row = [&](int nn) -> const uint4* {
       if (nn >= my_tiles) return nullptr;
@@ -600,9 +629,9 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     if (kLook) {
       const uint4* row0 = res_row(n_first);
 #pragma unroll
-      for (int c = 0; c < PF; ++c) load_res(row0, ch0 + c, yq[c]);
+      for (int c = 0; c < PF; ++c) load_res(row0, ch0 + c, yqA[c]);
     }
-    for (int n = n_first; n < my_tiles; n += G::TSTEP, tile_next()) {
+    auto store_tile = [&](const int n, uint4 (&yq)[PF][2], uint4 (&yn)[PF][2]) {
       const Cursor ab{n % G::NBUF, (uint32_t)(n / G::NBUF) & 1u};
       tile_seek();
       const int b = cur_b, t0 = tile_t0();
@@ -632,7 +661,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
       // conv2 bias of a chunk: requested before the accumulator wait (first chunk) / after the previous chunk's math
       float bv[16];
       auto load_bias2 = [&](int c0) { if (C >= kBiasSmemMinC) lds16(sb2 + 4 * c0, bv); else load16(a.bias2 + c0, bv); };
-      constexpr bool kAhead2 = C < 256;          // C = 256: 4 residual chunks in flight leave no registers for it (spills)
+      constexpr bool kAhead2 = kBiasAhead && C < 256;          // C = 256: 4 residual chunks in flight leave no registers for it (spills)
       if (kAhead2) load_bias2(16 * ch0);
       ptx::mbar_wait(acc2_full(s), ab.phase);
       ptx::tc_fence_after();
@@ -648,9 +677,14 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 #pragma unroll
           for (int i = 0; i < 16; ++i) ra[i] = 0u;
         }
+        if (kEarly && cc == NCH_S - 1) {         // the accumulator is in registers: hand it back before the math / staging / store tail
+          ptx::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) { if (G::PAIR) ptx::mbar_arrive_leader(acc2_empty(s)); else ptx::mbar_arrive(acc2_empty(s)); }
+        }
         const uint4 y0 = yq[cc % PF][0], y1 = yq[cc % PF][1];
         if (cc + PF < NCH_S) load_y(c + PF, yq[cc % PF]);
-        else if (kLook) load_res(ynext, ch0 + cc + PF - NCH_S, yq[cc % PF]);      // first chunks of the next tile
+        else if (kLook) load_res(ynext, ch0 + cc + PF - NCH_S, yn[cc % PF]);      // first chunks of the next tile
         const uint32_t yw[8] = {y0.x, y0.y, y0.z, y0.w, y1.x, y1.y, y1.z, y1.w};
         float v[16];
 #pragma unroll
@@ -700,15 +734,32 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           }
         }
       }
-      ptx::tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if (G::PAIR) ptx::mbar_arrive_leader(acc2_empty(s)); else ptx::mbar_arrive(acc2_empty(s));
-        if (!G::RES_GLOBAL) ptx::mbar_arrive(slab_empty(ss));
+      if (!kEarly) {
+        ptx::tc_fence_before();
+        __syncwarp();
+        if (lane == 0) { if (G::PAIR) ptx::mbar_arrive_leader(acc2_empty(s)); else ptx::mbar_arrive(acc2_empty(s)); }
+      }
+      if (!G::RES_GLOBAL) {                      // the residual reads of the slab are complete (their values were consumed above)
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive(slab_empty(ss));
       }
       if ((warp & 3) == 0) trace(4, n, 1);
 #pragma unroll
       for (int i = 0; i < G::TSTEP; ++i) sl.next(nSlab);
+    };
+#ifdef VITSB_RB_PING_ALL
+    constexpr bool kPing = kLook;
+#else
+    constexpr bool kPing = kLook && C == 64;      // measured per shape (ncu): C = 64 -3..-6 %, C = 128 / 256 +3..+5 % (column-split groups)
+#endif
+    if (kPing) {
+      for (int n = n_first; n < my_tiles;) {
+        store_tile(n, yqA, yqB); n += G::TSTEP; tile_next();
+        if (n >= my_tiles) break;
+        store_tile(n, yqB, yqA); n += G::TSTEP; tile_next();
+      }
+    } else {
+      for (int n = n_first; n < my_tiles; n += G::TSTEP, tile_next()) store_tile(n, yqA, yqA);
     }
     if (kStage && issuer) ptx::bulk_wait0();     // staged rows are in global memory before the CTA retires
   }
