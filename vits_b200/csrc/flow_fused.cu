@@ -107,7 +107,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
   // Programmatic dependent launch: everything above (and the L2 weight prefetch below, which reads constants only) may
   // overlap the previous kernel's tail; every other role waits here for that kernel's writes (z state, cond vectors).
   ptx::pdl_launch_dependents();
-  if (warp != 2 && warp != 3) ptx::pdl_wait();
+  if (warp != 2 && warp != 3) ptx::pdl_wait();      // warp 2 (L2 prefetch) and warp 3 (weight boxes) read constants only
   // clock64 timeline of CTA 0's first tile (debug build only): trace[slot] = cycles
 #ifdef VITSB_RB_DEBUG
   auto trace = [&](int slot) { if (a.trace && blockIdx.x == 0 && lane == 0 && slot < 256) a.trace[slot] = clock64(); };
@@ -126,7 +126,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
   };
   const int fills_per_tile = 1 + 2 * nl;                  // fills of one acts slot per tile: x0 tiles of `pre` + two gate passes per layer
 
-  if (warp == 2 || warp == 3) {
+  if (warp == 2) {
     // =================== L2 prefetch of this coupling's weights ===================
     // Every CTA streams the same 6.8 MB of weights, in lockstep, through a ring that holds ~2 k cycles of tensor work:
     // when a box misses L2 every CTA waits out the HBM latency together (first timeline: 305-350 cycles per stage
@@ -136,26 +136,34 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
     const char* wbase = reinterpret_cast<const char*>(a.w);
     const size_t seg_off[3] = {a.fw.w_pre * 2, a.fw.w_in * 2, a.fw.w_rs * 2};
     const size_t seg_len[3] = {(size_t)H * 2 * XW * 2, (size_t)nl * 2 * H * KT * H * 2, (size_t)nl * RS_ROWS * 2 * H * 2};
-    const int lane64 = (warp - 2) * 32 + lane;
+    const int lane64 = lane;
     const size_t nch[3] = {(seg_len[0] + CH - 1) / CH, (seg_len[1] + CH - 1) / CH, (seg_len[2] + CH - 1) / CH};
     // chunk g of the concatenated segments goes to CTA g % gridDim, lane (g / gridDim) % 64
-    for (size_t g = blockIdx.x + (size_t)gridDim.x * lane64; g < nch[0] + nch[1] + nch[2]; g += (size_t)gridDim.x * 64) {
+    for (size_t g = blockIdx.x + (size_t)gridDim.x * lane64; g < nch[0] + nch[1] + nch[2]; g += (size_t)gridDim.x * 32) {
       const int sg = g < nch[0] ? 0 : (g < nch[0] + nch[1] ? 1 : 2);
       const size_t c = g - (sg == 0 ? 0 : (sg == 1 ? nch[0] : nch[0] + nch[1]));
       const size_t off = c * CH;
       const uint32_t bytes = (uint32_t)(seg_len[sg] - off < CH ? seg_len[sg] - off : CH);
       ptx::prefetch_l2_bulk(wbase + seg_off[sg] + off, bytes);
     }
-  } else if (warp == 0) {
-    // =================== TMA producer: x0 operand tiles + every weight box, in the MMA warp's order ===================
+  } else if (warp == 0 || warp == 3) {
+    // =================== TMA producers: x0 operand tiles + every weight box, in the MMA warp's order ===================
+    // Two warps walk the same box sequence and each issues every other box (warp 0 also the x0 tiles): one warp needed
+    // ~330 cycles per box (barrier poll, expect_tx, coordinate set-up, all serial uniform-datapath code) against 256 cycles
+    // of MMA per ring stage, and the issuing warp spent half of its time waiting for stages to fill (warp-state samples).
     const bool leader = ptx::elect_one();
+    const int my_par = warp == 0 ? 0 : 1;
+    int seq = 0;
     Cursor rg{0, 0};
     auto put = [&](const CUtensorMap* m, int col, int row, uint32_t bytes) {
-      ptx::mbar_wait(bar(B_EMPTY + rg.idx), rg.phase ^ 1u);
-      if (leader) {
-        ptx::mbar_expect_tx(bar(B_FULL + rg.idx), bytes);
-        ptx::tma_load_2d(sR + rg.idx * STAGE_B, m, bar(B_FULL + rg.idx), col, row);
+      if ((seq & 1) == my_par) {
+        ptx::mbar_wait(bar(B_EMPTY + rg.idx), rg.phase ^ 1u);
+        if (leader) {
+          ptx::mbar_expect_tx(bar(B_FULL + rg.idx), bytes);
+          ptx::tma_load_2d(sR + rg.idx * STAGE_B, m, bar(B_FULL + rg.idx), col, row);
+        }
       }
+      ++seq;
       rg.next(NST);
     };
     for (int n = 0; n < my_tiles; ++n) {
@@ -163,7 +171,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
       tile_coords(n, b, t0);
       // x0 rows [t0 - halo, +128) as [hi | lo] 64-column tiles into the two acts slots (free once the previous tile's last
       // res / m MMAs have retired); rows outside [0, T) are zero-filled by TMA
-      for (int s = 0; s < 2; ++s) {
+      for (int s = 0; s < 2 && warp == 0; ++s) {
         const int k = n * fills_per_tile;                 // fill index of this slot; needs completion k - 1 of its empty barrier
         ptx::mbar_wait(bar(B_AEMPTY + s), (uint32_t)(k & 1) ^ 1u);
         if (leader) {
