@@ -43,28 +43,38 @@ constexpr int SLAB_ROWS = kTileM + KT - 1;                         // 132
 constexpr uint32_t HBLK = ((uint32_t)SLAB_ROWS * 128u + 1023u) & ~1023u;   // bytes per 64-channel block of the h slab
 constexpr uint32_t TILE_B = kTileM * 128u;                         // one [128 x 64] 16-bit operand tile
 constexpr uint32_t SLOT_B = 2 * TILE_B;                            // acts slot: hi tile + lo tile
-constexpr int NST = 5;                                             // ring stages (16 KB each)
-constexpr uint32_t STAGE_B = TILE_B;
+constexpr int NST1 = 5;                                            // ring stages per CTA (16 KB each; pair mode: 10 of 8 KB)
+constexpr int NST_MAX = 2 * NST1;
+constexpr uint32_t RING_B = NST1 * TILE_B;
 constexpr uint32_t TM_H = 0, TM_M = 256, TM_ACC = 384, TM_COLS = 512;
 constexpr int THREADS = 384;
 constexpr int RS_ROWS = H + HALF;                                  // rows per layer of the res / (post o skip) matrix
 constexpr int MAX_LAYERS = 4;
 
 // barrier slots (8 bytes each)
-enum { B_FULL = 0, B_EMPTY = B_FULL + NST, B_PRE = B_EMPTY + NST, B_AFULL = B_PRE + 2, B_AEMPTY = B_AFULL + 2,
+enum { B_FULL = 0, B_EMPTY = B_FULL + NST_MAX, B_PRE = B_EMPTY + NST_MAX, B_AFULL = B_PRE + 2, B_AEMPTY = B_AFULL + 2,
        B_ACCF = B_AEMPTY + 2, B_ACCE, B_HREADY, B_HFULL, B_MREADY = B_HFULL + NPASS, B_MEMPTY, B_COUNT };
 
 __host__ __device__ inline uint32_t smem_bytes(int nl) {
-  return 1024u + NPASS * HBLK + 2 * SLOT_B + NST * STAGE_B + (uint32_t)nl * 2 * H * 4u + 8u * B_COUNT + 64u;
+  return 1024u + NPASS * HBLK + 2 * SLOT_B + RING_B + (uint32_t)nl * 2 * H * 4u + 8u * B_COUNT + 64u;
 }
 }  // namespace ff
 
-template <typename OpT>
+// PAIR: clusters of two CTAs, tcgen05 cta_group::2.  One MMA covers the 128-row tiles of both CTAs (M = 256) and each CTA
+// holds HALF of every weight box, so the L2 -> shared-memory weight stream per SM halves.  That stream was the bound: a
+// CTA needs 1.3 MB of in_layer weights per layer against ~20 k cycles of MMA, 64 B/clk, and the ring sustained ~33 B/clk
+// (the issuing warp spent half of its time waiting for stages to fill: warp-state samples, profiles/).  The leader CTA's
+// warp 1 issues for both; commits are multicast to both CTAs' barrier copies; the peer's producer / epilogue warps signal
+// the leader's barriers remotely.  A pair whose second tile does not exist runs the protocol on a dead tile (no stores).
+template <typename OpT, bool PAIR>
 __global__ void __launch_bounds__(ff::THREADS, 1)
 flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant__ CUtensorMap tmPre,
                   const __grid_constant__ CUtensorMap tmIn, const __grid_constant__ CUtensorMap tmRS,
                   const __grid_constant__ CUtensorMap tmRSm, const FlowFusedArgs a) {
   using namespace ff;
+  constexpr int NCL = PAIR ? 2 : 1;
+  constexpr int NST = NST1 * NCL;                          // ring stages
+  constexpr uint32_t STAGE_B = TILE_B / NCL;               // bytes of a stage in THIS CTA (its half of the box)
   extern __shared__ uint8_t smem_raw[];
   __shared__ int s_prefix[kMaxBatchRows + 1];
   __shared__ uint32_t s_tmem;
@@ -74,12 +84,14 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
   const uint32_t sH = smem_base;                          // [NPASS][HBLK]   h slab, slab row s = tile row s - 2
   const uint32_t sA = sH + NPASS * HBLK;                  // [2][hi | lo]     acts chunk slots (and the x0 operand tiles of `pre`)
   const uint32_t sR = sA + 2 * SLOT_B;                    // [NST][STAGE_B]  weight ring
-  const uint32_t sC = sR + NST * STAGE_B;                 // fp32 [nl][2H]   conditioning + in_layer bias of the current batch row
+  const uint32_t sC = sR + RING_B;                        // fp32 [nl][2H]   conditioning + in_layer bias of the current batch row
   const uint32_t bars = sC + (uint32_t)nl * 2 * H * 4u;
   auto bar = [&](int i) { return bars + 8u * i; };
   float* s_cond = reinterpret_cast<float*>(smem_raw + (sC - ptx::smem_u32(smem_raw)));
 
   const int warp = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0), lane = threadIdx.x & 31;
+  const int rank = PAIR ? (int)ptx::cluster_ctarank() : 0;
+  const int unit_id = blockIdx.x / NCL, n_units = gridDim.x / NCL;      // a unit = one CTA, or one CTA pair
 
   // the four slab rows outside the tile are only ever read into rows that are discarded; keep them finite
   for (int i = threadIdx.x; i < NPASS * 4 * 8; i += blockDim.x) {
@@ -92,16 +104,17 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tmap(&tmZ); ptx::prefetch_tmap(&tmPre); ptx::prefetch_tmap(&tmIn); ptx::prefetch_tmap(&tmRS); ptx::prefetch_tmap(&tmRSm);
     for (int s = 0; s < NST; ++s) { ptx::mbar_init(bar(B_FULL + s), 1); ptx::mbar_init(bar(B_EMPTY + s), 1); }
-    for (int s = 0; s < 2; ++s) { ptx::mbar_init(bar(B_PRE + s), 1); ptx::mbar_init(bar(B_AFULL + s), 8); ptx::mbar_init(bar(B_AEMPTY + s), 1); }
-    ptx::mbar_init(bar(B_ACCF), 1);   ptx::mbar_init(bar(B_ACCE), 8);
+    // pair mode: the leader's copies collect the arrivals of both CTAs' epilogue warps
+    for (int s = 0; s < 2; ++s) { ptx::mbar_init(bar(B_PRE + s), 1); ptx::mbar_init(bar(B_AFULL + s), 8 * NCL); ptx::mbar_init(bar(B_AEMPTY + s), 1); }
+    ptx::mbar_init(bar(B_ACCF), 1);   ptx::mbar_init(bar(B_ACCE), 8 * NCL);
     ptx::mbar_init(bar(B_HREADY), 1);
-    for (int kb = 0; kb < NPASS; ++kb) ptx::mbar_init(bar(B_HFULL + kb), 4);      // one per 64-channel block of the h slab
-    ptx::mbar_init(bar(B_MREADY), 1); ptx::mbar_init(bar(B_MEMPTY), 8);
+    for (int kb = 0; kb < NPASS; ++kb) ptx::mbar_init(bar(B_HFULL + kb), 4 * NCL);      // one per 64-channel block of the h slab
+    ptx::mbar_init(bar(B_MREADY), 1); ptx::mbar_init(bar(B_MEMPTY), 8 * NCL);
     ptx::mbar_fence_init();
   }
-  if (warp == 1) ptx::tmem_alloc(ptx::smem_u32(&s_tmem), TM_COLS);
+  if (warp == 1) { if (PAIR) ptx::tmem_alloc_2sm(ptx::smem_u32(&s_tmem), TM_COLS); else ptx::tmem_alloc(ptx::smem_u32(&s_tmem), TM_COLS); }
   ptx::tc_fence_before();
-  __syncthreads();
+  if (PAIR) ptx::cluster_sync_all(); else __syncthreads();      // barrier inits visible to the peer before any remote signal
   ptx::tc_fence_after();
   const uint32_t tmem_base = s_tmem;
   // Programmatic dependent launch: everything above (and the L2 weight prefetch below, which reads constants only) may
@@ -116,13 +129,18 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
 #endif
 
   const int total_tiles = s_prefix[a.B];
-  const int my_tiles = total_tiles > (int)blockIdx.x ? (total_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  const int total_units = (total_tiles + NCL - 1) / NCL;  // pair mode: tiles 2u and 2u + 1 (the last may be missing)
+  const int my_tiles = total_units > unit_id ? (total_units - 1 - unit_id) / n_units + 1 : 0;
   int cur_b = 0;
-  auto tile_coords = [&](int n, int& b, int& t0) {        // b only grows along a CTA's tile sequence
-    const int tile = blockIdx.x + n * gridDim.x;
+  // returns false for the dead tile of an odd pair: same coordinates as the last real tile, nothing stored
+  auto tile_coords = [&](int n, int& b, int& t0) -> bool {        // b only grows along a CTA's tile sequence
+    int tile = (unit_id + n * n_units) * NCL + rank;
+    const bool real = tile < total_tiles;
+    if (!real) tile = total_tiles - 1;
     while (s_prefix[cur_b + 1] <= tile) ++cur_b;
     b = cur_b;
     t0 = (tile - s_prefix[cur_b]) * t_out;
+    return real;
   };
   const int fills_per_tile = 1 + 2 * nl;                  // fills of one acts slot per tile: x0 tiles of `pre` + two gate passes per layer
 
@@ -159,8 +177,11 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
       if ((seq & 1) == my_par) {
         ptx::mbar_wait(bar(B_EMPTY + rg.idx), rg.phase ^ 1u);
         if (leader) {
-          ptx::mbar_expect_tx(bar(B_FULL + rg.idx), bytes);
-          ptx::tma_load_2d(sR + rg.idx * STAGE_B, m, bar(B_FULL + rg.idx), col, row);
+          // pair: this CTA loads its half of the box rows; both halves complete on the leader's barrier
+          // (`bytes` = this CTA's share: box rows / NCL, 128 bytes each)
+          if (rank == 0) ptx::mbar_expect_tx(bar(B_FULL + rg.idx), bytes * NCL);
+          if (PAIR) ptx::tma_load_2d_2sm(sR + rg.idx * STAGE_B, m, bar(B_FULL + rg.idx), col, row + rank * (int)(bytes / 128u));
+          else ptx::tma_load_2d(sR + rg.idx * STAGE_B, m, bar(B_FULL + rg.idx), col, row);
         }
       }
       ++seq;
@@ -175,9 +196,14 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
         const int k = n * fills_per_tile;                 // fill index of this slot; needs completion k - 1 of its empty barrier
         ptx::mbar_wait(bar(B_AEMPTY + s), (uint32_t)(k & 1) ^ 1u);
         if (leader) {
-          ptx::mbar_expect_tx(bar(B_PRE + s), SLOT_B);
-          ptx::tma_load_3d(sA + s * SLOT_B, &tmZ, bar(B_PRE + s), a.fw.xwin + 64 * s, t0 - halo, b);
-          ptx::tma_load_3d(sA + s * SLOT_B + TILE_B, &tmZ, bar(B_PRE + s), IC + a.fw.xwin + 64 * s, t0 - halo, b);
+          if (rank == 0) ptx::mbar_expect_tx(bar(B_PRE + s), SLOT_B * NCL);
+          if (PAIR) {
+            ptx::tma_load_3d_2sm(sA + s * SLOT_B, &tmZ, bar(B_PRE + s), a.fw.xwin + 64 * s, t0 - halo, b);
+            ptx::tma_load_3d_2sm(sA + s * SLOT_B + TILE_B, &tmZ, bar(B_PRE + s), IC + a.fw.xwin + 64 * s, t0 - halo, b);
+          } else {
+            ptx::tma_load_3d(sA + s * SLOT_B, &tmZ, bar(B_PRE + s), a.fw.xwin + 64 * s, t0 - halo, b);
+            ptx::tma_load_3d(sA + s * SLOT_B + TILE_B, &tmZ, bar(B_PRE + s), IC + a.fw.xwin + 64 * s, t0 - halo, b);
+          }
         }
       }
       // pre: [Wh | Wl] over the x0 window, two 128-row halves of the H output channels
@@ -196,7 +222,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           for (int part = 0; part < 2; ++part) {          // Wh then Wl
             const int col = part * H + 64 * p;
             if (!last) { put(&tmRS, col, l * RS_ROWS, STAGE_B); put(&tmRS, col, l * RS_ROWS + 128, STAGE_B); }
-            put(&tmRSm, col, l * RS_ROWS + H, HALF * 128u);
+            put(&tmRSm, col, l * RS_ROWS + H, HALF * 128u / NCL);
           }
         };
         put_in(0);
@@ -205,19 +231,22 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
       }
     }
     __syncwarp();
-  } else if (warp == 1) {
-    // =================== MMA issuer ===================
+  } else if (warp == 1 && rank == 0) {
+    // =================== MMA issuer (pair mode: the leader CTA's, for both CTAs) ===================
     const bool leader = ptx::elect_one();
     const uint64_t dhi = ptx::umma_smem_desc(0, 128, 0);
     const bool bf = sizeof(OpT) == 2 && !std::is_same<OpT, __half>::value;
-    const uint32_t id128 = ptx::umma_idesc_f16(bf, kTileM, 128), id96 = ptx::umma_idesc_f16(bf, kTileM, HALF);
+    const uint32_t id128 = ptx::umma_idesc_f16(bf, kTileM * NCL, 128), id96 = ptx::umma_idesc_f16(bf, kTileM * NCL, HALF);
     auto d16 = [&](uint32_t addr) { return dhi | (uint64_t)((addr & 0x3FFFFu) >> 4); };
     Cursor rg{0, 0};
     // one ring stage against one [128 x 64] A tile: 4 K = 16 steps
     auto group = [&](uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, bool fresh) {
       if (leader) {
 #pragma unroll
-        for (int kk = 0; kk < 4; ++kk) ptx::umma_f16(d_tmem, adesc + 2 * kk, bdesc + 2 * kk, idesc, (fresh && kk == 0) ? 0u : 1u);
+        for (int kk = 0; kk < 4; ++kk) {
+          if (PAIR) ptx::umma_f16_2sm(d_tmem, adesc + 2 * kk, bdesc + 2 * kk, idesc, (fresh && kk == 0) ? 0u : 1u);
+          else ptx::umma_f16(d_tmem, adesc + 2 * kk, bdesc + 2 * kk, idesc, (fresh && kk == 0) ? 0u : 1u);
+        }
       }
     };
     auto stage_wait = [&]() -> uint64_t {
@@ -225,11 +254,11 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
       ptx::tc_fence_after();
       return d16(sR + rg.idx * STAGE_B);
     };
+    auto commit = [&](int b_) { if (leader) { if (PAIR) ptx::umma_commit_2sm(bar(b_)); else ptx::umma_commit(bar(b_)); } };
     auto stage_done = [&]() {
-      if (leader) ptx::umma_commit(bar(B_EMPTY + rg.idx));
+      commit(B_EMPTY + rg.idx);
       rg.next(NST);
     };
-    auto commit = [&](int b_) { if (leader) ptx::umma_commit(bar(b_)); };
     for (int n = 0; n < my_tiles; ++n) {
       // ---- pre: h = x0 * Wpre (3-term split), TMEM h columns written fresh ----
       if (n == 0) trace(0);
@@ -315,12 +344,13 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
     const float* bcum = a.bias + a.fw.b_cum;
     const float* bm = a.bias + a.fw.b_m;
     int staged_b = -1;
+    auto arrive = [&](int b_) { if (PAIR) ptx::mbar_arrive_leader(bar(b_)); else ptx::mbar_arrive(bar(b_)); };
     for (int n = 0; n < my_tiles; ++n) {
       int b, t0;
-      tile_coords(n, b, t0);
+      const bool real = tile_coords(n, b, t0);
       const int valid = a.len ? a.len[b] : a.T;
       const int t = t0 - halo + r;
-      const bool live = t >= 0 && t < valid;
+      const bool live = real && t >= 0 && t < valid;
       if (b != staged_b) {                                // uniform over the 8 warps (same tile sequence)
         asm volatile("bar.sync 1, 256;" ::: "memory");    // everyone is done with the previous row's vector
         const float* cv = a.cond + (long long)b * a.cond_bstride + a.fw.cond_off;
@@ -358,7 +388,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           fence_proxy_async_smem();
           ptx::tc_fence_before();
           __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(bar(B_HFULL + kb));
+          if (lane == 0) arrive(B_HFULL + kb);
         }
         if (n == 0 && warp == 4) trace(96 + l * 16 + 1);     // h epilogue done
         // ---- gate passes: acts[64 p .. 64 p + 63] = tanh(a + cond_a) * sigmoid(b + cond_b) as [hi | lo] tiles ----
@@ -381,7 +411,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           ptx::tmem_ld_wait();
           ptx::tc_fence_before();
           __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(bar(B_ACCE));
+          if (lane == 0) arrive(B_ACCE);
           ptx::mbar_wait(bar(B_AEMPTY + s), (uint32_t)(k & 1) ^ 1u);
 #pragma unroll
           for (int c = 0; c < 2; ++c) {
@@ -407,7 +437,7 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
           }
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0) ptx::mbar_arrive(bar(B_AFULL + s));
+          if (lane == 0) arrive(B_AFULL + s);
           if (n == 0 && warp == 4) trace(96 + l * 16 + 2 + p * 2 + 1); // gate(p) done
         }
       }
@@ -436,16 +466,16 @@ flow_fused_kernel(const __grid_constant__ CUtensorMap tmZ, const __grid_constant
       }
       ptx::tc_fence_before();
       __syncwarp();
-      if (lane == 0) ptx::mbar_arrive(bar(B_MEMPTY));
+      if (lane == 0) arrive(B_MEMPTY);
       if (n == 0 && warp == 4) trace(13);                    // tile done
     }
   }
 
   ptx::tc_fence_before();
-  __syncthreads();
+  if (PAIR) ptx::cluster_sync_all(); else __syncthreads();
   if (warp == 1) {
     ptx::tc_fence_after();
-    ptx::tmem_dealloc(tmem_base, TM_COLS);
+    if (PAIR) ptx::tmem_dealloc_2sm(tmem_base, TM_COLS); else ptx::tmem_dealloc(tmem_base, TM_COLS);
   }
 }
 
@@ -471,6 +501,12 @@ cudaError_t launch_flow_fused(const FlowFusedArgs& a, int op, const LaunchOpts& 
   if (!enc) return cudaErrorNotSupported;
   const CUtensorMapDataType dt = op == OP_BF16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
   const int nl = a.n_layers;
+#ifdef VITSB_FF_NO_PAIR
+  const bool pair = false;
+#else
+  const bool pair = lo.pair;
+#endif
+  const int ncl = pair ? 2 : 1;
   CUtensorMap tmZ, tmPre, tmIn, tmRS, tmRSm;
   cuuint32_t estr[3] = {1, 1, 1};
   bool ok = true;
@@ -489,28 +525,35 @@ cudaError_t launch_flow_fused(const FlowFusedArgs& a, int op, const LaunchOpts& 
     ok &= enc(m, dt, 2, p, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
   };
-  wmap(&tmPre, a.fw.w_pre, 2 * XW, H, 128);
-  wmap(&tmIn, a.fw.w_in, KT * H, nl * 2 * H, 128);
-  wmap(&tmRS, a.fw.w_rs, 2 * H, nl * RS_ROWS, 128);
-  wmap(&tmRSm, a.fw.w_rs, 2 * H, nl * RS_ROWS, HALF);
+  // pair mode: a CTA loads its half of the rows of every weight box
+  wmap(&tmPre, a.fw.w_pre, 2 * XW, H, 128 / ncl);
+  wmap(&tmIn, a.fw.w_in, KT * H, nl * 2 * H, 128 / ncl);
+  wmap(&tmRS, a.fw.w_rs, 2 * H, nl * RS_ROWS, 128 / ncl);
+  wmap(&tmRSm, a.fw.w_rs, 2 * H, nl * RS_ROWS, HALF / ncl);
   if (!ok) { fprintf(stderr, "flow_fused: tensor map encode failed\n"); return cudaErrorInvalidValue; }
   const size_t smem = smem_bytes(nl);
   static PerDeviceOnce smem_optin;
   const cudaError_t ae = smem_optin.run([] {
     cudaError_t e = cudaSuccess;
     cudaFuncAttributes fa{};
-    e = cudaFuncGetAttributes(&fa, flow_fused_kernel<__half>);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(flow_fused_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - (int)fa.sharedSizeBytes);
-    if (e == cudaSuccess) e = cudaFuncGetAttributes(&fa, flow_fused_kernel<__nv_bfloat16>);
-    if (e == cudaSuccess) e = cudaFuncSetAttribute(flow_fused_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - (int)fa.sharedSizeBytes);
+    auto optin = [&](auto kern) {
+      if (e != cudaSuccess) return;
+      e = cudaFuncGetAttributes(&fa, kern);
+      if (e == cudaSuccess) e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 232448 - (int)fa.sharedSizeBytes);
+    };
+    optin(flow_fused_kernel<__half, false>); optin(flow_fused_kernel<__half, true>);
+    optin(flow_fused_kernel<__nv_bfloat16, false>); optin(flow_fused_kernel<__nv_bfloat16, true>);
     return e;
   });
   if (ae != cudaSuccess) { fprintf(stderr, "flow_fused: cudaFuncSetAttribute failed: %s\n", cudaGetErrorString(ae)); return ae; }
   const int t_out = flow_fused_tile_rows(nl);
   const long long max_tiles = a.m_tiles > 0 ? a.m_tiles : (long long)a.B * ((a.T + t_out - 1) / t_out);
   const int num_sms = lo.num_sms > 0 ? lo.num_sms : 148;
-  int grid = (int)(max_tiles < num_sms ? max_tiles : num_sms);
-  if (grid < 1) grid = 1;
+  const long long max_units = (max_tiles + ncl - 1) / ncl;
+  const int sm_units = num_sms / ncl;
+  int units = (int)(max_units < sm_units ? max_units : sm_units);
+  if (units < 1) units = 1;
+  const int grid = units * ncl;
   FlowFusedArgs args = a;
 #ifdef VITSB_RB_DEBUG
   static long long* d_trace = nullptr;
@@ -524,12 +567,17 @@ cudaError_t launch_flow_fused(const FlowFusedArgs& a, int op, const LaunchOpts& 
   cfg.blockDim = dim3(THREADS, 1, 1);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  at[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = at; cfg.numAttrs = lo.pdl ? 1 : 0;
-  cudaError_t le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, flow_fused_kernel<__nv_bfloat16>, tmZ, tmPre, tmIn, tmRS, tmRSm, args)
-                                 : cudaLaunchKernelEx(&cfg, flow_fused_kernel<__half>, tmZ, tmPre, tmIn, tmRS, tmRSm, args);
+  cudaLaunchAttribute at[2];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = ncl; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+  at[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[1].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at; cfg.numAttrs = lo.pdl ? 2 : 1;
+  cudaError_t le;
+  if (pair) le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, flow_fused_kernel<__nv_bfloat16, true>, tmZ, tmPre, tmIn, tmRS, tmRSm, args)
+                               : cudaLaunchKernelEx(&cfg, flow_fused_kernel<__half, true>, tmZ, tmPre, tmIn, tmRS, tmRSm, args);
+  else le = op == OP_BF16 ? cudaLaunchKernelEx(&cfg, flow_fused_kernel<__nv_bfloat16, false>, tmZ, tmPre, tmIn, tmRS, tmRSm, args)
+                          : cudaLaunchKernelEx(&cfg, flow_fused_kernel<__half, false>, tmZ, tmPre, tmIn, tmRS, tmRSm, args);
   if (le == cudaSuccess) le = cudaGetLastError();
 #ifdef VITSB_RB_DEBUG
   if (tracing && le == cudaSuccess) {
