@@ -16,7 +16,7 @@ for lib in libs:
     h = rows[0]; ki, vi = h.index("Kernel Name"), h.index("Metric Value")
     per = collections.defaultdict(list)
     for r in rows[1:]:
-        per[r[ki].split("(")[0][-40:]].append(float(r[vi].replace(",", "")))
+        per[r[ki].split("(")[0].replace(", 1>", ">").replace(", 0>", ">")[-40:]].append(float(r[vi].replace(",", "")))
     tab[lib] = per
 names = list(tab[libs[0]].keys())
 tot = {l: 0.0 for l in libs}
