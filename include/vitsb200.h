@@ -107,7 +107,7 @@ int vitsb_load_weights(vitsb_handle* h, const vitsb_tensor_desc* tensors, int n)
 /* Options: per handle, never read from the environment.  Keys (int values):
  *   "cuda_graph" 0/1 (1)   replay the workspace-only launches of a repeated shape as a CUDA graph
  *   "pdl" 0/1 (1)          programmatic dependent launch between the tensor-core kernels
- *   "tc_pair" 0/1 (1)      CTA-pair (cta_group::2) mode of the generic conv kernel
+ *   "tc_pair" 0/1 (1)      CTA-pair (cta_group::2) mode of the generic conv kernel and of the coupling kernel
  *   "branch_streams" 0/1 (1)  the three MRF branches of a stage run concurrently (two extra streams owned by the handle)
  *   "rb_nslab" 0..16 (0)   fused-ResBlock slab count override, 0 = automatic
  *   "ups_split_mask" -1..255 bit i: upsampler i runs 3-term split precision (16-bit paths; -1 = automatic: fp16 the

@@ -3,9 +3,11 @@
 # less run-to-run noise than the bench's family table).  LIBS="a.so b.so" K=regex bash scripts/gpu_ab_ncu.sh
 mkdir -p gpurun_out
 LIBS=${LIBS:-"libvitsb200_base.so libvitsb200.so"}
-for lib in $LIBS; do
-  VITSB_LIB=$PWD/vits_b200/$lib timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"${K:-rb_fused|conv_tc|flow_fused}" \
-    --csv --log-file gpurun_out/abn_$lib.csv python scripts/one_call.py fp16 ${CALLS:-3} > gpurun_out/abn_$lib.log 2>&1 || tail -3 gpurun_out/abn_$lib.log
+# an entry may carry per-handle options for scripts/one_call.py: libvitsb200.so@rb_nslab=16,pdl=0
+for ent in $LIBS; do
+  lib=${ent%%@*}; opts=""; [ "$ent" != "$lib" ] && opts=${ent#*@}
+  VITSB_OPTS=$opts VITSB_LIB=$PWD/vits_b200/$lib timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"${K:-rb_fused|conv_tc|flow_fused}" \
+    --csv --log-file gpurun_out/abn_$ent.csv python scripts/one_call.py fp16 ${CALLS:-3} > gpurun_out/abn_$ent.log 2>&1 || tail -3 gpurun_out/abn_$ent.log
 done
 python - <<PY
 import csv, collections

@@ -566,3 +566,30 @@ def test_engines_on_two_devices_in_one_process(base_cfg, base_sd):
         rc = e1.lib.vitsb_flow_reverse_noalloc(e1._h, zp1.data_ptr(), g1.data_ptr(), arr, 2, max(lens), rc_dev.data_ptr(), e1._stream())
         torch.cuda.synchronize()
     assert rc == 0 and torch.equal(rc_dev.cpu(), z0.cpu())          # the static scratch array's address is per device
+
+
+@pytest.mark.parametrize("lens", [[100], [336], [113, 37, 230], [500] * 3 + [17], [417] * 41])
+def test_coupling_pairs_match_single_cta(base_cfg, base_sd, lens):
+    """The coupling kernel in CTA-pair mode (cta_group::2: one MMA over both CTAs' tiles, half of every weight box per CTA)
+    against the same kernel without pairs: one tile with a dead partner, exactly three tiles, odd / even tile counts across
+    batch rows, and more pairs than SM pairs (41 x 4 tiles = 82 pairs on 74: two tiles per pair for some).  The per-row
+    accumulation order is the same in both modes, so z is bit-identical; both stay within tolerance of the CPU oracle."""
+    from vits_b200 import FlowDecoder
+    lat = FX.make_latents(base_cfg, lens, seed=99)
+    zp, g = lat["z_p"].cuda(), lat["g"].cuda()
+    pair = engine(base_cfg, base_sd, "fp16")
+    single = FlowDecoder(base_cfg, base_sd, device="cuda:0", precision="fp16", options={"tc_pair": 0})
+    assert pair.get_option("tc_pair") == 1 and single.get_option("tc_pair") == 0
+    z1 = pair.flow_reverse(zp, g, lens)
+    z2 = pair.flow_reverse(zp, g, lens)
+    z0 = single.flow_reverse(zp, g, lens)
+    torch.cuda.synchronize()
+    assert torch.equal(z1, z2)
+    assert torch.equal(z1, z0)
+    if len(lens) <= 4:
+        with torch.no_grad():
+            for b, L in enumerate(lens):                        # per-utterance flow of the oracle (models.py:573)
+                z_ref = O.flow_reverse(base_sd, lat["z_p"][b:b + 1, :, :L], lat["g"][b:b + 1], base_cfg)
+                assert (z1[b:b + 1, :, :L].cpu() - z_ref).abs().max().item() <= TOL_Z["fp16"]
+    for b, L in enumerate(lens):
+        assert z1[b, :, L:].abs().sum().item() == 0

@@ -50,7 +50,7 @@ struct OptDesc { const char* key; int Engine::*field; int lo, hi; };
 const OptDesc kOpts[] = {
     {"cuda_graph", &Engine::opt_graph, 0, 1},             // replay the workspace-only launches of a repeated shape as a CUDA graph
     {"pdl", &Engine::opt_pdl, 0, 1},                      // programmatic dependent launch between tensor-core kernels
-    {"tc_pair", &Engine::opt_tc_pair, 0, 1},              // conv_tc CTA-pair mode
+    {"tc_pair", &Engine::opt_tc_pair, 0, 1},              // CTA-pair mode of conv_tc and of the coupling kernel
     {"rb_fused", &Engine::opt_rb_fused, -1, 1},           // fused ResBlock kernel (-1 auto); applies at the next load
     {"flow_fused", &Engine::opt_flow_fused, -1, 1},       // fused coupling-layer kernel (-1 auto); applies at the next load
     {"flow_in_split", &Engine::opt_flow_in_split, -1, 1}, // 3-term split WN in_layers (-1: bf16 yes, fp16 no); applies at the next load

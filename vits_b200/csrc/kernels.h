@@ -15,7 +15,7 @@ inline int op_bytes(int op) { return op == OP_F32 ? 4 : 2; }
 struct LaunchOpts {
   bool pdl = true;         // programmatic dependent launch between consecutive tensor-core kernels: their prologues (and the
                            // coupling kernel's L2 weight prefetch) overlap the previous kernel's tail; -1 % (C2) .. -5 % (B = 1)
-  bool pair = true;        // conv_tc: CTA-pair (cta_group::2) mode when the N tile allows it
+  bool pair = true;        // conv_tc (when the N tile allows it) and flow_fused: CTA-pair (cta_group::2) mode
   int num_sms = 148;
   int rb_nslab = 0;        // rb_fused: activation slab count override (0 = automatic)
 };

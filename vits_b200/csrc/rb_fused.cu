@@ -695,6 +695,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
           v[2 * i + 1] = (__uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1]) + fminf(y.y, 10.f * y.y);
         }
         if (kAhead2 && cc + 1 < NCH_S) load_bias2(c0 + 16);
+        if (!G::RES_GLOBAL && cc == NCH_S - 1) {   // every residual value read from the slab has been consumed: release it before
+          __syncwarp();                            // the staging / store tail (measured neutral: more or earlier slabs do not move C = 32)
+          if (lane == 0) ptx::mbar_arrive(slab_empty(ss));
+        }
         if (kStage) {
           if (cc % CH_BLK == 0) {                // block buffer reuse: the previous store must have read it
             if (issuer) ptx::bulk_wait_read0();
@@ -738,10 +742,6 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         ptx::tc_fence_before();
         __syncwarp();
         if (lane == 0) { if (G::PAIR) ptx::mbar_arrive_leader(acc2_empty(s)); else ptx::mbar_arrive(acc2_empty(s)); }
-      }
-      if (!G::RES_GLOBAL) {                      // the residual reads of the slab are complete (their values were consumed above)
-        __syncwarp();
-        if (lane == 0) ptx::mbar_arrive(slab_empty(ss));
       }
       if ((warp & 3) == 0) trace(4, n, 1);
 #pragma unroll
