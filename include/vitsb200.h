@@ -158,6 +158,20 @@ int vitsb_synthesize_pcm16(vitsb_handle* h, const float* z_p, const float* g, co
                            int B, int T_max, int ragged, float volume, int16_t* pcm,
                            void* ws, size_t ws_bytes, vitsb_stream stream);
 
+/* Replaces: the two librosa.resample calls of VITSWrap.speaking (vits_wrap.py:186-194: `pitch` resamples from
+ * int(sr / pitch) to sr, `sampling_rate` from sr to the requested rate) and, with `pcm`, the int16 conversion after them
+ * (vits_wrap.py:195), on the device.  The reference's resampler is whatever librosa defaults to (soxr_hq
+ * today, unpinned, not in this image): this entry point is the polyphase method of scipy.signal.resample_poly -
+ * y[n] = sum_k taps[(n + n_pre_remove) * down - k * up] * x[k], float64 accumulation - and is tested against scipy.
+ *   x     : device fp32, row b at x + b * x_stride, n_in samples per row
+ *   taps  : device float64 [n_taps]: the zero-padded low-pass filter scaled by `up` (vits_b200/resample.py computes it
+ *           and n_pre_remove / n_out per (orig_sr, target_sr); up / down are the rates divided by their gcd)
+ *   y/pcm : device (or page-locked host) fp32 / int16, row b at + b * y_stride, n_out samples per row; one may be NULL.
+ *           pcm = int16(clip(y * volume * 32767, -32768, 32767)) as in vitsb_synthesize_pcm16. */
+int vitsb_resample_poly(vitsb_handle* h, const float* x, int B, long long n_in, long long x_stride, int up, int down,
+                        const double* taps, int n_taps, long long n_pre_remove, long long n_out, float* y, int16_t* pcm,
+                        float volume, long long y_stride, vitsb_stream stream);
+
 /* Replaces: the head of SynthesizerTrn.infer_p2 (models.py:570-572) - the two length-regulation matmuls and the
  * noise FMA - as one gather/FMA kernel.  attn is the duration path of commons.generate_path
  * (commons.py:143-155); zero weights are skipped, any other weights are summed like the matmul.

@@ -17,7 +17,7 @@ CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libvitsb200.so")
 SOURCES = ["conv_f32.cu", "aux_kernels.cu", "conv_tc.cu", "rb_fused.cu", "flow_fused.cu", "engine_weights.cu", "engine_run.cu",
-           "capi.cu", "noalloc.cu", "p1.cu"]
+           "capi.cu", "noalloc.cu", "p1.cu", "resample.cu"]
 NVCC_FLAGS = ["-std=c++17", "-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-Xcompiler", "-fPIC"]
 LINK_FLAGS = ["-shared", "-cudart", "static"]
 

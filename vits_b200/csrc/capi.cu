@@ -133,6 +133,25 @@ int vitsb_length_regulate(vitsb_handle* h, const float* attn, const float* m_p, 
   return VITSB_OK;
 }
 
+int vitsb_resample_poly(vitsb_handle* h, const float* x, int B, long long n_in, long long x_stride, int up, int down,
+                        const double* taps, int n_taps, long long n_pre_remove, long long n_out, float* y, int16_t* pcm,
+                        float volume, long long y_stride, vitsb_stream stream) {
+  if (!h) return VITSB_ERR_BAD_ARG;
+  std::lock_guard<std::mutex> lk(h->eng.mu);
+  if (!x || !taps || (!y && !pcm)) return h->eng.fail(VITSB_ERR_BAD_ARG, "null pointer");
+  if (B < 1 || B > 65535) return h->eng.fail(VITSB_ERR_BAD_ARG, "B must be in [1, 65535]");
+  if (up < 1 || down < 1 || n_taps < 1 || n_in < 1 || n_out < 0 || n_pre_remove < 0)
+    return h->eng.fail(VITSB_ERR_BAD_ARG, "up, down, n_taps, n_in must be >= 1 and n_out, n_pre_remove >= 0");
+  if (x_stride < n_in || y_stride < n_out) return h->eng.fail(VITSB_ERR_BAD_ARG, "row strides must cover n_in / n_out");
+  if (n_out > 0x7fffffffLL * 256) return h->eng.fail(VITSB_ERR_BAD_ARG, "n_out too large");
+  cudaError_t e = cudaSetDevice(h->eng.device);
+  if (e == cudaSuccess)
+    e = vitsb::launch_resample_poly(x, B, n_in, x_stride, up, down, taps, n_taps, n_pre_remove, n_out, y, pcm, volume, y_stride,
+                                    (cudaStream_t)stream);
+  if (e != cudaSuccess) return h->eng.fail(VITSB_ERR_CUDA, std::string("resample_poly: ") + cudaGetErrorString(e));
+  return VITSB_OK;
+}
+
 int vitsb_total_upsample(const vitsb_handle* h) { return h ? h->eng.up_total : 0; }
 
 int vitsb_launches_per_call(const vitsb_handle* h, int B, int T_max) {

@@ -118,6 +118,11 @@ cudaError_t launch_conv_post(const float* in, int B, int L, int C, int k, float 
                              const int* len, int len_mul, float* wav, short* pcm, float volume, cudaStream_t stream);
 bool conv_post_supported(int C, int k);
 
+// resample.cu - polyphase FIR resampler of the output waveform (vits_wrap.py:186-194; scipy.signal.resample_poly's method)
+cudaError_t launch_resample_poly(const float* x, int B, long long n_in, long long x_stride, int up, int down, const double* taps,
+                                 int n_taps, long long n_pre_remove, long long n_out, float* y, short* pcm, float volume,
+                                 long long y_stride, cudaStream_t stream);
+
 // head of infer_p2 (models.py:570-572): z_p[B][C][T] = attn @ m_p^T + noise * (attn @ s_p^T), reference layouts, fp32
 cudaError_t launch_length_regulate(const float* attn, const float* m_p, const float* s_p, const float* noise,
                                    int B, int C, int T, int Tx, float* z_p, cudaStream_t stream);

@@ -17,6 +17,7 @@ without a CUDA device or without the built library raises.
 from __future__ import annotations
 
 import ctypes as C
+import numpy as np
 from typing import Dict, Optional, Sequence
 
 import torch
@@ -167,6 +168,35 @@ class FlowDecoder:
             self._check(self.lib.vitsb_flow_reverse(self._h, z_p.data_ptr(), g.data_ptr(), lens, B, T, z.data_ptr(),
                                                     ws.data_ptr(), ws.numel(), self._stream()))
         return z
+
+    @torch.no_grad()
+    def resample(self, wav: torch.Tensor, orig_sr: int, target_sr: int, pcm16: bool = False, volume: float = 1.0) -> torch.Tensor:
+        """VITSWrap.speaking's resampling step on the device (vits_wrap.py:186-194): `wav` [B, 1, N] or [B, N] fp32 at
+        `orig_sr` -> the same shape at `target_sr` (ceil(N * target / orig) samples), optionally followed by the int16
+        conversion of vits_wrap.py:195.  `pitch` is resample(wav, int(sr / pitch), sr); a requested output rate is
+        resample(wav, sr, sampling_rate).  Method: scipy.signal.resample_poly's polyphase filter (vits_b200/resample.py)."""
+        from . import resample as R
+        key = (int(orig_sr), int(target_sr))
+        cache = self.__dict__.setdefault("_resample_plans", {})
+        if key not in cache:
+            p = R.plan(*key)
+            cache[key] = (p, torch.from_numpy(np.ascontiguousarray(p.taps)).to(self.device))
+        p, taps = cache[key]
+        x = wav.to(self.device, torch.float32).contiguous()
+        shape = x.shape
+        x2 = x.reshape(-1, shape[-1])
+        B, n_in = x2.shape
+        n_out = p.n_out(n_in)
+        with torch.cuda.device(self.device):
+            out = torch.empty(B, n_out, dtype=torch.int16 if pcm16 else torch.float32, device=self.device)
+            if p.up == 1 and p.down == 1 and not pcm16:
+                out.copy_(x2)
+            else:
+                self._check(self.lib.vitsb_resample_poly(self._h, x2.data_ptr(), B, n_in, n_in, p.up, p.down, taps.data_ptr(),
+                                                         taps.numel(), p.n_pre_remove, n_out,
+                                                         None if pcm16 else out.data_ptr(), out.data_ptr() if pcm16 else None,
+                                                         float(volume), n_out, self._stream()))
+        return out.reshape(*shape[:-1], n_out)
 
     @torch.no_grad()
     def decode(self, z: torch.Tensor, g: torch.Tensor, lengths: Optional[Sequence[int]] = None,

@@ -51,6 +51,8 @@ SYMBOLS = {
     "vitsb_synthesize_pcm16": (C.c_int, [_P, _P, _P, C.POINTER(C.c_int32), C.c_int, C.c_int, C.c_int, C.c_float, _P, _P,
                                          C.c_size_t, _P]),
     "vitsb_length_regulate": (C.c_int, [_P, _P, _P, _P, _P, C.c_int, C.c_int, C.c_int, _P, _P]),
+    "vitsb_resample_poly": (C.c_int, [_P, _P, C.c_int, C.c_longlong, C.c_longlong, C.c_int, C.c_int, _P, C.c_int, C.c_longlong,
+                                      C.c_longlong, _P, _P, C.c_float, C.c_longlong, _P]),
     "vitsb_synthesize_durations": (C.c_int, [_P, _P, _P, _P, _P, C.POINTER(C.c_int32), _P, C.c_longlong, C.c_int, C.c_int, C.c_int,
                                              C.c_float, C.c_int, _P, _P, _P, C.c_float, _P, _P, C.c_size_t, _P]),
     "vitsb_p1_workspace_bytes": (C.c_size_t, [_P, C.c_int, C.c_int]),
