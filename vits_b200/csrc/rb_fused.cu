@@ -583,7 +583,10 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     const uint32_t sb2 = ptx::smem_u32(&s_bias2[0]);
     constexpr int NCH_S = G::COOP ? NCH / G::NGRP : NCH;      // chunks of a row this group handles (COOP: column split)
     const int ch0 = G::COOP ? grp * NCH_S : 0;
-    constexpr int PF = NCH_S < 4 ? NCH_S : 4;    // residual chunks kept in flight (2 x uint4 each; 96-register cap with 20 warps)
+#ifndef VITSB_RB_PF64
+#define VITSB_RB_PF64 2                          // C = 64 keeps two register sets (ping-pong, below): 2 chunks each, no spills, -1..-4 % against 4
+#endif
+    constexpr int PF = NCH_S < 4 ? NCH_S : (C == 64 ? VITSB_RB_PF64 : 4);    // residual chunks kept in flight (2 x uint4 each; 96-register cap with 20 warps)
     Cursor sl{0, 0};
     int len_b = -1, valid = a.L;                 // valid rows of batch row len_b (one global load per batch row, not per tile)
     if (!G::COOP) for (int i = 0; i < grp; ++i) sl.next(nSlab);
