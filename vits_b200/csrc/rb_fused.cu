@@ -584,7 +584,7 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
     constexpr int NCH_S = G::COOP ? NCH / G::NGRP : NCH;      // chunks of a row this group handles (COOP: column split)
     const int ch0 = G::COOP ? grp * NCH_S : 0;
 #ifndef VITSB_RB_PF64
-#define VITSB_RB_PF64 2                          // C = 64 keeps two register sets (ping-pong, below): 2 chunks each, no spills, -1..-4 % against 4
+#define VITSB_RB_PF64 2                          // C = 64 keeps two register sets (ping-pong, below): 2 chunks each, -1..-4 % against 4
 #endif
     constexpr int PF = NCH_S < 4 ? NCH_S : (C == 64 ? VITSB_RB_PF64 : 4);    // residual chunks kept in flight (2 x uint4 each; 96-register cap with 20 warps)
     Cursor sl{0, 0};
