@@ -385,9 +385,13 @@ __device__ __forceinline__ void y_accum8(const uint4& y, float (&x)[8]) {
   const uint32_t w[4] = {y.x, y.y, y.z, y.w};
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
+#ifdef VITSB_NO_MIX16
     const float2 f = Pack16<OpT>::unpack2(w[i]);
     x[2 * i] += fminf(f.x, 10.f * f.x);
     x[2 * i + 1] += fminf(f.y, 10.f * f.y);
+#else
+    add_inv_lrelu2<OpT>(w[i], x[2 * i], x[2 * i + 1]);      // x += min(y, 10 y), 2.5 instructions per element (tc_common.cuh)
+#endif
   }
 }
 

@@ -692,10 +692,16 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
         float v[16];
 #pragma unroll
         for (int i = 0; i < 8; ++i) {
-          const float2 y = Pack16<OpT>::unpack2(yw[i]);
           // inverse of leaky_relu(., 0.1): x = y >= 0 ? y : 10 y = min(y, 10 y)
+#ifdef VITSB_NO_MIX16
+          const float2 y = Pack16<OpT>::unpack2(yw[i]);
           v[2 * i] = (__uint_as_float(ra[2 * i]) + bv[2 * i]) + fminf(y.x, 10.f * y.x);
           v[2 * i + 1] = (__uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1]) + fminf(y.y, 10.f * y.y);
+#else
+          v[2 * i] = __uint_as_float(ra[2 * i]) + bv[2 * i];
+          v[2 * i + 1] = __uint_as_float(ra[2 * i + 1]) + bv[2 * i + 1];
+          add_inv_lrelu2<OpT>(yw[i], v[2 * i], v[2 * i + 1]);      // mixed-precision add / fma straight from the packed halves
+#endif
         }
         if (kAhead2 && cc + 1 < NCH_S) load_bias2(c0 + 16);
         if (!G::RES_GLOBAL && cc == NCH_S - 1) {   // every residual value read from the slab has been consumed: release it before

@@ -23,6 +23,32 @@ template <> struct Pack16<__nv_bfloat16> {
   __device__ static __forceinline__ float2 unpack2(uint32_t u) { return __bfloat1622float2(*reinterpret_cast<__nv_bfloat162*>(&u)); }
 };
 
+// Mixed-precision helpers (PTX ISA 8.6, sm_100: SASS FHADD / FHFMA / HMNMX2): a 16-bit value is converted and added (or
+// multiplied-and-added) into an fp32 accumulator by ONE instruction, its half selected in the operand (no unpack).  Used
+// where a stored y = op(leaky_relu(x, 0.1)) is turned back into x and added to an fp32 value:
+//   x = min(y, 10 y) = y + 9 * min(y, 0)      ->  acc = fma(min(y, 0), 9, acc + y)
+// (2.5 instructions per element instead of 4: unpack, 10 y, min, add; both forms are exact up to the fp32 adds).
+template <typename OpT> struct Mix16;
+template <> struct Mix16<__half> {
+  static constexpr uint16_t kNine = 0x4880;
+  __device__ static __forceinline__ float add(uint16_t h, float c) { float d; asm("add.rn.f32.f16 %0, %1, %2;" : "=f"(d) : "h"(h), "f"(c)); return d; }
+  __device__ static __forceinline__ float fma(uint16_t a, uint16_t b, float c) { float d; asm("fma.rn.f32.f16 %0, %1, %2, %3;" : "=f"(d) : "h"(a), "h"(b), "f"(c)); return d; }
+  __device__ static __forceinline__ uint32_t min0(uint32_t y) { uint32_t d; asm("min.f16x2 %0, %1, %2;" : "=r"(d) : "r"(y), "r"(0u)); return d; }
+};
+template <> struct Mix16<__nv_bfloat16> {
+  static constexpr uint16_t kNine = 0x4110;
+  __device__ static __forceinline__ float add(uint16_t h, float c) { float d; asm("add.rn.f32.bf16 %0, %1, %2;" : "=f"(d) : "h"(h), "f"(c)); return d; }
+  __device__ static __forceinline__ float fma(uint16_t a, uint16_t b, float c) { float d; asm("fma.rn.f32.bf16 %0, %1, %2, %3;" : "=f"(d) : "h"(a), "h"(b), "f"(c)); return d; }
+  __device__ static __forceinline__ uint32_t min0(uint32_t y) { uint32_t d; asm("min.bf16x2 %0, %1, %2;" : "=r"(d) : "r"(y), "r"(0u)); return d; }
+};
+// acc0 += x(lo half of y2), acc1 += x(hi half), x = inverse leaky_relu(0.1) of the stored value
+template <typename OpT>
+__device__ __forceinline__ void add_inv_lrelu2(uint32_t y2, float& acc0, float& acc1) {
+  const uint32_t m = Mix16<OpT>::min0(y2);
+  acc0 = Mix16<OpT>::fma((uint16_t)(m & 0xffffu), Mix16<OpT>::kNine, Mix16<OpT>::add((uint16_t)(y2 & 0xffffu), acc0));
+  acc1 = Mix16<OpT>::fma((uint16_t)(m >> 16), Mix16<OpT>::kNine, Mix16<OpT>::add((uint16_t)(y2 >> 16), acc1));
+}
+
 template <typename OpT>
 __device__ __forceinline__ void store_op16(OpT* dst, const float (&v)[16], float slope, int split) {
   uint32_t p[8], q[8];
