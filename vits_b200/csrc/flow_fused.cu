@@ -20,8 +20,9 @@
 // garbage but row-independent, and rows outside [0, len[b]) are stored as zeros in the h operand, which is exactly the
 // conv zero padding / x_mask of the reference.
 //
-// Roles (12 warps): warp 0 TMA producer (x0 rows + every weight box through one 16 KB-stage ring, in the MMA warp's
-// fixed consumption order), warp 1 tcgen05.mma issuer, warps 4-11 epilogues (TMEM -> registers -> shared / global).
+// Roles (12 warps): warps 0 and 3 TMA producers (x0 rows; every weight box through one ring, in the MMA warp's fixed
+// consumption order, alternate boxes each), warp 1 tcgen05.mma issuer (pair mode: the leader CTA's, for both CTAs), warp 2
+// L2 prefetch of the coupling's weights, warps 4-11 epilogues (TMEM -> registers -> shared / global).
 // Taps of the k = 5 conv are row-shifted UMMA descriptors over the h slab in shared memory (132 rows), as in rb_fused.
 // Precision follows DESIGN.md section 3: in_layers single term on hi(h); pre / res / (post o skip) 3-term split
 // (ah + al) * Wh + ah * Wl; exact-form gate (ex2 / rcp), because the split operand needs more than tanh.approx gives.

@@ -26,8 +26,10 @@
 //   warp 2      c2 MMA issuer (resident-weight mode: small N needs two issuing threads)
 //   warp 3      weight TMA producer
 //   warps 4-7   epilogue 1: TMEM -> bias + cond + gate -> G tile in smem (swizzled like TMA)
-//   warps 8-11  epilogue 2: TMEM -> bias + residual + leaky_relu -> global (+ MRF accumulate)
-//   warps 12-15 / 16-19  second gate / store group: the two groups take alternate tiles
+//   warps 8-11  epilogue 2: TMEM -> bias + residual + leaky_relu -> staged rows -> TMA store
+//   warps 12-15 / 16-19  second gate / store group: the two groups take alternate tiles (C <= 64) or split the columns (C >= 128)
+// Every CTA (pair) works through one contiguous run of tiles, so the batch row - its conditioning vector, length and
+// tile range, all cached in registers - changes a handful of times per launch.
 // Weights are resident in smem when they fit (C <= 64) and streamed through one ring in
 // the issuing warp's fixed order otherwise.  G tiles and both TMEM accumulators are
 // NBUF-deep (4 for C <= 64, where a tile is ~500 tensor cycles and the mbarrier / commit
