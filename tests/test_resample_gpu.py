@@ -47,3 +47,28 @@ def test_resample_identity_and_after_synthesis(eng):
     assert down.shape == (1, 1, wav.shape[-1] // 2)
     ref = ss.resample_poly(wav.cpu().numpy().astype(np.float64), 1, 2, axis=-1)
     assert np.abs(down.cpu().numpy() - ref).max() <= 2e-6
+
+
+@pytest.mark.parametrize("pitch,rate,tail", [(1.0, None, 0.0), (1.1, None, 0.25), (1.0, 8000, 0.1), (0.9, 24000, 0.0)])
+def test_speaking_output_matches_reference_steps(eng, pitch, rate, tail):
+    """VITSWrap.speaking's per-segment output steps (vits_wrap.py:186-197) with scipy's resample_poly standing in for
+    librosa.resample: same order of operations, same int16 conversion, same tail padding."""
+    rng = np.random.default_rng(7)
+    sr = 16000
+    wav = (0.4 * np.sin(2 * np.pi * 220.0 * np.arange(24000) / sr) + 0.05 * rng.standard_normal(24000)).astype(np.float32)
+    volume = 0.9
+    got = eng.speaking_output(torch.from_numpy(wav), volume=volume, pitch=pitch, sampling_rate=rate, tail_silence=tail).cpu().numpy()
+    from vits_b200 import resample as R
+    ref = wav.astype(np.float64)
+    if pitch != 1.0:
+        p = R.plan(int(sr / pitch), sr)
+        ref = ss.resample_poly(ref.astype(np.float32).astype(np.float64), p.up, p.down)
+    out_sr = sr if rate is None else rate
+    if out_sr != sr:
+        p = R.plan(sr, out_sr)
+        ref = ss.resample_poly(ref.astype(np.float32).astype(np.float64), p.up, p.down)
+    want = np.clip(ref.astype(np.float32) * np.float32(volume) * np.float32(32767), -32768, 32767).astype(np.int16)
+    if tail > 0:
+        want = np.pad(want, [0, int(tail * out_sr)])
+    assert got.dtype == np.int16 and got.shape == want.shape
+    assert np.abs(got.astype(np.int32) - want.astype(np.int32)).max() <= 1        # float32 rounding of the resampled value at an integer boundary

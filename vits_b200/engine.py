@@ -199,6 +199,32 @@ class FlowDecoder:
         return out.reshape(*shape[:-1], n_out)
 
     @torch.no_grad()
+    def speaking_output(self, wav: torch.Tensor, volume: float = 1.0, pitch: float = 1.0, sampling_rate: Optional[int] = None,
+                        tail_silence: float = 0.0, default_sampling_rate: int = 16000) -> torch.Tensor:
+        """The per-segment output steps of VITSWrap.speaking (vits_wrap.py:186-197) on the device, for one waveform
+        [N] / [1, N] / [1, 1, N] fp32 at `default_sampling_rate`: `pitch` resampling from int(sr / pitch) to sr, resampling
+        to the requested `sampling_rate`, int16 conversion with `volume`, zero padding of int(tail_silence * sampling_rate)
+        samples.  Returns int16 [N_out] on the device.  (The optional bandwidth-extension model `self.asv` of line 189 is
+        a separate network and is not part of this library; the resampler is the polyphase one of `resample()`.)"""
+        sr = int(default_sampling_rate)
+        out_sr = sr if sampling_rate is None else int(sampling_rate)
+        x = wav.to(self.device, torch.float32).reshape(1, -1)
+        steps = []
+        if pitch != 1.0:
+            steps.append((int(sr / pitch), sr))
+        if out_sr != sr:
+            steps.append((sr, out_sr))
+        for i, (a, b) in enumerate(steps[:-1]):
+            x = self.resample(x, a, b)
+        if steps:
+            pcm = self.resample(x, steps[-1][0], steps[-1][1], pcm16=True, volume=volume)
+        else:                                              # no resampling: the conversion alone (vits_wrap.py:195)
+            pcm = self.resample(x, sr, sr, pcm16=True, volume=volume)
+        pcm = pcm.reshape(-1)
+        pad = int(tail_silence * out_sr) if tail_silence > 0 else 0
+        return torch.nn.functional.pad(pcm, (0, pad)) if pad else pcm
+
+    @torch.no_grad()
     def decode(self, z: torch.Tensor, g: torch.Tensor, lengths: Optional[Sequence[int]] = None,
                ragged: bool = True) -> torch.Tensor:
         z, g, lens, B, T = self._prep(z, g, lengths)
