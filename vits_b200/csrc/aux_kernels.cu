@@ -612,11 +612,14 @@ bool conv_post_y_supported(int C, int k, int L) { return C == 32 && k == 7 && L 
 // streams and conv_post runs on it without shared memory.  A thread owns one ROW (time position): it sums the three
 // streams' 32 channels (x_j = min(y, 10 y)), applies leaky_relu and multiplies the row into its 7 per-tap partial dot
 // products d_j = sum_c w[j][c] x[c] (weights: broadcast 16-byte reads of a 896-byte shared-memory copy); output
-// t = sum_j d_j(row t + j - 3) then takes 12 warp shuffles.  A warp walks a run of 250 outputs in 8 chunks of 32 rows
+// t = sum_j d_j(row t + j - 3) then takes 12 warp shuffles.  A warp walks a run of 32 * kPrChunks - 6 outputs in chunks of 32 rows
 // (6 rows of overlap per run), carrying the previous chunk's partial dots, with the next chunk's 12 x 16-byte loads in
 // flight under the current chunk's math.  The tiled kernel it replaces (conv_post4_kernel with 16-bit input: fp32 tile
 // in shared memory, 64-thread blocks, 12 warps per SM, four dependent load passes per tile) reached 3.3 TB/s.
-constexpr int kPrChunks = 8, kPrRun = 32 * kPrChunks - 6, kPrWarps = 4;
+#ifndef VITSB_PR_CHUNKS
+#define VITSB_PR_CHUNKS 6              // 4-6 chunks per run: finer blocks fill the last wave (8: +2.5 %, 12: +10 %)
+#endif
+constexpr int kPrChunks = VITSB_PR_CHUNKS, kPrRun = 32 * kPrChunks - 6, kPrWarps = 4;
 struct PrCtx {
   int out0, out_end, valid, row_hi, lane, zmask;
   long long boff, ooff;
