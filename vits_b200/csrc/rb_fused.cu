@@ -811,7 +811,9 @@ cudaError_t launch_t(const RbLaunch& L, int op, const LaunchOpts& lo, cudaStream
     // slab lifetime: load + c1 only (RES_GLOBAL), or the whole 4-stage pipeline (C = 32 reads the residual from the slab:
     // ~6.7 k cycles from TMA issue to the store epilogue's release, so the tile period is that latency / nSlab - measured
     // 1.1 k cycles per tile with 6 slabs against ~0.4 k of tensor work; use all 8 barrier slots)
-    const int want = lo.rb_nslab > 0 ? (lo.rb_nslab > kRbMaxSlab ? kRbMaxSlab : lo.rb_nslab) : (G::RES_GLOBAL ? 4 : G::NBUF + 4);
+    // C = 64 (slab released after c1): measured per k with the rb_nslab option - 3 slabs for k = 3 (4: +2 %, 6: +12 %), 2 for k = 7 (-3 %)
+    const int want64 = KT == 3 ? 3 : (KT == 7 ? 2 : 4);
+    const int want = lo.rb_nslab > 0 ? (lo.rb_nslab > kRbMaxSlab ? kRbMaxSlab : lo.rb_nslab) : (G::RES_GLOBAL ? want64 : G::NBUF + 4);
     if (rt.nSlab > want) rt.nSlab = want;
   } else {
     // streamed weights: slabs first (2 when the accumulators are double-buffered), the rest to the ring
