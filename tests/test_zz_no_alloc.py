@@ -21,10 +21,15 @@ def _noalloc(eng, zp, g, lens):
     z = torch.full_like(zp, float("nan"))                       # caller-owned output
     arr = (C.c_int32 * B)(*lens) if lens is not None else None
     torch.cuda.synchronize()
-    before = torch.cuda.memory_allocated(), torch.cuda.memory_reserved()
+    # cumulative allocation / segment counters of torch's caching allocator: they only move when something is allocated
+    # (the byte totals also move when Python's garbage collector frees tensors of earlier tests during the call)
+    def counters():
+        st = torch.cuda.memory_stats()
+        return st.get("allocation.all.allocated", 0), st.get("segment.all.allocated", 0)
+    before = counters()
     rc = eng.lib.vitsb_flow_reverse_noalloc(eng._h, zp.data_ptr(), g.data_ptr(), arr, B, T, z.data_ptr(), eng._stream())
     torch.cuda.synchronize()
-    assert (torch.cuda.memory_allocated(), torch.cuda.memory_reserved()) == before      # the call allocated nothing through torch
+    assert counters() == before                                  # the call allocated nothing through torch
     return rc, z
 
 
