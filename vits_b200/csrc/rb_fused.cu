@@ -588,7 +588,13 @@ rb_fused_kernel(const __grid_constant__ CUtensorMap tmY, const __grid_constant__
 #ifndef VITSB_RB_PF64
 #define VITSB_RB_PF64 2                          // C = 64 keeps two register sets (ping-pong, below): 2 chunks each, -1..-4 % against 4
 #endif
-    constexpr int PF = NCH_S < 4 ? NCH_S : (C == 64 ? VITSB_RB_PF64 : 4);    // residual chunks kept in flight (2 x uint4 each; 96-register cap with 20 warps)
+#ifndef VITSB_RB_PF128
+#define VITSB_RB_PF128 2                         // C = 128: two chunks in flight (k = 11: -2.8 % against 4, others neutral)
+#endif
+#ifndef VITSB_RB_PF256
+#define VITSB_RB_PF256 4
+#endif
+    constexpr int PF = NCH_S < 4 ? NCH_S : (C == 64 ? VITSB_RB_PF64 : (C == 128 ? VITSB_RB_PF128 : (C == 256 ? VITSB_RB_PF256 : 4)));    // residual chunks kept in flight (2 x uint4 each; 96-register cap with 20 warps)
     Cursor sl{0, 0};
     int len_b = -1, valid = a.L;                 // valid rows of batch row len_b (one global load per batch row, not per tile)
     if (!G::COOP) for (int i = 0; i < grp; ++i) sl.next(nSlab);
